@@ -1,0 +1,388 @@
+// bvh.cu — parallel LBVH build for sm_100a.
+//
+// Replaces the `transform` kernel (reference src/path_tracer.cu:227-263) and BVH::construct
+// (src/bvh.cu:128-331).  Pipeline, all on the context stream with no host synchronisation:
+//   1. k_transform      per vertex: object->world position and (frsqrt-normalised) normal, and the
+//                       scene AABB by warp shuffle + one ordered-uint atomicMin/Max per warp.
+//   2. k_morton         per face: AABB centre -> 63-bit Morton key normalised to the SCENE bounds
+//                       (the reference uses a fixed 2^-12 grid over [-256,256) and saturates outside it).
+//   3. radix sort       (key64, face32) pairs — the reference sorts whole 36-byte nodes.
+//   4. k_hierarchy      Karras 2012 ranges/splits with (key, index) tie-break, so any number of equal
+//                       keys gives a valid tree (the reference breaks on runs of >= 3).
+//   5. k_leaves_refit   per sorted leaf: write the 48-B triangle and normal records, then walk to the
+//                       root with one atomic arrival counter per node; the second arrival owns the
+//                       node.  Grid-wide, replaces the reference's single 1024-thread block
+//                       (computeBBox, src/bvh.cu:220-302).
+#include <cub/device/device_radix_sort.cuh>
+
+#include "scene.cuh"
+
+namespace tpt {
+
+// ---- ordered-uint encoding of floats for atomicMin/Max ---------------------------------------
+__host__ __device__ __forceinline__ uint32_t f2ord(float f) {
+#ifdef __CUDA_ARCH__
+    uint32_t u = __float_as_uint(f);
+#else
+    uint32_t u;
+    memcpy(&u, &f, 4);
+#endif
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__host__ __device__ __forceinline__ float ord2f(uint32_t u) {
+    u = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
+#ifdef __CUDA_ARCH__
+    return __uint_as_float(u);
+#else
+    float f;
+    memcpy(&f, &u, 4);
+    return f;
+#endif
+}
+
+__global__ void k_init_bounds(uint32_t* bounds) {
+    if (threadIdx.x < 3) bounds[threadIdx.x] = 0xffffffffu;
+    else if (threadIdx.x < 6) bounds[threadIdx.x] = 0u;
+}
+
+// Built once per scene: which object each vertex belongs to, and the material of each face
+// (replaces findIdxOfTrans, src/path_tracer.cu:227-237, and mtlLinearSearch, :125-135, both O(#objects)
+// scans per use in the reference).
+__global__ void k_face_tables(const uint32_t* __restrict__ indices, const tpt_mtl_interval* __restrict__ objects, int nObjects,
+                              uint32_t nFaces, uint32_t* __restrict__ vertObj, uint32_t* __restrict__ faceMtl) {
+    const uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (f >= nFaces) return;
+    // last object whose begin <= f (objects are in ascending begin order)
+    int lo = 0, hi = nObjects - 1;
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if ((uint32_t)objects[mid].begin <= f) lo = mid;
+        else hi = mid - 1;
+    }
+    faceMtl[f] = (uint32_t)objects[lo].mtl_idx;
+    vertObj[indices[3 * f + 0]] = (uint32_t)lo;
+    vertObj[indices[3 * f + 1]] = (uint32_t)lo;
+    vertObj[indices[3 * f + 2]] = (uint32_t)lo;
+}
+
+__global__ void __launch_bounds__(256) k_transform(const float* __restrict__ objVerts, const float* __restrict__ objNorms,
+                                                   const uint32_t* __restrict__ vertObj, const float* __restrict__ vertTrans,
+                                                   const float* __restrict__ normalTrans, uint32_t nVerts,
+                                                   float* __restrict__ worldVerts, float* __restrict__ worldNorms,
+                                                   uint32_t* __restrict__ bounds) {
+    float3 mn = f3(FLT_MAX, FLT_MAX, FLT_MAX), mx = f3(-FLT_MAX, -FLT_MAX, -FLT_MAX);
+    for (uint32_t v = blockIdx.x * blockDim.x + threadIdx.x; v < nVerts; v += gridDim.x * blockDim.x) {
+        const uint32_t o = vertObj[v];
+        if (o == 0xffffffffu) continue;   // not referenced by any face: the reference never writes it either
+        const float3 p = f3(objVerts[3 * v], objVerts[3 * v + 1], objVerts[3 * v + 2]);
+        const float3 n = f3(objNorms[3 * v], objNorms[3 * v + 1], objNorms[3 * v + 2]);
+        const float3 wp = mat4_point(vertTrans + 16 * (size_t)o, p);
+        const float3 wn = ref_normalize(mat4_dir(normalTrans + 16 * (size_t)o, n));
+        worldVerts[3 * v] = wp.x; worldVerts[3 * v + 1] = wp.y; worldVerts[3 * v + 2] = wp.z;
+        worldNorms[3 * v] = wn.x; worldNorms[3 * v + 1] = wn.y; worldNorms[3 * v + 2] = wn.z;
+        mn = fmin3(mn, wp);
+        mx = fmax3(mx, wp);
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        mn.x = fminf(mn.x, __shfl_xor_sync(0xffffffffu, mn.x, off));
+        mn.y = fminf(mn.y, __shfl_xor_sync(0xffffffffu, mn.y, off));
+        mn.z = fminf(mn.z, __shfl_xor_sync(0xffffffffu, mn.z, off));
+        mx.x = fmaxf(mx.x, __shfl_xor_sync(0xffffffffu, mx.x, off));
+        mx.y = fmaxf(mx.y, __shfl_xor_sync(0xffffffffu, mx.y, off));
+        mx.z = fmaxf(mx.z, __shfl_xor_sync(0xffffffffu, mx.z, off));
+    }
+    if ((threadIdx.x & 31) == 0 && mn.x <= mx.x) {
+        atomicMin(bounds + 0, f2ord(mn.x)); atomicMin(bounds + 1, f2ord(mn.y)); atomicMin(bounds + 2, f2ord(mn.z));
+        atomicMax(bounds + 3, f2ord(mx.x)); atomicMax(bounds + 4, f2ord(mx.y)); atomicMax(bounds + 5, f2ord(mx.z));
+    }
+}
+
+__device__ __forceinline__ uint64_t expand21(uint64_t x) {   // spread 21 bits to every third bit
+    x &= 0x1fffffull;
+    x = (x | x << 32) & 0x1f00000000ffffull;
+    x = (x | x << 16) & 0x1f0000ff0000ffull;
+    x = (x | x << 8) & 0x100f00f00f00f00full;
+    x = (x | x << 4) & 0x10c30c30c30c30c3ull;
+    x = (x | x << 2) & 0x1249249249249249ull;
+    return x;
+}
+
+__global__ void __launch_bounds__(256) k_morton(const uint32_t* __restrict__ indices, const float* __restrict__ worldVerts,
+                                                const uint32_t* __restrict__ bounds, uint32_t nFaces,
+                                                unsigned long long* __restrict__ keys, uint32_t* __restrict__ vals) {
+    const float3 bmin = f3(ord2f(bounds[0]), ord2f(bounds[1]), ord2f(bounds[2]));
+    const float3 bmax = f3(ord2f(bounds[3]), ord2f(bounds[4]), ord2f(bounds[5]));
+    const float3 ext = bmax - bmin;
+    const float k = 2097152.0f;   // 2^21 cells per axis
+    const float3 scale = f3(ext.x > 0.f ? k / ext.x : 0.f, ext.y > 0.f ? k / ext.y : 0.f, ext.z > 0.f ? k / ext.z : 0.f);
+    for (uint32_t f = blockIdx.x * blockDim.x + threadIdx.x; f < nFaces; f += gridDim.x * blockDim.x) {
+        const uint32_t i0 = indices[3 * f], i1 = indices[3 * f + 1], i2 = indices[3 * f + 2];
+        const float3 a = f3(worldVerts[3 * i0], worldVerts[3 * i0 + 1], worldVerts[3 * i0 + 2]);
+        const float3 b = f3(worldVerts[3 * i1], worldVerts[3 * i1 + 1], worldVerts[3 * i1 + 2]);
+        const float3 c = f3(worldVerts[3 * i2], worldVerts[3 * i2 + 1], worldVerts[3 * i2 + 2]);
+        const float3 ctr = (fmin3(fmin3(a, b), c) + fmax3(fmax3(a, b), c)) * 0.5f;   // AABB centre, as bvh.cu:139-142
+        const float3 q = (ctr - bmin) * scale;
+        const uint64_t qx = (uint64_t)fminf(fmaxf(q.x, 0.f), 2097151.f);
+        const uint64_t qy = (uint64_t)fminf(fmaxf(q.y, 0.f), 2097151.f);
+        const uint64_t qz = (uint64_t)fminf(fmaxf(q.z, 0.f), 2097151.f);
+        keys[f] = expand21(qx) | (expand21(qy) << 1) | (expand21(qz) << 2);
+        vals[f] = f;
+    }
+}
+
+// Common-prefix length of the augmented keys (key, index): equal keys fall back to the index bits.
+__device__ __forceinline__ int delta(const unsigned long long* __restrict__ keys, int n, int i, int j) {
+    if (j < 0 || j >= n) return -1;
+    const unsigned long long a = keys[i], b = keys[j];
+    if (a != b) return __clzll((long long)(a ^ b));
+    return 64 + __clz(i ^ j);
+}
+
+__global__ void __launch_bounds__(256) k_hierarchy(const unsigned long long* __restrict__ keys, int nFaces, float4* __restrict__ nodes,
+                                                   int* __restrict__ parentInt, int* __restrict__ parentLeaf) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nFaces - 1) return;
+    const int d = delta(keys, nFaces, i, i + 1) > delta(keys, nFaces, i, i - 1) ? 1 : -1;
+    const int dMin = delta(keys, nFaces, i, i - d);
+    int lmax = 2;
+    while (delta(keys, nFaces, i, i + lmax * d) > dMin) lmax <<= 1;
+    int l = 0;
+    for (int t = lmax >> 1; t > 0; t >>= 1)
+        if (delta(keys, nFaces, i, i + (l + t) * d) > dMin) l += t;
+    const int j = i + l * d;
+    const int dNode = delta(keys, nFaces, i, j);
+    int s = 0;
+    for (int t = (l + 1) >> 1;; t = (t + 1) >> 1) {
+        if (delta(keys, nFaces, i, i + (s + t) * d) > dNode) s += t;
+        if (t == 1) break;
+    }
+    const int gamma = i + s * d + min(d, 0);
+    const int lo = min(i, j), hi = max(i, j);
+    const int left = (lo == gamma) ? ~gamma : gamma;
+    const int right = (hi == gamma + 1) ? ~(gamma + 1) : gamma + 1;
+    if (left < 0) parentLeaf[~left] = i; else parentInt[left] = i;
+    if (right < 0) parentLeaf[~right] = i; else parentInt[right] = i;
+    if (i == 0) parentInt[0] = -1;
+    reinterpret_cast<int4*>(nodes)[4 * (size_t)i + 3] = make_int4(left, right, 0, 0);
+}
+
+__device__ __forceinline__ void store_child_box(float4* node, bool isLeft, float3 mn, float3 mx) {
+    // n0/n1 hold x and y of the left/right child, n2 holds z of both (see scene.cuh).
+    float* n = reinterpret_cast<float*>(node);
+    float4* xy = node + (isLeft ? 0 : 1);
+    __stcg(xy, make_float4(mn.x, mx.x, mn.y, mx.y));
+    __stcg(reinterpret_cast<float2*>(n + 8 + (isLeft ? 0 : 2)), make_float2(mn.z, mx.z));
+}
+
+__global__ void __launch_bounds__(256) k_leaves_refit(const uint32_t* __restrict__ sortedFaces, const uint32_t* __restrict__ indices,
+                                                      const float* __restrict__ worldVerts, const float* __restrict__ worldNorms,
+                                                      const uint32_t* __restrict__ faceMtl, int nFaces, const int* __restrict__ parentInt,
+                                                      const int* __restrict__ parentLeaf, uint32_t* __restrict__ flags,
+                                                      float4* __restrict__ nodes, float4* __restrict__ triGeom,
+                                                      float4* __restrict__ triNorm) {
+    const int leaf = blockIdx.x * blockDim.x + threadIdx.x;
+    if (leaf >= nFaces) return;
+    const uint32_t f = sortedFaces[leaf];
+    const uint32_t i0 = indices[3 * f], i1 = indices[3 * f + 1], i2 = indices[3 * f + 2];
+    const float3 a = f3(worldVerts[3 * i0], worldVerts[3 * i0 + 1], worldVerts[3 * i0 + 2]);
+    const float3 b = f3(worldVerts[3 * i1], worldVerts[3 * i1 + 1], worldVerts[3 * i1 + 2]);
+    const float3 c = f3(worldVerts[3 * i2], worldVerts[3 * i2 + 1], worldVerts[3 * i2 + 2]);
+    const float3 e1 = b - a, e2 = c - a;   // exactly the edges Möller–Trumbore forms per test in the reference
+    triGeom[3 * (size_t)leaf + 0] = make_float4(a.x, a.y, a.z, e1.x);
+    triGeom[3 * (size_t)leaf + 1] = make_float4(e1.y, e1.z, e2.x, e2.y);
+    triGeom[3 * (size_t)leaf + 2] = make_float4(e2.z, __int_as_float((int)f), __int_as_float((int)faceMtl[f]), 0.f);
+    const float3 n0 = f3(worldNorms[3 * i0], worldNorms[3 * i0 + 1], worldNorms[3 * i0 + 2]);
+    const float3 n1 = f3(worldNorms[3 * i1], worldNorms[3 * i1 + 1], worldNorms[3 * i1 + 2]);
+    const float3 n2 = f3(worldNorms[3 * i2], worldNorms[3 * i2 + 1], worldNorms[3 * i2 + 2]);
+    triNorm[3 * (size_t)leaf + 0] = make_float4(n0.x, n0.y, n0.z, n1.x);
+    triNorm[3 * (size_t)leaf + 1] = make_float4(n1.y, n1.z, n2.x, n2.y);
+    triNorm[3 * (size_t)leaf + 2] = make_float4(n2.z, 0.f, 0.f, 0.f);
+    if (nFaces == 1) return;
+
+    float3 mn = fmin3(fmin3(a, b), c), mx = fmax3(fmax3(a, b), c);
+    int child = ~leaf;
+    int cur = parentLeaf[leaf];
+    while (cur >= 0) {
+        float4* node = nodes + 4 * (size_t)cur;
+        const int4 ch = reinterpret_cast<const int4*>(node)[3];
+        const bool isLeft = (ch.x == child);
+        store_child_box(node, isLeft, mn, mx);
+        __threadfence();
+        if (atomicAdd(flags + cur, 1u) == 0u) return;   // first arrival: the sibling will finish this node
+        __threadfence();
+        // second arrival: read the sibling's box (written by another SM: bypass L1) and go up
+        const float4 sxy = __ldcg(node + (isLeft ? 1 : 0));
+        const float2 sz = __ldcg(reinterpret_cast<const float2*>(reinterpret_cast<const float*>(node) + 8 + (isLeft ? 2 : 0)));
+        mn = fmin3(mn, f3(sxy.x, sxy.z, sz.x));
+        mx = fmax3(mx, f3(sxy.y, sxy.w, sz.y));
+        child = cur;
+        cur = parentInt[cur];
+    }
+}
+
+// ---- export in the reference's 36-byte layout (include/bvh.cuh:34-58) --------------------------
+struct RefNode36 {
+    uint32_t parent;
+    int32_t a, b;
+    float mn[3], mx[3];
+};
+static_assert(sizeof(RefNode36) == 36, "reference BVHNode is 36 bytes");
+
+__global__ void k_export_reference(const float4* __restrict__ nodes, const float4* __restrict__ triGeom, const int* __restrict__ parentInt,
+                                   const int* __restrict__ parentLeaf, int nFaces, RefNode36* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int nInt = nFaces - 1;
+    if (i < nInt) {
+        const float4 n0 = nodes[4 * (size_t)i], n1 = nodes[4 * (size_t)i + 1], n2 = nodes[4 * (size_t)i + 2];
+        const int4 ch = reinterpret_cast<const int4*>(nodes)[4 * (size_t)i + 3];
+        RefNode36 r;
+        r.parent = i == 0 ? 0u : (uint32_t)parentInt[i];
+        r.a = ch.x >= 0 ? ch.x : (~ch.x) + nInt;
+        r.b = ch.y >= 0 ? ch.y : (~ch.y) + nInt;
+        r.mn[0] = fminf(n0.x, n1.x); r.mx[0] = fmaxf(n0.y, n1.y);
+        r.mn[1] = fminf(n0.z, n1.z); r.mx[1] = fmaxf(n0.w, n1.w);
+        r.mn[2] = fminf(n2.x, n2.z); r.mx[2] = fmaxf(n2.y, n2.w);
+        out[i] = r;
+    }
+    if (i < nFaces) {
+        RefNode36 r;
+        const float4 c = triGeom[3 * (size_t)i + 2];
+        r.a = __float_as_int(c.y);
+        r.b = 0;
+        if (nFaces > 1) {
+            const int p = parentLeaf[i];
+            r.parent = (uint32_t)p;
+            const float4 n0 = nodes[4 * (size_t)p], n1 = nodes[4 * (size_t)p + 1], n2 = nodes[4 * (size_t)p + 2];
+            const int4 ch = reinterpret_cast<const int4*>(nodes)[4 * (size_t)p + 3];
+            const bool isLeft = ch.x == ~i;
+            const float4 xy = isLeft ? n0 : n1;
+            r.mn[0] = xy.x; r.mx[0] = xy.y; r.mn[1] = xy.z; r.mx[1] = xy.w;
+            r.mn[2] = isLeft ? n2.x : n2.z; r.mx[2] = isLeft ? n2.y : n2.w;
+        } else {
+            const float4 a = triGeom[0], b = triGeom[1];
+            const float3 v0 = f3(a.x, a.y, a.z), v1 = v0 + f3(a.w, b.x, b.y), v2 = v0 + f3(b.z, b.w, c.x);
+            const float3 mn = fmin3(fmin3(v0, v1), v2), mx = fmax3(fmax3(v0, v1), v2);
+            r.parent = 0;
+            r.mn[0] = mn.x; r.mn[1] = mn.y; r.mn[2] = mn.z; r.mx[0] = mx.x; r.mx[1] = mx.y; r.mx[2] = mx.z;
+        }
+        out[nInt + i] = r;
+    }
+}
+
+// ---- stats (only when the caller asks for them) --------------------------------------------------
+__global__ void k_bvh_stats(const float4* __restrict__ nodes, const int* __restrict__ parentLeaf, const int* __restrict__ parentInt,
+                            int nFaces, float* __restrict__ areaSum, uint32_t* __restrict__ maxDepth) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < nFaces - 1) {
+        const float4 n0 = nodes[4 * (size_t)i], n1 = nodes[4 * (size_t)i + 1], n2 = nodes[4 * (size_t)i + 2];
+        const float ex = fmaxf(n0.y, n1.y) - fminf(n0.x, n1.x), ey = fmaxf(n0.w, n1.w) - fminf(n0.z, n1.z),
+                    ez = fmaxf(n2.y, n2.w) - fminf(n2.x, n2.z);
+        atomicAdd(areaSum + (i == 0 ? 0 : 1), 2.0f * (ex * ey + ey * ez + ez * ex));
+        // children areas that are leaves
+        const float lx = n0.y - n0.x, ly = n0.w - n0.z, lz = n2.y - n2.x, rx = n1.y - n1.x, ry = n1.w - n1.z, rz = n2.w - n2.z;
+        const int4 ch = reinterpret_cast<const int4*>(nodes)[4 * (size_t)i + 3];
+        float leafArea = 0.f;
+        if (ch.x < 0) leafArea += 2.0f * (lx * ly + ly * lz + lz * lx);
+        if (ch.y < 0) leafArea += 2.0f * (rx * ry + ry * rz + rz * rx);
+        if (leafArea > 0.f) atomicAdd(areaSum + 2, leafArea);
+    }
+    if (i < nFaces && nFaces > 1) {
+        uint32_t depth = 1;
+        int cur = parentLeaf[i];
+        while (cur > 0) {
+            cur = parentInt[cur];
+            ++depth;
+        }
+        atomicMax(maxDepth, depth);
+    }
+}
+
+}   // namespace tpt
+
+using namespace tpt;
+
+static inline unsigned grid_for(size_t n, int block) { return (unsigned)((n + block - 1) / block); }
+
+int tpt_scene_build_tables(tpt_scene* s) {
+    cudaStream_t st = s->ctx->stream;
+    TPT_CUDA(cudaMemsetAsync(s->vert_obj, 0xff, s->n_vertices * sizeof(uint32_t), st));
+    k_face_tables<<<grid_for(s->n_faces, 256), 256, 0, st>>>(s->indices, s->objects, (int)s->n_objects, (uint32_t)s->n_faces, s->vert_obj,
+                                                             s->face_mtl);
+    TPT_CUDA(cudaGetLastError());
+    s->ctx->kernel_launches += 1;
+    return TPT_OK;
+}
+
+int tpt_bvh_build_impl(tpt_scene* s) {
+    tpt_context* ctx = s->ctx;
+    cudaStream_t st = ctx->stream;
+    const int F = (int)s->n_faces;
+    const uint32_t V = (uint32_t)s->n_vertices;
+    const int persistent = kNumSMs * 8;
+
+    k_init_bounds<<<1, 32, 0, st>>>(s->bounds);
+    k_transform<<<min(persistent, (int)grid_for(V, 256)), 256, 0, st>>>(s->obj_verts, s->obj_norms, s->vert_obj, s->vert_trans,
+                                                                         s->normal_trans, V, s->world_verts, s->world_norms, s->bounds);
+    k_morton<<<min(persistent, (int)grid_for(F, 256)), 256, 0, st>>>(s->indices, s->world_verts, s->bounds, (uint32_t)F, s->keys[0],
+                                                                      s->vals[0]);
+    TPT_CUDA(cudaGetLastError());
+    size_t need = 0;
+    TPT_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, need, s->keys[0], s->keys[1], s->vals[0], s->vals[1], F, 0, 63, st));
+    if (need > s->sort_tmp_bytes) {
+        TPT_CUDA(cudaStreamSynchronize(st));
+        if (s->sort_tmp) cudaFree(s->sort_tmp);
+        TPT_CUDA(cudaMalloc(&s->sort_tmp, need));
+        s->sort_tmp_bytes = need;
+    }
+    TPT_CUDA(cub::DeviceRadixSort::SortPairs(s->sort_tmp, s->sort_tmp_bytes, s->keys[0], s->keys[1], s->vals[0], s->vals[1], F, 0, 63, st));
+    if (F > 1) {
+        TPT_CUDA(cudaMemsetAsync(s->flags, 0, (size_t)(F - 1) * sizeof(uint32_t), st));
+        k_hierarchy<<<grid_for(F - 1, 256), 256, 0, st>>>(s->keys[1], F, s->nodes, s->parent_int, s->parent_leaf);
+    }
+    k_leaves_refit<<<grid_for(F, 256), 256, 0, st>>>(s->vals[1], s->indices, s->world_verts, s->world_norms, s->face_mtl, F, s->parent_int,
+                                                     s->parent_leaf, s->flags, s->nodes, s->tri_geom, s->tri_norm);
+    TPT_CUDA(cudaGetLastError());
+    ctx->kernel_launches += 5 + 8;   // + radix sort passes (library, counted nominally)
+    s->built = true;
+    return TPT_OK;
+}
+
+int tpt_bvh_stats_impl(tpt_scene* s, tpt_bvh_stats* stats) {
+    cudaStream_t st = s->ctx->stream;
+    const int F = (int)s->n_faces;
+    float* d_area = nullptr;
+    TPT_CUDA(cudaMalloc(&d_area, 4 * sizeof(float)));
+    TPT_CUDA(cudaMemsetAsync(d_area, 0, 4 * sizeof(float), st));
+    uint32_t* d_depth = reinterpret_cast<uint32_t*>(d_area + 3);
+    if (F > 1) k_bvh_stats<<<grid_for(F, 256), 256, 0, st>>>(s->nodes, s->parent_leaf, s->parent_int, F, d_area, d_depth);
+    float h[4];
+    uint32_t hb[6];
+    TPT_CUDA(cudaMemcpyAsync(h, d_area, sizeof h, cudaMemcpyDeviceToHost, st));
+    TPT_CUDA(cudaMemcpyAsync(hb, s->bounds, sizeof hb, cudaMemcpyDeviceToHost, st));
+    TPT_CUDA(cudaStreamSynchronize(st));
+    cudaFree(d_area);
+    stats->n_faces = (uint32_t)F;
+    stats->n_nodes = (uint32_t)(F > 0 ? F - 1 : 0);
+    memcpy(&stats->max_depth, &h[3], 4);
+    // SAH with Ct = 1.2, Ci = 1: (sum internal areas * Ct + sum leaf areas * Ci) / root area
+    stats->sah_cost = h[0] > 0.f ? (1.2f * (h[0] + h[1]) + h[2]) / h[0] : 0.f;
+    for (int k = 0; k < 3; ++k) {
+        stats->bounds_min[k] = ord2f(hb[k]);
+        stats->bounds_max[k] = ord2f(hb[3 + k]);
+    }
+    return TPT_OK;
+}
+
+int tpt_bvh_export_reference_impl(tpt_scene* s, void* out, size_t nNodes) {
+    cudaStream_t st = s->ctx->stream;
+    const int F = (int)s->n_faces;
+    RefNode36* d = nullptr;
+    TPT_CUDA(cudaMalloc(&d, nNodes * sizeof(RefNode36)));
+    k_export_reference<<<grid_for(F, 256), 256, 0, st>>>(s->nodes, s->tri_geom, s->parent_int, s->parent_leaf, F, d);
+    cudaError_t e = cudaMemcpyAsync(out, d, nNodes * sizeof(RefNode36), cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    cudaFree(d);
+    TPT_CUDA(e);
+    return TPT_OK;
+}

@@ -1,0 +1,500 @@
+// capi.cu — the extern "C" boundary declared in include/tpt.h.
+//
+// Host-side orchestration only: argument checks, device memory ownership, host<->device staging and
+// kernel sequencing.  There is no CPU implementation of any entry point: when no CUDA device is
+// usable, tpt_context_create fails and nothing else can be called.
+#include <cstring>
+#include <new>
+#include <vector>
+
+#include "scene.cuh"
+
+namespace tpt {
+
+static thread_local std::string g_last_error;
+
+void set_error(const std::string& msg) { g_last_error = msg; }
+
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
+    g_last_error = std::string("CUDA error ") + cudaGetErrorName(e) + " (" + cudaGetErrorString(e) + ") at " + file + ":" +
+                   std::to_string(line) + " in " + what;
+    return TPT_ERR_CUDA;
+}
+
+}   // namespace tpt
+
+using namespace tpt;
+
+// implemented in bvh.cu / render.cu
+int tpt_scene_build_tables(tpt_scene* s);
+int tpt_bvh_build_impl(tpt_scene* s);
+int tpt_bvh_stats_impl(tpt_scene* s, tpt_bvh_stats* stats);
+int tpt_bvh_export_reference_impl(tpt_scene* s, void* out, size_t nNodes);
+int tpt_primary_rays_impl(tpt_context* ctx, const tpt_camera* cam, int W, int H, int jitter, uint64_t seed, tpt_ray* d_rays);
+int tpt_trace_rays_impl(tpt_scene* s, const tpt_ray* d_rays, size_t n, tpt_hit* d_hits, int anyHit, int counted);
+int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config* cfg, tpt_accum* acc);
+int tpt_accum_add_impl(tpt_accum* dst, const tpt_accum* src);
+int tpt_accum_to_f32_impl(tpt_accum* acc, float* d_out);
+int tpt_resolve_impl(tpt_accum* acc, int sppTotal, uint8_t* d_fb);
+
+namespace {
+
+template <typename T>
+int dev_alloc(T** p, size_t count) {
+    *p = nullptr;
+    if (count == 0) count = 1;
+    TPT_CUDA(cudaMalloc(reinterpret_cast<void**>(p), count * sizeof(T)));
+    return TPT_OK;
+}
+template <typename T>
+int upload(tpt_context* ctx, T* dst, const T* src, size_t count) {
+    if (count == 0) return TPT_OK;
+    TPT_CUDA(cudaMemcpyAsync(dst, src, count * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
+    return TPT_OK;
+}
+int bind(tpt_context* ctx) {
+    TPT_CUDA(cudaSetDevice(ctx->device));
+    return TPT_OK;
+}
+int ensure_io(tpt_context* ctx, size_t n) {
+    if (n <= ctx->io_capacity) return TPT_OK;
+    TPT_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (ctx->io_rays) cudaFree(ctx->io_rays);
+    if (ctx->io_hits) cudaFree(ctx->io_hits);
+    ctx->io_rays = ctx->io_hits = nullptr;
+    ctx->io_capacity = 0;
+    TPT_CUDA(cudaMalloc(&ctx->io_rays, n * sizeof(tpt_ray)));
+    TPT_CUDA(cudaMalloc(&ctx->io_hits, n * sizeof(tpt_hit)));
+    ctx->io_capacity = n;
+    return TPT_OK;
+}
+
+}   // namespace
+
+extern "C" {
+
+const char* tpt_last_error(void) { return g_last_error.c_str(); }
+int tpt_abi_version(void) { return TPT_ABI_VERSION; }
+
+int tpt_context_create(int device, tpt_context** out) {
+    TPT_REQUIRE(out != nullptr, "tpt_context_create: out is NULL");
+    *out = nullptr;
+    int count = 0;
+    TPT_CUDA(cudaGetDeviceCount(&count));
+    if (device < 0 || device >= count) {
+        set_error("tpt_context_create: no such CUDA device " + std::to_string(device) + " (" + std::to_string(count) + " visible); there is no CPU fallback");
+        return TPT_ERR_CUDA;
+    }
+    TPT_CUDA(cudaSetDevice(device));
+    tpt_context* ctx = new (std::nothrow) tpt_context();
+    if (!ctx) return TPT_ERR_NOMEM;
+    ctx->device = device;
+    cudaError_t e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaMalloc(&ctx->d_counters, sizeof(DeviceCounters));
+    if (e == cudaSuccess) e = cudaMemset(ctx->d_counters, 0, sizeof(DeviceCounters));
+    if (e == cudaSuccess) e = cudaMalloc(&ctx->queue_counts, 4 * sizeof(uint32_t));
+    if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev0);
+    if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev1);
+    if (e != cudaSuccess) {
+        delete ctx;
+        return cuda_fail(e, "context setup", __FILE__, __LINE__);
+    }
+    ctx->own_stream = true;
+    *out = ctx;
+    return TPT_OK;
+}
+
+int tpt_context_destroy(tpt_context* ctx) {
+    if (!ctx) return TPT_OK;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    cudaFree(ctx->env);
+    cudaFree(ctx->d_counters);
+    cudaFree(ctx->path_state[0]);
+    cudaFree(ctx->path_state[1]);
+    cudaFree(ctx->hits);
+    cudaFree(ctx->sec_rays);
+    cudaFree(ctx->queue_counts);
+    cudaFree(ctx->io_rays);
+    cudaFree(ctx->io_hits);
+    if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+    if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return TPT_OK;
+}
+
+int tpt_context_synchronize(tpt_context* ctx) {
+    TPT_REQUIRE(ctx, "tpt_context_synchronize: ctx is NULL");
+    TPT_CHECK(bind(ctx));
+    TPT_CUDA(cudaStreamSynchronize(ctx->stream));
+    return TPT_OK;
+}
+
+int tpt_context_set_stream(tpt_context* ctx, void* cuda_stream) {
+    TPT_REQUIRE(ctx, "tpt_context_set_stream: ctx is NULL");
+    TPT_CHECK(bind(ctx));
+    TPT_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
+    ctx->stream = reinterpret_cast<cudaStream_t>(cuda_stream);
+    ctx->own_stream = false;
+    return TPT_OK;
+}
+
+int tpt_get_counters(tpt_context* ctx, tpt_counters* out) {
+    TPT_REQUIRE(ctx && out, "tpt_get_counters: NULL argument");
+    TPT_CHECK(bind(ctx));
+    DeviceCounters h;
+    TPT_CUDA(cudaMemcpyAsync(&h, ctx->d_counters, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
+    TPT_CUDA(cudaStreamSynchronize(ctx->stream));
+    out->rays_primary = h.rays_primary;
+    out->rays_extension = h.rays_extension;
+    out->rays_direct = h.rays_direct;
+    out->rays_shadow = h.rays_shadow - h.rays_direct;   // the connect kernel counts the whole secondary queue
+    out->node_visits = h.node_visits;
+    out->tri_tests = h.tri_tests;
+    out->samples = ctx->samples;
+    out->dropped_nonfinite = h.dropped_nonfinite;
+    out->kernel_launches = ctx->kernel_launches;
+    return TPT_OK;
+}
+
+int tpt_reset_counters(tpt_context* ctx) {
+    TPT_REQUIRE(ctx, "tpt_reset_counters: ctx is NULL");
+    TPT_CHECK(bind(ctx));
+    TPT_CUDA(cudaMemsetAsync(ctx->d_counters, 0, sizeof(DeviceCounters), ctx->stream));
+    ctx->samples = 0;
+    ctx->kernel_launches = 0;
+    return TPT_OK;
+}
+
+int tpt_scene_destroy(tpt_scene* s) {
+    if (!s) return TPT_OK;
+    cudaSetDevice(s->ctx->device);
+    cudaStreamSynchronize(s->ctx->stream);
+    cudaFree(s->indices); cudaFree(s->obj_verts); cudaFree(s->obj_norms); cudaFree(s->vert_obj); cudaFree(s->face_mtl);
+    cudaFree(s->objects); cudaFree(s->vert_trans); cudaFree(s->normal_trans); cudaFree(s->mtl_table); cudaFree(s->lights);
+    cudaFree(s->world_verts); cudaFree(s->world_norms); cudaFree(s->keys[0]); cudaFree(s->keys[1]); cudaFree(s->vals[0]);
+    cudaFree(s->vals[1]); cudaFree(s->sort_tmp); cudaFree(s->parent_int); cudaFree(s->parent_leaf); cudaFree(s->flags);
+    cudaFree(s->bounds); cudaFree(s->nodes); cudaFree(s->tri_geom); cudaFree(s->tri_norm);
+    delete s;
+    return TPT_OK;
+}
+
+int tpt_scene_create(tpt_context* ctx, const tpt_scene_desc* d, tpt_scene** out) {
+    TPT_REQUIRE(ctx && d && out, "tpt_scene_create: NULL argument");
+    *out = nullptr;
+    TPT_REQUIRE(d->n_indices >= 3 && d->n_indices % 3 == 0, "tpt_scene_create: n_indices must be a positive multiple of 3");
+    TPT_REQUIRE(d->n_indices / 3 < (size_t)1 << 30, "tpt_scene_create: too many faces");
+    TPT_REQUIRE(d->n_vertices > 0 && d->indices && d->vertices && d->normals, "tpt_scene_create: geometry arrays missing");
+    TPT_REQUIRE(d->n_objects > 0 && d->objects && d->vert_trans && d->normal_trans, "tpt_scene_create: object table missing");
+    TPT_REQUIRE(d->n_materials > 0 && d->materials, "tpt_scene_create: at least one material is required");
+    TPT_REQUIRE(d->n_lights == 0 || d->lights, "tpt_scene_create: lights pointer is NULL");
+    const size_t F = d->n_indices / 3;
+    for (size_t i = 0; i < d->n_indices; ++i)
+        TPT_REQUIRE(d->indices[i] < d->n_vertices, "tpt_scene_create: vertex index out of range");
+    TPT_REQUIRE(d->objects[0].begin == 0, "tpt_scene_create: first object must begin at face 0");
+    for (size_t o = 0; o < d->n_objects; ++o) {
+        TPT_REQUIRE(d->objects[o].mtl_idx >= 0 && (size_t)d->objects[o].mtl_idx < d->n_materials, "tpt_scene_create: material index out of range");
+        TPT_REQUIRE(o == 0 || d->objects[o].begin >= d->objects[o - 1].begin, "tpt_scene_create: object face ranges must ascend");
+        TPT_REQUIRE((size_t)d->objects[o].begin <= F, "tpt_scene_create: object begin beyond face count");
+    }
+    TPT_CHECK(bind(ctx));
+    tpt_scene* s = new (std::nothrow) tpt_scene();
+    if (!s) return TPT_ERR_NOMEM;
+    s->ctx = ctx;
+    s->n_faces = F;
+    s->n_vertices = d->n_vertices;
+    s->n_objects = d->n_objects;
+    s->n_materials = d->n_materials;
+    s->n_lights = d->n_lights;
+    const size_t V = d->n_vertices, O = d->n_objects;
+    std::vector<float4> mtl(2 * d->n_materials);
+    for (size_t m = 0; m < d->n_materials; ++m) {
+        const tpt_material& M = d->materials[m];
+        mtl[2 * m] = make_float4(M.base_color[0], M.base_color[1], M.base_color[2], M.emission);
+        mtl[2 * m + 1] = make_float4(M.eta, M.metallic, 0.f, 0.f);
+    }
+    int rc = TPT_OK;
+    auto A = [&](int r) { if (rc == TPT_OK) rc = r; };
+    A(dev_alloc(&s->indices, 3 * F)); A(dev_alloc(&s->obj_verts, 3 * V)); A(dev_alloc(&s->obj_norms, 3 * V));
+    A(dev_alloc(&s->vert_obj, V)); A(dev_alloc(&s->face_mtl, F)); A(dev_alloc(&s->objects, O));
+    A(dev_alloc(&s->vert_trans, 16 * O)); A(dev_alloc(&s->normal_trans, 16 * O)); A(dev_alloc(&s->mtl_table, 2 * d->n_materials));
+    A(dev_alloc(&s->lights, d->n_lights)); A(dev_alloc(&s->world_verts, 3 * V)); A(dev_alloc(&s->world_norms, 3 * V));
+    A(dev_alloc(&s->keys[0], F)); A(dev_alloc(&s->keys[1], F)); A(dev_alloc(&s->vals[0], F)); A(dev_alloc(&s->vals[1], F));
+    A(dev_alloc(&s->parent_int, F)); A(dev_alloc(&s->parent_leaf, F)); A(dev_alloc(&s->flags, F)); A(dev_alloc(&s->bounds, 8));
+    A(dev_alloc(&s->nodes, 4 * F)); A(dev_alloc(&s->tri_geom, 3 * F)); A(dev_alloc(&s->tri_norm, 3 * F));
+    A(upload(ctx, s->indices, d->indices, 3 * F));
+    A(upload(ctx, s->obj_verts, d->vertices, 3 * V));
+    A(upload(ctx, s->obj_norms, d->normals, 3 * V));
+    A(upload(ctx, s->objects, d->objects, O));
+    A(upload(ctx, s->vert_trans, d->vert_trans, 16 * O));
+    A(upload(ctx, s->normal_trans, d->normal_trans, 16 * O));
+    A(upload(ctx, s->mtl_table, mtl.data(), mtl.size()));
+    A(upload(ctx, s->lights, d->lights, d->n_lights));
+    if (rc == TPT_OK) rc = tpt_scene_build_tables(s);
+    if (rc == TPT_OK) {
+        cudaError_t e = cudaStreamSynchronize(ctx->stream);   // host staging (mtl vector, caller arrays) may go away
+        if (e != cudaSuccess) rc = cuda_fail(e, "scene upload", __FILE__, __LINE__);
+    }
+    if (rc != TPT_OK) {
+        std::string keep = g_last_error;
+        tpt_scene_destroy(s);
+        g_last_error = keep;
+        return rc;
+    }
+    *out = s;
+    return TPT_OK;
+}
+
+int tpt_scene_set_transforms(tpt_scene* s, const float* vert_trans, const float* normal_trans) {
+    TPT_REQUIRE(s && vert_trans && normal_trans, "tpt_scene_set_transforms: NULL argument");
+    TPT_CHECK(bind(s->ctx));
+    TPT_CHECK(upload(s->ctx, s->vert_trans, vert_trans, 16 * s->n_objects));
+    TPT_CHECK(upload(s->ctx, s->normal_trans, normal_trans, 16 * s->n_objects));
+    TPT_CUDA(cudaStreamSynchronize(s->ctx->stream));
+    s->built = false;
+    return TPT_OK;
+}
+
+int tpt_bvh_build(tpt_scene* s, tpt_bvh_stats* stats) {
+    TPT_REQUIRE(s, "tpt_bvh_build: scene is NULL");
+    tpt_context* ctx = s->ctx;
+    TPT_CHECK(bind(ctx));
+    if (stats) TPT_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
+    TPT_CHECK(tpt_bvh_build_impl(s));
+    if (stats) {
+        TPT_CUDA(cudaEventRecord(ctx->ev1, ctx->stream));
+        TPT_CUDA(cudaEventSynchronize(ctx->ev1));
+        memset(stats, 0, sizeof *stats);
+        TPT_CHECK(tpt_bvh_stats_impl(s, stats));
+        TPT_CUDA(cudaEventElapsedTime(&stats->build_ms, ctx->ev0, ctx->ev1));
+    }
+    return TPT_OK;
+}
+
+int tpt_bvh_export_reference_nodes(tpt_scene* s, void* out_nodes36, size_t n_nodes) {
+    TPT_REQUIRE(s && out_nodes36, "tpt_bvh_export_reference_nodes: NULL argument");
+    if (!s->built) {
+        set_error("tpt_bvh_export_reference_nodes: call tpt_bvh_build first");
+        return TPT_ERR_STATE;
+    }
+    TPT_REQUIRE(n_nodes == 2 * s->n_faces - 1, "tpt_bvh_export_reference_nodes: n_nodes must be 2F-1");
+    TPT_CHECK(bind(s->ctx));
+    return tpt_bvh_export_reference_impl(s, out_nodes36, n_nodes);
+}
+
+int tpt_scene_export_world(tpt_scene* s, float* wv, float* wn) {
+    TPT_REQUIRE(s, "tpt_scene_export_world: scene is NULL");
+    if (!s->built) {
+        set_error("tpt_scene_export_world: call tpt_bvh_build first");
+        return TPT_ERR_STATE;
+    }
+    TPT_CHECK(bind(s->ctx));
+    if (wv) TPT_CUDA(cudaMemcpyAsync(wv, s->world_verts, 3 * s->n_vertices * sizeof(float), cudaMemcpyDeviceToHost, s->ctx->stream));
+    if (wn) TPT_CUDA(cudaMemcpyAsync(wn, s->world_norms, 3 * s->n_vertices * sizeof(float), cudaMemcpyDeviceToHost, s->ctx->stream));
+    TPT_CUDA(cudaStreamSynchronize(s->ctx->stream));
+    return TPT_OK;
+}
+
+int tpt_env_set_rgba8(tpt_context* ctx, const uint8_t* rgba8, int w, int h) {
+    TPT_REQUIRE(ctx && rgba8, "tpt_env_set_rgba8: NULL argument");
+    TPT_REQUIRE(w > 0 && h > 0, "tpt_env_set_rgba8: bad size");
+    TPT_CHECK(bind(ctx));
+    TPT_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (ctx->env) cudaFree(ctx->env);
+    ctx->env = nullptr;
+    TPT_CUDA(cudaMalloc(&ctx->env, (size_t)w * h * 4));
+    TPT_CUDA(cudaMemcpyAsync(ctx->env, rgba8, (size_t)w * h * 4, cudaMemcpyHostToDevice, ctx->stream));
+    TPT_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->env_w = w;
+    ctx->env_h = h;
+    return TPT_OK;
+}
+
+int tpt_env_clear(tpt_context* ctx) {
+    TPT_REQUIRE(ctx, "tpt_env_clear: ctx is NULL");
+    TPT_CHECK(bind(ctx));
+    TPT_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (ctx->env) cudaFree(ctx->env);
+    ctx->env = nullptr;
+    ctx->env_w = ctx->env_h = 0;
+    return TPT_OK;
+}
+
+static int trace_common(tpt_scene* s, const tpt_ray* rays, size_t n, tpt_hit* hits, int any_hit, int device_ptrs, int counted) {
+    TPT_REQUIRE(s && (n == 0 || (rays && hits)), "tpt_trace_rays: NULL argument");
+    if (!s->built) {
+        set_error("tpt_trace_rays: call tpt_bvh_build first");
+        return TPT_ERR_STATE;
+    }
+    if (n == 0) return TPT_OK;
+    tpt_context* ctx = s->ctx;
+    TPT_CHECK(bind(ctx));
+    if (device_ptrs) return tpt_trace_rays_impl(s, rays, n, hits, any_hit, counted);
+    TPT_CHECK(ensure_io(ctx, n));
+    TPT_CUDA(cudaMemcpyAsync(ctx->io_rays, rays, n * sizeof(tpt_ray), cudaMemcpyHostToDevice, ctx->stream));
+    TPT_CHECK(tpt_trace_rays_impl(s, static_cast<const tpt_ray*>(ctx->io_rays), n, static_cast<tpt_hit*>(ctx->io_hits), any_hit, counted));
+    TPT_CUDA(cudaMemcpyAsync(hits, ctx->io_hits, n * sizeof(tpt_hit), cudaMemcpyDeviceToHost, ctx->stream));
+    TPT_CUDA(cudaStreamSynchronize(ctx->stream));
+    return TPT_OK;
+}
+
+int tpt_trace_rays(tpt_scene* s, const tpt_ray* rays, size_t n, tpt_hit* hits, int any_hit, int device_ptrs) {
+    return trace_common(s, rays, n, hits, any_hit, device_ptrs, 0);
+}
+int tpt_trace_rays_counted(tpt_scene* s, const tpt_ray* rays, size_t n, tpt_hit* hits, int any_hit, int device_ptrs) {
+    return trace_common(s, rays, n, hits, any_hit, device_ptrs, 1);
+}
+
+int tpt_generate_primary_rays(tpt_context* ctx, const tpt_camera* cam, int w, int h, int jitter, uint64_t seed, tpt_ray* rays, int device_ptrs) {
+    TPT_REQUIRE(ctx && cam && rays, "tpt_generate_primary_rays: NULL argument");
+    TPT_REQUIRE(w > 0 && h > 0, "tpt_generate_primary_rays: bad size");
+    TPT_CHECK(bind(ctx));
+    const size_t n = (size_t)w * h;
+    if (device_ptrs) return tpt_primary_rays_impl(ctx, cam, w, h, jitter, seed, rays);
+    TPT_CHECK(ensure_io(ctx, n));
+    TPT_CHECK(tpt_primary_rays_impl(ctx, cam, w, h, jitter, seed, static_cast<tpt_ray*>(ctx->io_rays)));
+    TPT_CUDA(cudaMemcpyAsync(rays, ctx->io_rays, n * sizeof(tpt_ray), cudaMemcpyDeviceToHost, ctx->stream));
+    TPT_CUDA(cudaStreamSynchronize(ctx->stream));
+    return TPT_OK;
+}
+
+int tpt_accum_create(tpt_context* ctx, int w, int h, tpt_accum** out) {
+    TPT_REQUIRE(ctx && out, "tpt_accum_create: NULL argument");
+    TPT_REQUIRE(w > 0 && h > 0, "tpt_accum_create: bad size");
+    TPT_CHECK(bind(ctx));
+    tpt_accum* a = new (std::nothrow) tpt_accum();
+    if (!a) return TPT_ERR_NOMEM;
+    a->ctx = ctx;
+    a->width = w;
+    a->height = h;
+    a->owned = true;
+    const size_t bytes = (size_t)w * h * 3 * sizeof(unsigned long long);
+    cudaError_t e = cudaMalloc(&a->data, bytes);
+    if (e == cudaSuccess) e = cudaMemsetAsync(a->data, 0, bytes, ctx->stream);
+    if (e != cudaSuccess) {
+        delete a;
+        return cuda_fail(e, "accum alloc", __FILE__, __LINE__);
+    }
+    *out = a;
+    return TPT_OK;
+}
+
+int tpt_accum_wrap(tpt_context* ctx, void* device_i64, int w, int h, tpt_accum** out) {
+    TPT_REQUIRE(ctx && out && device_i64, "tpt_accum_wrap: NULL argument");
+    TPT_REQUIRE(w > 0 && h > 0, "tpt_accum_wrap: bad size");
+    tpt_accum* a = new (std::nothrow) tpt_accum();
+    if (!a) return TPT_ERR_NOMEM;
+    a->ctx = ctx;
+    a->width = w;
+    a->height = h;
+    a->owned = false;
+    a->data = static_cast<unsigned long long*>(device_i64);
+    *out = a;
+    return TPT_OK;
+}
+
+int tpt_accum_destroy(tpt_accum* a) {
+    if (!a) return TPT_OK;
+    if (a->owned) {
+        cudaSetDevice(a->ctx->device);
+        cudaStreamSynchronize(a->ctx->stream);
+        cudaFree(a->data);
+    }
+    delete a;
+    return TPT_OK;
+}
+
+int tpt_accum_clear(tpt_accum* a) {
+    TPT_REQUIRE(a, "tpt_accum_clear: NULL argument");
+    TPT_CHECK(bind(a->ctx));
+    TPT_CUDA(cudaMemsetAsync(a->data, 0, (size_t)a->width * a->height * 3 * sizeof(unsigned long long), a->ctx->stream));
+    return TPT_OK;
+}
+
+int tpt_accum_add(tpt_accum* dst, const tpt_accum* src) {
+    TPT_REQUIRE(dst && src, "tpt_accum_add: NULL argument");
+    TPT_REQUIRE(dst->ctx == src->ctx && dst->width == src->width && dst->height == src->height, "tpt_accum_add: mismatched buffers");
+    TPT_CHECK(bind(dst->ctx));
+    return tpt_accum_add_impl(dst, src);
+}
+
+void* tpt_accum_device_ptr(tpt_accum* a) { return a ? a->data : nullptr; }
+
+int tpt_accum_export_f32(tpt_accum* a, float* host_rgb) {
+    TPT_REQUIRE(a && host_rgb, "tpt_accum_export_f32: NULL argument");
+    TPT_CHECK(bind(a->ctx));
+    const size_t n = (size_t)a->width * a->height * 3;
+    float* d = nullptr;
+    TPT_CUDA(cudaMalloc(&d, n * sizeof(float)));
+    int rc = tpt_accum_to_f32_impl(a, d);
+    cudaError_t e = cudaSuccess;
+    if (rc == TPT_OK) e = cudaMemcpyAsync(host_rgb, d, n * sizeof(float), cudaMemcpyDeviceToHost, a->ctx->stream);
+    if (rc == TPT_OK && e == cudaSuccess) e = cudaStreamSynchronize(a->ctx->stream);
+    cudaFree(d);
+    TPT_CHECK(rc);
+    TPT_CUDA(e);
+    return TPT_OK;
+}
+
+int tpt_accum_export_i64(tpt_accum* a, int64_t* host) {
+    TPT_REQUIRE(a && host, "tpt_accum_export_i64: NULL argument");
+    TPT_CHECK(bind(a->ctx));
+    TPT_CUDA(cudaMemcpyAsync(host, a->data, (size_t)a->width * a->height * 3 * sizeof(int64_t), cudaMemcpyDeviceToHost, a->ctx->stream));
+    TPT_CUDA(cudaStreamSynchronize(a->ctx->stream));
+    return TPT_OK;
+}
+
+int tpt_accum_import_i64(tpt_accum* a, const int64_t* host) {
+    TPT_REQUIRE(a && host, "tpt_accum_import_i64: NULL argument");
+    TPT_CHECK(bind(a->ctx));
+    TPT_CUDA(cudaMemcpyAsync(a->data, host, (size_t)a->width * a->height * 3 * sizeof(int64_t), cudaMemcpyHostToDevice, a->ctx->stream));
+    TPT_CUDA(cudaStreamSynchronize(a->ctx->stream));
+    return TPT_OK;
+}
+
+int tpt_render(tpt_scene* s, const tpt_camera* cam, const tpt_render_config* cfg, tpt_accum* acc) {
+    TPT_REQUIRE(s && cam && cfg && acc, "tpt_render: NULL argument");
+    TPT_REQUIRE(cfg->width > 0 && cfg->height > 0 && cfg->width <= 16384 && cfg->height <= 16384, "tpt_render: bad resolution");
+    TPT_REQUIRE(cfg->spp > 0, "tpt_render: spp must be positive");
+    TPT_REQUIRE(cfg->max_depth >= 1 && cfg->max_depth <= 64, "tpt_render: max_depth must be in 1..64");
+    TPT_REQUIRE(cfg->sample_stride >= 1 && cfg->sample_offset >= 0, "tpt_render: bad sample slice");
+    TPT_REQUIRE(acc->width == cfg->width && acc->height == cfg->height, "tpt_render: accumulator size differs from the render size");
+    TPT_REQUIRE(acc->ctx == s->ctx, "tpt_render: accumulator belongs to another context");
+    if (!s->built) {
+        set_error("tpt_render: call tpt_bvh_build first");
+        return TPT_ERR_STATE;
+    }
+    TPT_CHECK(bind(s->ctx));
+    return tpt_render_impl(s, cam, cfg, acc);
+}
+
+int tpt_resolve_bgra8(tpt_accum* a, int spp_total, uint8_t* fb, int device_ptr) {
+    TPT_REQUIRE(a && fb, "tpt_resolve_bgra8: NULL argument");
+    TPT_REQUIRE(spp_total > 0, "tpt_resolve_bgra8: spp_total must be positive");
+    TPT_CHECK(bind(a->ctx));
+    if (device_ptr) return tpt_resolve_impl(a, spp_total, fb);
+    const size_t bytes = (size_t)a->width * a->height * 4;
+    uint8_t* d = nullptr;
+    TPT_CUDA(cudaMalloc(&d, bytes));
+    // the reference leaves the alpha byte as it finds it: start from the caller's buffer
+    cudaError_t e = cudaMemcpyAsync(d, fb, bytes, cudaMemcpyHostToDevice, a->ctx->stream);
+    int rc = e == cudaSuccess ? tpt_resolve_impl(a, spp_total, d) : TPT_OK;
+    if (e == cudaSuccess && rc == TPT_OK) e = cudaMemcpyAsync(fb, d, bytes, cudaMemcpyDeviceToHost, a->ctx->stream);
+    if (e == cudaSuccess && rc == TPT_OK) e = cudaStreamSynchronize(a->ctx->stream);
+    cudaFree(d);
+    TPT_CHECK(rc);
+    TPT_CUDA(e);
+    return TPT_OK;
+}
+
+int tpt_do_trace(tpt_scene* s, const tpt_camera* cam, const tpt_render_config* cfg, tpt_accum* acc, uint8_t* host_fb) {
+    TPT_REQUIRE(s && cam && cfg && acc && host_fb, "tpt_do_trace: NULL argument");
+    TPT_CHECK(tpt_bvh_build(s, nullptr));
+    TPT_CHECK(tpt_accum_clear(acc));
+    TPT_CHECK(tpt_render(s, cam, cfg, acc));
+    return tpt_resolve_bgra8(acc, cfg->spp, host_fb, 0);
+}
+
+}   // extern "C"

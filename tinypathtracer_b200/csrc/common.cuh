@@ -1,0 +1,132 @@
+// common.cuh — device math, RNG and error plumbing shared by the kernels of libtpt_b200.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <cfloat>
+#include <cstdint>
+#include <cstdio>
+#include <string>
+
+#include "tpt.h"
+
+namespace tpt {
+
+// ------------------------------------------------------------------------------------------------
+// errors (the C ABI returns codes; message kept per host thread)
+// ------------------------------------------------------------------------------------------------
+void set_error(const std::string& msg);
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
+
+#define TPT_CUDA(call)                                                          \
+    do {                                                                        \
+        cudaError_t e__ = (call);                                               \
+        if (e__ != cudaSuccess) return ::tpt::cuda_fail(e__, #call, __FILE__, __LINE__); \
+    } while (0)
+#define TPT_CHECK(expr)                 \
+    do {                                \
+        int rc__ = (expr);              \
+        if (rc__ != TPT_OK) return rc__; \
+    } while (0)
+#define TPT_REQUIRE(cond, msg)              \
+    do {                                    \
+        if (!(cond)) {                      \
+            ::tpt::set_error(msg);          \
+            return TPT_ERR_INVALID;         \
+        }                                   \
+    } while (0)
+
+constexpr int kNumSMs = 148;        // B200: 2 dies x 74 SMs
+constexpr float kPi = 3.141592653589793f;
+constexpr float kDelta = 2e-4f;     // reference MathConst::Delta (include/math/vec.h:70)
+constexpr int kAccumFracBits = 36;  // fixed-point accumulation: value * 2^36 in int64
+
+// ------------------------------------------------------------------------------------------------
+// float3 helpers
+// ------------------------------------------------------------------------------------------------
+__host__ __device__ __forceinline__ float3 f3(float x, float y, float z) { return make_float3(x, y, z); }
+__host__ __device__ __forceinline__ float3 operator+(float3 a, float3 b) { return f3(a.x + b.x, a.y + b.y, a.z + b.z); }
+__host__ __device__ __forceinline__ float3 operator-(float3 a, float3 b) { return f3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__host__ __device__ __forceinline__ float3 operator-(float3 a) { return f3(-a.x, -a.y, -a.z); }
+__host__ __device__ __forceinline__ float3 operator*(float3 a, float3 b) { return f3(a.x * b.x, a.y * b.y, a.z * b.z); }
+__host__ __device__ __forceinline__ float3 operator*(float3 a, float s) { return f3(a.x * s, a.y * s, a.z * s); }
+__host__ __device__ __forceinline__ float3 operator*(float s, float3 a) { return f3(a.x * s, a.y * s, a.z * s); }
+__host__ __device__ __forceinline__ float dot(float3 a, float3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__host__ __device__ __forceinline__ float3 cross(float3 a, float3 b) {
+    return f3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
+}
+__host__ __device__ __forceinline__ float3 fmin3(float3 a, float3 b) { return f3(fminf(a.x, b.x), fminf(a.y, b.y), fminf(a.z, b.z)); }
+__host__ __device__ __forceinline__ float3 fmax3(float3 a, float3 b) { return f3(fmaxf(a.x, b.x), fmaxf(a.y, b.y), fmaxf(a.z, b.z)); }
+
+// The reference normalises every direction and shading normal with the Quake reciprocal square
+// root and ONE Newton step (include/math/vec.h:25-38,155): lengths are off by up to 0.175 %, and hit
+// distances are measured in units of that non-unit direction.  t-parity at 1e-5 requires the same
+// function, so it is part of the contract, not an approximation of ours.
+__host__ __device__ __forceinline__ float ref_frsqrt(float num) {
+    float x2 = num * 0.5f;
+#ifdef __CUDA_ARCH__
+    int i = __float_as_int(num);
+    i = 0x5f3759df - (i >> 1);
+    float y = __int_as_float(i);
+#else
+    int i;
+    float y = num;
+    memcpy(&i, &y, 4);
+    i = 0x5f3759df - (i >> 1);
+    memcpy(&y, &i, 4);
+#endif
+    return y * (1.5f - (x2 * y * y));
+}
+__host__ __device__ __forceinline__ float3 ref_normalize(float3 v) { return v * ref_frsqrt(dot(v, v)); }
+
+// column-major Mat4 (reference include/math/mat.h:37-51)
+__host__ __device__ __forceinline__ float3 mat4_point(const float* m, float3 p) {
+    return f3(m[0] * p.x + m[4] * p.y + m[8] * p.z + m[12], m[1] * p.x + m[5] * p.y + m[9] * p.z + m[13],
+              m[2] * p.x + m[6] * p.y + m[10] * p.z + m[14]);
+}
+__host__ __device__ __forceinline__ float3 mat4_dir(const float* m, float3 d) {
+    return f3(m[0] * d.x + m[4] * d.y + m[8] * d.z, m[1] * d.x + m[5] * d.y + m[9] * d.z, m[2] * d.x + m[6] * d.y + m[10] * d.z);
+}
+
+// ------------------------------------------------------------------------------------------------
+// RNG — counter-based, stateless.  Spec (DESIGN.md "RNG spec"; oracle/oracle.cpp restates it):
+//   key(seed, pixel, sample) = mix64( mix64(seed + G) ^ (pixel << 32 | sample) ),  G = 0x9E3779B97F4A7C15
+//   pair(key, j)             = mix64( key + (j + 1) * G )   ->  a = u01(hi32), b = u01(lo32)
+//   u01(x)                   = ((x >> 8) + 1) * 2^-24   in (0, 1]   (the range of curand_uniform)
+//   mix64 = the SplitMix64 finaliser.
+// Pair 0 is the pixel jitter; at path vertex d pair 1+2d drives the BSDF sample (dielectric: a is the
+// Fresnel coin; diffuse: a -> phi, b -> cos^2) and pair 2+2d the extra "direct" cosine ray.
+// Replaces the per-pixel cuRAND XORWOW state in global memory (include/sampler.h:12-15,
+// src/path_tracer.cu:34-40): no state buffer, and a sample's value does not depend on which GPU,
+// kernel or thread evaluates it.
+// ------------------------------------------------------------------------------------------------
+constexpr uint64_t kGolden = 0x9E3779B97F4A7C15ull;
+__host__ __device__ __forceinline__ uint64_t mix64(uint64_t z) {
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+__host__ __device__ __forceinline__ uint64_t rng_seed_key(uint64_t seed) { return mix64(seed + kGolden); }
+__host__ __device__ __forceinline__ uint64_t rng_path_key(uint64_t seedKey, uint32_t pixel, uint32_t sample) {
+    return mix64(seedKey ^ (((uint64_t)pixel << 32) | (uint64_t)sample));
+}
+__host__ __device__ __forceinline__ float rng_u01(uint32_t x) { return (float)((x >> 8) + 1u) * (1.0f / 16777216.0f); }
+__host__ __device__ __forceinline__ void rng_pair(uint64_t key, uint32_t j, float& a, float& b) {
+    uint64_t z = mix64(key + (uint64_t)(j + 1u) * kGolden);
+    a = rng_u01((uint32_t)(z >> 32));
+    b = rng_u01((uint32_t)z);
+}
+
+// ------------------------------------------------------------------------------------------------
+// warp-aggregated queue append: one atomicAdd per warp (ballot + popc + shuffle of the base).
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t warp_append(bool pred, uint32_t* counter) {
+    const unsigned mask = __ballot_sync(0xffffffffu, pred);
+    if (mask == 0) return 0;
+    const int lane = threadIdx.x & 31;
+    const int leader = __ffs(mask) - 1;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(counter, (uint32_t)__popc(mask));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    return base + __popc(mask & ((1u << lane) - 1u));
+}
+
+}   // namespace tpt

@@ -1,0 +1,100 @@
+// scene.cuh — device-side data layout of a scene, its BVH and the per-context state.
+//
+// HBM layout (all arrays 256-B aligned cudaMalloc blocks, sizes for F faces / V vertices):
+//   indices      u32[3F]           as uploaded (DeviceScene.indices)
+//   obj_verts    float[3V]         object-space positions      obj_norms float[3V]
+//   vert_obj     u32[V]            object id of each vertex (built once per scene)
+//   face_mtl     u32[F]            material index of each face  (replaces mtlLinearSearch per hit)
+//   world_verts  float[3V]         rebuilt by every tpt_bvh_build   world_norms float[3V]
+//   nodes        float4[4*(F-1)]   64-B BVH2 nodes, both child boxes in the parent (Aila–Laine packing):
+//                                    n0 = (L.lo.x, L.hi.x, L.lo.y, L.hi.y)   n1 = (R.lo.x, R.hi.x, R.lo.y, R.hi.y)
+//                                    n2 = (L.lo.z, L.hi.z, R.lo.z, R.hi.z)   n3 = (left, right, -, -) as int bits
+//                                  child >= 0: internal node index; child < 0: leaf ~child (sorted triangle index)
+//   tri_geom     float4[3F]        per leaf, in Morton order: (v0.xyz, e1.x) (e1.yz, e2.xy) (e2.z, prim, mtl, -)
+//   tri_norm     float4[3F]        per leaf: (n0.xyz, n1.x) (n1.yz, n2.xy) (n2.z, -, -, -)  world shading normals
+//   mtl_table    float4[2M]        (base.rgb, emission) (eta, metallic, -, -)
+//   lights       tpt_delta_light[L]
+// Every traversal read is a 128-bit load at a 16-B aligned address.
+#pragma once
+#include "common.cuh"
+
+namespace tpt {
+
+struct DeviceCounters {
+    unsigned long long rays_primary, rays_extension, rays_shadow, rays_direct;
+    unsigned long long node_visits, tri_tests;
+    unsigned long long dropped_nonfinite;
+    unsigned long long pad;
+};
+
+struct BvhView {
+    const float4* nodes;
+    const float4* tri_geom;
+    const float4* tri_norm;
+    int n_faces;
+};
+
+}   // namespace tpt
+
+struct tpt_context {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    // environment map (RGBA8, row 0 = bottom)
+    uchar4* env = nullptr;
+    int env_w = 0, env_h = 0;
+    // counters
+    tpt::DeviceCounters* d_counters = nullptr;
+    uint64_t samples = 0;
+    uint64_t kernel_launches = 0;
+    // wavefront pools (grown on demand)
+    size_t pool_paths = 0;
+    float4* path_state[2] = {nullptr, nullptr};   // 3 float4 per path
+    float4* hits = nullptr;                       // 1 float4 per path
+    float4* sec_rays = nullptr;                   // 3 float4 per secondary ray
+    size_t sec_capacity = 0;
+    uint32_t* queue_counts = nullptr;             // [0],[1] extension ping-pong, [2] secondary
+    // scratch for trace_rays with host pointers
+    void* io_rays = nullptr;
+    void* io_hits = nullptr;
+    size_t io_capacity = 0;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+};
+
+struct tpt_scene {
+    tpt_context* ctx = nullptr;
+    size_t n_faces = 0, n_vertices = 0, n_objects = 0, n_materials = 0, n_lights = 0;
+    uint32_t* indices = nullptr;
+    float* obj_verts = nullptr;
+    float* obj_norms = nullptr;
+    uint32_t* vert_obj = nullptr;
+    uint32_t* face_mtl = nullptr;
+    tpt_mtl_interval* objects = nullptr;
+    float* vert_trans = nullptr;
+    float* normal_trans = nullptr;
+    float4* mtl_table = nullptr;
+    tpt_delta_light* lights = nullptr;
+    // per-build
+    float* world_verts = nullptr;
+    float* world_norms = nullptr;
+    unsigned long long* keys[2] = {nullptr, nullptr};
+    uint32_t* vals[2] = {nullptr, nullptr};
+    void* sort_tmp = nullptr;
+    size_t sort_tmp_bytes = 0;
+    int* parent_int = nullptr;    // parent of internal node i
+    int* parent_leaf = nullptr;   // parent of leaf i
+    uint32_t* flags = nullptr;    // refit arrival counters
+    uint32_t* bounds = nullptr;   // 6 ordered-uint encoded floats (min xyz, max xyz)
+    float4* nodes = nullptr;
+    float4* tri_geom = nullptr;
+    float4* tri_norm = nullptr;
+    bool built = false;
+    tpt::BvhView view() const { return tpt::BvhView{nodes, tri_geom, tri_norm, (int)n_faces}; }
+};
+
+struct tpt_accum {
+    tpt_context* ctx = nullptr;
+    int width = 0, height = 0;
+    unsigned long long* data = nullptr;   // [h][w][3] int64 fixed point, row 0 = bottom
+    bool owned = true;
+};

@@ -1,0 +1,125 @@
+// traverse.cuh — software BVH traversal (B200 has no RT cores).
+//
+// Replaces traverseBVH / rayHitBBox / rayHitTriangle of the reference (src/path_tracer.cu:61-107,
+// include/geometry_queries.h:18-46,66-86).  Same acceptance rule for a hit — Möller–Trumbore,
+// two-sided, u >= 0, v >= 0, u+v <= 1, t > 2e-4, strictly closer than the best so far — but:
+//   * ordered (near child first) with the far child pushed, and boxes are culled against the current
+//     best t (the reference visits every box the infinite LINE touches);
+//   * one reciprocal per ray, not three divisions per box;
+//   * 64-B nodes read with four 128-bit loads, both child boxes in the parent;
+//   * exact-t ties resolve to the LOWEST primitive id, so the result does not depend on tree shape
+//     (the reference keeps the first triangle met in its own traversal order).
+#pragma once
+#include "scene.cuh"
+
+namespace tpt {
+
+constexpr int kStackSize = 96;   // LBVH depth <= 63 key bits + 32 index tie-break bits
+
+struct HitRec {
+    float t, u, v;
+    int leaf;    // sorted triangle index, -1 = miss
+    int prim;    // original face id
+};
+
+__device__ __forceinline__ float safe_rcp(float d) {
+    // A zero direction component makes the slab parallel: substitute a tiny value of the same sign
+    // so that (b - o) * inv is +-huge with the right sign (or 0 when the origin lies on the plane).
+    return 1.0f / (fabsf(d) > 1e-30f ? d : copysignf(1e-30f, d));
+}
+
+// Conservative slab test for one child: returns entry distance in `lo`.  The exit distance is
+// widened and the entry distance narrowed by 2^-21 relative so that rounding in (b-o)*inv can
+// never cull a box whose triangle the Möller–Trumbore test would accept.
+__device__ __forceinline__ bool slab(float lox, float hix, float loy, float hiy, float loz, float hiz, float3 o, float3 inv,
+                                     float tbest, float& lo) {
+    float t0x = (lox - o.x) * inv.x, t1x = (hix - o.x) * inv.x;
+    float t0y = (loy - o.y) * inv.y, t1y = (hiy - o.y) * inv.y;
+    float t0z = (loz - o.z) * inv.z, t1z = (hiz - o.z) * inv.z;
+    float tn = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fminf(t0z, t1z));
+    float tf = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fmaxf(t0z, t1z));
+    tn = fmaxf(tn * 0.9999995f, 0.0f);
+    tf = fminf(tf * 1.0000005f, tbest);
+    lo = tn;
+    return tn <= tf;
+}
+
+template <bool ANY, bool COUNT>
+__device__ __forceinline__ HitRec traverse(const BvhView& bvh, float3 o, float3 d, unsigned long long* nodeVisits,
+                                           unsigned long long* triTests) {
+    HitRec best;
+    best.t = FLT_MAX;
+    best.u = best.v = 0.0f;
+    best.leaf = -1;
+    best.prim = -1;
+
+    const float3 inv = f3(safe_rcp(d.x), safe_rcp(d.y), safe_rcp(d.z));
+    int stack[kStackSize];
+    int sp = 0;
+    int cur = bvh.n_faces > 1 ? 0 : ~0;   // single-triangle scene: the root is leaf 0
+    unsigned nv = 0, nt = 0;
+
+    while (true) {
+        if (cur >= 0) {
+            const float4* n = bvh.nodes + 4 * (size_t)cur;
+            const float4 n0 = __ldg(n), n1 = __ldg(n + 1), n2 = __ldg(n + 2);
+            const int4 n3 = __ldg(reinterpret_cast<const int4*>(n + 3));
+            if (COUNT) ++nv;
+            float loL, loR;
+            const bool hL = slab(n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, o, inv, best.t, loL);
+            const bool hR = slab(n1.x, n1.y, n1.z, n1.w, n2.z, n2.w, o, inv, best.t, loR);
+            if (hL && hR) {
+                const bool rightFirst = loR < loL;
+                cur = rightFirst ? n3.y : n3.x;
+                stack[sp++] = rightFirst ? n3.x : n3.y;
+            } else if (hL) {
+                cur = n3.x;
+            } else if (hR) {
+                cur = n3.y;
+            } else {
+                if (sp == 0) break;
+                cur = stack[--sp];
+            }
+        } else {
+            const int leaf = ~cur;
+            const float4* tp = bvh.tri_geom + 3 * (size_t)leaf;
+            const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
+            if (COUNT) ++nt;
+            const float3 v0 = f3(a.x, a.y, a.z), e1 = f3(a.w, b.x, b.y), e2 = f3(b.z, b.w, c.x);
+            const float3 tv = o - v0;
+            const float3 p = cross(d, e2);
+            const float3 q = cross(tv, e1);
+            const float denom = dot(p, e1);
+            if (denom != 0.0f) {
+                const float invDenom = 1.0f / denom;
+                const float u = dot(p, tv) * invDenom;
+                const float v = dot(q, d) * invDenom;
+                if (!(u < 0.0f || v < 0.0f || u + v > 1.0f)) {
+                    const float t = dot(q, e2) * invDenom;
+                    const int prim = __float_as_int(c.y);
+                    if (t > kDelta && (t < best.t || (t == best.t && prim < best.prim))) {
+                        best.t = t;
+                        best.u = u;
+                        best.v = v;
+                        best.leaf = leaf;
+                        best.prim = prim;
+                        if (ANY) break;
+                    }
+                }
+            }
+            if (sp == 0) break;
+            cur = stack[--sp];
+        }
+    }
+    if (COUNT) {   // one atomic per converged group of lanes, not per ray
+        const unsigned m = __activemask();
+        const unsigned sv = __reduce_add_sync(m, nv), st = __reduce_add_sync(m, nt);
+        if ((threadIdx.x & 31) == __ffs(m) - 1) {
+            atomicAdd(nodeVisits, (unsigned long long)sv);
+            atomicAdd(triTests, (unsigned long long)st);
+        }
+    }
+    return best;
+}
+
+}   // namespace tpt
