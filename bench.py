@@ -1,0 +1,378 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the path-tracing hot path (BASELINE.json metric: Mrays/s & samples/s at
+1920x1080; BVH build ms).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload ball|light|box|tir]
+
+A *step* is one whole frame of the workload, as PathTracer::doTrace does it in the reference
+(src/path_tracer.cu:491-554): object->world transform + full BVH rebuild + clear + `spp` samples per pixel
++ resolve to BGRA8.  Default workload = BASELINE.json configs[1]: ball.gltf, 1920x1080, 256 spp, depth 8,
+synthetic sky environment (the shipped JPG is a missing blob).  Inputs are the flattened scene fixtures under
+tests/golden/scenes (no /root/reference at run time); the camera, materials and lights are the glTF's.
+
+N > 1 (torchrun, one rank per GPU): the 8 fixed spp slices of SURVEY §8(e) are dealt round-robin to the
+ranks (strong scaling: total spp fixed); every rank holds a replicated scene + BVH; one NCCL all-reduce (SUM,
+int64 fixed point — exact, so the image is bit-identical for any N) combines the accumulation buffers.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+if str(ROOT) not in sys.path:
+    sys.path.insert(0, str(ROOT))
+
+WORKLOADS = {
+    # name: (scene fixture, width, height, spp, max_depth, env, seed)   — BASELINE.json configs
+    "ball": ("ball", 1920, 1080, 256, 8, "sky", 2),     # configs[1] (a)
+    "light": ("light", 1920, 1080, 256, 8, "sky", 2),   # configs[1] (b)
+    "box": ("box", 512, 512, 64, 8, None, 1),           # configs[0]
+    "tir": ("tir", 1920, 1080, 256, 32, None, 3),       # configs[2]
+    "box2_4k": ("box2", 3840, 2160, 4096, 8, "sky", 5),  # configs[4]
+}
+N_SLICES = 8
+
+
+def synthetic_sky(width=4096, height=2048):
+    from tinypathtracer_b200.sky import synthetic_sky as sky
+    return sky(width, height)
+
+
+def load_scene(name):
+    from tinypathtracer_b200.scene_io import load_scene_npz
+    return load_scene_npz(ROOT / "tests" / "golden" / "scenes" / f"{name}.npz")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    def __init__(self, index: int):
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "200", "-i", str(self.index)],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, smax, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                smax.append(float(r[1]))
+            except Exception:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(smax) if smax else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+def my_slices(rank: int, world: int):
+    """8 fixed slices (slice s = sample indices s, s+8, ...), slice -> GPU map s mod N."""
+    return [s for s in range(N_SLICES) if s % world == rank]
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import tinypathtracer_b200 as tpt
+    from tinypathtracer_b200.scene_io import scene_upload_bytes
+
+    rank, world, local = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the hot path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    fixture, W, H, spp, depth, envkind, seed = WORKLOADS[args.workload]
+    if args.spp:
+        spp = args.spp
+    assert spp % N_SLICES == 0, "spp must be a multiple of the 8 fixed slices"
+    per_slice = spp // N_SLICES
+    scene = load_scene(fixture)
+    env = synthetic_sky() if envkind == "sky" else None
+
+    ctx = tpt.Context(local)
+    stream = torch.cuda.current_stream()
+    ctx.set_stream(stream.cuda_stream)          # kernels, torch events and NCCL all on one stream
+    pt = tpt.PathTracer(ctx, W, H, env_rgba8=env)
+    acc_t = torch.zeros((H, W, 3), dtype=torch.int64, device="cuda")     # accumulation buffer owned by torch (NCCL operand)
+    acc = tpt.Accum(ctx, W, H, device_ptr=acc_t.data_ptr())
+    fb_dev = torch.zeros((H, W, 4), dtype=torch.uint8, device="cuda")
+    fb_host = torch.zeros((H, W, 4), dtype=torch.uint8).pin_memory()
+    cam = tpt.Camera.from_scene(scene)
+    slices = my_slices(rank, world)
+    import ctypes as C
+    from tinypathtracer_b200._capi import lib, check
+
+    def frame(dscene, counters=False, stage_times=False):
+        """One doTrace (reference src/path_tracer.cu:491-554) with device-resident inputs."""
+        tpt.BVH(dscene).construct(stats=False)
+        acc.clear()
+        for s in slices:
+            pt.render_into(dscene, cam, spp=per_slice, max_depth=depth, seed=seed, sample_offset=s, sample_stride=N_SLICES,
+                           accum=acc, counters=counters, stage_times=stage_times, paths_in_flight=args.paths_in_flight)
+        if world > 1:
+            dist.all_reduce(acc_t, op=dist.ReduceOp.SUM)
+        check(lib.tpt_resolve_bgra8(acc._h, spp, C.c_void_p(fb_dev.data_ptr()), 1))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(steps):
+            fn()
+        e1.record(stream)
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    dscene = tpt.DeviceScene(ctx, scene)
+    for _ in range(args.warmup):
+        frame(dscene)
+    # ---- value: device-resident inputs -------------------------------------------------------------------
+    ctx.reset_counters()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    ms_total = timed(lambda: frame(dscene), args.steps)
+    clk = clocks.stop() if rank == 0 else {}
+    ctr = ctx.counters()
+    launches = ctr["kernel_launches"]
+    ms_step = ms_total / args.steps
+    samples_step = W * H * spp                       # whole job, all ranks
+    rays_rank = ctr["rays_primary"] + ctr["rays_extension"] + ctr["rays_shadow"] + ctr["rays_direct"]
+    rays_t = torch.tensor([rays_rank], device="cuda", dtype=torch.int64)
+    if world > 1:
+        dist.all_reduce(rays_t)
+    rays_step = int(rays_t.item()) / args.steps
+    value = samples_step / (ms_step * 1e-3) / 1e6
+
+    # ---- e2e: host buffers in, host framebuffer out, through the C ABI -------------------------------------
+    def frame_e2e():
+        ds = tpt.DeviceScene(ctx, scene)          # tpt_scene_create: H2D of every scene array
+        frame(ds)
+        fb_host.copy_(fb_dev, non_blocking=True)  # D2H of the step's result
+        torch.cuda.current_stream().synchronize()
+        ds.close()
+
+    frame_e2e()
+    ms_e2e = timed(frame_e2e, args.steps) / args.steps
+    e2e_value = samples_step / (ms_e2e * 1e-3) / 1e6
+
+    line = None
+    if rank == 0:
+        # ---- roofline pass (untimed for `value`): per-stage CUDA-event times + node/triangle counters --------
+        ctx.reset_counters()
+        bvh = tpt.BVH(dscene)
+        bstats = bvh.construct(stats=True)
+        acc.clear()
+        prof_spp = max(1, min(per_slice, 4))
+        pt.render_into(dscene, cam, spp=prof_spp, max_depth=depth, seed=seed, accum=acc, stage_times=True,
+                       paths_in_flight=args.paths_in_flight)
+        st = ctx.stage_times()
+        c1 = ctx.counters()
+        ctx.reset_counters()
+        pt.render_into(dscene, cam, spp=prof_spp, max_depth=depth, seed=seed, accum=acc, counters=True,
+                       paths_in_flight=args.paths_in_flight)
+        c2 = ctx.counters()
+        ctx.synchronize()
+        n_ext = c1["rays_primary"] + c1["rays_extension"]
+        n_sec = c1["rays_shadow"] + c1["rays_direct"]
+        n_all = n_ext + n_sec
+        n_int = c2["node_visits"] / max(n_all, 1)
+        n_leaf = c2["tri_tests"] / max(n_all, 1)
+        bytes_per_ray = 56.0 * n_int + 40.0 * n_leaf + 88.0          # SURVEY §8(d) algorithmic bytes per ray
+        trav_ms = st["extend"]["ms"] + st["connect"]["ms"]
+        trav_launches = st["extend"]["launches"] + st["connect"]["launches"]
+        peaks = {}
+        try:
+            peaks = json.loads((ROOT / "MEASURED_PEAKS.json").read_text())
+        except Exception:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        achieved = bytes_per_ray * n_all / (trav_ms * 1e-3) / 1e9 if trav_ms > 0 else 0.0
+        stage_total = sum(v["ms"] for v in st.values())
+        roofline = {"bound": "hbm", "kernel": "k_extend+k_connect (BVH traversal)", "achieved": round(achieved, 2), "peak": peak,
+                    "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback (B200_PROFILING.md)", "unit": "GB/s",
+                    "frac": round(achieved / peak, 5), "traffic": None,
+                    "bytes_per_ray": round(bytes_per_ray, 1), "n_int_per_ray": round(n_int, 2), "n_leaf_per_ray": round(n_leaf, 2),
+                    "rays_per_launch": round(n_all / max(trav_launches, 1), 1),
+                    "avg_launch_us": round(1e3 * trav_ms / max(trav_launches, 1), 2),
+                    "share_of_step": round(trav_ms / stage_total, 4) if stage_total > 0 else None,
+                    "stage_ms": {k: round(v["ms"], 3) for k, v in st.items()},
+                    "note": "BVH of this workload is L1/L2-resident; node fetches never reach HBM, the HBM fraction is an upper-bound accounting (SURVEY §8d)"}
+        cpu = cpu_baseline(args, fixture, W, H, depth, env, seed) if world == 1 and not args.no_cpu_baseline else None
+        line = {
+            "metric": "Msamples/s (whole frames: transform + BVH build + render + resolve)", "value": round(value, 3), "unit": "Msamples/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 3), "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{fixture}.gltf {W}x{H} {spp}spp depth{depth} env={envkind or 'black'} seed={seed}",
+                       "parallelism": f"spp-slices x{world}", "slices": N_SLICES,
+                       "l2": "per-step working set (path pools + accumulators, ~0.5 GB) exceeds the 126 MB L2"},
+            "mrays_per_s": round(rays_step / (ms_step * 1e-3) / 1e6, 2), "rays_per_sample": round(rays_step / samples_step, 4),
+            "bvh_build_ms": round(bstats["build_ms"], 4), "bvh_faces": bstats["n_faces"],
+            "e2e": {"value": round(e2e_value, 3), "unit": "Msamples/s", "ms_per_step": round(ms_e2e, 3),
+                    "h2d_bytes_per_step": scene_upload_bytes(scene), "d2h_bytes_per_step": W * H * 4},
+            "gpu_launches": int(launches), "clocks": clk, "roofline": roofline,
+        }
+        if cpu is not None:
+            line["cpu_baseline"] = cpu
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank == 0:
+        print(json.dumps(line))
+
+
+def cpu_baseline(args, fixture, W, H, depth, env, seed):
+    """The oracle (a port: the reference has no CPU path) on a bounded sample of the same workload."""
+    from oracle import gltf_scene, pyoracle as orc
+    scene = gltf_scene.load_scene(ROOT / "tests" / "golden" / "scenes" / f"{fixture}.npz")
+    wv, wn = orc.transform(scene)
+    nodes, _, _ = orc.build_reference_bvh(wv, scene["indices"])
+    # centre crop, 4 spp; grow until ~10 s of CPU work
+    cw, ch, spp = max(32, W // 8), max(32, H // 8), 4
+    x0, y0 = (W - cw) // 2, (H - ch) // 2
+    t_used, n_samples, n_rays = 0.0, 0, 0
+    while t_used < args.cpu_seconds:
+        t0 = time.perf_counter()
+        _, cnt = orc.render(scene, W, H, spp, max_depth=depth, seed=seed, env=env, region=(x0, y0, x0 + cw, y0 + ch),
+                            prepared=(wv, wn, nodes), counters=True, sample_offset=n_samples // (cw * ch))
+        t_used += time.perf_counter() - t0
+        n_samples += cw * ch * spp
+        n_rays += int(cnt[0])
+    return {"value": round(n_samples / t_used / 1e6, 4), "unit": "Msamples/s", "cores": orc.num_threads(), "kind": "port",
+            "mrays_per_s": round(n_rays / t_used / 1e6, 3),
+            "sample": f"centre {cw}x{ch} crop of the {W}x{H} frame, {n_samples // (cw * ch)} spp, {t_used:.1f} s of CPU work"}
+
+
+def run_reference(args):
+    """Reference arm.  The reference has NO CPU implementation of this path; its own code is CUDA.
+    When oracle/_ref/tpt_ref_headless (the UNMODIFIED reference sources built headless for sm_100 by
+    oracle/ref_build.py) is present it is run on GPU 0 for the same workload; otherwise the CPU oracle port
+    is timed on all host cores on a bounded sample."""
+    rank, world, local = dist_env()
+    if rank != 0:
+        return
+    fixture, W, H, spp, depth, envkind, seed = WORKLOADS[args.workload]
+    if args.spp:
+        spp = args.spp
+    cfg = {"workload": f"{fixture}.gltf {W}x{H} {spp}spp depth{depth} env={envkind or 'black'} seed={seed}"}
+    exe = ROOT / "oracle" / "_ref" / "tpt_ref_headless"
+    ref_scene = ROOT / "oracle" / "_ref" / "input" / f"{fixture}.gltf"
+    if exe.exists() and ref_scene.exists() and not args.ref_cpu:
+        import torch
+        if torch.cuda.is_available():
+            out = run_reference_cuda(args, exe, ref_scene, W, H, spp, depth, envkind, cfg)
+            if out is not None:
+                print(json.dumps(out))
+                return
+    env = synthetic_sky() if envkind == "sky" else None
+    res = []
+    for _ in range(args.warmup + args.steps):
+        res.append(cpu_baseline(args, fixture, W, H, depth, env, seed))
+    res = res[args.warmup:]
+    v = float(np.mean([r["value"] for r in res]))
+    cb = dict(res[-1])
+    cb["value"] = round(v, 4)
+    print(json.dumps({"impl": "reference", "metric": "Msamples/s (whole frames: transform + BVH build + render + resolve)",
+                      "value": round(v, 4), "unit": "Msamples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                      "ms_per_step": round(1e3 * W * H * spp / (v * 1e6), 1), "higher_is_better": True, "scaling": "strong",
+                      "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg, "cpu_baseline": cb,
+                      "reference_kind": "cpu oracle port (reference CUDA build not present)",
+                      "e2e": {"value": round(v, 4), "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+def run_reference_cuda(args, exe, ref_scene, W, H, spp, depth, envkind, cfg):
+    """Runs the headless build of the reference's own CUDA sources; it prints one JSON object with frame times."""
+    env_png = ROOT / "oracle" / "_ref" / "sky.png"
+    cmd = [str(exe), "--scene", str(ref_scene), "--width", str(W), "--height", str(H), "--spp", str(spp), "--depth", str(depth),
+           "--frames", str(args.steps), "--warmup", str(args.warmup)]
+    if envkind == "sky" and env_png.exists():
+        cmd += ["--env", str(env_png)]
+    try:
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=args.ref_timeout)
+        data = json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1])
+    except Exception as e:   # the binary is a build of foreign code: fall back to the port, loudly
+        sys.stderr.write(f"reference CUDA build failed to run ({e}); falling back to the CPU oracle port\n")
+        return None
+    ms = float(data["ms_per_frame"])
+    v = W * H * spp / (ms * 1e-3) / 1e6
+    return {"impl": "reference", "metric": "Msamples/s (whole frames: transform + BVH build + render + resolve)", "value": round(v, 3),
+            "unit": "Msamples/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms, 3),
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
+            "reference_kind": f"reference CUDA sources, headless, -O3 sm_100 ({data.get('build', '')}) on GPU 0; depth is compile-time {data.get('depth')}",
+            "cpu_baseline": {"value": round(v, 3), "unit": "Msamples/s", "cores": 0, "kind": "reference",
+                             "sample": "whole workload on the GPU (the reference has no CPU path)"},
+            "e2e": {"value": round(v, 3), "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="ball", choices=sorted(WORKLOADS))
+    ap.add_argument("--spp", type=int, default=0, help="override the workload's spp (multiple of 8)")
+    ap.add_argument("--paths-in-flight", type=int, default=0)
+    ap.add_argument("--cpu-seconds", type=float, default=10.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--ref-cpu", action="store_true", help="reference arm: force the CPU oracle port")
+    ap.add_argument("--ref-timeout", type=float, default=900.0)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

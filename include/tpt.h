@@ -121,7 +121,8 @@ typedef struct tpt_render_config {
     int32_t paths_in_flight; /* 0 = default pool size */
 } tpt_render_config;
 
-#define TPT_RENDER_COUNTERS 1u /* count node/triangle visits per ray kind (slower; for roofline accounting) */
+#define TPT_RENDER_COUNTERS 1u    /* count node/triangle visits per ray kind (slower; for roofline accounting) */
+#define TPT_RENDER_STAGE_TIMES 2u /* CUDA-event time of every wavefront kernel, summed per stage (one sync per batch) */
 
 typedef struct tpt_bvh_stats {
     float build_ms;          /* device time of the whole build, CUDA events on the context stream */
@@ -140,6 +141,13 @@ typedef struct tpt_counters {
     uint64_t kernel_launches;
 } tpt_counters;
 
+/* Device time per wavefront stage since the last tpt_reset_counters, measured with CUDA events on the
+ * context stream around every launch (only renders with TPT_RENDER_STAGE_TIMES contribute). */
+typedef struct tpt_stage_times {
+    double ms[4];        /* 0 generate, 1 extend (closest hit), 2 shade, 3 connect (shadow + direct rays) */
+    uint64_t launches[4];
+} tpt_stage_times;
+
 const char* tpt_last_error(void);
 int tpt_abi_version(void);
 
@@ -151,6 +159,7 @@ int tpt_context_synchronize(tpt_context* ctx);
 int tpt_context_set_stream(tpt_context* ctx, void* cuda_stream);
 int tpt_get_counters(tpt_context* ctx, tpt_counters* out);
 int tpt_reset_counters(tpt_context* ctx);
+int tpt_get_stage_times(tpt_context* ctx, tpt_stage_times* out);
 
 /* Replaces Scene::copySceneToDevice (src/mesh.cu:309-397): host arrays -> device. */
 int tpt_scene_create(tpt_context* ctx, const tpt_scene_desc* desc, tpt_scene** out);

@@ -64,8 +64,9 @@ def test_transform_matches_oracle(name, built, scenes, orc):
     ov, on = orc.transform(scenes[name])
     used = np.zeros(wv.shape[0], bool)
     used[scenes[name]["indices"]] = True
-    np.testing.assert_allclose(wv[used], ov[used], rtol=2e-6, atol=2e-6)
-    np.testing.assert_allclose(wn[used], on[used], rtol=2e-6, atol=2e-6)
+    # the geometric core is evaluated with one IEEE rounding per operation in the reference's order: bit-exact
+    assert np.array_equal(wv[used], ov[used])
+    assert np.array_equal(wn[used], on[used])
 
 
 @pytest.mark.parametrize("name", SCENES)
@@ -102,22 +103,18 @@ def test_primary_hits_vs_bruteforce(name, tpt, ctx, built, scenes, orc):
     rays = orc.primary_rays(scenes[name], W, H)
     gpu_rays = ctx.primary_rays(tpt.Camera.from_scene(scenes[name]), W, H)
     g6 = np.concatenate([gpu_rays["origin"], gpu_rays["dir"]], axis=1)
-    np.testing.assert_allclose(g6, rays, rtol=3e-6, atol=1e-6)   # sampleRays incl. frsqrt normalisation
+    assert np.array_equal(g6, rays)   # sampleRays incl. the frsqrt normalisation: bit-exact
     wv, _ = orc.transform(scenes[name])
     got = bvh.trace(rays)
     ref = orc.trace_rays(wv, scenes[name]["indices"], rays, mode=0)
     same = got["prim"] == ref["prim"]
     ties, grazing, wrong = classify_hit_mismatches(orc, wv, scenes[name]["indices"], rays, got, ref)
     assert wrong == 0, f"{wrong} real primitive-id mismatches (ties {ties}, grazing {grazing})"
-    assert ties + grazing <= max(4, int(2e-4 * W * H)), f"too many tie/grazing pixels: {ties}+{grazing}"
-    hit = same & (ref["prim"] >= 0)
-    if hit.any():
-        rel = np.abs(got["t"][hit] - ref["t"][hit]) / np.abs(ref["t"][hit])
-        assert rel.max() <= T_REL_TOL, f"max relative t error {rel.max():.3e}"
-        # barycentrics are not part of the north_star bar; sliver triangles make them ill-conditioned (FMA vs no FMA)
-        np.testing.assert_allclose(got["u"][hit], ref["u"][hit], atol=5e-4)
-        np.testing.assert_allclose(got["v"][hit], ref["v"][hit], atol=5e-4)
-    miss = same & (ref["prim"] < 0)
+    # Möller–Trumbore is evaluated op-for-op like the oracle and exact-t ties go to the lowest id on both sides,
+    # so in fact nothing may differ at all: id, t, u, v bit-exact (the 1e-5 bar of north_star is met with 0).
+    assert ties == 0 and grazing == 0 and same.all()
+    assert np.array_equal(got["t"], ref["t"]) and np.array_equal(got["u"], ref["u"]) and np.array_equal(got["v"], ref["v"])
+    miss = ref["prim"] < 0
     assert (got["t"][miss] == np.float32(3.4028234663852886e38)).all()   # HitStatus() default hitDist = FLT_MAX
 
 
@@ -137,15 +134,11 @@ def test_random_rays_vs_bruteforce(name, built, scenes, orc):
     got = bvh.trace(rays)
     ref = orc.trace_rays(wv, scenes[name]["indices"], rays, mode=0)
     ties, grazing, wrong = classify_hit_mismatches(orc, wv, scenes[name]["indices"], rays, got, ref)
-    assert wrong == 0, f"{wrong} real mismatches (ties {ties}, grazing {grazing})"
-    assert ties + grazing <= 30
-    hit = (got["prim"] == ref["prim"]) & (ref["prim"] >= 0)
-    rel = np.abs(got["t"][hit] - ref["t"][hit]) / np.abs(ref["t"][hit])
-    assert rel.max() <= T_REL_TOL
+    assert wrong == 0 and ties == 0 and grazing == 0, f"mismatches: wrong {wrong}, ties {ties}, grazing {grazing}"
+    assert np.array_equal(got["prim"], ref["prim"]) and np.array_equal(got["t"], ref["t"])
     # any-hit agrees with "closest hit exists" (the reference's shadow-ray visibility, src/path_tracer.cu:278-279)
     anyh = bvh.trace(rays, any_hit=True)
-    agree = (anyh["prim"] >= 0) == (ref["prim"] >= 0)
-    assert (~agree).sum() <= grazing + ties + 5
+    assert np.array_equal(anyh["prim"] >= 0, ref["prim"] >= 0)
 
 
 def test_counted_trace_matches_uncounted(built, scenes, orc, ctx):
@@ -186,9 +179,9 @@ def test_converged_image_relmse(name, depth, use_env, tpt, ctx, built, scenes, o
     """north_star: converged-image relative MSE <= 1e-3 — GPU at high spp vs the oracle at high spp with a
     DIFFERENT seed (independent estimates of the same expectation)."""
     ds, _ = built[name]
-    W, H = 64, 36
+    W, H = 48, 27
     env = synthetic_sky(256, 128) if use_env else None
-    spp_gpu, spp_cpu = 8192, 2048
+    spp_gpu = spp_cpu = {"box": 8192, "tir": 65536, "ball": 2048}[name]   # enough that MC noise sits below the 1e-3 bar
     pt = tpt.PathTracer(ctx, W, H, env_rgba8=env)
     pt.render_into(ds, tpt.Camera.from_scene(scenes[name]), spp=spp_gpu, max_depth=depth, seed=21)
     img = pt.m_radiance.to_f32() / spp_gpu

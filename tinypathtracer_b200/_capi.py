@@ -20,6 +20,7 @@ lib = C.CDLL(str(LIB_PATH))
 
 TPT_OK = 0
 TPT_RENDER_COUNTERS = 1
+TPT_RENDER_STAGE_TIMES = 2
 
 
 class Ray(C.Structure):
@@ -59,6 +60,10 @@ class Counters(C.Structure):
                                           "tri_tests", "samples", "dropped_nonfinite", "kernel_launches")]
 
 
+class StageTimes(C.Structure):
+    _fields_ = [("ms", C.c_double * 4), ("launches", C.c_uint64 * 4)]
+
+
 # every symbol include/tpt.h declares, with its signature
 SIGNATURES = {
     "tpt_last_error": (C.c_char_p, []),
@@ -69,6 +74,7 @@ SIGNATURES = {
     "tpt_context_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
     "tpt_get_counters": (C.c_int, [C.c_void_p, C.POINTER(Counters)]),
     "tpt_reset_counters": (C.c_int, [C.c_void_p]),
+    "tpt_get_stage_times": (C.c_int, [C.c_void_p, C.POINTER(StageTimes)]),
     "tpt_scene_create": (C.c_int, [C.c_void_p, C.POINTER(SceneDesc), C.POINTER(C.c_void_p)]),
     "tpt_scene_destroy": (C.c_int, [C.c_void_p]),
     "tpt_scene_set_transforms": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),

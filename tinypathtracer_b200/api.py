@@ -13,6 +13,7 @@ Everything here is argument marshalling; all compute is in libtpt_b200.so.
 from __future__ import annotations
 
 import ctypes as C
+import weakref
 
 import numpy as np
 
@@ -39,9 +40,12 @@ class Context:
         check(lib.tpt_context_create(device, C.byref(h)))
         self._h = h
         self.device = device
+        self._children = weakref.WeakSet()   # scenes / accumulators must be destroyed before their context
 
     def close(self):
         if self._h:
+            for child in list(self._children):
+                child.close()
             lib.tpt_context_destroy(self._h)
             self._h = None
 
@@ -61,6 +65,12 @@ class Context:
         c = capi.Counters()
         check(lib.tpt_get_counters(self._h, C.byref(c)))
         return {n: int(getattr(c, n)) for n, _ in capi.Counters._fields_}
+
+    def stage_times(self) -> dict:
+        st = capi.StageTimes()
+        check(lib.tpt_get_stage_times(self._h, C.byref(st)))
+        names = ("generate", "extend", "shade", "connect")
+        return {n: {"ms": float(st.ms[i]), "launches": int(st.launches[i])} for i, n in enumerate(names)}
 
     def reset_counters(self):
         check(lib.tpt_reset_counters(self._h))
@@ -123,6 +133,7 @@ class DeviceScene:
         h = C.c_void_p()
         check(lib.tpt_scene_create(ctx._h, C.byref(d), C.byref(h)))
         self._h = h
+        ctx._children.add(self)
         self.n_faces = keep["indices"].size // 3
         self.n_vertices = keep["vertices"].shape[0]
         self.n_objects = keep["objects"].shape[0]
@@ -207,6 +218,7 @@ class Accum:
             check(lib.tpt_accum_wrap(ctx._h, C.c_void_p(device_ptr), width, height, C.byref(h)))
         self._h = h
         self.ctx = ctx
+        ctx._children.add(self)
         self.width, self.height = width, height
 
     def close(self):
@@ -250,12 +262,13 @@ class Accum:
         return fb
 
 
-def render_config(width, height, spp, max_depth=8, seed=1, sample_offset=0, sample_stride=1, counters=False, paths_in_flight=0):
+def render_config(width, height, spp, max_depth=8, seed=1, sample_offset=0, sample_stride=1, counters=False, paths_in_flight=0,
+                  stage_times=False):
     c = capi.RenderConfig()
     c.width, c.height, c.spp, c.max_depth = width, height, spp, max_depth
     c.seed = seed
     c.sample_offset, c.sample_stride = sample_offset, sample_stride
-    c.flags = capi.TPT_RENDER_COUNTERS if counters else 0
+    c.flags = (capi.TPT_RENDER_COUNTERS if counters else 0) | (capi.TPT_RENDER_STAGE_TIMES if stage_times else 0)
     c.paths_in_flight = paths_in_flight
     return c
 
@@ -271,8 +284,10 @@ class PathTracer:
         self.m_radiance = Accum(ctx, width, height)
 
     def render_into(self, scene: DeviceScene, camera: Camera, spp: int, max_depth: int = 8, seed: int = 1, sample_offset: int = 0,
-                    sample_stride: int = 1, counters: bool = False, paths_in_flight: int = 0, accum: Accum | None = None):
-        cfg = render_config(self.m_width, self.m_height, spp, max_depth, seed, sample_offset, sample_stride, counters, paths_in_flight)
+                    sample_stride: int = 1, counters: bool = False, paths_in_flight: int = 0, accum: Accum | None = None,
+                    stage_times: bool = False):
+        cfg = render_config(self.m_width, self.m_height, spp, max_depth, seed, sample_offset, sample_stride, counters, paths_in_flight,
+                            stage_times)
         acc = accum or self.m_radiance
         check(lib.tpt_render(scene._h, C.byref(camera.c), C.byref(cfg), acc._h))
 

@@ -76,8 +76,8 @@ __global__ void __launch_bounds__(256) k_transform(const float* __restrict__ obj
         if (o == 0xffffffffu) continue;   // not referenced by any face: the reference never writes it either
         const float3 p = f3(objVerts[3 * v], objVerts[3 * v + 1], objVerts[3 * v + 2]);
         const float3 n = f3(objNorms[3 * v], objNorms[3 * v + 1], objNorms[3 * v + 2]);
-        const float3 wp = mat4_point(vertTrans + 16 * (size_t)o, p);
-        const float3 wn = ref_normalize(mat4_dir(normalTrans + 16 * (size_t)o, n));
+        const float3 wp = xmat4_point(vertTrans + 16 * (size_t)o, p);
+        const float3 wn = xnormalize(xmat4_dir(normalTrans + 16 * (size_t)o, n));
         worldVerts[3 * v] = wp.x; worldVerts[3 * v + 1] = wp.y; worldVerts[3 * v + 2] = wp.z;
         worldNorms[3 * v] = wn.x; worldNorms[3 * v + 1] = wn.y; worldNorms[3 * v + 2] = wn.z;
         mn = fmin3(mn, wp);
@@ -188,7 +188,7 @@ __global__ void __launch_bounds__(256) k_leaves_refit(const uint32_t* __restrict
     const float3 a = f3(worldVerts[3 * i0], worldVerts[3 * i0 + 1], worldVerts[3 * i0 + 2]);
     const float3 b = f3(worldVerts[3 * i1], worldVerts[3 * i1 + 1], worldVerts[3 * i1 + 2]);
     const float3 c = f3(worldVerts[3 * i2], worldVerts[3 * i2 + 1], worldVerts[3 * i2 + 2]);
-    const float3 e1 = b - a, e2 = c - a;   // exactly the edges Möller–Trumbore forms per test in the reference
+    const float3 e1 = xsub3(b, a), e2 = xsub3(c, a);   // exactly the edges Möller–Trumbore forms per test in the reference
     triGeom[3 * (size_t)leaf + 0] = make_float4(a.x, a.y, a.z, e1.x);
     triGeom[3 * (size_t)leaf + 1] = make_float4(e1.y, e1.z, e2.x, e2.y);
     triGeom[3 * (size_t)leaf + 2] = make_float4(e2.z, __int_as_float((int)f), __int_as_float((int)faceMtl[f]), 0.f);

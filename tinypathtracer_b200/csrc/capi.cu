@@ -117,6 +117,7 @@ int tpt_context_destroy(tpt_context* ctx) {
     cudaFree(ctx->queue_counts);
     cudaFree(ctx->io_rays);
     cudaFree(ctx->io_hits);
+    for (cudaEvent_t e : ctx->stage_events) cudaEventDestroy(e);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
     if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -165,6 +166,19 @@ int tpt_reset_counters(tpt_context* ctx) {
     TPT_CUDA(cudaMemsetAsync(ctx->d_counters, 0, sizeof(DeviceCounters), ctx->stream));
     ctx->samples = 0;
     ctx->kernel_launches = 0;
+    for (int k = 0; k < 4; ++k) {
+        ctx->stage_ms[k] = 0.0;
+        ctx->stage_launches[k] = 0;
+    }
+    return TPT_OK;
+}
+
+int tpt_get_stage_times(tpt_context* ctx, tpt_stage_times* out) {
+    TPT_REQUIRE(ctx && out, "tpt_get_stage_times: NULL argument");
+    for (int k = 0; k < 4; ++k) {
+        out->ms[k] = ctx->stage_ms[k];
+        out->launches[k] = ctx->stage_launches[k];
+    }
     return TPT_OK;
 }
 

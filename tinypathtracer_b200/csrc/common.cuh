@@ -77,6 +77,48 @@ __host__ __device__ __forceinline__ float ref_frsqrt(float num) {
 }
 __host__ __device__ __forceinline__ float3 ref_normalize(float3 v) { return v * ref_frsqrt(dot(v, v)); }
 
+// ------------------------------------------------------------------------------------------------
+// Exactly-rounded arithmetic for the geometric core.  The quantities the parity bars are stated on
+// (world vertices, primary rays, hit distance t, barycentrics, primitive id) are computed with one
+// IEEE rounding per operation in the reference's operand order — no FMA contraction — so that they
+// are BIT-IDENTICAL to the reference source evaluated op by op (which is what the CPU oracle and a
+// host compile of the reference's CUDA_CALLABLE code produce).  __fmul_rn/__fadd_rn are never fused
+// by nvcc.  Shading arithmetic (BSDF, lights, throughput) is left to the compiler: it is only
+// compared statistically.
+// ------------------------------------------------------------------------------------------------
+#ifdef __CUDACC__
+__device__ __forceinline__ float xmul(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float xadd(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float xsub(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float3 xsub3(float3 a, float3 b) { return f3(xsub(a.x, b.x), xsub(a.y, b.y), xsub(a.z, b.z)); }
+__device__ __forceinline__ float xdot(float3 a, float3 b) {   // vec.h:151, left-associated
+    return xadd(xadd(xmul(a.x, b.x), xmul(a.y, b.y)), xmul(a.z, b.z));
+}
+__device__ __forceinline__ float3 xcross(float3 a, float3 b) {   // vec.h:152
+    return f3(xsub(xmul(a.y, b.z), xmul(a.z, b.y)), xsub(xmul(a.z, b.x), xmul(a.x, b.z)), xsub(xmul(a.x, b.y), xmul(a.y, b.x)));
+}
+__device__ __forceinline__ float xfrsqrt(float num) {   // vec.h:25-38
+    const float x2 = xmul(num, 0.5f);
+    float y = __int_as_float(0x5f3759df - (__float_as_int(num) >> 1));
+    return xmul(y, xsub(1.5f, xmul(xmul(x2, y), y)));
+}
+__device__ __forceinline__ float3 xnormalize(float3 v) {   // vec.h:155: v * frsqrt(norm2)
+    const float s = xfrsqrt(xdot(v, v));
+    return f3(xmul(v.x, s), xmul(v.y, s), xmul(v.z, s));
+}
+// MatrixVectorMultiply (mat.h:37-51): res[i] = (((0 + m[0][i]*v0) + m[1][i]*v1) + m[2][i]*v2) + m[3][i]*v3
+__device__ __forceinline__ float3 xmat4_point(const float* m, float3 p) {
+    return f3(xadd(xadd(xadd(xmul(m[0], p.x), xmul(m[4], p.y)), xmul(m[8], p.z)), m[12]),
+              xadd(xadd(xadd(xmul(m[1], p.x), xmul(m[5], p.y)), xmul(m[9], p.z)), m[13]),
+              xadd(xadd(xadd(xmul(m[2], p.x), xmul(m[6], p.y)), xmul(m[10], p.z)), m[14]));
+}
+__device__ __forceinline__ float3 xmat4_dir(const float* m, float3 d) {   // w = 0: the last term adds +-0
+    return f3(xadd(xadd(xadd(xmul(m[0], d.x), xmul(m[4], d.y)), xmul(m[8], d.z)), xmul(m[12], 0.0f)),
+              xadd(xadd(xadd(xmul(m[1], d.x), xmul(m[5], d.y)), xmul(m[9], d.z)), xmul(m[13], 0.0f)),
+              xadd(xadd(xadd(xmul(m[2], d.x), xmul(m[6], d.y)), xmul(m[10], d.z)), xmul(m[14], 0.0f)));
+}
+#endif
+
 // column-major Mat4 (reference include/math/mat.h:37-51)
 __host__ __device__ __forceinline__ float3 mat4_point(const float* m, float3 p) {
     return f3(m[0] * p.x + m[4] * p.y + m[8] * p.z + m[12], m[1] * p.x + m[5] * p.y + m[9] * p.z + m[13],

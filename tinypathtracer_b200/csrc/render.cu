@@ -73,13 +73,14 @@ struct CameraParams {
     float invW, invH;
 };
 __device__ __forceinline__ void primary_ray(const CameraParams& cam, int px, int py, float ju, float jv, float3& o, float3& d) {
-    float plx = (ju + (float)px) * cam.invW;
-    float ply = (jv + (float)py) * cam.invH;
-    plx *= cam.sensorW;
-    ply *= cam.sensorH;
-    const float3 dir = f3(plx - 0.5f * cam.sensorW, ply - 0.5f * cam.sensorH, -1.0f);
-    d = ref_normalize(mat4_dir(cam.c2w, dir));
-    o = f3(cam.c2w[12], cam.c2w[13], cam.c2w[14]);
+    // one rounding per operation, in the reference's order (bit-identical primary rays)
+    float plx = xmul(xadd(ju, (float)px), cam.invW);
+    float ply = xmul(xadd(jv, (float)py), cam.invH);
+    plx = xmul(plx, cam.sensorW);
+    ply = xmul(ply, cam.sensorH);
+    const float3 dir = f3(xsub(plx, xmul(0.5f, cam.sensorW)), xsub(ply, xmul(0.5f, cam.sensorH)), -1.0f);
+    d = xnormalize(xmat4_dir(cam.c2w, dir));
+    o = xmat4_point(cam.c2w, f3(0.f, 0.f, 0.f));
 }
 
 __global__ void __launch_bounds__(256) k_primary_rays(CameraParams cam, int W, int H, int jitter, uint64_t seedKey, tpt_ray* __restrict__ rays) {
@@ -286,9 +287,12 @@ __global__ void __launch_bounds__(256) k_shade(BvhView bvh, ShadeParams sp, cons
                 } else {
                     const float4 na = __ldg(bvh.tri_norm + 3 * (size_t)leaf), nb = __ldg(bvh.tri_norm + 3 * (size_t)leaf + 1),
                                  nc = __ldg(bvh.tri_norm + 3 * (size_t)leaf + 2);
-                    const float u = h.y, v = h.z, w = 1.0f - u - v;
-                    nrm = ref_normalize(w * f3(na.x, na.y, na.z) + u * f3(na.w, nb.x, nb.y) + v * f3(nb.z, nb.w, nc.x));
-                    P = p.o + h.x * p.d;
+                    const float u = h.y, v = h.z, w = xsub(xsub(1.0f, u), v);
+                    const float3 n0 = f3(na.x, na.y, na.z), n1 = f3(na.w, nb.x, nb.y), n2 = f3(nb.z, nb.w, nc.x);
+                    nrm = xnormalize(f3(xadd(xadd(xmul(w, n0.x), xmul(u, n1.x)), xmul(v, n2.x)),
+                                        xadd(xadd(xmul(w, n0.y), xmul(u, n1.y)), xmul(v, n2.y)),
+                                        xadd(xadd(xmul(w, n0.z), xmul(u, n1.z)), xmul(v, n2.z))));
+                    P = f3(xadd(p.o.x, xmul(h.x, p.d.x)), xadd(p.o.y, xmul(h.x, p.d.y)), xadd(p.o.z, xmul(h.x, p.d.z)));
                     base3 = f3(m0.x, m0.y, m0.z);
                     eta = m1.x;
                     metallic = m1.y;
@@ -483,6 +487,17 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
     const CameraParams cp = make_camera(cam, W, H);
     const uint64_t seedKey = rng_seed_key(cfg->seed);
     const bool counted = (cfg->flags & TPT_RENDER_COUNTERS) != 0;
+    const bool timed = (cfg->flags & TPT_RENDER_STAGE_TIMES) != 0;
+    const size_t nEvents = 2 + 3 * (size_t)cfg->max_depth;
+    if (timed) {
+        while (ctx->stage_events.size() < nEvents) {
+            cudaEvent_t e;
+            TPT_CUDA(cudaEventCreate(&e));
+            ctx->stage_events.push_back(e);
+        }
+    }
+    size_t ev = 0;
+    auto mark = [&]() { if (timed) cudaEventRecord(ctx->stage_events[ev++], st); };
     const BvhView view = s->view();
     uint32_t* counts = ctx->queue_counts;
     const unsigned gridGen = kNumSMs * 8, gridTrace = kNumSMs * 16, gridShade = kNumSMs * 8;
@@ -500,9 +515,12 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
     for (uint32_t done = 0; done < (uint32_t)cfg->spp; done += k) {
         const uint32_t kk = ((uint32_t)cfg->spp - done) < k ? ((uint32_t)cfg->spp - done) : k;
         TPT_CUDA(cudaMemsetAsync(counts, 0, 4 * sizeof(uint32_t), st));
+        ev = 0;
+        mark();
         k_generate<<<gridGen, 256, 0, st>>>(cp, W, H, nPadded, kk, (uint32_t)cfg->sample_offset + done * (uint32_t)cfg->sample_stride,
                                             (uint32_t)cfg->sample_stride, seedKey, ctx->path_state[0], counts);
         ctx->kernel_launches += 1;
+        mark();
         for (int depth = 0; depth < cfg->max_depth; ++depth) {
             const int cur = depth & 1, nxt = cur ^ 1;
             sp.depth = depth;
@@ -512,13 +530,26 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
             else
                 k_extend<false><<<gridTrace, 128, 0, st>>>(view, ctx->path_state[cur], counts + cur, counts + nxt, counts + 2, ctx->hits,
                                                            ctx->d_counters, depth);
+            mark();
             k_shade<<<gridShade, 256, 0, st>>>(view, sp, ctx->path_state[cur], ctx->hits, counts + cur, ctx->path_state[nxt], counts + nxt,
                                                ctx->sec_rays, counts + 2, acc->data, ctx->d_counters);
+            mark();
             if (counted) k_connect<true><<<gridTrace, 128, 0, st>>>(view, s->mtl_table, ctx->sec_rays, counts + 2, acc->data, ctx->d_counters);
             else k_connect<false><<<gridTrace, 128, 0, st>>>(view, s->mtl_table, ctx->sec_rays, counts + 2, acc->data, ctx->d_counters);
+            mark();
             ctx->kernel_launches += 3;
         }
         TPT_CUDA(cudaGetLastError());
+        if (timed) {
+            TPT_CUDA(cudaEventSynchronize(ctx->stage_events[ev - 1]));
+            for (size_t k = 1; k < ev; ++k) {
+                float ms = 0.f;
+                TPT_CUDA(cudaEventElapsedTime(&ms, ctx->stage_events[k - 1], ctx->stage_events[k]));
+                const int stage = k == 1 ? 0 : 1 + (int)((k - 2) % 3);
+                ctx->stage_ms[stage] += ms;
+                ctx->stage_launches[stage] += 1;
+            }
+        }
     }
     ctx->samples += (uint64_t)W * H * (uint64_t)cfg->spp;
     return TPT_OK;

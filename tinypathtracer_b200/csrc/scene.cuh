@@ -16,6 +16,8 @@
 //   lights       tpt_delta_light[L]
 // Every traversal read is a 128-bit load at a 16-B aligned address.
 #pragma once
+#include <vector>
+
 #include "common.cuh"
 
 namespace tpt {
@@ -59,6 +61,10 @@ struct tpt_context {
     void* io_hits = nullptr;
     size_t io_capacity = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // per-stage timing (TPT_RENDER_STAGE_TIMES)
+    std::vector<cudaEvent_t> stage_events;
+    double stage_ms[4] = {0, 0, 0, 0};
+    uint64_t stage_launches[4] = {0, 0, 0, 0};
 };
 
 struct tpt_scene {

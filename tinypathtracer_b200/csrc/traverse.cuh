@@ -86,16 +86,17 @@ __device__ __forceinline__ HitRec traverse(const BvhView& bvh, float3 o, float3 
             const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
             if (COUNT) ++nt;
             const float3 v0 = f3(a.x, a.y, a.z), e1 = f3(a.w, b.x, b.y), e2 = f3(b.z, b.w, c.x);
-            const float3 tv = o - v0;
-            const float3 p = cross(d, e2);
-            const float3 q = cross(tv, e1);
-            const float denom = dot(p, e1);
+            // Möller–Trumbore exactly as geometry_queries.h:66-86 evaluates it, one rounding per operation
+            const float3 tv = xsub3(o, v0);
+            const float3 p = xcross(d, e2);
+            const float3 q = xcross(tv, e1);
+            const float denom = xdot(p, e1);
             if (denom != 0.0f) {
-                const float invDenom = 1.0f / denom;
-                const float u = dot(p, tv) * invDenom;
-                const float v = dot(q, d) * invDenom;
-                if (!(u < 0.0f || v < 0.0f || u + v > 1.0f)) {
-                    const float t = dot(q, e2) * invDenom;
+                const float invDenom = __fdiv_rn(1.0f, denom);
+                const float u = xmul(xdot(p, tv), invDenom);
+                const float v = xmul(xdot(q, d), invDenom);
+                if (!(u < 0.0f || v < 0.0f || xadd(u, v) > 1.0f)) {
+                    const float t = xmul(xdot(q, e2), invDenom);
                     const int prim = __float_as_int(c.y);
                     if (t > kDelta && (t < best.t || (t == best.t && prim < best.prim))) {
                         best.t = t;
