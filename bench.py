@@ -332,10 +332,13 @@ def run_reference(args):
 
 def run_reference_cuda(args, exe, ref_scene, W, H, spp, depth, envkind, cfg):
     """Runs the headless build of the reference's own CUDA sources; it prints one JSON object with frame times."""
-    env_png = ROOT / "oracle" / "_ref" / "sky.png"
+    # the reference cannot run without an env texture (uninitialised handle, SURVEY §3.3): black env = a black PNG
+    env_png = ROOT / "oracle" / "_ref" / ("sky.png" if envkind == "sky" else "black.png")
+    if depth == 32:
+        exe = exe.with_name("tpt_ref_headless_d32")     # DEPTH_TRACE is a compile-time constant of the reference
     cmd = [str(exe), "--scene", str(ref_scene), "--width", str(W), "--height", str(H), "--spp", str(spp), "--depth", str(depth),
            "--frames", str(args.steps), "--warmup", str(args.warmup)]
-    if envkind == "sky" and env_png.exists():
+    if env_png.exists():
         cmd += ["--env", str(env_png)]
     try:
         r = subprocess.run(cmd, capture_output=True, text=True, timeout=args.ref_timeout)
