@@ -223,14 +223,12 @@ def run_ours(args):
                        paths_in_flight=args.paths_in_flight)
         c2 = ctx.counters()
         ctx.synchronize()
-        n_ext = c1["rays_primary"] + c1["rays_extension"]
-        n_sec = c1["rays_shadow"] + c1["rays_direct"]
-        n_all = n_ext + n_sec
+        n_all = c1["rays_primary"] + c1["rays_extension"] + c1["rays_shadow"] + c1["rays_direct"]
         n_int = c2["node_visits"] / max(n_all, 1)
         n_leaf = c2["tri_tests"] / max(n_all, 1)
         bytes_per_ray = 56.0 * n_int + 40.0 * n_leaf + 88.0          # SURVEY §8(d) algorithmic bytes per ray
-        trav_ms = st["extend"]["ms"] + st["connect"]["ms"]
-        trav_launches = st["extend"]["launches"] + st["connect"]["launches"]
+        trav_ms = st["primary"]["ms"] + st["wave"]["ms"]            # every ray is traced inside these two kernels
+        trav_launches = st["primary"]["launches"] + st["wave"]["launches"]
         peaks = {}
         try:
             peaks = json.loads((ROOT / "MEASURED_PEAKS.json").read_text())
@@ -238,15 +236,15 @@ def run_ours(args):
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
         achieved = bytes_per_ray * n_all / (trav_ms * 1e-3) / 1e9 if trav_ms > 0 else 0.0
-        stage_total = sum(v["ms"] for v in st.values())
-        roofline = {"bound": "hbm", "kernel": "k_extend+k_connect (BVH traversal)", "achieved": round(achieved, 2), "peak": peak,
+        roofline = {"bound": "hbm", "kernel": "k_primary+k_wave (BVH traversal fused with shading)", "achieved": round(achieved, 2), "peak": peak,
                     "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback (B200_PROFILING.md)", "unit": "GB/s",
                     "frac": round(achieved / peak, 5), "traffic": None,
                     "bytes_per_ray": round(bytes_per_ray, 1), "n_int_per_ray": round(n_int, 2), "n_leaf_per_ray": round(n_leaf, 2),
                     "rays_per_launch": round(n_all / max(trav_launches, 1), 1),
                     "avg_launch_us": round(1e3 * trav_ms / max(trav_launches, 1), 2),
-                    "share_of_step": round(trav_ms / stage_total, 4) if stage_total > 0 else None,
+                    "share_of_step": round(min(1.0, trav_ms * (per_slice * len(slices) / prof_spp) / ms_step), 4),
                     "stage_ms": {k: round(v["ms"], 3) for k, v in st.items()},
+                    "rays": {k: c1[k] for k in ("rays_primary", "rays_extension", "rays_shadow", "rays_direct")},
                     "note": "BVH of this workload is L1/L2-resident; node fetches never reach HBM, the HBM fraction is an upper-bound accounting (SURVEY §8d)"}
         cpu = cpu_baseline(args, fixture, W, H, depth, env, seed) if world == 1 and not args.no_cpu_baseline else None
         line = {

@@ -144,7 +144,8 @@ typedef struct tpt_counters {
 /* Device time per wavefront stage since the last tpt_reset_counters, measured with CUDA events on the
  * context stream around every launch (only renders with TPT_RENDER_STAGE_TIMES contribute). */
 typedef struct tpt_stage_times {
-    double ms[4];        /* 0 generate, 1 extend (closest hit), 2 shade, 3 connect (shadow + direct rays) */
+    double ms[4];        /* 0 k_primary (generate + closest hit + shade of the camera vertex), 1 k_wave (all later waves:
+                          * extension + shadow + direct rays, shading), 2-3 reserved */
     uint64_t launches[4];
 } tpt_stage_times;
 

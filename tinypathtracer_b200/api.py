@@ -69,7 +69,7 @@ class Context:
     def stage_times(self) -> dict:
         st = capi.StageTimes()
         check(lib.tpt_get_stage_times(self._h, C.byref(st)))
-        names = ("generate", "extend", "shade", "connect")
+        names = ("primary", "wave")
         return {n: {"ms": float(st.ms[i]), "launches": int(st.launches[i])} for i, n in enumerate(names)}
 
     def reset_counters(self):

@@ -92,7 +92,6 @@ int tpt_context_create(int device, tpt_context** out) {
     cudaError_t e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaMalloc(&ctx->d_counters, sizeof(DeviceCounters));
     if (e == cudaSuccess) e = cudaMemset(ctx->d_counters, 0, sizeof(DeviceCounters));
-    if (e == cudaSuccess) e = cudaMalloc(&ctx->queue_counts, 4 * sizeof(uint32_t));
     if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev0);
     if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev1);
     if (e != cudaSuccess) {
@@ -110,11 +109,11 @@ int tpt_context_destroy(tpt_context* ctx) {
     cudaStreamSynchronize(ctx->stream);
     cudaFree(ctx->env);
     cudaFree(ctx->d_counters);
-    cudaFree(ctx->path_state[0]);
-    cudaFree(ctx->path_state[1]);
-    cudaFree(ctx->hits);
-    cudaFree(ctx->sec_rays);
-    cudaFree(ctx->queue_counts);
+    cudaFree(ctx->q_ext[0]);
+    cudaFree(ctx->q_ext[1]);
+    cudaFree(ctx->q_sec[0]);
+    cudaFree(ctx->q_sec[1]);
+    cudaFree(ctx->levels);
     cudaFree(ctx->io_rays);
     cudaFree(ctx->io_hits);
     for (cudaEvent_t e : ctx->stage_events) cudaEventDestroy(e);
@@ -151,7 +150,7 @@ int tpt_get_counters(tpt_context* ctx, tpt_counters* out) {
     out->rays_primary = h.rays_primary;
     out->rays_extension = h.rays_extension;
     out->rays_direct = h.rays_direct;
-    out->rays_shadow = h.rays_shadow - h.rays_direct;   // the connect kernel counts the whole secondary queue
+    out->rays_shadow = h.rays_shadow;
     out->node_visits = h.node_visits;
     out->tri_tests = h.tri_tests;
     out->samples = ctx->samples;

@@ -1,8 +1,19 @@
-// render.cu — wavefront path tracer for sm_100a (generate / extend / shade / connect queues).
+// render.cu — wavefront path tracer for sm_100a.
 //
 // Replaces the `trace` megakernel of the reference (src/path_tracer.cu:296-435), its ray generator
 // sampleRays (:42-59), BSDF sampling getNewDirection (:187-225), delta-light NEE sampleDeltaLights
 // (:265-286), env lookup sampleEnvLights (:288-294) and copyToFB (:451-471).
+//
+// Kernels per batch (= all pixels x k samples):
+//   k_primary   wave 0: generate + closest hit + shade of the camera vertex, fused.  Primary rays are
+//               coherent (a warp = an 8x4 pixel tile), so nothing is gained by queueing them; paths
+//               that miss or hit an emitter end in registers (per-thread int64 sums, one atomic per
+//               pixel and batch) and never touch a queue.
+//   k_wave      wave w >= 1: one persistent launch consumes the two queues the previous wave filled —
+//               extension rays towards vertex w (closest hit -> shade -> emit) and the secondary rays
+//               of vertex w-1 (shadow rays: any hit; the reference's extra cosine "direct" rays:
+//               closest hit -> emission) — 32-item chunks handed to warps by an atomic cursor,
+//               output compacted by warp-aggregated append.
 //
 // Estimator.  The reference unwinds  radiance = (direct[d] + radiance) * atten[d] / p[d]  backwards
 // over a per-thread stack.  With T_d = prod_{k<=d} atten_k / p_k this is, forwards,
@@ -11,8 +22,8 @@
 // direct_d = sum_lights visible * baseColor * Li  (+ emission of whatever the extra cosine "direct"
 // ray hits, diffuse vertices only), and L_end is env(dir) on a miss, the grey emission when the
 // vertex is emissive (which also discards that vertex's own direct term, :421-424), or 0 at the depth
-// cut.  Every term is added to the pixel as soon as it is known, as an exact fixed-point integer, so
-// the result does not depend on the order in which kernels, warps or GPUs finish.
+// cut.  Every term is added to the pixel as an exact fixed-point integer, so the result does not
+// depend on the order in which kernels, warps or GPUs finish, nor on how terms are grouped.
 #include "traverse.cuh"
 
 namespace tpt {
@@ -42,17 +53,52 @@ __device__ __forceinline__ void store_path(float4* __restrict__ p, uint32_t i, f
 }
 
 // ---- accumulation: 3 x int64 fixed point per pixel ----------------------------------------------
+// One contribution channel -> fixed point: min(c, 2^26) * 2^36, round to nearest.  Integer sums are
+// exact, so summing in registers first and adding once gives the same bits as one atomic per term.
+__device__ __forceinline__ long long to_fixed(float c) {
+    const float scale = 68719476736.0f;   // 2^36
+    const float cap = 67108864.0f;        // 2^26 per contribution keeps int64 far from overflow
+    return __float2ll_rn(fminf(c, cap) * scale);
+}
+__device__ __forceinline__ bool finite3(float3 c) { return isfinite(c.x) && isfinite(c.y) && isfinite(c.z); }
 __device__ __forceinline__ void accum_add(unsigned long long* __restrict__ acc, uint32_t pixel, float3 c, DeviceCounters* ctr) {
-    if (!(isfinite(c.x) && isfinite(c.y) && isfinite(c.z))) {
+    if (!finite3(c)) {
         atomicAdd(&ctr->dropped_nonfinite, 1ull);
         return;
     }
-    const float scale = 68719476736.0f;   // 2^36
-    const float cap = 67108864.0f;        // 2^26 per contribution keeps int64 far from overflow
     unsigned long long* p = acc + 3 * (size_t)pixel;
-    if (c.x != 0.f) atomicAdd(p + 0, (unsigned long long)__float2ll_rn(fminf(c.x, cap) * scale));
-    if (c.y != 0.f) atomicAdd(p + 1, (unsigned long long)__float2ll_rn(fminf(c.y, cap) * scale));
-    if (c.z != 0.f) atomicAdd(p + 2, (unsigned long long)__float2ll_rn(fminf(c.z, cap) * scale));
+    if (c.x != 0.f) atomicAdd(p + 0, (unsigned long long)to_fixed(c.x));
+    if (c.y != 0.f) atomicAdd(p + 1, (unsigned long long)to_fixed(c.y));
+    if (c.z != 0.f) atomicAdd(p + 2, (unsigned long long)to_fixed(c.z));
+}
+
+// ---- queues -----------------------------------------------------------------------------------------
+// Level w describes what wave w consumes: {nExt, cursor, nSec | nDirect << 32}.  Items are 3 float4
+// (PathRec above); secondary items carry the contribution weight in T and their kind in s2.w.
+struct QueueLevel {
+    uint32_t n_ext;                  // extension rays towards vertex w
+    uint32_t cursor;                 // next 32-item chunk to hand out (k_wave)
+    unsigned long long n_sec;        // low 32 bits: secondary rays of vertex w-1; high 32 bits: how many are "direct" rays
+};
+constexpr uint32_t kKindShadow = 0u, kKindDirect = 1u;
+
+// Append from a possibly diverged warp: the lanes that are here together share one atomic.
+__device__ __forceinline__ uint32_t append_ext(QueueLevel* q) {
+    const unsigned m = __activemask();
+    const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(&q->n_ext, (uint32_t)__popc(m));
+    base = __shfl_sync(m, base, leader);
+    return base + __popc(m & ((1u << lane) - 1u));
+}
+__device__ __forceinline__ uint32_t append_sec(QueueLevel* q, bool direct) {
+    const unsigned m = __activemask();
+    const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+    const unsigned long long n = (unsigned long long)__popc(m);
+    uint32_t base = 0;
+    if (lane == leader) base = (uint32_t)atomicAdd(&q->n_sec, direct ? (n | (n << 32)) : n);
+    base = __shfl_sync(m, base, leader);
+    return base + __popc(m & ((1u << lane) - 1u));
 }
 
 // ---- pixel enumeration: 8x4 tiles so that a warp's primary rays are coherent ---------------------
@@ -106,55 +152,8 @@ __global__ void __launch_bounds__(128) k_trace_rays(BvhView bvh, const tpt_ray* 
         const float* r = reinterpret_cast<const float*>(rays + i);
         const float2 a = __ldg(reinterpret_cast<const float2*>(r)), b = __ldg(reinterpret_cast<const float2*>(r) + 1),
                      c = __ldg(reinterpret_cast<const float2*>(r) + 2);
-        const HitRec h = traverse<ANY, COUNT>(bvh, f3(a.x, a.y, b.x), f3(b.y, c.x, c.y), &ctr->node_visits, &ctr->tri_tests);
+        const HitRec h = traverse<COUNT>(bvh, f3(a.x, a.y, b.x), f3(b.y, c.x, c.y), ANY, &ctr->node_visits, &ctr->tri_tests);
         reinterpret_cast<float4*>(hits)[i] = make_float4(__int_as_float(h.prim), h.t, h.u, h.v);
-    }
-}
-
-// ---- generate ------------------------------------------------------------------------------------
-// Batch = all pixels x `k` consecutive samples.  Slot i -> (tile-ordered pixel, local sample).
-__global__ void __launch_bounds__(256) k_generate(CameraParams cam, int W, int H, uint32_t nPadded, uint32_t kSamples, uint32_t sampleBase,
-                                                  uint32_t sampleStride, uint64_t seedKey, float4* __restrict__ paths,
-                                                  uint32_t* __restrict__ counts) {
-    const uint32_t total = nPadded * kSamples;
-    for (uint32_t base = blockIdx.x * blockDim.x; base < total; base += gridDim.x * blockDim.x) {
-        const uint32_t i = base + threadIdx.x;
-        bool valid = i < total;
-        int px = 0, py = 0;
-        uint32_t sIdx = 0;
-        if (valid) {
-            const uint32_t sLocal = i / nPadded, p = i - sLocal * nPadded;
-            valid = tile_decode(p, W, H, px, py);
-            sIdx = sampleBase + sLocal * sampleStride;
-        }
-        const uint32_t slot = warp_append(valid, counts + 0);
-        if (valid) {
-            const uint32_t pixel = (uint32_t)(px + py * W);
-            float ju, jv;
-            rng_pair(rng_path_key(seedKey, pixel, sIdx), 0u, ju, jv);
-            float3 o, d;
-            primary_ray(cam, px, py, ju, jv, o, d);
-            store_path(paths, slot, o, d, f3(1.f, 1.f, 1.f), pixel, sIdx, 0u);
-        }
-    }
-}
-
-// ---- extend: closest hit for every live path --------------------------------------------------------
-template <bool COUNT>
-__global__ void __launch_bounds__(128) k_extend(BvhView bvh, const float4* __restrict__ paths, const uint32_t* __restrict__ countIn,
-                                                uint32_t* __restrict__ countNext, uint32_t* __restrict__ countSec, float4* __restrict__ hits,
-                                                DeviceCounters* ctr, int depth) {
-    const uint32_t n = *countIn;
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
-        // The shade kernel of this bounce appends to these; nothing reads them before it runs.
-        *countNext = 0u;
-        *countSec = 0u;
-        atomicAdd(depth == 0 ? &ctr->rays_primary : &ctr->rays_extension, (unsigned long long)n);
-    }
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const float4 a = __ldg(paths + 3 * (size_t)i), b = __ldg(paths + 3 * (size_t)i + 1);
-        const HitRec h = traverse<false, COUNT>(bvh, f3(a.x, a.y, a.z), f3(a.w, b.x, b.y), &ctr->node_visits, &ctr->tri_tests);
-        __stcs(hits + i, make_float4(h.t, h.u, h.v, __int_as_float(h.leaf)));
     }
 }
 
@@ -256,121 +255,181 @@ struct ShadeParams {
     uint64_t seedKey;
 };
 
-// ---- shade: material evaluation, NEE ray emission, path continuation ------------------------------
-__global__ void __launch_bounds__(256) k_shade(BvhView bvh, ShadeParams sp, const float4* __restrict__ pathsIn, const float4* __restrict__ hits,
-                                               const uint32_t* __restrict__ countIn, float4* __restrict__ pathsOut, uint32_t* __restrict__ countNext,
-                                               float4* __restrict__ sec, uint32_t* __restrict__ countSec, unsigned long long* __restrict__ acc,
-                                               DeviceCounters* ctr) {
-    const uint32_t n = *countIn;
-    // every lane of a warp must reach the warp_append calls: iterate whole warps
-    for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x) {
-        const uint32_t i = base + threadIdx.x;
-        const bool live = i < n;
-        bool wantNext = false, wantDirect = false;
-        int nShadow = 0;
-        PathRec p{};
-        float3 P = f3(0, 0, 0), nrm = f3(0, 0, 0), base3 = f3(0, 0, 0), Tn = f3(0, 0, 0);
-        float eta = 0.f, metallic = 0.f;
-        uint64_t key = 0;
-        if (live) {
-            p = load_path(pathsIn, i);
-            const float4 h = __ldcs(hits + i);
-            const int leaf = __float_as_int(h.w);
-            if (leaf < 0) {
-                accum_add(acc, p.pixel, p.T * env_lookup(sp.env, sp.envW, sp.envH, p.d), ctr);
-            } else {
-                const float4 g2 = __ldg(bvh.tri_geom + 3 * (size_t)leaf + 2);
-                const int mtlIdx = __float_as_int(g2.z);
-                const float4 m0 = __ldg(sp.mtl + 2 * mtlIdx), m1 = __ldg(sp.mtl + 2 * mtlIdx + 1);
-                if (m0.w > 0.0f) {
-                    accum_add(acc, p.pixel, p.T * m0.w, ctr);   // emissive vertex: terminal, grey emission
-                } else {
-                    const float4 na = __ldg(bvh.tri_norm + 3 * (size_t)leaf), nb = __ldg(bvh.tri_norm + 3 * (size_t)leaf + 1),
-                                 nc = __ldg(bvh.tri_norm + 3 * (size_t)leaf + 2);
-                    const float u = h.y, v = h.z, w = xsub(xsub(1.0f, u), v);
-                    const float3 n0 = f3(na.x, na.y, na.z), n1 = f3(na.w, nb.x, nb.y), n2 = f3(nb.z, nb.w, nc.x);
-                    nrm = xnormalize(f3(xadd(xadd(xmul(w, n0.x), xmul(u, n1.x)), xmul(v, n2.x)),
-                                        xadd(xadd(xmul(w, n0.y), xmul(u, n1.y)), xmul(v, n2.y)),
-                                        xadd(xadd(xmul(w, n0.z), xmul(u, n1.z)), xmul(v, n2.z))));
-                    P = f3(xadd(p.o.x, xmul(h.x, p.d.x)), xadd(p.o.y, xmul(h.x, p.d.y)), xadd(p.o.z, xmul(h.x, p.d.z)));
-                    base3 = f3(m0.x, m0.y, m0.z);
-                    eta = m1.x;
-                    metallic = m1.y;
-                    Tn = p.T * base3;
-                    key = rng_path_key(sp.seedKey, p.pixel, p.sample);
-                    nShadow = sp.nLights;
-                    wantDirect = !(eta >= 1.0f || metallic > 0.0f);
-                    wantNext = sp.depth + 1 < sp.maxDepth;
-                }
-            }
-        }
-        // delta lights: one infinite shadow ray per light, contribution T_d * baseColor * Li
-        for (int l = 0; l < sp.nLights; ++l) {
-            const bool emit = l < nShadow;
-            float3 ldir = f3(0, 0, 1), lrad = f3(0, 0, 0);
-            if (emit) light_incoming(sp.lights[l], P, ldir, lrad);
-            const uint32_t slot = warp_append(emit, countSec);
-            if (emit) store_path(sec, slot, P, ldir, Tn * (base3 * lrad), p.pixel, p.sample, 0u);
-        }
-        // the reference's extra cosine "direct" ray (diffuse only): adds emission of what it hits
-        {
-            float3 ddir = f3(0, 0, 1);
-            if (wantDirect) {
-                float a, b;
-                rng_pair(key, 2u + 2u * (uint32_t)sp.depth, a, b);
-                wantDirect = new_direction(p.d, nrm, eta, metallic, a, b, ddir);
-                if (!wantDirect) atomicAdd(&ctr->dropped_nonfinite, 1ull);
-            }
-            const uint32_t slot = warp_append(wantDirect, countSec);
-            if (wantDirect) store_path(sec, slot, P, ddir, Tn, p.pixel, p.sample, 1u);
-        }
-        {
-            float3 ndir = f3(0, 0, 1);
-            if (wantNext) {
-                float a, b;
-                rng_pair(key, 1u + 2u * (uint32_t)sp.depth, a, b);
-                wantNext = new_direction(p.d, nrm, eta, metallic, a, b, ndir);
-                if (!wantNext) atomicAdd(&ctr->dropped_nonfinite, 1ull);
-                wantNext = wantNext && (Tn.x > 0.f || Tn.y > 0.f || Tn.z > 0.f);   // a black path adds nothing further
-            }
-            const uint32_t slot = warp_append(wantNext, countNext);
-            if (wantNext) store_path(pathsOut, slot, P, ndir, Tn, p.pixel, p.sample, 0u);
-        }
+// ---- one path vertex ------------------------------------------------------------------------------
+// Shades the vertex an extension ray (o, d, throughput T) arrives at (steps 1-7 of the reference's bounce
+// loop, src/path_tracer.cu:353-414).  Returns false when the path ends here, with `terminal` = the
+// contribution to add (env on a miss, grey emission on an emitter); returns true with the data needed to
+// emit the next extension ray, one shadow ray per delta light and the extra cosine "direct" ray.
+struct Vertex {
+    float3 P;        // hit point
+    float3 Tn;       // throughput after this vertex = T * baseColor
+    float3 base;     // baseColor (delta-light terms carry it twice, SURVEY §3.3 iii)
+    float3 ndir;     // next direction
+    float3 ddir;     // direction of the "direct" ray
+    bool next, direct;
+};
+
+__device__ __forceinline__ bool shade_vertex(const BvhView& bvh, const ShadeParams& sp, int depth, float3 o, float3 d, float3 T,
+                                             uint32_t pixel, uint32_t sample, const HitRec& h, float3& terminal, Vertex& vx,
+                                             DeviceCounters* ctr) {
+    if (h.leaf < 0) {
+        terminal = T * env_lookup(sp.env, sp.envW, sp.envH, d);
+        return false;
+    }
+    const float4 g2 = __ldg(bvh.tri_geom + 3 * (size_t)h.leaf + 2);
+    const int mtlIdx = __float_as_int(g2.z);
+    const float4 m0 = __ldg(sp.mtl + 2 * mtlIdx), m1 = __ldg(sp.mtl + 2 * mtlIdx + 1);
+    if (m0.w > 0.0f) {   // emissive vertex: terminal, grey emission
+        terminal = T * m0.w;
+        return false;
+    }
+    terminal = f3(0.f, 0.f, 0.f);
+    const float4 na = __ldg(bvh.tri_norm + 3 * (size_t)h.leaf), nb = __ldg(bvh.tri_norm + 3 * (size_t)h.leaf + 1),
+                 nc = __ldg(bvh.tri_norm + 3 * (size_t)h.leaf + 2);
+    const float u = h.u, v = h.v, w = xsub(xsub(1.0f, u), v);
+    const float3 n0 = f3(na.x, na.y, na.z), n1 = f3(na.w, nb.x, nb.y), n2 = f3(nb.z, nb.w, nc.x);
+    const float3 nrm = xnormalize(f3(xadd(xadd(xmul(w, n0.x), xmul(u, n1.x)), xmul(v, n2.x)),
+                                     xadd(xadd(xmul(w, n0.y), xmul(u, n1.y)), xmul(v, n2.y)),
+                                     xadd(xadd(xmul(w, n0.z), xmul(u, n1.z)), xmul(v, n2.z))));
+    vx.P = f3(xadd(o.x, xmul(h.t, d.x)), xadd(o.y, xmul(h.t, d.y)), xadd(o.z, xmul(h.t, d.z)));
+    vx.base = f3(m0.x, m0.y, m0.z);
+    vx.Tn = T * vx.base;
+    const float eta = m1.x, metallic = m1.y;
+    const uint64_t key = rng_path_key(sp.seedKey, pixel, sample);
+    vx.direct = !(eta >= 1.0f || metallic > 0.0f);
+    vx.next = depth + 1 < sp.maxDepth;
+    vx.ddir = vx.ndir = f3(0.f, 0.f, 1.f);
+    if (vx.direct) {   // the reference's extra cosine "direct" ray (diffuse only)
+        float a, b;
+        rng_pair(key, 2u + 2u * (uint32_t)depth, a, b);
+        vx.direct = new_direction(d, nrm, eta, metallic, a, b, vx.ddir);
+        if (!vx.direct) atomicAdd(&ctr->dropped_nonfinite, 1ull);
+    }
+    if (vx.next) {
+        float a, b;
+        rng_pair(key, 1u + 2u * (uint32_t)depth, a, b);
+        vx.next = new_direction(d, nrm, eta, metallic, a, b, vx.ndir);
+        if (!vx.next) atomicAdd(&ctr->dropped_nonfinite, 1ull);
+        vx.next = vx.next && (vx.Tn.x > 0.f || vx.Tn.y > 0.f || vx.Tn.z > 0.f);   // a black path adds nothing further
+    }
+    return true;
+}
+
+struct QueueOut {
+    float4* ext;
+    float4* sec;
+    QueueLevel* level;
+};
+
+// Emit the rays of a shaded vertex from whatever lanes are here (diverged callers allowed).
+__device__ __forceinline__ void emit_vertex(const ShadeParams& sp, const QueueOut& q, const Vertex& vx, uint32_t pixel, uint32_t sample) {
+    // delta lights: one infinite shadow ray per light, contribution T_d * baseColor * Li
+    for (int l = 0; l < sp.nLights; ++l) {
+        float3 ldir, lrad;
+        light_incoming(sp.lights[l], vx.P, ldir, lrad);
+        const uint32_t slot = append_sec(q.level, false);
+        store_path(q.sec, slot, vx.P, ldir, vx.Tn * (vx.base * lrad), pixel, sample, kKindShadow);
+    }
+    if (vx.direct) {
+        const uint32_t slot = append_sec(q.level, true);
+        store_path(q.sec, slot, vx.P, vx.ddir, vx.Tn, pixel, sample, kKindDirect);
+    }
+    if (vx.next) {
+        const uint32_t slot = append_ext(q.level);
+        store_path(q.ext, slot, vx.P, vx.ndir, vx.Tn, pixel, sample, 0u);
     }
 }
 
-// ---- connect: shadow rays (any hit, infinite) and direct rays (closest hit -> emission) --------------
+// ---- wave 0: generate + extend + shade, fused ---------------------------------------------------------
+// Thread = (pixel of an 8x4 tile, group of `spt` consecutive local samples).
 template <bool COUNT>
-__global__ void __launch_bounds__(128) k_connect(BvhView bvh, const float4* __restrict__ mtl, const float4* __restrict__ sec,
-                                                 const uint32_t* __restrict__ countSec, unsigned long long* __restrict__ acc, DeviceCounters* ctr) {
-    const uint32_t n = *countSec;
-    unsigned nDirect = 0;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const float4 a = __ldcs(sec + 3 * (size_t)i), b = __ldcs(sec + 3 * (size_t)i + 1), c = __ldcs(sec + 3 * (size_t)i + 2);
-        const float3 o = f3(a.x, a.y, a.z), d = f3(a.w, b.x, b.y), wgt = f3(b.z, b.w, c.x);
-        const uint32_t pixel = __float_as_uint(c.y), kind = __float_as_uint(c.w);
-        if (kind == 0u) {
-            const HitRec h = traverse<true, COUNT>(bvh, o, d, &ctr->node_visits, &ctr->tri_tests);
-            if (h.leaf < 0) accum_add(acc, pixel, wgt, ctr);
+__global__ void __launch_bounds__(128) k_primary(BvhView bvh, ShadeParams sp, CameraParams cam, int W, int H, uint32_t nPadded,
+                                                 uint32_t kSamples, uint32_t spt, uint32_t sampleBase, uint32_t sampleStride, QueueOut q,
+                                                 unsigned long long* __restrict__ acc, DeviceCounters* ctr) {
+    const uint32_t groups = (kSamples + spt - 1) / spt;
+    const uint32_t total = nPadded * groups;
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    if (i == 0) atomicAdd(&ctr->rays_primary, (unsigned long long)W * (unsigned long long)H * kSamples);
+    const uint32_t g = i / nPadded, p = i - g * nPadded;
+    int px, py;
+    if (!tile_decode(p, W, H, px, py)) return;
+    const uint32_t pixel = (uint32_t)(px + py * W);
+    const uint32_t s0 = g * spt, s1 = min(kSamples, s0 + spt);
+    long long aR = 0, aG = 0, aB = 0;
+    for (uint32_t sl = s0; sl < s1; ++sl) {
+        const uint32_t sIdx = sampleBase + sl * sampleStride;
+        float ju, jv;
+        rng_pair(rng_path_key(sp.seedKey, pixel, sIdx), 0u, ju, jv);
+        float3 o, d;
+        primary_ray(cam, px, py, ju, jv, o, d);
+        const HitRec h = traverse<COUNT>(bvh, o, d, false, &ctr->node_visits, &ctr->tri_tests);
+        float3 term;
+        Vertex vx;
+        if (shade_vertex(bvh, sp, 0, o, d, f3(1.f, 1.f, 1.f), pixel, sIdx, h, term, vx, ctr)) {
+            emit_vertex(sp, q, vx, pixel, sIdx);
+        } else if (finite3(term)) {
+            aR += to_fixed(term.x);
+            aG += to_fixed(term.y);
+            aB += to_fixed(term.z);
         } else {
-            ++nDirect;
-            const HitRec h = traverse<false, COUNT>(bvh, o, d, &ctr->node_visits, &ctr->tri_tests);
-            if (h.leaf >= 0) {
-                const int mtlIdx = __float_as_int(__ldg(bvh.tri_geom + 3 * (size_t)h.leaf + 2).z);
-                const float e = __ldg(mtl + 2 * mtlIdx).w;
-                if (e != 0.0f) accum_add(acc, pixel, wgt * e, ctr);
-            }
+            atomicAdd(&ctr->dropped_nonfinite, 1ull);
         }
     }
-    // ray accounting: one atomic per block
-    __shared__ unsigned sDirect;
-    if (threadIdx.x == 0) sDirect = 0;
-    __syncthreads();
-    if (nDirect) atomicAdd(&sDirect, nDirect);
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        if (sDirect) atomicAdd(&ctr->rays_direct, (unsigned long long)sDirect);
-        if (blockIdx.x == 0) atomicAdd(&ctr->rays_shadow, (unsigned long long)n);   // = shadow + direct; host subtracts
+    unsigned long long* dst = acc + 3 * (size_t)pixel;
+    if (aR) atomicAdd(dst + 0, (unsigned long long)aR);
+    if (aG) atomicAdd(dst + 1, (unsigned long long)aG);
+    if (aB) atomicAdd(dst + 2, (unsigned long long)aB);
+}
+
+// ---- wave w >= 1: extension rays towards vertex w + secondary rays of vertex w-1 --------------------------
+template <bool COUNT>
+__global__ void __launch_bounds__(128) k_wave(BvhView bvh, ShadeParams sp, const float4* __restrict__ extIn, const float4* __restrict__ secIn,
+                                              QueueLevel* __restrict__ levelIn, QueueOut q, unsigned long long* __restrict__ acc,
+                                              DeviceCounters* ctr) {
+    const uint32_t nExt = levelIn->n_ext;
+    const unsigned long long secWord = levelIn->n_sec;
+    const uint32_t nSec = (uint32_t)secWord, nDirect = (uint32_t)(secWord >> 32);
+    if (nExt + nSec == 0u) return;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        atomicAdd(&ctr->rays_extension, (unsigned long long)nExt);
+        atomicAdd(&ctr->rays_direct, (unsigned long long)nDirect);
+        atomicAdd(&ctr->rays_shadow, (unsigned long long)(nSec - nDirect));
+    }
+    const uint32_t chunksExt = (nExt + 31u) >> 5, chunksAll = chunksExt + ((nSec + 31u) >> 5);
+    const int lane = threadIdx.x & 31;
+    while (true) {
+        uint32_t chunk = 0;
+        if (lane == 0) chunk = atomicAdd(&levelIn->cursor, 1u);
+        chunk = __shfl_sync(0xffffffffu, chunk, 0);
+        if (chunk >= chunksAll) break;
+        if (chunk < chunksExt) {
+            const uint32_t i = chunk * 32u + lane;
+            if (i < nExt) {
+                const PathRec p = load_path(extIn, i);
+                const HitRec h = traverse<COUNT>(bvh, p.o, p.d, false, &ctr->node_visits, &ctr->tri_tests);
+                float3 term;
+                Vertex vx;
+                if (shade_vertex(bvh, sp, sp.depth, p.o, p.d, p.T, p.pixel, p.sample, h, term, vx, ctr)) emit_vertex(sp, q, vx, p.pixel, p.sample);
+                else accum_add(acc, p.pixel, term, ctr);
+            }
+        } else {
+            const uint32_t i = (chunk - chunksExt) * 32u + lane;
+            if (i < nSec) {
+                const float4 a = __ldcs(secIn + 3 * (size_t)i), b = __ldcs(secIn + 3 * (size_t)i + 1), c = __ldcs(secIn + 3 * (size_t)i + 2);
+                const float3 o = f3(a.x, a.y, a.z), d = f3(a.w, b.x, b.y), wgt = f3(b.z, b.w, c.x);
+                const uint32_t pixel = __float_as_uint(c.y), kind = __float_as_uint(c.w);
+                const HitRec h = traverse<COUNT>(bvh, o, d, kind == kKindShadow, &ctr->node_visits, &ctr->tri_tests);
+                if (kind == kKindShadow) {
+                    if (h.leaf < 0) accum_add(acc, pixel, wgt, ctr);
+                } else if (h.leaf >= 0) {
+                    const int mtlIdx = __float_as_int(__ldg(bvh.tri_geom + 3 * (size_t)h.leaf + 2).z);
+                    const float e = __ldg(sp.mtl + 2 * mtlIdx).w;
+                    if (e != 0.0f) accum_add(acc, pixel, wgt * e, ctr);
+                }
+            }
+        }
+        __syncwarp();
     }
 }
 
@@ -451,25 +510,41 @@ int tpt_trace_rays_impl(tpt_scene* s, const tpt_ray* d_rays, size_t n, tpt_hit* 
     return TPT_OK;
 }
 
+constexpr int kMaxLevels = 72;   // waves 0..max_depth (max_depth <= 64), see tpt_render's argument check
+
+// Queue pools: a batch of P camera samples can emit at most P extension rays and P*(L+1) secondary rays
+// per wave (every live path emits one ray of each sort and one shadow ray per light).
 static int ensure_pools(tpt_context* ctx, size_t paths, size_t secPerPath) {
     const size_t secNeed = paths * secPerPath;
-    if (paths > ctx->pool_paths) {
+    if (!ctx->levels) TPT_CUDA(cudaMalloc(&ctx->levels, kMaxLevels * sizeof(QueueLevel)));
+    if (paths > ctx->ext_capacity) {
         TPT_CUDA(cudaStreamSynchronize(ctx->stream));
         for (int k = 0; k < 2; ++k) {
-            if (ctx->path_state[k]) cudaFree(ctx->path_state[k]);
-            TPT_CUDA(cudaMalloc(&ctx->path_state[k], paths * 3 * sizeof(float4)));
+            if (ctx->q_ext[k]) cudaFree(ctx->q_ext[k]);
+            ctx->q_ext[k] = nullptr;
         }
-        if (ctx->hits) cudaFree(ctx->hits);
-        TPT_CUDA(cudaMalloc(&ctx->hits, paths * sizeof(float4)));
-        ctx->pool_paths = paths;
+        ctx->ext_capacity = 0;
+        for (int k = 0; k < 2; ++k) TPT_CUDA(cudaMalloc(&ctx->q_ext[k], paths * 3 * sizeof(float4)));
+        ctx->ext_capacity = paths;
     }
     if (secNeed > ctx->sec_capacity) {
         TPT_CUDA(cudaStreamSynchronize(ctx->stream));
-        if (ctx->sec_rays) cudaFree(ctx->sec_rays);
-        TPT_CUDA(cudaMalloc(&ctx->sec_rays, secNeed * 3 * sizeof(float4)));
+        for (int k = 0; k < 2; ++k) {
+            if (ctx->q_sec[k]) cudaFree(ctx->q_sec[k]);
+            ctx->q_sec[k] = nullptr;
+        }
+        ctx->sec_capacity = 0;
+        for (int k = 0; k < 2; ++k) TPT_CUDA(cudaMalloc(&ctx->q_sec[k], secNeed * 3 * sizeof(float4)));
         ctx->sec_capacity = secNeed;
     }
     return TPT_OK;
+}
+
+template <typename K>
+static int resident_blocks(K kernel, int block) {
+    int n = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, block, 0) != cudaSuccess || n < 1) n = 1;
+    return n;
 }
 
 int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config* cfg, tpt_accum* acc) {
@@ -477,7 +552,7 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
     cudaStream_t st = ctx->stream;
     const int W = cfg->width, H = cfg->height;
     const uint32_t nPadded = tiles_x(W) * tiles_y(H) * 32u;
-    size_t target = cfg->paths_in_flight > 0 ? (size_t)cfg->paths_in_flight : (size_t)1 << 21;
+    const size_t target = cfg->paths_in_flight > 0 ? (size_t)cfg->paths_in_flight : (size_t)1 << 24;
     uint32_t k = (uint32_t)(target / nPadded);
     if (k < 1) k = 1;
     if (k > (uint32_t)cfg->spp) k = (uint32_t)cfg->spp;
@@ -485,10 +560,9 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
     TPT_CHECK(ensure_pools(ctx, pool, s->n_lights + 1));
 
     const CameraParams cp = make_camera(cam, W, H);
-    const uint64_t seedKey = rng_seed_key(cfg->seed);
     const bool counted = (cfg->flags & TPT_RENDER_COUNTERS) != 0;
     const bool timed = (cfg->flags & TPT_RENDER_STAGE_TIMES) != 0;
-    const size_t nEvents = 2 + 3 * (size_t)cfg->max_depth;
+    const size_t nEvents = 3 + (size_t)cfg->max_depth;
     if (timed) {
         while (ctx->stage_events.size() < nEvents) {
             cudaEvent_t e;
@@ -499,8 +573,11 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
     size_t ev = 0;
     auto mark = [&]() { if (timed) cudaEventRecord(ctx->stage_events[ev++], st); };
     const BvhView view = s->view();
-    uint32_t* counts = ctx->queue_counts;
-    const unsigned gridGen = kNumSMs * 8, gridTrace = kNumSMs * 16, gridShade = kNumSMs * 8;
+    if (ctx->wave_grid == 0) {
+        ctx->wave_grid = kNumSMs * resident_blocks(k_wave<false>, 128);
+        ctx->wave_grid_counted = kNumSMs * resident_blocks(k_wave<true>, 128);
+    }
+    const unsigned gridWave = counted ? ctx->wave_grid_counted : ctx->wave_grid;
 
     ShadeParams sp;
     sp.mtl = s->mtl_table;
@@ -510,42 +587,51 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
     sp.envW = ctx->env_w;
     sp.envH = ctx->env_h;
     sp.maxDepth = cfg->max_depth;
-    sp.seedKey = seedKey;
+    sp.seedKey = rng_seed_key(cfg->seed);
+    sp.depth = 0;
 
     for (uint32_t done = 0; done < (uint32_t)cfg->spp; done += k) {
         const uint32_t kk = ((uint32_t)cfg->spp - done) < k ? ((uint32_t)cfg->spp - done) : k;
-        TPT_CUDA(cudaMemsetAsync(counts, 0, 4 * sizeof(uint32_t), st));
+        // enough threads to fill the machine several times over, else as many samples per thread as possible
+        uint32_t spt = (uint32_t)(((size_t)nPadded * kk) / ((size_t)kNumSMs * 2048 * 4));
+        if (spt < 1) spt = 1;
+        if (spt > kk) spt = kk;
+        const uint32_t groups = (kk + spt - 1) / spt;
+        TPT_CUDA(cudaMemsetAsync(ctx->levels, 0, (size_t)(cfg->max_depth + 2) * sizeof(QueueLevel), st));
         ev = 0;
         mark();
-        k_generate<<<gridGen, 256, 0, st>>>(cp, W, H, nPadded, kk, (uint32_t)cfg->sample_offset + done * (uint32_t)cfg->sample_stride,
-                                            (uint32_t)cfg->sample_stride, seedKey, ctx->path_state[0], counts);
-        ctx->kernel_launches += 1;
-        mark();
-        for (int depth = 0; depth < cfg->max_depth; ++depth) {
-            const int cur = depth & 1, nxt = cur ^ 1;
-            sp.depth = depth;
+        {
+            const QueueOut q{ctx->q_ext[1], ctx->q_sec[1], static_cast<QueueLevel*>(ctx->levels) + 1};
+            const unsigned grid = (unsigned)(((size_t)nPadded * groups + 127) / 128);
+            const uint32_t sampleBase = (uint32_t)cfg->sample_offset + done * (uint32_t)cfg->sample_stride;
             if (counted)
-                k_extend<true><<<gridTrace, 128, 0, st>>>(view, ctx->path_state[cur], counts + cur, counts + nxt, counts + 2, ctx->hits,
-                                                          ctx->d_counters, depth);
+                k_primary<true><<<grid, 128, 0, st>>>(view, sp, cp, W, H, nPadded, kk, spt, sampleBase, (uint32_t)cfg->sample_stride, q, acc->data,
+                                                      ctx->d_counters);
             else
-                k_extend<false><<<gridTrace, 128, 0, st>>>(view, ctx->path_state[cur], counts + cur, counts + nxt, counts + 2, ctx->hits,
-                                                           ctx->d_counters, depth);
-            mark();
-            k_shade<<<gridShade, 256, 0, st>>>(view, sp, ctx->path_state[cur], ctx->hits, counts + cur, ctx->path_state[nxt], counts + nxt,
-                                               ctx->sec_rays, counts + 2, acc->data, ctx->d_counters);
-            mark();
-            if (counted) k_connect<true><<<gridTrace, 128, 0, st>>>(view, s->mtl_table, ctx->sec_rays, counts + 2, acc->data, ctx->d_counters);
-            else k_connect<false><<<gridTrace, 128, 0, st>>>(view, s->mtl_table, ctx->sec_rays, counts + 2, acc->data, ctx->d_counters);
-            mark();
-            ctx->kernel_launches += 3;
+                k_primary<false><<<grid, 128, 0, st>>>(view, sp, cp, W, H, nPadded, kk, spt, sampleBase, (uint32_t)cfg->sample_stride, q, acc->data,
+                                                       ctx->d_counters);
         }
+        mark();
+        // wave w traces extension rays towards vertex w and the secondary rays of vertex w-1; the last wave
+        // (w == max_depth) only has secondary rays left.
+        for (int w = 1; w <= cfg->max_depth; ++w) {
+            const int in = w & 1, out = in ^ 1;
+            sp.depth = w;
+            const QueueOut q{ctx->q_ext[out], ctx->q_sec[out], static_cast<QueueLevel*>(ctx->levels) + w + 1};
+            if (counted)
+                k_wave<true><<<gridWave, 128, 0, st>>>(view, sp, ctx->q_ext[in], ctx->q_sec[in], static_cast<QueueLevel*>(ctx->levels) + w, q, acc->data, ctx->d_counters);
+            else
+                k_wave<false><<<gridWave, 128, 0, st>>>(view, sp, ctx->q_ext[in], ctx->q_sec[in], static_cast<QueueLevel*>(ctx->levels) + w, q, acc->data, ctx->d_counters);
+            mark();
+        }
+        ctx->kernel_launches += 1 + (uint64_t)cfg->max_depth;
         TPT_CUDA(cudaGetLastError());
         if (timed) {
             TPT_CUDA(cudaEventSynchronize(ctx->stage_events[ev - 1]));
-            for (size_t k = 1; k < ev; ++k) {
+            for (size_t j = 1; j < ev; ++j) {
                 float ms = 0.f;
-                TPT_CUDA(cudaEventElapsedTime(&ms, ctx->stage_events[k - 1], ctx->stage_events[k]));
-                const int stage = k == 1 ? 0 : 1 + (int)((k - 2) % 3);
+                TPT_CUDA(cudaEventElapsedTime(&ms, ctx->stage_events[j - 1], ctx->stage_events[j]));
+                const int stage = j == 1 ? 0 : 1;
                 ctx->stage_ms[stage] += ms;
                 ctx->stage_launches[stage] += 1;
             }

@@ -49,13 +49,12 @@ struct tpt_context {
     tpt::DeviceCounters* d_counters = nullptr;
     uint64_t samples = 0;
     uint64_t kernel_launches = 0;
-    // wavefront pools (grown on demand)
-    size_t pool_paths = 0;
-    float4* path_state[2] = {nullptr, nullptr};   // 3 float4 per path
-    float4* hits = nullptr;                       // 1 float4 per path
-    float4* sec_rays = nullptr;                   // 3 float4 per secondary ray
-    size_t sec_capacity = 0;
-    uint32_t* queue_counts = nullptr;             // [0],[1] extension ping-pong, [2] secondary
+    // wavefront queues (grown on demand): ping-pong extension / secondary ray queues, 3 float4 per item
+    float4* q_ext[2] = {nullptr, nullptr};
+    float4* q_sec[2] = {nullptr, nullptr};
+    size_t ext_capacity = 0, sec_capacity = 0;
+    void* levels = nullptr;                       // QueueLevel[kMaxLevels] (render.cu)
+    unsigned wave_grid = 0, wave_grid_counted = 0; // persistent grid sizes of k_wave (148 x resident blocks)
     // scratch for trace_rays with host pointers
     void* io_rays = nullptr;
     void* io_hits = nullptr;

@@ -3,7 +3,7 @@
 // Replaces traverseBVH / rayHitBBox / rayHitTriangle of the reference (src/path_tracer.cu:61-107,
 // include/geometry_queries.h:18-46,66-86).  Same acceptance rule for a hit — Möller–Trumbore,
 // two-sided, u >= 0, v >= 0, u+v <= 1, t > 2e-4, strictly closer than the best so far — but:
-//   * ordered (near child first) with the far child pushed, and boxes are culled against the current
+//   * while-while loop structure; ordered (near child first) with the far child pushed, and boxes are culled against the current
 //     best t (the reference visits every box the infinite LINE touches);
 //   * one reciprocal per ray, not three divisions per box;
 //   * 64-B nodes read with four 128-bit loads, both child boxes in the parent;
@@ -44,8 +44,41 @@ __device__ __forceinline__ bool slab(float lox, float hix, float loy, float hiy,
     return tn <= tf;
 }
 
-template <bool ANY, bool COUNT>
-__device__ __forceinline__ HitRec traverse(const BvhView& bvh, float3 o, float3 d, unsigned long long* nodeVisits,
+// One Möller–Trumbore test exactly as geometry_queries.h:66-86 evaluates it (one rounding per operation),
+// followed by the acceptance rule of src/path_tracer.cu:83 with the lowest-primitive-id tie-break.
+__device__ __forceinline__ bool leaf_test(const BvhView& bvh, int leaf, float3 o, float3 d, HitRec& best) {
+    const float4* tp = bvh.tri_geom + 3 * (size_t)leaf;
+    const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
+    const float3 v0 = f3(a.x, a.y, a.z), e1 = f3(a.w, b.x, b.y), e2 = f3(b.z, b.w, c.x);
+    const float3 tv = xsub3(o, v0);
+    const float3 p = xcross(d, e2);
+    const float3 q = xcross(tv, e1);
+    const float denom = xdot(p, e1);
+    if (denom == 0.0f) return false;
+    const float invDenom = __fdiv_rn(1.0f, denom);
+    const float u = xmul(xdot(p, tv), invDenom);
+    const float v = xmul(xdot(q, d), invDenom);
+    if (u < 0.0f || v < 0.0f || xadd(u, v) > 1.0f) return false;
+    const float t = xmul(xdot(q, e2), invDenom);
+    const int prim = __float_as_int(c.y);
+    if (t > kDelta && (t < best.t || (t == best.t && prim < best.prim))) {
+        best.t = t;
+        best.u = u;
+        best.v = v;
+        best.leaf = leaf;
+        best.prim = prim;
+        return true;
+    }
+    return false;
+}
+
+constexpr int kStackSentinel = (int)0x80000000;   // negative, and never a valid leaf code (~leaf >= -2^30)
+
+// "while-while" traversal (Aila & Laine 2009): the inner loop descends internal nodes until the lane holds
+// a leaf, so that the lanes of a warp run their (expensive, exactly-rounded) triangle tests together
+// instead of one lane's leaf serialising against the other lanes' box tests.
+template <bool COUNT>
+__device__ __forceinline__ HitRec traverse(const BvhView& bvh, float3 o, float3 d, bool anyHit, unsigned long long* nodeVisits,
                                            unsigned long long* triTests) {
     HitRec best;
     best.t = FLT_MAX;
@@ -55,15 +88,16 @@ __device__ __forceinline__ HitRec traverse(const BvhView& bvh, float3 o, float3 
 
     const float3 inv = f3(safe_rcp(d.x), safe_rcp(d.y), safe_rcp(d.z));
     int stack[kStackSize];
-    int sp = 0;
+    stack[0] = kStackSentinel;
+    int sp = 1;
     int cur = bvh.n_faces > 1 ? 0 : ~0;   // single-triangle scene: the root is leaf 0
     unsigned nv = 0, nt = 0;
 
-    while (true) {
-        if (cur >= 0) {
+    while (cur != kStackSentinel) {
+        while (cur >= 0) {
             const float4* n = bvh.nodes + 4 * (size_t)cur;
             const float4 n0 = __ldg(n), n1 = __ldg(n + 1), n2 = __ldg(n + 2);
-            const int4 n3 = __ldg(reinterpret_cast<const int4*>(n + 3));
+            const int2 n3 = __ldg(reinterpret_cast<const int2*>(n + 3));
             if (COUNT) ++nv;
             float loL, loR;
             const bool hL = slab(n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, o, inv, best.t, loL);
@@ -77,40 +111,13 @@ __device__ __forceinline__ HitRec traverse(const BvhView& bvh, float3 o, float3 
             } else if (hR) {
                 cur = n3.y;
             } else {
-                if (sp == 0) break;
                 cur = stack[--sp];
             }
-        } else {
-            const int leaf = ~cur;
-            const float4* tp = bvh.tri_geom + 3 * (size_t)leaf;
-            const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
-            if (COUNT) ++nt;
-            const float3 v0 = f3(a.x, a.y, a.z), e1 = f3(a.w, b.x, b.y), e2 = f3(b.z, b.w, c.x);
-            // Möller–Trumbore exactly as geometry_queries.h:66-86 evaluates it, one rounding per operation
-            const float3 tv = xsub3(o, v0);
-            const float3 p = xcross(d, e2);
-            const float3 q = xcross(tv, e1);
-            const float denom = xdot(p, e1);
-            if (denom != 0.0f) {
-                const float invDenom = __fdiv_rn(1.0f, denom);
-                const float u = xmul(xdot(p, tv), invDenom);
-                const float v = xmul(xdot(q, d), invDenom);
-                if (!(u < 0.0f || v < 0.0f || xadd(u, v) > 1.0f)) {
-                    const float t = xmul(xdot(q, e2), invDenom);
-                    const int prim = __float_as_int(c.y);
-                    if (t > kDelta && (t < best.t || (t == best.t && prim < best.prim))) {
-                        best.t = t;
-                        best.u = u;
-                        best.v = v;
-                        best.leaf = leaf;
-                        best.prim = prim;
-                        if (ANY) break;
-                    }
-                }
-            }
-            if (sp == 0) break;
-            cur = stack[--sp];
         }
+        if (cur == kStackSentinel) break;
+        if (COUNT) ++nt;
+        if (leaf_test(bvh, ~cur, o, d, best) && anyHit) break;
+        cur = stack[--sp];
     }
     if (COUNT) {   // one atomic per converged group of lanes, not per ray
         const unsigned m = __activemask();
