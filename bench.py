@@ -125,6 +125,7 @@ def run_ours(args):
     if args.spp:
         spp = args.spp
     assert spp % N_SLICES == 0, "spp must be a multiple of the 8 fixed slices"
+    assert N_SLICES % world == 0, "the 8 fixed slices are dealt to 1, 2, 4 or 8 ranks"
     per_slice = spp // N_SLICES
     scene = load_scene(fixture)
     env = synthetic_sky() if envkind == "sky" else None
@@ -146,9 +147,10 @@ def run_ours(args):
         """One doTrace (reference src/path_tracer.cu:491-554) with device-resident inputs."""
         tpt.BVH(dscene).construct(stats=False)
         acc.clear()
-        for s in slices:
-            pt.render_into(dscene, cam, spp=per_slice, max_depth=depth, seed=seed, sample_offset=s, sample_stride=N_SLICES,
-                           accum=acc, counters=counters, stage_times=stage_times, paths_in_flight=args.paths_in_flight)
+        # this rank's slices {s : s mod N == rank} are exactly the sample indices i with i mod N == rank (N divides 8):
+        # one call with offset = rank, stride = N renders them all (integer accumulation: grouping cannot change a bit)
+        pt.render_into(dscene, cam, spp=per_slice * len(slices), max_depth=depth, seed=seed, sample_offset=rank, sample_stride=world,
+                       accum=acc, counters=counters, stage_times=stage_times, paths_in_flight=args.paths_in_flight)
         if world > 1:
             dist.all_reduce(acc_t, op=dist.ReduceOp.SUM)
         check(lib.tpt_resolve_bgra8(acc._h, spp, C.c_void_p(fb_dev.data_ptr()), 1))

@@ -6,10 +6,12 @@ there is no Python, PyTorch or CPU stand-in for any entry point.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from pathlib import Path
 
 _PKG = Path(__file__).resolve().parent
-LIB_PATH = _PKG / "lib" / "libtpt_b200.so"
+# TPT_B200_LIB selects a tuning variant of the same library (tinypathtracer_b200/build.py -D... -o...)
+LIB_PATH = Path(os.environ.get("TPT_B200_LIB") or (_PKG / "lib" / "libtpt_b200.so"))
 
 if not LIB_PATH.exists():
     raise ImportError(

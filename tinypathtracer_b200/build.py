@@ -23,12 +23,14 @@ def _stale() -> bool:
     return any(d.stat().st_mtime > t for d in deps)
 
 
-def build_library(force: bool = False, verbose: bool = False) -> Path:
-    if not force and not _stale():
+def build_library(force: bool = False, verbose: bool = False, defines=(), out: Path | None = None) -> Path:
+    """`defines`/`out` build a tuning variant beside the product library (loaded with TPT_B200_LIB=<path>)."""
+    if out is None and not force and not _stale():
         return LIB
-    LIB.parent.mkdir(parents=True, exist_ok=True)
+    out = out or LIB
+    out.parent.mkdir(parents=True, exist_ok=True)
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc, *NVCC_FLAGS, "-shared", "-o", str(LIB), *[str(CSRC / s) for s in SOURCES]]
+    cmd = [nvcc, *NVCC_FLAGS, *[f"-D{d}" for d in defines], "-shared", "-o", str(out), *[str(CSRC / s) for s in SOURCES]]
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
     r = subprocess.run(cmd, capture_output=True, text=True)
@@ -37,8 +39,10 @@ def build_library(force: bool = False, verbose: bool = False) -> Path:
         raise RuntimeError("nvcc failed building libtpt_b200.so")
     if verbose:
         print(r.stderr)
-    return LIB
+    return out
 
 
 if __name__ == "__main__":
-    print(build_library(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    defs = [a[2:] for a in sys.argv[1:] if a.startswith("-D")]
+    outs = [a[2:] for a in sys.argv[1:] if a.startswith("-o")]
+    print(build_library(force="--force" in sys.argv, verbose="-v" in sys.argv, defines=defs, out=Path(outs[0]).resolve() if outs else None))

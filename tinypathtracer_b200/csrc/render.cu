@@ -77,7 +77,7 @@ __device__ __forceinline__ void accum_add(unsigned long long* __restrict__ acc, 
 // (PathRec above); secondary items carry the contribution weight in T and their kind in s2.w.
 struct QueueLevel {
     uint32_t n_ext;                  // extension rays towards vertex w
-    uint32_t cursor;                 // next 32-item chunk to hand out (k_wave)
+    uint32_t cursor;                 // next item not yet handed to a warp (k_wave)
     unsigned long long n_sec;        // low 32 bits: secondary rays of vertex w-1; high 32 bits: how many are "direct" rays
 };
 constexpr uint32_t kKindShadow = 0u, kKindDirect = 1u;
@@ -383,53 +383,183 @@ __global__ void __launch_bounds__(128) k_primary(BvhView bvh, ShadeParams sp, Ca
 }
 
 // ---- wave w >= 1: extension rays towards vertex w + secondary rays of vertex w-1 --------------------------
+// Persistent warps.  Incoherent rays finish after very different numbers of steps, and a lane that waits
+// for the slowest ray of its warp is a wasted lane, so each lane runs the traversal state machine of
+// traverse.cuh and the warp schedules itself:
+//   * every iteration the warp votes and executes ONE step kind — the box step for the lanes that sit at an
+//     internal node, or the (exactly rounded, expensive) triangle step for the lanes that sit at a leaf —
+//     whichever has more lanes ready; the others keep their state and wait;
+//   * when kRefillThreshold lanes are idle, finished lanes retire their ray and idle lanes take new items
+//     (ray replacement); items come from the global cursor kGrab at a time and are dealt out warp-locally;
+//   * retiring an extension ray only stages (item, hit) in shared memory; once 32 are staged the whole
+//     warp shades them together (shade_vertex + emit), so the divergent BSDF code also runs on full warps.
+#ifndef TPT_REFILL_THRESHOLD
+#define TPT_REFILL_THRESHOLD 8
+#endif
+constexpr int kRefillThreshold = TPT_REFILL_THRESHOLD;
+constexpr uint32_t kGrab = 256;
+constexpr int kStage = 64;
+constexpr uint32_t kNoItem = 0xffffffffu;
+
+__device__ __forceinline__ void shade_staged(const BvhView& bvh, const ShadeParams& sp, const float4* __restrict__ extIn, const QueueOut& q,
+                                             unsigned long long* __restrict__ acc, DeviceCounters* ctr, const uint32_t* myIdx,
+                                             const float4* myHit, uint32_t count) {
+    const uint32_t lane = threadIdx.x & 31;
+    if (lane < count) {
+        const PathRec p = load_path(extIn, myIdx[lane]);
+        const float4 hv = myHit[lane];
+        HitRec h;
+        h.t = hv.x;
+        h.u = hv.y;
+        h.v = hv.z;
+        h.leaf = __float_as_int(hv.w);
+        h.prim = -1;
+        float3 term;
+        Vertex vx;
+        if (shade_vertex(bvh, sp, sp.depth, p.o, p.d, p.T, p.pixel, p.sample, h, term, vx, ctr)) emit_vertex(sp, q, vx, p.pixel, p.sample);
+        else accum_add(acc, p.pixel, term, ctr);
+    }
+    __syncwarp();
+}
+
+#ifndef TPT_WAVE_MIN_BLOCKS
+#define TPT_WAVE_MIN_BLOCKS 8
+#endif
 template <bool COUNT>
-__global__ void __launch_bounds__(128) k_wave(BvhView bvh, ShadeParams sp, const float4* __restrict__ extIn, const float4* __restrict__ secIn,
+__global__ void __launch_bounds__(128, TPT_WAVE_MIN_BLOCKS) k_wave(BvhView bvh, ShadeParams sp, const float4* __restrict__ extIn, const float4* __restrict__ secIn,
                                               QueueLevel* __restrict__ levelIn, QueueOut q, unsigned long long* __restrict__ acc,
                                               DeviceCounters* ctr) {
+    __shared__ uint32_t sIdx[4][kStage];
+    __shared__ float4 sHit[4][kStage];
     const uint32_t nExt = levelIn->n_ext;
     const unsigned long long secWord = levelIn->n_sec;
     const uint32_t nSec = (uint32_t)secWord, nDirect = (uint32_t)(secWord >> 32);
-    if (nExt + nSec == 0u) return;
+    const uint32_t total = nExt + nSec;
+    if (total == 0u) return;
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         atomicAdd(&ctr->rays_extension, (unsigned long long)nExt);
         atomicAdd(&ctr->rays_direct, (unsigned long long)nDirect);
         atomicAdd(&ctr->rays_shadow, (unsigned long long)(nSec - nDirect));
     }
-    const uint32_t chunksExt = (nExt + 31u) >> 5, chunksAll = chunksExt + ((nSec + 31u) >> 5);
-    const int lane = threadIdx.x & 31;
+    const uint32_t lane = threadIdx.x & 31, ltMask = (1u << lane) - 1u;
+    uint32_t* myIdx = sIdx[threadIdx.x >> 5];
+    float4* myHit = sHit[threadIdx.x >> 5];
+    int stack[kStackSize];
+    TravState ts;
+    ts.cur = kStackSentinel;
+    ts.sp = 1;
+    uint32_t item = kNoItem, kind = 0;   // kind: 0 extension, 1 shadow (any hit), 2 direct
+    uint32_t lo = 0, hi = 0;             // warp-local range of items not yet dealt out
+    bool more = true;                    // the global cursor may still have items
+    uint32_t nStaged = 0;
+    unsigned nv = 0, nt = 0;
+
     while (true) {
-        uint32_t chunk = 0;
-        if (lane == 0) chunk = atomicAdd(&levelIn->cursor, 1u);
-        chunk = __shfl_sync(0xffffffffu, chunk, 0);
-        if (chunk >= chunksAll) break;
-        if (chunk < chunksExt) {
-            const uint32_t i = chunk * 32u + lane;
-            if (i < nExt) {
-                const PathRec p = load_path(extIn, i);
-                const HitRec h = traverse<COUNT>(bvh, p.o, p.d, false, &ctr->node_visits, &ctr->tri_tests);
-                float3 term;
-                Vertex vx;
-                if (shade_vertex(bvh, sp, sp.depth, p.o, p.d, p.T, p.pixel, p.sample, h, term, vx, ctr)) emit_vertex(sp, q, vx, p.pixel, p.sample);
-                else accum_add(acc, p.pixel, term, ctr);
+        const bool atNode = ts.cur >= 0;
+        const bool atLeaf = ts.cur < 0 && ts.cur != kStackSentinel;
+        const unsigned mNode = __ballot_sync(0xffffffffu, atNode), mLeaf = __ballot_sync(0xffffffffu, atLeaf);
+        const unsigned mBusy = mNode | mLeaf;
+        if (mBusy == 0u || (more && 32 - __popc(mBusy) >= kRefillThreshold)) {
+            // ---- retire finished rays
+            const bool fin = item != kNoItem && !atNode && !atLeaf;
+            const bool finExt = fin && kind == 0u;
+            const unsigned mExt = __ballot_sync(0xffffffffu, finExt);
+            if (finExt) {
+                const uint32_t slot = nStaged + __popc(mExt & ltMask);
+                myIdx[slot] = item;
+                myHit[slot] = make_float4(ts.best.t, ts.best.u, ts.best.v, __int_as_float(ts.best.leaf));
             }
-        } else {
-            const uint32_t i = (chunk - chunksExt) * 32u + lane;
-            if (i < nSec) {
-                const float4 a = __ldcs(secIn + 3 * (size_t)i), b = __ldcs(secIn + 3 * (size_t)i + 1), c = __ldcs(secIn + 3 * (size_t)i + 2);
-                const float3 o = f3(a.x, a.y, a.z), d = f3(a.w, b.x, b.y), wgt = f3(b.z, b.w, c.x);
-                const uint32_t pixel = __float_as_uint(c.y), kind = __float_as_uint(c.w);
-                const HitRec h = traverse<COUNT>(bvh, o, d, kind == kKindShadow, &ctr->node_visits, &ctr->tri_tests);
-                if (kind == kKindShadow) {
-                    if (h.leaf < 0) accum_add(acc, pixel, wgt, ctr);
-                } else if (h.leaf >= 0) {
-                    const int mtlIdx = __float_as_int(__ldg(bvh.tri_geom + 3 * (size_t)h.leaf + 2).z);
-                    const float e = __ldg(sp.mtl + 2 * mtlIdx).w;
-                    if (e != 0.0f) accum_add(acc, pixel, wgt * e, ctr);
+            nStaged += __popc(mExt);
+            if (fin && kind != 0u) {
+                float e = 1.0f;
+                bool add = ts.best.leaf < 0;   // shadow ray: unoccluded
+                if (kind == 2u) {              // direct ray: emission of what it hit
+                    add = false;
+                    if (ts.best.leaf >= 0) {
+                        const int mtlIdx = __float_as_int(__ldg(bvh.tri_geom + 3 * (size_t)ts.best.leaf + 2).z);
+                        e = __ldg(sp.mtl + 2 * mtlIdx).w;
+                        add = e != 0.0f;
+                    }
+                }
+                if (add) {
+                    const size_t i = (size_t)(item - nExt);
+                    const float4 b = __ldcs(secIn + 3 * i + 1), c = __ldcs(secIn + 3 * i + 2);
+                    accum_add(acc, __float_as_uint(c.y), f3(b.z, b.w, c.x) * e, ctr);
                 }
             }
+            if (fin) item = kNoItem;
+            __syncwarp();
+            if (nStaged >= 32u) {
+                shade_staged(bvh, sp, extIn, q, acc, ctr, myIdx, myHit, 32u);
+                const uint32_t r = nStaged - 32u;
+                uint32_t ti = 0;
+                float4 th = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (lane < r) {
+                    ti = myIdx[32 + lane];
+                    th = myHit[32 + lane];
+                }
+                __syncwarp();
+                if (lane < r) {
+                    myIdx[lane] = ti;
+                    myHit[lane] = th;
+                }
+                __syncwarp();
+                nStaged = r;
+            }
+            // ---- deal new items to the idle lanes
+            if (more && lo == hi) {
+                if (lane == 0) lo = atomicAdd(&levelIn->cursor, kGrab);
+                lo = __shfl_sync(0xffffffffu, lo, 0);
+                hi = min(lo + kGrab, total);
+                if (lo >= total) {
+                    more = false;
+                    lo = hi = 0;
+                }
+            }
+            if (more) {
+                const bool empty = item == kNoItem;
+                const unsigned mEmpty = __ballot_sync(0xffffffffu, empty);
+                const uint32_t avail = hi - lo, rank = __popc(mEmpty & ltMask);
+                if (empty && rank < avail) {
+                    item = lo + rank;
+                    const bool isExt = item < nExt;
+                    const float4* src = isExt ? extIn + 3 * (size_t)item : secIn + 3 * (size_t)(item - nExt);
+                    const float4 a = __ldcs(src), b = __ldcs(src + 1);
+                    kind = isExt ? 0u : 1u + __float_as_uint(__ldcs(reinterpret_cast<const float*>(src + 2) + 3));
+                    trav_begin(ts, bvh, f3(a.x, a.y, a.z), f3(a.w, b.x, b.y), stack);
+                }
+                lo += min((uint32_t)__popc(mEmpty), avail);
+            }
+            if (!more && __ballot_sync(0xffffffffu, item != kNoItem) == 0u) break;
+            continue;
         }
-        __syncwarp();
+        if (__popc(mNode) >= __popc(mLeaf)) {
+            // box steps for the lanes at internal nodes; keep going without a full re-vote while at least
+            // three quarters of them are still descending (coherent rays stay in this loop for many steps)
+            const int keep = max(1, (3 * __popc(mNode)) >> 2);
+            do {
+                if (ts.cur >= 0) {
+                    trav_node_step(ts, bvh, stack);
+                    if (COUNT) ++nv;
+                }
+            } while (__popc(__ballot_sync(0xffffffffu, ts.cur >= 0)) >= keep);
+        } else {
+            const int keep = max(1, (3 * __popc(mLeaf)) >> 2);
+            do {
+                if (ts.cur < 0 && ts.cur != kStackSentinel) {
+                    trav_leaf_step(ts, bvh, kind == 1u, stack);
+                    if (COUNT) ++nt;
+                }
+            } while (__popc(__ballot_sync(0xffffffffu, ts.cur < 0 && ts.cur != kStackSentinel)) >= keep);
+        }
+    }
+    if (nStaged) shade_staged(bvh, sp, extIn, q, acc, ctr, myIdx, myHit, nStaged);
+    if (COUNT) {
+        const unsigned sv = __reduce_add_sync(0xffffffffu, nv), st = __reduce_add_sync(0xffffffffu, nt);
+        if (lane == 0) {
+            atomicAdd(&ctr->node_visits, (unsigned long long)sv);
+            atomicAdd(&ctr->tri_tests, (unsigned long long)st);
+        }
     }
 }
 
@@ -552,7 +682,10 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
     cudaStream_t st = ctx->stream;
     const int W = cfg->width, H = cfg->height;
     const uint32_t nPadded = tiles_x(W) * tiles_y(H) * 32u;
-    const size_t target = cfg->paths_in_flight > 0 ? (size_t)cfg->paths_in_flight : (size_t)1 << 24;
+    // default batch: as many camera samples as a 12 GiB queue budget allows (2 sides x (2+L) rays x 48 B each), at most 2^26
+    size_t target = ((size_t)12 << 30) / (96 * (2 + s->n_lights));
+    if (target > ((size_t)1 << 26)) target = (size_t)1 << 26;
+    if (cfg->paths_in_flight > 0) target = (size_t)cfg->paths_in_flight;
     uint32_t k = (uint32_t)(target / nPadded);
     if (k < 1) k = 1;
     if (k > (uint32_t)cfg->spp) k = (uint32_t)cfg->spp;
