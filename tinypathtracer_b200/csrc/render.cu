@@ -390,14 +390,14 @@ __global__ void __launch_bounds__(128) k_primary(BvhView bvh, ShadeParams sp, Ca
 //     internal node, or the (exactly rounded, expensive) triangle step for the lanes that sit at a leaf —
 //     whichever has more lanes ready; the others keep their state and wait;
 //   * when kRefillThreshold lanes are idle, finished lanes retire their ray and idle lanes take new items
-//     (ray replacement); items come from the global cursor kGrab at a time and are dealt out warp-locally;
+//     (ray replacement); items come from the global cursor 32-256 at a time and are dealt out warp-locally;
 //   * retiring an extension ray only stages (item, hit) in shared memory; once 32 are staged the whole
 //     warp shades them together (shade_vertex + emit), so the divergent BSDF code also runs on full warps.
 #ifndef TPT_REFILL_THRESHOLD
 #define TPT_REFILL_THRESHOLD 8
 #endif
 constexpr int kRefillThreshold = TPT_REFILL_THRESHOLD;
-constexpr uint32_t kGrab = 256;
+constexpr uint32_t kGrabMax = 256;
 constexpr int kStage = 64;
 constexpr uint32_t kNoItem = 0xffffffffu;
 
@@ -442,6 +442,9 @@ __global__ void __launch_bounds__(128, TPT_WAVE_MIN_BLOCKS) k_wave(BvhView bvh, 
         atomicAdd(&ctr->rays_shadow, (unsigned long long)(nSec - nDirect));
     }
     const uint32_t lane = threadIdx.x & 31, ltMask = (1u << lane) - 1u;
+    // items taken from the global cursor at a time: large for big waves (few atomics), 32 for small ones so
+    // that every resident warp gets work
+    const uint32_t kGrab = min(max((total / (gridDim.x * 8u)) & ~31u, 32u), kGrabMax);
     uint32_t* myIdx = sIdx[threadIdx.x >> 5];
     float4* myHit = sHit[threadIdx.x >> 5];
     int stack[kStackSize];
@@ -524,8 +527,14 @@ __global__ void __launch_bounds__(128, TPT_WAVE_MIN_BLOCKS) k_wave(BvhView bvh, 
                     item = lo + rank;
                     const bool isExt = item < nExt;
                     const float4* src = isExt ? extIn + 3 * (size_t)item : secIn + 3 * (size_t)(item - nExt);
+#ifdef TPT_REFILL_LDCS
                     const float4 a = __ldcs(src), b = __ldcs(src + 1);
                     kind = isExt ? 0u : 1u + __float_as_uint(__ldcs(reinterpret_cast<const float*>(src + 2) + 3));
+#else
+                    // cached loads: the rest of the item is read again when the ray retires (shade_staged / accumulate)
+                    const float4 a = __ldg(src), b = __ldg(src + 1);
+                    kind = isExt ? 0u : 1u + __float_as_uint(__ldg(reinterpret_cast<const float*>(src + 2) + 3));
+#endif
                     trav_begin(ts, bvh, f3(a.x, a.y, a.z), f3(a.w, b.x, b.y), stack);
                 }
                 lo += min((uint32_t)__popc(mEmpty), avail);
@@ -562,6 +571,61 @@ __global__ void __launch_bounds__(128, TPT_WAVE_MIN_BLOCKS) k_wave(BvhView bvh, 
         }
     }
 }
+
+#ifdef TPT_WAVE_CHUNKED
+// tuning variant: static 32-item chunks, plain while-while traversal, shading inline (no ray replacement)
+// ---- wave w >= 1: extension rays towards vertex w + secondary rays of vertex w-1 --------------------------
+template <bool COUNT>
+__global__ void __launch_bounds__(128) k_wave_chunked(BvhView bvh, ShadeParams sp, const float4* __restrict__ extIn, const float4* __restrict__ secIn,
+                                              QueueLevel* __restrict__ levelIn, QueueOut q, unsigned long long* __restrict__ acc,
+                                              DeviceCounters* ctr) {
+    const uint32_t nExt = levelIn->n_ext;
+    const unsigned long long secWord = levelIn->n_sec;
+    const uint32_t nSec = (uint32_t)secWord, nDirect = (uint32_t)(secWord >> 32);
+    if (nExt + nSec == 0u) return;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        atomicAdd(&ctr->rays_extension, (unsigned long long)nExt);
+        atomicAdd(&ctr->rays_direct, (unsigned long long)nDirect);
+        atomicAdd(&ctr->rays_shadow, (unsigned long long)(nSec - nDirect));
+    }
+    const uint32_t chunksExt = (nExt + 31u) >> 5, chunksAll = chunksExt + ((nSec + 31u) >> 5);
+    const int lane = threadIdx.x & 31;
+    while (true) {
+        uint32_t chunk = 0;
+        if (lane == 0) chunk = atomicAdd(&levelIn->cursor, 1u);
+        chunk = __shfl_sync(0xffffffffu, chunk, 0);
+        if (chunk >= chunksAll) break;
+        if (chunk < chunksExt) {
+            const uint32_t i = chunk * 32u + lane;
+            if (i < nExt) {
+                const PathRec p = load_path(extIn, i);
+                const HitRec h = traverse<COUNT>(bvh, p.o, p.d, false, &ctr->node_visits, &ctr->tri_tests);
+                float3 term;
+                Vertex vx;
+                if (shade_vertex(bvh, sp, sp.depth, p.o, p.d, p.T, p.pixel, p.sample, h, term, vx, ctr)) emit_vertex(sp, q, vx, p.pixel, p.sample);
+                else accum_add(acc, p.pixel, term, ctr);
+            }
+        } else {
+            const uint32_t i = (chunk - chunksExt) * 32u + lane;
+            if (i < nSec) {
+                const float4 a = __ldcs(secIn + 3 * (size_t)i), b = __ldcs(secIn + 3 * (size_t)i + 1), c = __ldcs(secIn + 3 * (size_t)i + 2);
+                const float3 o = f3(a.x, a.y, a.z), d = f3(a.w, b.x, b.y), wgt = f3(b.z, b.w, c.x);
+                const uint32_t pixel = __float_as_uint(c.y), kind = __float_as_uint(c.w);
+                const HitRec h = traverse<COUNT>(bvh, o, d, kind == kKindShadow, &ctr->node_visits, &ctr->tri_tests);
+                if (kind == kKindShadow) {
+                    if (h.leaf < 0) accum_add(acc, pixel, wgt, ctr);
+                } else if (h.leaf >= 0) {
+                    const int mtlIdx = __float_as_int(__ldg(bvh.tri_geom + 3 * (size_t)h.leaf + 2).z);
+                    const float e = __ldg(sp.mtl + 2 * mtlIdx).w;
+                    if (e != 0.0f) accum_add(acc, pixel, wgt * e, ctr);
+                }
+            }
+        }
+        __syncwarp();
+    }
+}
+
+#endif
 
 // ---- accumulation buffer utilities ---------------------------------------------------------------
 __global__ void k_accum_add(unsigned long long* __restrict__ dst, const unsigned long long* __restrict__ src, size_t n) {
@@ -754,7 +818,11 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
             if (counted)
                 k_wave<true><<<gridWave, 128, 0, st>>>(view, sp, ctx->q_ext[in], ctx->q_sec[in], static_cast<QueueLevel*>(ctx->levels) + w, q, acc->data, ctx->d_counters);
             else
+#ifdef TPT_WAVE_CHUNKED
+                k_wave_chunked<false><<<kNumSMs * 9, 128, 0, st>>>(view, sp, ctx->q_ext[in], ctx->q_sec[in], static_cast<QueueLevel*>(ctx->levels) + w, q, acc->data, ctx->d_counters);
+#else
                 k_wave<false><<<gridWave, 128, 0, st>>>(view, sp, ctx->q_ext[in], ctx->q_sec[in], static_cast<QueueLevel*>(ctx->levels) + w, q, acc->data, ctx->d_counters);
+#endif
             mark();
         }
         ctx->kernel_launches += 1 + (uint64_t)cfg->max_depth;
