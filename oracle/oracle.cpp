@@ -459,7 +459,7 @@ inline uint64_t path_key(uint64_t seed, uint32_t pixel, uint32_t sample) {
 }
 inline float u01(uint32_t x) { return (float)((x >> 8) + 1u) * (1.0f / 16777216.0f); }
 inline void draw_pair(uint64_t key, uint32_t pairIdx, float& a, float& b) {
-    uint64_t z = mix64(key + (uint64_t)(pairIdx + 1u) * kGolden);
+    uint64_t z = pairIdx == 0u ? key : mix64(key + (uint64_t)pairIdx * kGolden);
     a = u01((uint32_t)(z >> 32));
     b = u01((uint32_t)z);
 }

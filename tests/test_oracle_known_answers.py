@@ -211,7 +211,7 @@ def test_rng_spec(orc):
     def pair(seed, pixel, sample, j):
         G = 0x9E3779B97F4A7C15
         key = mix(mix((seed + G) & M) ^ ((pixel << 32) | sample))
-        z = mix((key + (j + 1) * G) & M)
+        z = key if j == 0 else mix((key + j * G) & M)
         u = lambda x: np.float32(((x >> 8) + 1)) * np.float32(2.0 ** -24)
         return u(z >> 32), u(z & 0xFFFFFFFF)
 

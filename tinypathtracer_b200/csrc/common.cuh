@@ -131,7 +131,7 @@ __host__ __device__ __forceinline__ float3 mat4_dir(const float* m, float3 d) {
 // ------------------------------------------------------------------------------------------------
 // RNG — counter-based, stateless.  Spec (DESIGN.md "RNG spec"; oracle/oracle.cpp restates it):
 //   key(seed, pixel, sample) = mix64( mix64(seed + G) ^ (pixel << 32 | sample) ),  G = 0x9E3779B97F4A7C15
-//   pair(key, j)             = mix64( key + (j + 1) * G )   ->  a = u01(hi32), b = u01(lo32)
+//   pair(key, j)             = z_j -> a = u01(hi32 z_j), b = u01(lo32 z_j);  z_0 = key,  z_j = mix64( key + j * G ) for j >= 1
 //   u01(x)                   = ((x >> 8) + 1) * 2^-24   in (0, 1]   (the range of curand_uniform)
 //   mix64 = the SplitMix64 finaliser.
 // Pair 0 is the pixel jitter; at path vertex d pair 1+2d drives the BSDF sample (dielectric: a is the
@@ -152,7 +152,8 @@ __host__ __device__ __forceinline__ uint64_t rng_path_key(uint64_t seedKey, uint
 }
 __host__ __device__ __forceinline__ float rng_u01(uint32_t x) { return (float)((x >> 8) + 1u) * (1.0f / 16777216.0f); }
 __host__ __device__ __forceinline__ void rng_pair(uint64_t key, uint32_t j, float& a, float& b) {
-    uint64_t z = mix64(key + (uint64_t)(j + 1u) * kGolden);
+    // pair 0 (the pixel jitter, drawn for every camera sample) uses the already-mixed key itself: one mix64 less per sample
+    const uint64_t z = j == 0u ? key : mix64(key + (uint64_t)j * kGolden);
     a = rng_u01((uint32_t)(z >> 32));
     b = rng_u01((uint32_t)z);
 }

@@ -118,14 +118,17 @@ struct CameraParams {
     float sensorW, sensorH;
     float invW, invH;
 };
-__device__ __forceinline__ void primary_ray(const CameraParams& cam, int px, int py, float ju, float jv, float3& o, float3& d) {
+__device__ __forceinline__ float3 primary_dir(const CameraParams& cam, int px, int py, float ju, float jv) {
     // one rounding per operation, in the reference's order (bit-identical primary rays)
     float plx = xmul(xadd(ju, (float)px), cam.invW);
     float ply = xmul(xadd(jv, (float)py), cam.invH);
     plx = xmul(plx, cam.sensorW);
     ply = xmul(ply, cam.sensorH);
     const float3 dir = f3(xsub(plx, xmul(0.5f, cam.sensorW)), xsub(ply, xmul(0.5f, cam.sensorH)), -1.0f);
-    d = xnormalize(xmat4_dir(cam.c2w, dir));
+    return xnormalize(xmat4_dir(cam.c2w, dir));
+}
+__device__ __forceinline__ void primary_ray(const CameraParams& cam, int px, int py, float ju, float jv, float3& o, float3& d) {
+    d = primary_dir(cam, px, py, ju, jv);
     o = xmat4_point(cam.c2w, f3(0.f, 0.f, 0.f));
 }
 
@@ -148,11 +151,13 @@ __global__ void __launch_bounds__(256) k_primary_rays(CameraParams cam, int W, i
 template <bool ANY, bool COUNT>
 __global__ void __launch_bounds__(128) k_trace_rays(BvhView bvh, const tpt_ray* __restrict__ rays, size_t n, tpt_hit* __restrict__ hits,
                                                     DeviceCounters* ctr) {
+    int stack[kStackSize];
+    stack[0] = kStackSentinel;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
         const float* r = reinterpret_cast<const float*>(rays + i);
         const float2 a = __ldg(reinterpret_cast<const float2*>(r)), b = __ldg(reinterpret_cast<const float2*>(r) + 1),
                      c = __ldg(reinterpret_cast<const float2*>(r) + 2);
-        const HitRec h = traverse<COUNT>(bvh, f3(a.x, a.y, b.x), f3(b.y, c.x, c.y), ANY, &ctr->node_visits, &ctr->tri_tests);
+        const HitRec h = traverse<COUNT>(bvh, f3(a.x, a.y, b.x), f3(b.y, c.x, c.y), ANY, stack, &ctr->node_visits, &ctr->tri_tests);
         reinterpret_cast<float4*>(hits)[i] = make_float4(__int_as_float(h.prim), h.t, h.u, h.v);
     }
 }
@@ -357,23 +362,27 @@ __global__ void __launch_bounds__(128) k_primary(BvhView bvh, ShadeParams sp, Ca
     const uint32_t pixel = (uint32_t)(px + py * W);
     const uint32_t s0 = g * spt, s1 = min(kSamples, s0 + spt);
     long long aR = 0, aG = 0, aB = 0;
+    int stack[kStackSize];
+    stack[0] = kStackSentinel;
+    const float3 o = xmat4_point(cam.c2w, f3(0.f, 0.f, 0.f));   // the camera position: the same for every sample
     for (uint32_t sl = s0; sl < s1; ++sl) {
         const uint32_t sIdx = sampleBase + sl * sampleStride;
         float ju, jv;
         rng_pair(rng_path_key(sp.seedKey, pixel, sIdx), 0u, ju, jv);
-        float3 o, d;
-        primary_ray(cam, px, py, ju, jv, o, d);
-        const HitRec h = traverse<COUNT>(bvh, o, d, false, &ctr->node_visits, &ctr->tri_tests);
+        const float3 d = primary_dir(cam, px, py, ju, jv);
+        const HitRec h = traverse<COUNT>(bvh, o, d, false, stack, &ctr->node_visits, &ctr->tri_tests);
         float3 term;
         Vertex vx;
         if (shade_vertex(bvh, sp, 0, o, d, f3(1.f, 1.f, 1.f), pixel, sIdx, h, term, vx, ctr)) {
             emit_vertex(sp, q, vx, pixel, sIdx);
-        } else if (finite3(term)) {
-            aR += to_fixed(term.x);
-            aG += to_fixed(term.y);
-            aB += to_fixed(term.z);
-        } else {
-            atomicAdd(&ctr->dropped_nonfinite, 1ull);
+        } else if (term.x != 0.f || term.y != 0.f || term.z != 0.f) {
+            if (finite3(term)) {
+                aR += to_fixed(term.x);
+                aG += to_fixed(term.y);
+                aB += to_fixed(term.z);
+            } else {
+                atomicAdd(&ctr->dropped_nonfinite, 1ull);
+            }
         }
     }
     unsigned long long* dst = acc + 3 * (size_t)pixel;
@@ -448,6 +457,7 @@ __global__ void __launch_bounds__(128, TPT_WAVE_MIN_BLOCKS) k_wave(BvhView bvh, 
     uint32_t* myIdx = sIdx[threadIdx.x >> 5];
     float4* myHit = sHit[threadIdx.x >> 5];
     int stack[kStackSize];
+    stack[0] = kStackSentinel;
     TravState ts;
     ts.cur = kStackSentinel;
     ts.sp = 1;
@@ -535,7 +545,7 @@ __global__ void __launch_bounds__(128, TPT_WAVE_MIN_BLOCKS) k_wave(BvhView bvh, 
                     const float4 a = __ldg(src), b = __ldg(src + 1);
                     kind = isExt ? 0u : 1u + __float_as_uint(__ldg(reinterpret_cast<const float*>(src + 2) + 3));
 #endif
-                    trav_begin(ts, bvh, f3(a.x, a.y, a.z), f3(a.w, b.x, b.y), stack);
+                    trav_begin(ts, bvh, f3(a.x, a.y, a.z), f3(a.w, b.x, b.y));
                 }
                 lo += min((uint32_t)__popc(mEmpty), avail);
             }
@@ -571,61 +581,6 @@ __global__ void __launch_bounds__(128, TPT_WAVE_MIN_BLOCKS) k_wave(BvhView bvh, 
         }
     }
 }
-
-#ifdef TPT_WAVE_CHUNKED
-// tuning variant: static 32-item chunks, plain while-while traversal, shading inline (no ray replacement)
-// ---- wave w >= 1: extension rays towards vertex w + secondary rays of vertex w-1 --------------------------
-template <bool COUNT>
-__global__ void __launch_bounds__(128) k_wave_chunked(BvhView bvh, ShadeParams sp, const float4* __restrict__ extIn, const float4* __restrict__ secIn,
-                                              QueueLevel* __restrict__ levelIn, QueueOut q, unsigned long long* __restrict__ acc,
-                                              DeviceCounters* ctr) {
-    const uint32_t nExt = levelIn->n_ext;
-    const unsigned long long secWord = levelIn->n_sec;
-    const uint32_t nSec = (uint32_t)secWord, nDirect = (uint32_t)(secWord >> 32);
-    if (nExt + nSec == 0u) return;
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
-        atomicAdd(&ctr->rays_extension, (unsigned long long)nExt);
-        atomicAdd(&ctr->rays_direct, (unsigned long long)nDirect);
-        atomicAdd(&ctr->rays_shadow, (unsigned long long)(nSec - nDirect));
-    }
-    const uint32_t chunksExt = (nExt + 31u) >> 5, chunksAll = chunksExt + ((nSec + 31u) >> 5);
-    const int lane = threadIdx.x & 31;
-    while (true) {
-        uint32_t chunk = 0;
-        if (lane == 0) chunk = atomicAdd(&levelIn->cursor, 1u);
-        chunk = __shfl_sync(0xffffffffu, chunk, 0);
-        if (chunk >= chunksAll) break;
-        if (chunk < chunksExt) {
-            const uint32_t i = chunk * 32u + lane;
-            if (i < nExt) {
-                const PathRec p = load_path(extIn, i);
-                const HitRec h = traverse<COUNT>(bvh, p.o, p.d, false, &ctr->node_visits, &ctr->tri_tests);
-                float3 term;
-                Vertex vx;
-                if (shade_vertex(bvh, sp, sp.depth, p.o, p.d, p.T, p.pixel, p.sample, h, term, vx, ctr)) emit_vertex(sp, q, vx, p.pixel, p.sample);
-                else accum_add(acc, p.pixel, term, ctr);
-            }
-        } else {
-            const uint32_t i = (chunk - chunksExt) * 32u + lane;
-            if (i < nSec) {
-                const float4 a = __ldcs(secIn + 3 * (size_t)i), b = __ldcs(secIn + 3 * (size_t)i + 1), c = __ldcs(secIn + 3 * (size_t)i + 2);
-                const float3 o = f3(a.x, a.y, a.z), d = f3(a.w, b.x, b.y), wgt = f3(b.z, b.w, c.x);
-                const uint32_t pixel = __float_as_uint(c.y), kind = __float_as_uint(c.w);
-                const HitRec h = traverse<COUNT>(bvh, o, d, kind == kKindShadow, &ctr->node_visits, &ctr->tri_tests);
-                if (kind == kKindShadow) {
-                    if (h.leaf < 0) accum_add(acc, pixel, wgt, ctr);
-                } else if (h.leaf >= 0) {
-                    const int mtlIdx = __float_as_int(__ldg(bvh.tri_geom + 3 * (size_t)h.leaf + 2).z);
-                    const float e = __ldg(sp.mtl + 2 * mtlIdx).w;
-                    if (e != 0.0f) accum_add(acc, pixel, wgt * e, ctr);
-                }
-            }
-        }
-        __syncwarp();
-    }
-}
-
-#endif
 
 // ---- accumulation buffer utilities ---------------------------------------------------------------
 __global__ void k_accum_add(unsigned long long* __restrict__ dst, const unsigned long long* __restrict__ src, size_t n) {
@@ -818,11 +773,7 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
             if (counted)
                 k_wave<true><<<gridWave, 128, 0, st>>>(view, sp, ctx->q_ext[in], ctx->q_sec[in], static_cast<QueueLevel*>(ctx->levels) + w, q, acc->data, ctx->d_counters);
             else
-#ifdef TPT_WAVE_CHUNKED
-                k_wave_chunked<false><<<kNumSMs * 9, 128, 0, st>>>(view, sp, ctx->q_ext[in], ctx->q_sec[in], static_cast<QueueLevel*>(ctx->levels) + w, q, acc->data, ctx->d_counters);
-#else
                 k_wave<false><<<gridWave, 128, 0, st>>>(view, sp, ctx->q_ext[in], ctx->q_sec[in], static_cast<QueueLevel*>(ctx->levels) + w, q, acc->data, ctx->d_counters);
-#endif
             mark();
         }
         ctx->kernel_launches += 1 + (uint64_t)cfg->max_depth;

@@ -95,8 +95,10 @@ constexpr int kStackSentinel = (int)0x80000000;   // negative, and never a valid
 // "while-while" traversal (Aila & Laine 2009): the inner loop descends internal nodes until the lane holds
 // a leaf, so that the lanes of a warp run their (expensive, exactly-rounded) triangle tests together
 // instead of one lane's leaf serialising against the other lanes' box tests.
+// `stack` is caller-owned (kStackSize ints) with stack[0] == kStackSentinel already written: a kernel that
+// traces many rays per thread initialises it once.
 template <bool COUNT>
-__device__ __forceinline__ HitRec traverse(const BvhView& bvh, float3 o, float3 d, bool anyHit, unsigned long long* nodeVisits,
+__device__ __forceinline__ HitRec traverse(const BvhView& bvh, float3 o, float3 d, bool anyHit, int* stack, unsigned long long* nodeVisits,
                                            unsigned long long* triTests) {
     HitRec best;
     best.t = FLT_MAX;
@@ -105,8 +107,6 @@ __device__ __forceinline__ HitRec traverse(const BvhView& bvh, float3 o, float3 
     best.prim = -1;
 
     const float3 inv = f3(safe_rcp(d.x), safe_rcp(d.y), safe_rcp(d.z));
-    int stack[kStackSize];
-    stack[0] = kStackSentinel;
     int sp = 1;
     int cur = bvh.n_faces > 1 ? 0 : ~0;   // single-triangle scene: the root is leaf 0
     unsigned nv = 0, nt = 0;
@@ -157,7 +157,8 @@ struct TravState {
     HitRec best;
     int cur, sp;
 };
-__device__ __forceinline__ void trav_begin(TravState& s, const BvhView& bvh, float3 o, float3 d, int* stack) {
+// stack[0] must hold kStackSentinel (written once by the kernel)
+__device__ __forceinline__ void trav_begin(TravState& s, const BvhView& bvh, float3 o, float3 d) {
     s.o = o;
     s.d = d;
     s.inv = f3(safe_rcp(d.x), safe_rcp(d.y), safe_rcp(d.z));
@@ -165,7 +166,6 @@ __device__ __forceinline__ void trav_begin(TravState& s, const BvhView& bvh, flo
     s.best.u = s.best.v = 0.0f;
     s.best.leaf = -1;
     s.best.prim = -1;
-    stack[0] = kStackSentinel;
     s.sp = 1;
     s.cur = bvh.n_faces > 1 ? 0 : ~0;
 }
