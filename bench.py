@@ -271,6 +271,120 @@ def run_ours(args):
         print(json.dumps(line))
 
 
+def run_soup(args):
+    """BASELINE.json configs[3]: synthetic 10 000 004-triangle instanced soup — BVH build time and primary / secondary
+    ray traversal throughput through tpt_trace_rays (device buffers for `value`, host buffers for `e2e`)."""
+    import torch
+    import tinypathtracer_b200 as tpt
+    from tinypathtracer_b200.api import primary_rays_device
+    from tinypathtracer_b200.scene_io import scene_upload_bytes
+    from tinypathtracer_b200.soup import make_soup, secondary_rays
+
+    rank, world, local = dist_env()
+    torch.cuda.set_device(local)
+    nb, nx = (8192, 3211) if not args.soup_small else (64, 25)
+    scene = make_soup(load_scene("ball"), nb, nx)
+    F = scene["indices"].size // 3
+    W, H = 3840, 2160
+    ctx = tpt.Context(local)
+    stream = torch.cuda.current_stream()
+    ctx.set_stream(stream.cuda_stream)
+    dscene = tpt.DeviceScene(ctx, scene)
+    bvh = tpt.BVH(dscene)
+    cam = tpt.Camera.from_scene(scene)
+    n = W * H
+    rays_t = torch.empty((n, 6), dtype=torch.float32, device="cuda")
+    hits_t = torch.empty((n, 4), dtype=torch.float32, device="cuda")
+    # ---- BVH build: median of 5 after warm-up (CUDA events inside tpt_bvh_build)
+    for _ in range(max(1, args.warmup)):
+        bvh.construct(stats=True)
+    builds = sorted(bvh.construct(stats=True)["build_ms"] for _ in range(5))
+    build_ms = builds[2]
+    bstats = bvh.stats
+    # ---- ray sets: primary = pixel centres; secondary = one cosine ray per primary hit (seeded, host-generated once)
+    primary_rays_device(ctx, cam, W, H, rays_t.data_ptr())
+    bvh.trace_device(rays_t.data_ptr(), n, hits_t.data_ptr())
+    torch.cuda.synchronize()
+    rays_h = rays_t.cpu().numpy().view(tpt.RAY_DTYPE).reshape(-1)
+    hits_h = hits_t.cpu().numpy().view(tpt.HIT_DTYPE).reshape(-1)
+    wv, _ = dscene.world()
+    sec_h = secondary_rays(rays_h, hits_h, wv, scene["indices"])
+    ns = sec_h.shape[0]
+    sec_t = torch.from_numpy(sec_h.view(np.float32).reshape(-1, 6)).cuda()
+    sec_hits_t = torch.empty((ns, 4), dtype=torch.float32, device="cuda")
+
+    def timed(fn, steps):
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(steps):
+            fn()
+        e1.record(stream)
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / steps
+
+    def step():   # one pass of the hot path over the batch: both ray sets
+        bvh.trace_device(rays_t.data_ptr(), n, hits_t.data_ptr())
+        bvh.trace_device(sec_t.data_ptr(), ns, sec_hits_t.data_ptr())
+
+    for _ in range(args.warmup):
+        step()
+    ctx.reset_counters()
+    clocks = ClockSampler(local)
+    clocks.start()
+    ms_step = timed(step, args.steps)
+    clk = clocks.stop()
+    launches = ctx.counters()["kernel_launches"]
+    ms_pri = timed(lambda: bvh.trace_device(rays_t.data_ptr(), n, hits_t.data_ptr()), args.steps)
+    ms_sec = timed(lambda: bvh.trace_device(sec_t.data_ptr(), ns, sec_hits_t.data_ptr()), args.steps)
+    # ---- e2e: host ray buffers in, host hits out, through tpt_trace_rays(device_ptrs = 0)
+    hits_host = np.zeros(n, tpt.HIT_DTYPE)
+    t0 = time.perf_counter()
+    for _ in range(max(1, args.steps // 2)):
+        hp = bvh.trace(rays_h)
+        hs = bvh.trace(sec_h)
+    e2e_ms = (time.perf_counter() - t0) * 1e3 / max(1, args.steps // 2)
+    # ---- counted pass for the roofline: node / triangle visits per ray on the same tree
+    ctx.reset_counters()
+    bvh.trace_device(rays_t.data_ptr(), n, hits_t.data_ptr(), counted=True)
+    c_pri = ctx.counters()
+    ctx.reset_counters()
+    bvh.trace_device(sec_t.data_ptr(), ns, sec_hits_t.data_ptr(), counted=True)
+    c_sec = ctx.counters()
+    peaks = {}
+    try:
+        peaks = json.loads((ROOT / "MEASURED_PEAKS.json").read_text())
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    bpr_sec = 56.0 * c_sec["node_visits"] / ns + 40.0 * c_sec["tri_tests"] / ns + 88.0
+    bpr_pri = 56.0 * c_pri["node_visits"] / n + 40.0 * c_pri["tri_tests"] / n + 88.0
+    ach = bpr_sec * ns / (ms_sec * 1e-3) / 1e9
+    build_gbs = 408.0 * F / (build_ms * 1e-3) / 1e9
+    line = {
+        "metric": "Mrays/s (tpt_trace_rays, primary + secondary ray sets; BVH build ms beside it)", "value": round((n + ns) / (ms_step * 1e-3) / 1e6, 2),
+        "unit": "Mrays/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 3), "higher_is_better": True,
+        "scaling": "replicas only", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"synthetic soup {F} triangles ({nb} spheres x 1216 + {nx} boxes x 12), {W}x{H} pixel-centre primary rays + {ns} cosine secondary rays",
+                   "l2": "BVH (640 MB nodes + 480 MB triangles) and ray buffers exceed the 126 MB L2"},
+        "bvh_build_ms": round(build_ms, 4), "bvh_build_ms_all": [round(b, 4) for b in builds], "bvh_faces": int(F), "bvh_max_depth": bstats["max_depth"],
+        "bvh_sah_cost": round(bstats["sah_cost"], 2),
+        "primary_mrays_per_s": round(n / (ms_pri * 1e-3) / 1e6, 2), "secondary_mrays_per_s": round(ns / (ms_sec * 1e-3) / 1e6, 2),
+        "primary_hit_fraction": round(float((hits_h["prim"] >= 0).mean()), 4),
+        "e2e": {"value": round((n + ns) / (e2e_ms * 1e-3) / 1e6, 2), "unit": "Mrays/s", "ms_per_step": round(e2e_ms, 3),
+                "h2d_bytes_per_step": int((n + ns) * 24), "d2h_bytes_per_step": int((n + ns) * 16)},
+        "gpu_launches": int(launches), "clocks": clk,
+        "roofline": {"bound": "hbm", "kernel": "k_trace_rays (secondary ray set, incoherent)", "achieved": round(ach, 2), "peak": peak,
+                     "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback (B200_PROFILING.md)", "unit": "GB/s", "frac": round(ach / peak, 5),
+                     "traffic": None, "bytes_per_ray": round(bpr_sec, 1), "n_int_per_ray": round(c_sec["node_visits"] / ns, 2),
+                     "n_leaf_per_ray": round(c_sec["tri_tests"] / ns, 2), "rays_per_launch": ns, "avg_launch_us": round(ms_sec * 1e3, 1),
+                     "primary": {"bytes_per_ray": round(bpr_pri, 1), "n_int_per_ray": round(c_pri["node_visits"] / n, 2),
+                                 "n_leaf_per_ray": round(c_pri["tri_tests"] / n, 2), "achieved": round(bpr_pri * n / (ms_pri * 1e-3) / 1e9, 2)},
+                     "bvh_build": {"algorithmic_bytes_per_triangle": 408, "achieved": round(build_gbs, 2), "frac": round(build_gbs / peak, 5)}},
+    }
+    print(json.dumps(line))
+
+
 def cpu_baseline(args, fixture, W, H, depth, env, seed):
     """The oracle (a port: the reference has no CPU path) on a bounded sample of the same workload."""
     from oracle import gltf_scene, pyoracle as orc
@@ -363,7 +477,8 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="ball", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="ball", choices=sorted(WORKLOADS) + ["soup"])
+    ap.add_argument("--soup-small", action="store_true", help="soup workload at 1/128 size (smoke test)")
     ap.add_argument("--spp", type=int, default=0, help="override the workload's spp (multiple of 8)")
     ap.add_argument("--paths-in-flight", type=int, default=0)
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
@@ -371,7 +486,9 @@ def main():
     ap.add_argument("--ref-cpu", action="store_true", help="reference arm: force the CPU oracle port")
     ap.add_argument("--ref-timeout", type=float, default=900.0)
     args = ap.parse_args()
-    if args.impl == "reference":
+    if args.workload == "soup" and args.impl != "reference":
+        run_soup(args)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_ours(args)

@@ -81,6 +81,10 @@ class Context:
         return rays
 
 
+def primary_rays_device(ctx: Context, cam: "Camera", width: int, height: int, rays_ptr: int, jitter: bool = False, seed: int = 0):
+    check(lib.tpt_generate_primary_rays(ctx._h, C.byref(cam.c), width, height, int(jitter), seed, C.c_void_p(rays_ptr), 1))
+
+
 class Camera:
     """include/camera.h: vfov in radians, aspect from the glTF camera, c2w = Transform::localToWorld()."""
 
@@ -194,6 +198,12 @@ class BVH:
         fn = lib.tpt_trace_rays_counted if counted else lib.tpt_trace_rays
         check(fn(self.scene._h, _ptr(rays), rays.shape[0], _ptr(hits), int(any_hit), 0))
         return hits
+
+
+    def trace_device(self, rays_ptr: int, n: int, hits_ptr: int, any_hit: bool = False, counted: bool = False):
+        """Same entry with DEVICE buffers (n tpt_ray in, n tpt_hit out), asynchronous on the context stream."""
+        fn = lib.tpt_trace_rays_counted if counted else lib.tpt_trace_rays
+        check(fn(self.scene._h, C.c_void_p(rays_ptr), n, C.c_void_p(hits_ptr), int(any_hit), 1))
 
 
 class EnvLight:

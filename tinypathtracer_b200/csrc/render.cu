@@ -582,6 +582,83 @@ __global__ void __launch_bounds__(128, TPT_WAVE_MIN_BLOCKS) k_wave(BvhView bvh, 
     }
 }
 
+// ---- tpt_trace_rays, persistent form: the scheduler of k_wave without the shading ------------------------
+template <bool COUNT>
+__global__ void __launch_bounds__(128, 10) k_trace_rays_persistent(BvhView bvh, const tpt_ray* __restrict__ rays, unsigned long long n,
+                                                                   tpt_hit* __restrict__ hits, int anyHit, unsigned long long* cursor,
+                                                                   DeviceCounters* ctr) {
+    const uint32_t lane = threadIdx.x & 31, ltMask = (1u << lane) - 1u;
+    const unsigned long long perWarp = n / ((unsigned long long)gridDim.x * 8ull);
+    const unsigned long long grab = perWarp >= kGrabMax ? kGrabMax : (perWarp >= 32ull ? (perWarp & ~31ull) : 32ull);
+    int stack[kStackSize];
+    stack[0] = kStackSentinel;
+    TravState ts;
+    ts.cur = kStackSentinel;
+    ts.sp = 1;
+    unsigned long long item = ~0ull, lo = 0, hi = 0;
+    bool more = true;
+    unsigned nv = 0, nt = 0;
+    while (true) {
+        const unsigned mNode = __ballot_sync(0xffffffffu, ts.cur >= 0);
+        const unsigned mLeaf = __ballot_sync(0xffffffffu, ts.cur < 0 && ts.cur != kStackSentinel);
+        const unsigned mBusy = mNode | mLeaf;
+        if (mBusy == 0u || (more && 32 - __popc(mBusy) >= kRefillThreshold)) {
+            if (item != ~0ull && !((mBusy >> lane) & 1u)) {   // retire: write the hit
+                reinterpret_cast<float4*>(hits)[item] = make_float4(__int_as_float(ts.best.prim), ts.best.t, ts.best.u, ts.best.v);
+                item = ~0ull;
+            }
+            if (more && lo == hi) {
+                if (lane == 0) lo = atomicAdd(cursor, grab);
+                lo = __shfl_sync(0xffffffffu, lo, 0);
+                hi = min(lo + grab, n);
+                if (lo >= n) {
+                    more = false;
+                    lo = hi = 0;
+                }
+            }
+            if (more) {
+                const bool empty = item == ~0ull;
+                const unsigned mEmpty = __ballot_sync(0xffffffffu, empty);
+                const unsigned long long avail = hi - lo;
+                const uint32_t rank = __popc(mEmpty & ltMask);
+                if (empty && rank < avail) {
+                    item = lo + rank;
+                    const float2* r = reinterpret_cast<const float2*>(rays + item);
+                    const float2 a = __ldg(r), b = __ldg(r + 1), c = __ldg(r + 2);
+                    trav_begin(ts, bvh, f3(a.x, a.y, b.x), f3(b.y, c.x, c.y));
+                }
+                lo += min((unsigned long long)__popc(mEmpty), avail);
+            }
+            if (!more && __ballot_sync(0xffffffffu, item != ~0ull) == 0u) break;
+            continue;
+        }
+        if (__popc(mNode) >= __popc(mLeaf)) {
+            const int keep = max(1, (3 * __popc(mNode)) >> 2);
+            do {
+                if (ts.cur >= 0) {
+                    trav_node_step(ts, bvh, stack);
+                    if (COUNT) ++nv;
+                }
+            } while (__popc(__ballot_sync(0xffffffffu, ts.cur >= 0)) >= keep);
+        } else {
+            const int keep = max(1, (3 * __popc(mLeaf)) >> 2);
+            do {
+                if (ts.cur < 0 && ts.cur != kStackSentinel) {
+                    trav_leaf_step(ts, bvh, anyHit != 0, stack);
+                    if (COUNT) ++nt;
+                }
+            } while (__popc(__ballot_sync(0xffffffffu, ts.cur < 0 && ts.cur != kStackSentinel)) >= keep);
+        }
+    }
+    if (COUNT) {
+        const unsigned sv = __reduce_add_sync(0xffffffffu, nv), st = __reduce_add_sync(0xffffffffu, nt);
+        if (lane == 0) {
+            atomicAdd(&ctr->node_visits, (unsigned long long)sv);
+            atomicAdd(&ctr->tri_tests, (unsigned long long)st);
+        }
+    }
+}
+
 // ---- accumulation buffer utilities ---------------------------------------------------------------
 __global__ void k_accum_add(unsigned long long* __restrict__ dst, const unsigned long long* __restrict__ src, size_t n) {
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) dst[i] += src[i];
@@ -636,6 +713,13 @@ static CameraParams make_camera(const tpt_camera* cam, int W, int H) {
     return c;
 }
 
+template <typename K>
+static int resident_blocks(K kernel, int block) {
+    int n = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, block, 0) != cudaSuccess || n < 1) n = 1;
+    return n;
+}
+
 int tpt_primary_rays_impl(tpt_context* ctx, const tpt_camera* cam, int W, int H, int jitter, uint64_t seed, tpt_ray* d_rays) {
     k_primary_rays<<<grid_for((size_t)W * H, 256, kNumSMs * 8), 256, 0, ctx->stream>>>(make_camera(cam, W, H), W, H, jitter, rng_seed_key(seed), d_rays);
     TPT_CUDA(cudaGetLastError());
@@ -645,14 +729,28 @@ int tpt_primary_rays_impl(tpt_context* ctx, const tpt_camera* cam, int W, int H,
 
 int tpt_trace_rays_impl(tpt_scene* s, const tpt_ray* d_rays, size_t n, tpt_hit* d_hits, int anyHit, int counted) {
     tpt_context* ctx = s->ctx;
-    const unsigned grid = grid_for(n, 128, kNumSMs * 16);
     const BvhView v = s->view();
-    if (anyHit) {
-        if (counted) k_trace_rays<true, true><<<grid, 128, 0, ctx->stream>>>(v, d_rays, n, d_hits, ctx->d_counters);
-        else k_trace_rays<true, false><<<grid, 128, 0, ctx->stream>>>(v, d_rays, n, d_hits, ctx->d_counters);
+    static const bool simple = getenv("TPT_TRACE_SIMPLE") != nullptr;   // tuning switch: static grid-stride kernel
+    if (simple) {
+        const unsigned grid = grid_for(n, 128, kNumSMs * 16);
+        if (anyHit) {
+            if (counted) k_trace_rays<true, true><<<grid, 128, 0, ctx->stream>>>(v, d_rays, n, d_hits, ctx->d_counters);
+            else k_trace_rays<true, false><<<grid, 128, 0, ctx->stream>>>(v, d_rays, n, d_hits, ctx->d_counters);
+        } else {
+            if (counted) k_trace_rays<false, true><<<grid, 128, 0, ctx->stream>>>(v, d_rays, n, d_hits, ctx->d_counters);
+            else k_trace_rays<false, false><<<grid, 128, 0, ctx->stream>>>(v, d_rays, n, d_hits, ctx->d_counters);
+        }
     } else {
-        if (counted) k_trace_rays<false, true><<<grid, 128, 0, ctx->stream>>>(v, d_rays, n, d_hits, ctx->d_counters);
-        else k_trace_rays<false, false><<<grid, 128, 0, ctx->stream>>>(v, d_rays, n, d_hits, ctx->d_counters);
+        if (!ctx->trace_cursor) TPT_CUDA(cudaMalloc(&ctx->trace_cursor, sizeof(unsigned long long)));
+        if (ctx->trace_grid == 0) {
+            ctx->trace_grid = kNumSMs * resident_blocks(k_trace_rays_persistent<false>, 128);
+            ctx->trace_grid_counted = kNumSMs * resident_blocks(k_trace_rays_persistent<true>, 128);
+        }
+        TPT_CUDA(cudaMemsetAsync(ctx->trace_cursor, 0, sizeof(unsigned long long), ctx->stream));
+        if (counted)
+            k_trace_rays_persistent<true><<<ctx->trace_grid_counted, 128, 0, ctx->stream>>>(v, d_rays, n, d_hits, anyHit, ctx->trace_cursor, ctx->d_counters);
+        else
+            k_trace_rays_persistent<false><<<ctx->trace_grid, 128, 0, ctx->stream>>>(v, d_rays, n, d_hits, anyHit, ctx->trace_cursor, ctx->d_counters);
     }
     TPT_CUDA(cudaGetLastError());
     ctx->kernel_launches += 1;
@@ -689,12 +787,6 @@ static int ensure_pools(tpt_context* ctx, size_t paths, size_t secPerPath) {
     return TPT_OK;
 }
 
-template <typename K>
-static int resident_blocks(K kernel, int block) {
-    int n = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, block, 0) != cudaSuccess || n < 1) n = 1;
-    return n;
-}
 
 int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config* cfg, tpt_accum* acc) {
     tpt_context* ctx = s->ctx;

@@ -55,6 +55,8 @@ struct tpt_context {
     size_t ext_capacity = 0, sec_capacity = 0;
     void* levels = nullptr;                       // QueueLevel[kMaxLevels] (render.cu)
     unsigned wave_grid = 0, wave_grid_counted = 0; // persistent grid sizes of k_wave (148 x resident blocks)
+    unsigned long long* trace_cursor = nullptr;    // item cursor of k_trace_rays_persistent
+    unsigned trace_grid = 0, trace_grid_counted = 0;
     // scratch for trace_rays with host pointers
     void* io_rays = nullptr;
     void* io_hits = nullptr;
