@@ -64,7 +64,7 @@ class ClockSampler:
         q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "200", "-i", str(self.index)],
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(self.index)],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -333,17 +333,27 @@ def run_soup(args):
     clocks = ClockSampler(local)
     clocks.start()
     ms_step = timed(step, args.steps)
-    clk = clocks.stop()
     launches = ctx.counters()["kernel_launches"]
+    timed(step, max(args.steps, 40))            # keep the GPU under the same load long enough for nvidia-smi's 100 ms sampler
+    clk = clocks.stop()
     ms_pri = timed(lambda: bvh.trace_device(rays_t.data_ptr(), n, hits_t.data_ptr()), args.steps)
     ms_sec = timed(lambda: bvh.trace_device(sec_t.data_ptr(), ns, sec_hits_t.data_ptr()), args.steps)
     # ---- e2e: host ray buffers in, host hits out, through tpt_trace_rays(device_ptrs = 0)
-    hits_host = np.zeros(n, tpt.HIT_DTYPE)
+    def pinned(a):   # host staging in page-locked memory, as a caller who cares about PCIe throughput would hold it
+        t = torch.from_numpy(a.view(np.float32).reshape(a.shape[0], -1).copy()).pin_memory()
+        return t, t.numpy().view(a.dtype).reshape(-1)
+    _k1, rays_p = pinned(rays_h)
+    _k2, sec_p = pinned(sec_h)
+    _k3, hits_p = pinned(np.zeros(n, tpt.HIT_DTYPE))
+    _k4, shits_p = pinned(np.zeros(ns, tpt.HIT_DTYPE))
+    bvh.trace(rays_p, out=hits_p)
+    reps = max(1, args.steps // 2)
     t0 = time.perf_counter()
-    for _ in range(max(1, args.steps // 2)):
-        hp = bvh.trace(rays_h)
-        hs = bvh.trace(sec_h)
-    e2e_ms = (time.perf_counter() - t0) * 1e3 / max(1, args.steps // 2)
+    for _ in range(reps):
+        bvh.trace(rays_p, out=hits_p)
+        bvh.trace(sec_p, out=shits_p)
+    e2e_ms = (time.perf_counter() - t0) * 1e3 / reps
+    assert np.array_equal(hits_p["prim"], hits_h["prim"])
     # ---- counted pass for the roofline: node / triangle visits per ray on the same tree
     ctx.reset_counters()
     bvh.trace_device(rays_t.data_ptr(), n, hits_t.data_ptr(), counted=True)
@@ -415,6 +425,8 @@ def run_reference(args):
     rank, world, local = dist_env()
     if rank != 0:
         return
+    if args.workload == "soup":
+        return run_reference_soup(args)
     fixture, W, H, spp, depth, envkind, seed = WORKLOADS[args.workload]
     if args.spp:
         spp = args.spp
@@ -442,6 +454,102 @@ def run_reference(args):
                       "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg, "cpu_baseline": cb,
                       "reference_kind": "cpu oracle port (reference CUDA build not present)",
                       "e2e": {"value": round(v, 4), "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+def _world_vertices_numpy(scene):
+    """object -> world vertices with the reference's operation order in float32 (bit-identical to its transform kernel)."""
+    idx = np.asarray(scene["indices"]).reshape(-1, 3)
+    face_obj = np.searchsorted(scene["objects"]["begin"], np.arange(idx.shape[0]), side="right") - 1
+    vobj = np.zeros(scene["vertices"].shape[0], np.int64)
+    for k in range(3):
+        vobj[idx[:, k]] = face_obj
+    m = np.asarray(scene["vert_trans"], np.float32)[vobj]
+    v = np.asarray(scene["vertices"], np.float32)
+    out = np.empty_like(v)
+    for i in range(3):
+        out[:, i] = ((m[:, i] * v[:, 0] + m[:, 4 + i] * v[:, 1]) + m[:, 8 + i] * v[:, 2]) + m[:, 12 + i]
+    return out
+
+
+def _reference_morton_cells(c):
+    """floatTo21Int of the reference (src/bvh.cu:23-46), vectorised: the 21-bit cell of one coordinate."""
+    ix = np.ascontiguousarray(c, np.float32).view(np.int32).astype(np.int64)
+    exponent = ((ix >> 23) & 0xff) - 127
+    mant = (ix & 0x00ffffff) | 0x00800000
+    sign = np.where(ix < 0, -1, 1)
+    sh = np.clip(np.abs(exponent), 0, 31)
+    value = np.where(exponent >= 8, 2**31 - 1, np.where(exponent >= 0, mant << sh, mant >> sh))
+    value = (value * sign + (2**31 - 1)) & 0xffffffff
+    return (value & 0xfffff800) >> 11
+
+
+def run_reference_soup(args):
+    """configs[3] through the reference's own BVH::construct and traverseBVH (oracle/_ref/tpt_ref_headless --soup),
+    on the same world-space triangles and the same two ray files as the product arm."""
+    import tempfile
+    from oracle import pyoracle as orc
+    from tinypathtracer_b200.soup import make_soup, secondary_rays
+    from tinypathtracer_b200.scene_io import load_scene_npz
+    exe = ROOT / "oracle" / "_ref" / "tpt_ref_headless"
+    if not exe.exists():
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/tpt_ref_headless is not built (needs /root/reference at build time)"}))
+        return
+    nb, nx = (8192, 3211) if not args.soup_small else (64, 25)
+    scene = make_soup(load_scene_npz(ROOT / "tests" / "golden" / "scenes" / "ball.npz"), nb, nx)
+    F = scene["indices"].size // 3
+    W, H = 3840, 2160
+    wv = _world_vertices_numpy(scene)
+    # the reference's hierarchy breaks (and its refit can spin forever) on runs of >= 3 equal Morton keys (SURVEY fact 9): check first
+    tri = wv[np.asarray(scene["indices"]).reshape(-1, 3)]
+    ctr = (tri.min(1) + tri.max(1)) * np.float32(0.5)
+    cells = (_reference_morton_cells(ctr[:, 0]) | (_reference_morton_cells(ctr[:, 1]) << 21) | (_reference_morton_cells(ctr[:, 2]) << 42))
+    _, counts = np.unique(cells, return_counts=True)
+    if counts.max() >= 3:
+        print(json.dumps({"impl": "reference", "unavailable": f"soup has a run of {int(counts.max())} equal reference Morton keys: its builder would hang"}))
+        return
+    rays = orc.primary_rays(scene, W, H).astype(np.float32).reshape(-1, 6)
+    tmp = Path(tempfile.mkdtemp(prefix="tpt_soup_"))
+
+    def write(path, rb):
+        with open(path, "wb") as f:
+            np.array([wv.shape[0], F, rays.shape[0], rb.shape[0]], np.uint64).tofile(f)
+            wv.tofile(f)
+            np.asarray(scene["indices"], np.uint32).tofile(f)
+            rays.tofile(f)
+            rb.tofile(f)
+
+    def run(path, out, builds, reps):
+        cmd = [str(exe), "--soup", str(path), "--soup-builds", str(builds), "--soup-reps", str(reps)] + (["--out", str(out)] if out else [])
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=args.ref_timeout)
+        return json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1])
+
+    try:
+        # pass 1: primary rays only -> the reference's own hits -> the seeded secondary ray file
+        write(tmp / "a.bin", np.zeros((0, 6), np.float32))
+        run(tmp / "a.bin", tmp / "a.hits", 1, 1)
+        hs = np.fromfile(tmp / "a.hits", np.dtype([("prim", "<i4"), ("t", "<f4"), ("u", "<f4"), ("v", "<f4")]))
+        rs = rays.view(np.dtype([("origin", "<f4", (3,)), ("dir", "<f4", (3,))])).reshape(-1)
+        sec = secondary_rays(rs, hs, wv, scene["indices"]).view(np.float32).reshape(-1, 6)
+        write(tmp / "b.bin", sec)
+        d = run(tmp / "b.bin", None, max(1, min(args.steps, 3)), max(1, min(args.steps, 3)))
+    except Exception as e:
+        print(json.dumps({"impl": "reference", "unavailable": f"reference soup run failed: {e}"}))
+        return
+    finally:
+        import shutil
+        shutil.rmtree(tmp, ignore_errors=True)
+    n, ns = d["primary_rays"], d["secondary_rays"]
+    ms = d["primary_ms"] + d["secondary_ms"]
+    v = (n + ns) / (ms * 1e-3) / 1e6
+    print(json.dumps({"impl": "reference", "metric": "Mrays/s (tpt_trace_rays, primary + secondary ray sets; BVH build ms beside it)", "value": round(v, 3),
+                      "unit": "Mrays/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms, 3), "higher_is_better": True,
+                      "scaling": "replicas only", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                      "config": {"workload": f"synthetic soup {F} triangles, {W}x{H} pixel-centre primary rays + {ns} cosine secondary rays"},
+                      "bvh_build_ms": d["bvh_build_ms"], "primary_mrays_per_s": round(n / d["primary_ms"] / 1e3, 3),
+                      "secondary_mrays_per_s": round(ns / d["secondary_ms"] / 1e3, 3), "primary_hit_fraction": round(float((hs["prim"] >= 0).mean()), 4),
+                      "reference_kind": f"reference BVH::construct + traverseBVH, headless, {d['build']}, on GPU 0",
+                      "cpu_baseline": {"value": round(v, 3), "unit": "Mrays/s", "cores": 0, "kind": "reference", "sample": "whole workload on the GPU (the reference has no CPU path)"},
+                      "e2e": {"value": round(v, 3), "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
 
 
 def run_reference_cuda(args, exe, ref_scene, W, H, spp, depth, envkind, cfg):

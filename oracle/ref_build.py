@@ -118,6 +118,10 @@ def main():
     patch_sources()
     copy_inputs()
     built = {}
+    try:   # a partial rebuild keeps the record of the other targets
+        built = json.loads((OUT / "BUILD.json").read_text()).get("built", {})
+    except Exception:
+        pass
     only = set(sys.argv[1:])
     targets = [("libref_host.so", None), ("tpt_ref_headless", (["-O3", "-arch=sm_100"], 8, "-O3 -arch=sm_100")),
                ("tpt_ref_headless_d32", (["-O3", "-arch=sm_100"], 32, "-O3 -arch=sm_100 DEPTH_TRACE=32")),

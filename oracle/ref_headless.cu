@@ -9,6 +9,7 @@
 //   * extern "C" hooks around the reference's own CUDA_CALLABLE functions compiled for the HOST (traverseBVH,
 //     rayHitTriangle, rayHitBBox, reflect/refract/shlickFresnel, getMortonCode, DeltaLight::sample, Vec2UV,
 //     Transform::localToWorld, Mat4 inverse/transpose, Scene loader) — used to pin the oracle in this container.
+#include <algorithm>
 #include <chrono>
 #include <cstdio>
 #include <cstring>
@@ -60,12 +61,85 @@ void VkEngine::cleanup() {
 }
 void VkEngine::render() {}
 
+
+// ---- BASELINE.json configs[3]: the reference's own BVH::construct (src/bvh.cu:304-331) and traverseBVH
+// (src/path_tracer.cu:61-107) on a pre-flattened world-space triangle soup and two ray files --------------------
+// File: uint64 {V, F, nA, nB}; float[3V] world vertices; uint32[3F] indices; float[6 nA] rays A; float[6 nB] rays B.
+__global__ void tptRefTraceRays(const float* rays6, size_t n, BVHNode* nodes, Vec3* vertices, uint32_t* indices, int nFaces, HitStatus* hits)
+{
+	size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	Ray r(Vec3(rays6[6 * i], rays6[6 * i + 1], rays6[6 * i + 2]), Vec3(rays6[6 * i + 3], rays6[6 * i + 4], rays6[6 * i + 5]));
+	HitStatus st;
+	traverseBVH(r, nodes, vertices, indices, nFaces, st);
+	hits[i] = st;
+}
+
+static int runSoup(const std::string& file, const std::string& out, int builds, int reps)
+{
+	FILE* f = fopen(file.c_str(), "rb");
+	if (!f) { fprintf(stderr, "cannot open %s\n", file.c_str()); return 2; }
+	unsigned long long hdr[4];
+	if (fread(hdr, 8, 4, f) != 4) return 2;
+	const size_t V = hdr[0], F = hdr[1], nA = hdr[2], nB = hdr[3];
+	std::vector<Vec3> hv(V);
+	std::vector<uint32_t> hi(3 * F);
+	std::vector<float> ra(6 * nA), rb(6 * nB);
+	if (fread(hv.data(), 12, V, f) != V || fread(hi.data(), 4, 3 * F, f) != 3 * F || fread(ra.data(), 24, nA, f) != nA || fread(rb.data(), 24, nB, f) != nB) return 2;
+	fclose(f);
+	thrust::device_vector<Vec3> dv(hv.begin(), hv.end());
+	thrust::device_vector<uint32_t> di(hi.begin(), hi.end());
+	BVH bvh(F);
+	std::vector<double> buildMs;
+	for (int b = 0; b < builds; ++b) {
+		auto t0 = std::chrono::steady_clock::now();
+		bvh.construct(dv, di);                       // synchronises internally (src/bvh.cu:325,328,330)
+		auto t1 = std::chrono::steady_clock::now();
+		buildMs.push_back(std::chrono::duration<double, std::milli>(t1 - t0).count());
+	}
+	std::sort(buildMs.begin(), buildMs.end());
+	double ms[2] = {0, 0};
+	std::vector<HitStatus> hostHits;
+	FILE* fo = out.empty() ? nullptr : fopen(out.c_str(), "wb");
+	for (int set = 0; set < 2; ++set) {
+		const std::vector<float>& r = set ? rb : ra;
+		const size_t n = set ? nB : nA;
+		thrust::device_vector<float> dr(r.begin(), r.end());
+		thrust::device_vector<HitStatus> dh(n);
+		cudaEvent_t e0, e1;
+		cudaEventCreate(&e0); cudaEventCreate(&e1);
+		for (int k = 0; k < reps + 1; ++k) {          // first pass is the warm-up
+			if (k == 1) cudaEventRecord(e0);
+			tptRefTraceRays KERNEL_DIM((unsigned)((n + 255) / 256), 256) (thrust::raw_pointer_cast(dr.data()), n, thrust::raw_pointer_cast(bvh.m_nodes.data()),
+				thrust::raw_pointer_cast(dv.data()), thrust::raw_pointer_cast(di.data()), (int)F, thrust::raw_pointer_cast(dh.data()));
+		}
+		cudaEventRecord(e1);
+		CUDA_CHECK(cudaDeviceSynchronize());
+		float t = 0;
+		cudaEventElapsedTime(&t, e0, e1);
+		ms[set] = t / reps;
+		if (fo) {
+			hostHits.resize(n);
+			thrust::copy(dh.begin(), dh.end(), hostHits.begin());
+			fwrite(hostHits.data(), sizeof(HitStatus), n, fo);
+		}
+	}
+	if (fo) fclose(fo);
+	printf("{\"faces\": %zu, \"bvh_build_ms\": %.4f, \"bvh_build_ms_min\": %.4f, \"builds\": %d, \"primary_rays\": %zu, \"primary_ms\": %.4f, \"secondary_rays\": %zu, \"secondary_ms\": %.4f, \"build\": \"%s\"}\n",
+		F, buildMs[buildMs.size() / 2], buildMs[0], builds, nA, ms[0], nB, ms[1], TPT_REF_BUILD);
+	return 0;
+}
+
 #ifndef TPT_REF_NO_MAIN
 int main(int argc, char** argv) {
-    std::string scene, env;
+    std::string scene, env, soup;
+    int soupBuilds = 1, soupReps = 1;
     for (int i = 1; i + 1 < argc; i += 2) {
         std::string k = argv[i], v = argv[i + 1];
         if (k == "--scene") scene = v;
+        else if (k == "--soup") soup = v;
+        else if (k == "--soup-builds") soupBuilds = atoi(v.c_str());
+        else if (k == "--soup-reps") soupReps = atoi(v.c_str());
         else if (k == "--env") env = v;
         else if (k == "--width") g_tpt_ref_width = (uint32_t)atoi(v.c_str());
         else if (k == "--height") g_tpt_ref_height = (uint32_t)atoi(v.c_str());
@@ -74,6 +148,10 @@ int main(int argc, char** argv) {
         else if (k == "--warmup") g_warmup = atoi(v.c_str());
         else if (k == "--out") g_out = v;
         else if (k == "--depth") { if (atoi(v.c_str()) != DEPTH_TRACE) { fprintf(stderr, "this binary was built with DEPTH_TRACE=%d\n", DEPTH_TRACE); return 3; } }
+    }
+    if (!soup.empty()) {
+        try { return runSoup(soup, g_out, soupBuilds, soupReps); }
+        catch (const std::exception& e) { fprintf(stderr, "reference threw: %s\n", e.what()); return 1; }
     }
     if (scene.empty()) { fprintf(stderr, "usage: --scene file.gltf [--env img] [--width W --height H --spp N --frames K --warmup W --out raw]\n"); return 2; }
     try {

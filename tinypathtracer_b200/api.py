@@ -190,11 +190,12 @@ class BVH:
         check(lib.tpt_bvh_export_reference_nodes(self.scene._h, _ptr(out), n))
         return out
 
-    def trace(self, rays: np.ndarray, any_hit: bool = False, counted: bool = False) -> np.ndarray:
+    def trace(self, rays: np.ndarray, any_hit: bool = False, counted: bool = False, out: np.ndarray | None = None) -> np.ndarray:
+        """Host buffers in, host buffers out (`out`: caller's HIT_DTYPE array, e.g. pinned memory)."""
         rays = np.ascontiguousarray(rays)
         if rays.dtype != RAY_DTYPE:
             rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 6).view(RAY_DTYPE).reshape(-1)
-        hits = np.zeros(rays.shape[0], HIT_DTYPE)
+        hits = np.zeros(rays.shape[0], HIT_DTYPE) if out is None else out
         fn = lib.tpt_trace_rays_counted if counted else lib.tpt_trace_rays
         check(fn(self.scene._h, _ptr(rays), rays.shape[0], _ptr(hits), int(any_hit), 0))
         return hits

@@ -42,7 +42,7 @@ __host__ __device__ __forceinline__ float ord2f(uint32_t u) {
 
 __global__ void k_init_bounds(uint32_t* bounds) {
     if (threadIdx.x < 3) bounds[threadIdx.x] = 0xffffffffu;
-    else if (threadIdx.x < 6) bounds[threadIdx.x] = 0u;
+    else if (threadIdx.x < 8) bounds[threadIdx.x] = 0u;   // [3..5] max, [6] refit frontier count, [7] spare
 }
 
 // Built once per scene: which object each vertex belongs to, and the material of each face
@@ -109,12 +109,13 @@ __device__ __forceinline__ uint64_t expand21(uint64_t x) {   // spread 21 bits t
 }
 
 __global__ void __launch_bounds__(256) k_morton(const uint32_t* __restrict__ indices, const float* __restrict__ worldVerts,
-                                                const uint32_t* __restrict__ bounds, uint32_t nFaces,
+                                                const uint32_t* __restrict__ bounds, uint32_t nFaces, int bitsPerAxis,
                                                 unsigned long long* __restrict__ keys, uint32_t* __restrict__ vals) {
     const float3 bmin = f3(ord2f(bounds[0]), ord2f(bounds[1]), ord2f(bounds[2]));
     const float3 bmax = f3(ord2f(bounds[3]), ord2f(bounds[4]), ord2f(bounds[5]));
     const float3 ext = bmax - bmin;
-    const float k = 2097152.0f;   // 2^21 cells per axis
+    const float k = (float)(1u << bitsPerAxis);   // cells per axis (2^21: the reference's key width; 2^16 for huge scenes)
+    const float qmax = k - 1.0f;
     const float3 scale = f3(ext.x > 0.f ? k / ext.x : 0.f, ext.y > 0.f ? k / ext.y : 0.f, ext.z > 0.f ? k / ext.z : 0.f);
     for (uint32_t f = blockIdx.x * blockDim.x + threadIdx.x; f < nFaces; f += gridDim.x * blockDim.x) {
         const uint32_t i0 = indices[3 * f], i1 = indices[3 * f + 1], i2 = indices[3 * f + 2];
@@ -123,9 +124,9 @@ __global__ void __launch_bounds__(256) k_morton(const uint32_t* __restrict__ ind
         const float3 c = f3(worldVerts[3 * i2], worldVerts[3 * i2 + 1], worldVerts[3 * i2 + 2]);
         const float3 ctr = (fmin3(fmin3(a, b), c) + fmax3(fmax3(a, b), c)) * 0.5f;   // AABB centre, as bvh.cu:139-142
         const float3 q = (ctr - bmin) * scale;
-        const uint64_t qx = (uint64_t)fminf(fmaxf(q.x, 0.f), 2097151.f);
-        const uint64_t qy = (uint64_t)fminf(fmaxf(q.y, 0.f), 2097151.f);
-        const uint64_t qz = (uint64_t)fminf(fmaxf(q.z, 0.f), 2097151.f);
+        const uint64_t qx = (uint64_t)fminf(fmaxf(q.x, 0.f), qmax);
+        const uint64_t qy = (uint64_t)fminf(fmaxf(q.y, 0.f), qmax);
+        const uint64_t qz = (uint64_t)fminf(fmaxf(q.z, 0.f), qmax);
         keys[f] = expand21(qx) | (expand21(qy) << 1) | (expand21(qz) << 2);
         vals[f] = f;
     }
@@ -140,7 +141,7 @@ __device__ __forceinline__ int delta(const unsigned long long* __restrict__ keys
 }
 
 __global__ void __launch_bounds__(256) k_hierarchy(const unsigned long long* __restrict__ keys, int nFaces, float4* __restrict__ nodes,
-                                                   int* __restrict__ parentInt, int* __restrict__ parentLeaf) {
+                                                   int* __restrict__ parentInt, int* __restrict__ parentLeaf, int* __restrict__ rangeOther) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nFaces - 1) return;
     const int d = delta(keys, nFaces, i, i + 1) > delta(keys, nFaces, i, i - 1) ? 1 : -1;
@@ -151,6 +152,7 @@ __global__ void __launch_bounds__(256) k_hierarchy(const unsigned long long* __r
     for (int t = lmax >> 1; t > 0; t >>= 1)
         if (delta(keys, nFaces, i, i + (l + t) * d) > dMin) l += t;
     const int j = i + l * d;
+    rangeOther[i] = j;   // node i covers the sorted leaves [min(i,j), max(i,j)]
     const int dNode = delta(keys, nFaces, i, j);
     int s = 0;
     for (int t = (l + 1) >> 1;; t = (t + 1) >> 1) {
@@ -175,13 +177,30 @@ __device__ __forceinline__ void store_child_box(float4* node, bool isLeft, float
     __stcg(reinterpret_cast<float2*>(n + 8 + (isLeft ? 0 : 2)), make_float2(mn.z, mx.z));
 }
 
-__global__ void __launch_bounds__(256) k_leaves_refit(const uint32_t* __restrict__ sortedFaces, const uint32_t* __restrict__ indices,
+// Refit, two kernels.  A bottom-up walk with one global atomic + two fences per level keeps a 256-thread block
+// resident for as long as its longest chain, and at 10 M triangles that residency — not bandwidth — set the
+// build time.  So:
+//   k_leaves_refit  (one thread per sorted leaf) writes the triangle/normal records and walks up while the
+//                   node's whole leaf range lies inside this block's 256 leaves: sibling boxes are exchanged
+//                   through shared memory (shared atomics, block-scope fences).  At the first node that spans
+//                   blocks it falls back to the global arrival counter; the second arrival does not continue
+//                   but appends the (now complete) node to a frontier list.
+//   k_refit_upper   one thread per frontier node finishes the walk to the root with the global protocol; there
+//                   are only ~F/100 of them, all resident at once.
+constexpr int kRefitBlock = 256;
+
+__global__ void __launch_bounds__(kRefitBlock) k_leaves_refit(const uint32_t* __restrict__ sortedFaces, const uint32_t* __restrict__ indices,
                                                       const float* __restrict__ worldVerts, const float* __restrict__ worldNorms,
                                                       const uint32_t* __restrict__ faceMtl, int nFaces, const int* __restrict__ parentInt,
-                                                      const int* __restrict__ parentLeaf, uint32_t* __restrict__ flags,
-                                                      float4* __restrict__ nodes, float4* __restrict__ triGeom,
-                                                      float4* __restrict__ triNorm) {
-    const int leaf = blockIdx.x * blockDim.x + threadIdx.x;
+                                                      const int* __restrict__ parentLeaf, const int* __restrict__ rangeOther,
+                                                      uint32_t* __restrict__ flags, float4* __restrict__ nodes, float4* __restrict__ triGeom,
+                                                      float4* __restrict__ triNorm, int* __restrict__ frontier, uint32_t* __restrict__ frontierCount) {
+    __shared__ unsigned sFlag[kRefitBlock];
+    __shared__ float sBox[kRefitBlock][2][6];
+    sFlag[threadIdx.x] = 0u;
+    __syncthreads();
+    const int b0 = blockIdx.x * kRefitBlock;
+    const int leaf = b0 + threadIdx.x;
     if (leaf >= nFaces) return;
     const uint32_t f = sortedFaces[leaf];
     const uint32_t i0 = indices[3 * f], i1 = indices[3 * f + 1], i2 = indices[3 * f + 2];
@@ -189,15 +208,15 @@ __global__ void __launch_bounds__(256) k_leaves_refit(const uint32_t* __restrict
     const float3 b = f3(worldVerts[3 * i1], worldVerts[3 * i1 + 1], worldVerts[3 * i1 + 2]);
     const float3 c = f3(worldVerts[3 * i2], worldVerts[3 * i2 + 1], worldVerts[3 * i2 + 2]);
     const float3 e1 = xsub3(b, a), e2 = xsub3(c, a);   // exactly the edges Möller–Trumbore forms per test in the reference
-    triGeom[3 * (size_t)leaf + 0] = make_float4(a.x, a.y, a.z, e1.x);
-    triGeom[3 * (size_t)leaf + 1] = make_float4(e1.y, e1.z, e2.x, e2.y);
-    triGeom[3 * (size_t)leaf + 2] = make_float4(e2.z, __int_as_float((int)f), __int_as_float((int)faceMtl[f]), 0.f);
+    __stcs(triGeom + 3 * (size_t)leaf + 0, make_float4(a.x, a.y, a.z, e1.x));
+    __stcs(triGeom + 3 * (size_t)leaf + 1, make_float4(e1.y, e1.z, e2.x, e2.y));
+    __stcs(triGeom + 3 * (size_t)leaf + 2, make_float4(e2.z, __int_as_float((int)f), __int_as_float((int)faceMtl[f]), 0.f));
     const float3 n0 = f3(worldNorms[3 * i0], worldNorms[3 * i0 + 1], worldNorms[3 * i0 + 2]);
     const float3 n1 = f3(worldNorms[3 * i1], worldNorms[3 * i1 + 1], worldNorms[3 * i1 + 2]);
     const float3 n2 = f3(worldNorms[3 * i2], worldNorms[3 * i2 + 1], worldNorms[3 * i2 + 2]);
-    triNorm[3 * (size_t)leaf + 0] = make_float4(n0.x, n0.y, n0.z, n1.x);
-    triNorm[3 * (size_t)leaf + 1] = make_float4(n1.y, n1.z, n2.x, n2.y);
-    triNorm[3 * (size_t)leaf + 2] = make_float4(n2.z, 0.f, 0.f, 0.f);
+    __stcs(triNorm + 3 * (size_t)leaf + 0, make_float4(n0.x, n0.y, n0.z, n1.x));
+    __stcs(triNorm + 3 * (size_t)leaf + 1, make_float4(n1.y, n1.z, n2.x, n2.y));
+    __stcs(triNorm + 3 * (size_t)leaf + 2, make_float4(n2.z, 0.f, 0.f, 0.f));
     if (nFaces == 1) return;
 
     float3 mn = fmin3(fmin3(a, b), c), mx = fmax3(fmax3(a, b), c);
@@ -205,7 +224,49 @@ __global__ void __launch_bounds__(256) k_leaves_refit(const uint32_t* __restrict
     int cur = parentLeaf[leaf];
     while (cur >= 0) {
         float4* node = nodes + 4 * (size_t)cur;
-        const int4 ch = reinterpret_cast<const int4*>(node)[3];
+        const int2 ch = *reinterpret_cast<const int2*>(node + 3);
+        const bool isLeft = (ch.x == child);
+        store_child_box(node, isLeft, mn, mx);
+        const int other = rangeOther[cur];
+        const int lo = min(cur, other), hi = max(cur, other);
+        if (lo >= b0 && hi < b0 + kRefitBlock) {
+            // both children arrive from this block: exchange through shared memory
+            const int k = cur - b0, side = isLeft ? 0 : 1;
+            float* mine = sBox[k][side];
+            mine[0] = mn.x; mine[1] = mn.y; mine[2] = mn.z; mine[3] = mx.x; mine[4] = mx.y; mine[5] = mx.z;
+            __threadfence_block();
+            if (atomicAdd(&sFlag[k], 1u) == 0u) return;   // first arrival: the sibling will finish this node
+            __threadfence_block();
+            const volatile float* sib = sBox[k][side ^ 1];
+            mn = fmin3(mn, f3(sib[0], sib[1], sib[2]));
+            mx = fmax3(mx, f3(sib[3], sib[4], sib[5]));
+            child = cur;
+            cur = parentInt[cur];
+        } else {
+            __threadfence();
+            if (atomicAdd(flags + cur, 1u) == 1u) frontier[atomicAdd(frontierCount, 1u)] = cur;   // complete: k_refit_upper goes on
+            return;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) k_refit_upper(const int* __restrict__ frontier, const uint32_t* __restrict__ frontierCount,
+                                                     const int* __restrict__ parentInt, uint32_t* __restrict__ flags,
+                                                     float4* __restrict__ nodes) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= *frontierCount) return;
+    int child = frontier[t];
+    float3 mn, mx;
+    {
+        const float4* node = nodes + 4 * (size_t)child;
+        const float4 n0 = __ldcg(node), n1 = __ldcg(node + 1), n2 = __ldcg(node + 2);
+        mn = f3(fminf(n0.x, n1.x), fminf(n0.z, n1.z), fminf(n2.x, n2.z));
+        mx = f3(fmaxf(n0.y, n1.y), fmaxf(n0.w, n1.w), fmaxf(n2.y, n2.w));
+    }
+    int cur = parentInt[child];
+    while (cur >= 0) {
+        float4* node = nodes + 4 * (size_t)cur;
+        const int2 ch = *reinterpret_cast<const int2*>(node + 3);
         const bool isLeft = (ch.x == child);
         store_child_box(node, isLeft, mn, mx);
         __threadfence();
@@ -324,26 +385,35 @@ int tpt_bvh_build_impl(tpt_scene* s) {
     k_init_bounds<<<1, 32, 0, st>>>(s->bounds);
     k_transform<<<min(persistent, (int)grid_for(V, 256)), 256, 0, st>>>(s->obj_verts, s->obj_norms, s->vert_obj, s->vert_trans,
                                                                          s->normal_trans, V, s->world_verts, s->world_norms, s->bounds);
-    k_morton<<<min(persistent, (int)grid_for(F, 256)), 256, 0, st>>>(s->indices, s->world_verts, s->bounds, (uint32_t)F, s->keys[0],
-                                                                      s->vals[0]);
+    // 63-bit keys like the reference (21 bits per axis); from 2^20 triangles on, 16 bits per axis (65 536^3 cells is still far
+    // finer than the triangles, equal keys are ordered by index) so that the radix sort runs 6 passes instead of 8
+    const int bitsPerAxis = F >= (1 << 20) ? 16 : 21;
+    const int keyBits = 3 * bitsPerAxis;
+    k_morton<<<min(persistent, (int)grid_for(F, 256)), 256, 0, st>>>(s->indices, s->world_verts, s->bounds, (uint32_t)F, bitsPerAxis,
+                                                                      s->keys[0], s->vals[0]);
     TPT_CUDA(cudaGetLastError());
     size_t need = 0;
-    TPT_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, need, s->keys[0], s->keys[1], s->vals[0], s->vals[1], F, 0, 63, st));
+    TPT_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, need, s->keys[0], s->keys[1], s->vals[0], s->vals[1], F, 0, keyBits, st));
     if (need > s->sort_tmp_bytes) {
         TPT_CUDA(cudaStreamSynchronize(st));
         if (s->sort_tmp) cudaFree(s->sort_tmp);
         TPT_CUDA(cudaMalloc(&s->sort_tmp, need));
         s->sort_tmp_bytes = need;
     }
-    TPT_CUDA(cub::DeviceRadixSort::SortPairs(s->sort_tmp, s->sort_tmp_bytes, s->keys[0], s->keys[1], s->vals[0], s->vals[1], F, 0, 63, st));
+    TPT_CUDA(cub::DeviceRadixSort::SortPairs(s->sort_tmp, s->sort_tmp_bytes, s->keys[0], s->keys[1], s->vals[0], s->vals[1], F, 0, keyBits, st));
     if (F > 1) {
         TPT_CUDA(cudaMemsetAsync(s->flags, 0, (size_t)(F - 1) * sizeof(uint32_t), st));
-        k_hierarchy<<<grid_for(F - 1, 256), 256, 0, st>>>(s->keys[1], F, s->nodes, s->parent_int, s->parent_leaf);
+        // vals[0] / keys[0] were the sort's input and are free now: range ends and the refit frontier live there
+        k_hierarchy<<<grid_for(F - 1, 256), 256, 0, st>>>(s->keys[1], F, s->nodes, s->parent_int, s->parent_leaf,
+                                                          reinterpret_cast<int*>(s->vals[0]));
     }
-    k_leaves_refit<<<grid_for(F, 256), 256, 0, st>>>(s->vals[1], s->indices, s->world_verts, s->world_norms, s->face_mtl, F, s->parent_int,
-                                                     s->parent_leaf, s->flags, s->nodes, s->tri_geom, s->tri_norm);
+    int* frontier = reinterpret_cast<int*>(s->keys[0]);
+    k_leaves_refit<<<grid_for(F, kRefitBlock), kRefitBlock, 0, st>>>(s->vals[1], s->indices, s->world_verts, s->world_norms, s->face_mtl, F,
+                                                                     s->parent_int, s->parent_leaf, reinterpret_cast<const int*>(s->vals[0]),
+                                                                     s->flags, s->nodes, s->tri_geom, s->tri_norm, frontier, s->bounds + 6);
+    if (F > 1) k_refit_upper<<<grid_for((size_t)F / 2 + 1, 256), 256, 0, st>>>(frontier, s->bounds + 6, s->parent_int, s->flags, s->nodes);
     TPT_CUDA(cudaGetLastError());
-    ctx->kernel_launches += 5 + 8;   // + radix sort passes (library, counted nominally)
+    ctx->kernel_launches += 6 + 8;   // + radix sort passes (library, counted nominally)
     s->built = true;
     return TPT_OK;
 }
