@@ -208,6 +208,12 @@ def run_ours(args):
     ms_e2e = timed(frame_e2e, args.steps) / args.steps
     e2e_value = samples_step / (ms_e2e * 1e-3) / 1e6
 
+    # ---- determinism evidence: SHA-256 of the all-reduced int64 accumulation buffer of one more frame (untimed)
+    frame(dscene)
+    torch.cuda.synchronize()
+    import hashlib
+    accum_sha = hashlib.sha256(acc_t.cpu().numpy().tobytes()).hexdigest() if rank == 0 else None
+
     line = None
     if rank == 0:
         # ---- roofline pass (untimed for `value`): per-stage CUDA-event times + node/triangle counters --------
@@ -261,6 +267,7 @@ def run_ours(args):
             "e2e": {"value": round(e2e_value, 3), "unit": "Msamples/s", "ms_per_step": round(ms_e2e, 3),
                     "h2d_bytes_per_step": scene_upload_bytes(scene), "d2h_bytes_per_step": W * H * 4},
             "gpu_launches": int(launches), "clocks": clk, "roofline": roofline,
+            "accum_sha256": accum_sha,   # identical for 1, 2, 4 and 8 GPUs (exact integer accumulation + all-reduce)
         }
         if cpu is not None:
             line["cpu_baseline"] = cpu
