@@ -1,0 +1,191 @@
+// host.hpp — C++ mirrors of the reference's host classes over the C ABI of include/tpt.h.
+//
+// Same names, argument meaning and error behaviour as the reference (a non-zero status becomes
+// std::runtime_error, its CUDA_CHECK convention, include/intellisense_cuda.h:14-20):
+//   Transform   include/transform.h:8-59        Camera      include/camera.h:9-65
+//   Mesh        include/mesh.cuh:16-70          Scene       include/mesh.cuh:98-115, src/mesh.cu:68-397
+//   DeviceScene include/mesh.cuh:80-96          BVH         include/bvh.cuh:60-68, src/bvh.cu:304-331
+//   EnvLight    include/env_light.cuh:9-19      PathTracer  include/path_tracer.h:16-35, src/path_tracer.cu:477-579
+//   Picture     include/picture.h:12-55 (FreeImage in the reference; PNG/PPM codecs of this repository here)
+// No CUDA header is needed to use these: device work happens behind libtpt_b200.so.
+#pragma once
+#include <cstdint>
+#include <map>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../tpt.h"
+
+namespace tpt {
+
+using Real = float;
+struct Vec2 { Real x = 0, y = 0; };
+struct Vec3 {
+    Real x = 0, y = 0, z = 0;
+    Vec3() = default;
+    explicit Vec3(Real s) : x(s), y(s), z(s) {}
+    Vec3(Real a, Real b, Real c) : x(a), y(b), z(c) {}
+};
+struct Quat {   // include/math/quat.h: (x, y, z, w); the default (all zero) rotates like the identity
+    Real x = 0, y = 0, z = 0, w = 0;
+    Quat() = default;
+    Quat(Real a, Real b, Real c, Real d) : x(a), y(b), z(c), w(d) {}
+};
+struct Mat4 {   // column-major, include/math/mat.h:37-51
+    Real m[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+    Real& at(int col, int row) { return m[col * 4 + row]; }
+    Real at(int col, int row) const { return m[col * 4 + row]; }
+};
+Mat4 operator*(const Mat4& a, const Mat4& b);
+
+using Material = tpt_material;        // include/material.h:86-120, 60 bytes
+using DeltaLight = tpt_delta_light;   // include/delta_light.h:96-130, 52 bytes
+using MtlInterval = tpt_mtl_interval; // include/mesh.cuh:74-78
+Material defaultMaterial();           // Material() of include/material.h:88-103
+
+class Transform {
+public:
+    Transform() = default;
+    Transform(Vec3 loc, Quat quat, Vec3 s) : m_location(loc), m_rotation(quat), m_scale(s) {}
+    Mat4 localToParent() const;   // Translate * Rotate * Scale, include/transform.h:28-33
+    Mat4 localToWorld() const { return localToParent(); }   // the reference never sets a parent (src/mesh.cu:265 TODO)
+    Vec3 m_location{0, 0, 0};
+    Quat m_rotation;
+    Vec3 m_scale{1, 1, 1};
+};
+Mat4 normalToWorld(const Mat4& localToWorld);   // inverse transpose of the upper 3x3, src/mesh.cu:371-378
+
+class Camera {
+public:
+    Camera() : m_transform(std::make_shared<Transform>()) {}
+    Camera(Real fov, Real asp, Real nearZ, const Transform& trans)
+        : m_transform(std::make_shared<Transform>(trans)), m_verticalFOV(fov), m_aspectRatio(asp), m_nearPlane(nearZ) {}
+    Real getVFov() const { return m_verticalFOV; }        // radians, straight from glTF yfov (src/mesh.cu:148)
+    Real getAspRatio() const { return m_aspectRatio; }
+    Real getNearPlane() const { return m_nearPlane; }
+    tpt_camera toABI() const;
+    std::shared_ptr<Transform> m_transform;
+
+private:
+    Real m_verticalFOV = 60.0f, m_aspectRatio = 1.77778f, m_nearPlane = 0.1f;
+};
+
+struct Mesh {
+    std::vector<uint32_t> m_polygons;
+    std::vector<Vec3> m_vertexCoords, m_vertexNormals;
+    std::vector<Vec2> m_vertexTexCoords;
+    std::string m_material;
+    std::shared_ptr<Transform> m_transform;
+};
+
+[[noreturn]] void throwLastError(const char* where);
+inline void check(int status, const char* where) {
+    if (status != TPT_OK) throwLastError(where);
+}
+
+// One per GPU: replaces the reference's implicit device 0 / default stream.
+class Context {
+public:
+    explicit Context(int device = 0);
+    ~Context();
+    Context(const Context&) = delete;
+    Context& operator=(const Context&) = delete;
+    tpt_context* handle() const { return m_ctx; }
+    void synchronize();
+    tpt_counters counters();
+
+private:
+    tpt_context* m_ctx = nullptr;
+};
+
+// The flattened arrays of the reference's DeviceScene; the device copy lives behind `handle`.
+struct DeviceScene {
+    std::vector<uint32_t> indices;
+    std::vector<Vec3> vertices, normals;
+    std::vector<Vec2> texCoords;
+    std::vector<Material> materials;
+    std::vector<MtlInterval> materialsLUT;
+    std::vector<Mat4> vertTrans, normalTrans;
+    std::vector<DeltaLight> lights;
+    std::shared_ptr<tpt_scene> handle;   // tpt_scene_create / tpt_scene_destroy
+    size_t nFaces() const { return indices.size() / 3; }
+};
+
+class Scene {
+public:
+    Scene() = default;
+    Scene(const std::string& filename, const std::string& type);   // type must be "gltf" (src/mesh.cu:68-78)
+    DeviceScene flatten() const;                                   // host part of copySceneToDevice (src/mesh.cu:309-397)
+    DeviceScene copySceneToDevice(Context& ctx) const;             // + tpt_scene_create
+    Camera m_camera;
+    const std::vector<Mesh>& meshes() const { return m_meshes; }
+    const std::map<std::string, Material>& materials() const { return m_materials; }
+    const std::map<std::string, DeltaLight>& lights() const { return m_lights; }
+
+private:
+    void readFromGLTF(const std::string& filename);
+    std::vector<Mesh> m_meshes;
+    std::map<std::string, Material> m_materials;   // std::map: name order, as uploaded by the reference (src/mesh.cu:326-333)
+    std::map<std::string, DeltaLight> m_lights;
+};
+
+struct BVHNode36 {   // include/bvh.cuh:34-58, the reference's 36-byte node (structural export only)
+    uint32_t parent;
+    int32_t a, b;
+    float mn[3], mx[3];
+};
+
+class BVH {
+public:
+    explicit BVH(DeviceScene& scene) : m_scene(scene.handle) {}
+    void construct();                       // `transform` kernel + BVH::construct of the reference
+    tpt_bvh_stats constructWithStats();
+    std::vector<BVHNode36> exportReferenceLayout(size_t nFaces);
+    void traceRays(const tpt_ray* rays, size_t n, tpt_hit* hits, bool anyHit = false);   // host buffers
+
+private:
+    std::shared_ptr<tpt_scene> m_scene;
+};
+
+// 8-bit image, top-down rows, 3 or 4 channels (include/picture.h loads through FreeImage; here: PNG and binary PPM).
+struct Picture {
+    int width = 0, height = 0, channels = 0;
+    std::vector<uint8_t> pixels;
+    Picture() = default;
+    explicit Picture(const std::string& filename);
+};
+void writePNG(const std::string& filename, const uint8_t* rgba, int width, int height, int channels);
+
+class EnvLight {
+public:
+    EnvLight(Context& ctx, const std::string& file);   // "" -> black environment (the reference: uninitialised texture)
+};
+
+class PathTracer {
+public:
+    PathTracer();
+    explicit PathTracer(const std::string& envLightFile);
+    void render(const std::string& meshFile);   // load, upload, m_frames x doTrace, PNG of the last frame if m_output is set
+    void doTrace(DeviceScene& scene, Camera& camera, unsigned char* framebuffer /*host BGRA8*/, int nSamplesPerPixel);
+
+    // run-time forms of the reference's compile-time constants (include/vkEngine.h:24, src/path_tracer.cu:17,559,493)
+    int m_width = 1920, m_height = 1080;
+    int m_spp = 64, m_depth = 8, m_frames = 1;
+    uint64_t m_seed = 1;
+    std::string m_output;
+    double m_lastFrameMs = 0.0;
+    Context& context() { return *m_ctx; }
+
+private:
+    std::unique_ptr<Context> m_ctx;
+    std::string m_envFile;
+    tpt_accum* m_radiance = nullptr;
+    int m_accW = 0, m_accH = 0;
+
+public:
+    ~PathTracer();
+};
+
+}   // namespace tpt

@@ -1,0 +1,158 @@
+// path_tracer.cpp — EnvLight and PathTracer of the reference (include/env_light.cuh:9-19, include/path_tracer.h:16-35,
+// src/path_tracer.cu:477-579) over the C ABI, plus the extern "C" hooks the tests use to read the loader's output.
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+
+#include "tpt/host.hpp"
+
+namespace tpt {
+
+// EnvLight(file): decode, swizzle to RGBA8 and upload with row 0 = the BOTTOM scanline — what FreeImage's bottom-up
+// bitmap + the BGR->RGBA transform give the reference's texture (include/picture.h:19-45, src/texture.cu:33-47,64-171).
+EnvLight::EnvLight(Context& ctx, const std::string& file) {
+    if (file.empty()) {
+        check(tpt_env_clear(ctx.handle()), "tpt_env_clear");
+        return;
+    }
+    const Picture pic(file);
+    std::vector<uint8_t> rgba((size_t)pic.width * pic.height * 4);
+    for (int y = 0; y < pic.height; ++y) {
+        const uint8_t* src = &pic.pixels[(size_t)(pic.height - 1 - y) * pic.width * pic.channels];
+        uint8_t* dst = &rgba[(size_t)y * pic.width * 4];
+        for (int x = 0; x < pic.width; ++x) {
+            dst[4 * x + 0] = src[pic.channels * x + 0];
+            dst[4 * x + 1] = src[pic.channels * x + 1];
+            dst[4 * x + 2] = src[pic.channels * x + 2];
+            dst[4 * x + 3] = pic.channels == 4 ? src[4 * x + 3] : 255;
+        }
+    }
+    check(tpt_env_set_rgba8(ctx.handle(), rgba.data(), pic.width, pic.height), "tpt_env_set_rgba8");
+}
+
+PathTracer::PathTracer() : PathTracer(std::string()) {}
+PathTracer::PathTracer(const std::string& envLightFile) : m_ctx(new Context(0)), m_envFile(envLightFile) {
+    EnvLight env(*m_ctx, m_envFile);
+}
+PathTracer::~PathTracer() {
+    if (m_radiance) tpt_accum_destroy(m_radiance);
+}
+
+// One frame exactly as src/path_tracer.cu:491-554: transform + BVH rebuild, clear, trace, copyToFB.
+void PathTracer::doTrace(DeviceScene& scene, Camera& camera, unsigned char* framebuffer, int nSamplesPerPixel) {
+    if (!m_radiance || m_accW != m_width || m_accH != m_height) {
+        if (m_radiance) tpt_accum_destroy(m_radiance);
+        m_radiance = nullptr;
+        check(tpt_accum_create(m_ctx->handle(), m_width, m_height, &m_radiance), "tpt_accum_create");
+        m_accW = m_width;
+        m_accH = m_height;
+    }
+    tpt_render_config cfg;
+    std::memset(&cfg, 0, sizeof cfg);
+    cfg.width = m_width;
+    cfg.height = m_height;
+    cfg.spp = nSamplesPerPixel;
+    cfg.max_depth = m_depth;
+    cfg.seed = m_seed;
+    cfg.sample_offset = 0;
+    cfg.sample_stride = 1;
+    const tpt_camera cam = camera.toABI();
+    const auto t0 = std::chrono::steady_clock::now();
+    check(tpt_do_trace(scene.handle.get(), &cam, &cfg, m_radiance, framebuffer), "tpt_do_trace");
+    m_lastFrameMs = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+}
+
+void PathTracer::render(const std::string& meshFile) {
+    Scene scene(meshFile, "gltf");                            // src/path_tracer.cu:558
+    DeviceScene d_scene = scene.copySceneToDevice(*m_ctx);    // :560
+    Camera& camera = scene.m_camera;                          // :562
+    std::vector<unsigned char> fb((size_t)m_width * m_height * 4, 0);
+    // the reference hands this job to VkEngine::run, which calls it once per presented frame until the window closes
+    // (src/vkEngine.cu:294-302); headless: m_frames frames, each an independent nSamplesPerPixel render with a new seed
+    for (int f = 0; f < m_frames; ++f) {
+        doTrace(d_scene, camera, fb.data(), m_spp);
+        std::printf("1 frame: %.3f ms\n", m_lastFrameMs);     // src/vkEngine.cu:300 prints "1 frame"
+        ++m_seed;
+    }
+    if (!m_output.empty()) {
+        std::vector<uint8_t> rgb((size_t)m_width * m_height * 3);
+        for (size_t i = 0; i < (size_t)m_width * m_height; ++i) {   // framebuffer is B,G,R,(A untouched), row 0 = top
+            rgb[3 * i + 0] = fb[4 * i + 2];
+            rgb[3 * i + 1] = fb[4 * i + 1];
+            rgb[3 * i + 2] = fb[4 * i + 0];
+        }
+        writePNG(m_output, rgb.data(), m_width, m_height, 3);
+    }
+}
+
+}   // namespace tpt
+
+// ---- C hooks for the tests: the loader's flattened arrays -----------------------------------------------------------
+extern "C" {
+struct tpt_host_scene {
+    tpt::DeviceScene d;
+    tpt::Camera cam;
+    tpt_camera abi;
+    std::string error;
+};
+static thread_local std::string g_host_error;
+const char* tpt_host_last_error(void) { return g_host_error.c_str(); }
+
+tpt_host_scene* tpt_host_load_gltf(const char* path) {
+    try {
+        tpt::Scene scene(path, "gltf");
+        tpt_host_scene* h = new tpt_host_scene();
+        h->d = scene.flatten();
+        h->cam = scene.m_camera;
+        h->abi = h->cam.toABI();
+        return h;
+    } catch (const std::exception& e) {
+        g_host_error = e.what();
+        return nullptr;
+    }
+}
+void tpt_host_scene_free(tpt_host_scene* h) { delete h; }
+// sizes: {n_indices, n_vertices, n_materials, n_objects, n_lights}
+void tpt_host_scene_sizes(const tpt_host_scene* h, size_t* out5) {
+    out5[0] = h->d.indices.size();
+    out5[1] = h->d.vertices.size();
+    out5[2] = h->d.materials.size();
+    out5[3] = h->d.materialsLUT.size();
+    out5[4] = h->d.lights.size();
+}
+void tpt_host_scene_copy(const tpt_host_scene* h, uint32_t* indices, float* vertices, float* normals, float* texcoords, void* materials,
+                         void* objects, float* vertTrans, float* normalTrans, void* lights, tpt_camera* cam) {
+    const tpt::DeviceScene& d = h->d;
+    std::memcpy(indices, d.indices.data(), d.indices.size() * 4);
+    std::memcpy(vertices, d.vertices.data(), d.vertices.size() * 12);
+    std::memcpy(normals, d.normals.data(), d.normals.size() * 12);
+    std::memcpy(texcoords, d.texCoords.data(), d.texCoords.size() * 8);
+    std::memcpy(materials, d.materials.data(), d.materials.size() * sizeof(tpt_material));
+    std::memcpy(objects, d.materialsLUT.data(), d.materialsLUT.size() * sizeof(tpt_mtl_interval));
+    std::memcpy(vertTrans, d.vertTrans.data(), d.vertTrans.size() * 64);
+    std::memcpy(normalTrans, d.normalTrans.data(), d.normalTrans.size() * 64);
+    if (!d.lights.empty()) std::memcpy(lights, d.lights.data(), d.lights.size() * sizeof(tpt_delta_light));
+    *cam = h->abi;
+}
+// PNG round trip through the repository's codecs (width*height*channels bytes, top-down rows)
+int tpt_host_write_png(const char* path, const uint8_t* px, int w, int h, int channels) {
+    try {
+        tpt::writePNG(path, px, w, h, channels);
+        return 0;
+    } catch (const std::exception& e) {
+        g_host_error = e.what();
+        return -1;
+    }
+}
+int tpt_host_read_image(const char* path, uint8_t* out, size_t capacity, int* whc3) {
+    try {
+        tpt::Picture p(path);
+        whc3[0] = p.width; whc3[1] = p.height; whc3[2] = p.channels;
+        if (out && p.pixels.size() <= capacity) std::memcpy(out, p.pixels.data(), p.pixels.size());
+        return 0;
+    } catch (const std::exception& e) {
+        g_host_error = e.what();
+        return -1;
+    }
+}
+}   // extern "C"
