@@ -189,7 +189,8 @@ def run_ours(args):
     launches = ctr["kernel_launches"]
     ms_step = ms_total / args.steps
     samples_step = W * H * spp                       # whole job, all ranks
-    rays_rank = ctr["rays_primary"] + ctr["rays_extension"] + ctr["rays_shadow"] + ctr["rays_direct"]
+    # rays actually traversed: camera samples whose pixel pyramid misses every leaf box are answered without a traversal
+    rays_rank = ctr["rays_primary"] - ctr["rays_culled"] + ctr["rays_extension"] + ctr["rays_shadow"] + ctr["rays_direct"]
     rays_t = torch.tensor([rays_rank], device="cuda", dtype=torch.int64)
     if world > 1:
         dist.all_reduce(rays_t)
@@ -231,7 +232,7 @@ def run_ours(args):
                        paths_in_flight=args.paths_in_flight)
         c2 = ctx.counters()
         ctx.synchronize()
-        n_all = c1["rays_primary"] + c1["rays_extension"] + c1["rays_shadow"] + c1["rays_direct"]
+        n_all = c1["rays_primary"] - c1["rays_culled"] + c1["rays_extension"] + c1["rays_shadow"] + c1["rays_direct"]
         n_int = c2["node_visits"] / max(n_all, 1)
         n_leaf = c2["tri_tests"] / max(n_all, 1)
         bytes_per_ray = 56.0 * n_int + 40.0 * n_leaf + 88.0          # SURVEY §8(d) algorithmic bytes per ray
@@ -252,7 +253,7 @@ def run_ours(args):
                     "avg_launch_us": round(1e3 * trav_ms / max(trav_launches, 1), 2),
                     "share_of_step": round(min(1.0, trav_ms * (per_slice * len(slices) / prof_spp) / ms_step), 4),
                     "stage_ms": {k: round(v["ms"], 3) for k, v in st.items()},
-                    "rays": {k: c1[k] for k in ("rays_primary", "rays_extension", "rays_shadow", "rays_direct")},
+                    "rays": {k: c1[k] for k in ("rays_primary", "rays_culled", "rays_extension", "rays_shadow", "rays_direct")},
                     "note": "BVH of this workload is L1/L2-resident; node fetches never reach HBM, the HBM fraction is an upper-bound accounting (SURVEY §8d)"}
         cpu = cpu_baseline(args, fixture, W, H, depth, env, seed) if world == 1 and not args.no_cpu_baseline else None
         line = {

@@ -139,6 +139,8 @@ typedef struct tpt_counters {
     uint64_t samples;
     uint64_t dropped_nonfinite;           /* contributions that were NaN/Inf and were not accumulated */
     uint64_t kernel_launches;
+    uint64_t rays_culled;                 /* camera samples (part of rays_primary) answered without a traversal: their pixel's
+                                           * pyramid misses every leaf box of the tree (k_primary's pixel-frustum culling) */
 } tpt_counters;
 
 /* Device time per wavefront stage since the last tpt_reset_counters, measured with CUDA events on the

@@ -157,6 +157,7 @@ int tpt_get_counters(tpt_context* ctx, tpt_counters* out) {
     out->samples = ctx->samples;
     out->dropped_nonfinite = h.dropped_nonfinite;
     out->kernel_launches = ctx->kernel_launches;
+    out->rays_culled = h.rays_culled;
     return TPT_OK;
 }
 
@@ -222,6 +223,7 @@ int tpt_scene_create(tpt_context* ctx, const tpt_scene_desc* d, tpt_scene** out)
     s->n_objects = d->n_objects;
     s->n_materials = d->n_materials;
     s->n_lights = d->n_lights;
+    for (size_t m = 0; m < d->n_materials; ++m) s->any_emissive = s->any_emissive || d->materials[m].emission > 0.0f;
     const size_t V = d->n_vertices, O = d->n_objects;
     std::vector<float4> mtl(2 * d->n_materials);
     for (size_t m = 0; m < d->n_materials; ++m) {

@@ -132,6 +132,25 @@ __device__ __forceinline__ void primary_ray(const CameraParams& cam, int px, int
     o = xmat4_point(cam.c2w, f3(0.f, 0.f, 0.f));
 }
 
+// The pyramid that contains every jittered ray of pixel (px, py): see traverse.cuh "pixel-frustum culling".
+__device__ __forceinline__ PixelFrustum pixel_frustum(const CameraParams& cam, int px, int py, float3 o) {
+    const float eps = 1.0f / 64.0f;
+    const float x0 = ((float)px - eps) * cam.invW * cam.sensorW - 0.5f * cam.sensorW, x1 = ((float)px + 1.0f + eps) * cam.invW * cam.sensorW - 0.5f * cam.sensorW;
+    const float y0 = ((float)py - eps) * cam.invH * cam.sensorH - 0.5f * cam.sensorH, y1 = ((float)py + 1.0f + eps) * cam.invH * cam.sensorH - 0.5f * cam.sensorH;
+    float3 c[4] = {mat4_dir(cam.c2w, f3(x0, y0, -1.f)), mat4_dir(cam.c2w, f3(x1, y0, -1.f)), mat4_dir(cam.c2w, f3(x1, y1, -1.f)),
+                   mat4_dir(cam.c2w, f3(x0, y1, -1.f))};
+    const float3 centre = (c[0] + c[1]) + (c[2] + c[3]);
+    PixelFrustum f;
+    f.o = o;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        float3 n = cross(c[k], c[(k + 1) & 3]);
+        if (dot(n, centre) < 0.f) n = -n;   // inward, whatever the handedness of c2w
+        f.n[k] = n;
+    }
+    return f;
+}
+
 __global__ void __launch_bounds__(256) k_primary_rays(CameraParams cam, int W, int H, int jitter, uint64_t seedKey, tpt_ray* __restrict__ rays) {
     const uint32_t n = (uint32_t)W * (uint32_t)H;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
@@ -258,6 +277,7 @@ struct ShadeParams {
     int envW, envH;
     int depth, maxDepth;
     uint64_t seedKey;
+    int directRays;          // 0 when no material of the scene is emissive: the extra cosine "direct" ray can only add emission
 };
 
 // ---- one path vertex ------------------------------------------------------------------------------
@@ -301,7 +321,7 @@ __device__ __forceinline__ bool shade_vertex(const BvhView& bvh, const ShadePara
     vx.Tn = T * vx.base;
     const float eta = m1.x, metallic = m1.y;
     const uint64_t key = rng_path_key(sp.seedKey, pixel, sample);
-    vx.direct = !(eta >= 1.0f || metallic > 0.0f);
+    vx.direct = sp.directRays && !(eta >= 1.0f || metallic > 0.0f);
     vx.next = depth + 1 < sp.maxDepth;
     vx.ddir = vx.ndir = f3(0.f, 0.f, 1.f);
     if (vx.direct) {   // the reference's extra cosine "direct" ray (diffuse only)
@@ -365,12 +385,22 @@ __global__ void __launch_bounds__(128) k_primary(BvhView bvh, ShadeParams sp, Ca
     int stack[kStackSize];
     stack[0] = kStackSentinel;
     const float3 o = xmat4_point(cam.c2w, f3(0.f, 0.f, 0.f));   // the camera position: the same for every sample
+    // no sample of this pixel can hit anything when the pixel's pyramid misses every leaf box: skip their traversals
+    const bool mayHit = frustum_may_hit(bvh, pixel_frustum(cam, px, py, o), stack);
+    if (!mayHit) {
+        const unsigned m = __activemask();
+        const unsigned culled = __reduce_add_sync(m, s1 - s0);
+        if ((threadIdx.x & 31) == __ffs(m) - 1) atomicAdd(&ctr->rays_culled, (unsigned long long)culled);
+        if (sp.env == nullptr) return;   // black environment: nothing to add either
+    }
     for (uint32_t sl = s0; sl < s1; ++sl) {
         const uint32_t sIdx = sampleBase + sl * sampleStride;
         float ju, jv;
         rng_pair(rng_path_key(sp.seedKey, pixel, sIdx), 0u, ju, jv);
         const float3 d = primary_dir(cam, px, py, ju, jv);
-        const HitRec h = traverse<COUNT>(bvh, o, d, false, stack, &ctr->node_visits, &ctr->tri_tests);
+        HitRec h;
+        h.leaf = -1;
+        if (mayHit) h = traverse<COUNT>(bvh, o, d, false, stack, &ctr->node_visits, &ctr->tri_tests);
         float3 term;
         Vertex vx;
         if (shade_vertex(bvh, sp, 0, o, d, f3(1.f, 1.f, 1.f), pixel, sIdx, h, term, vx, ctr)) {
@@ -833,6 +863,7 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
     sp.maxDepth = cfg->max_depth;
     sp.seedKey = rng_seed_key(cfg->seed);
     sp.depth = 0;
+    sp.directRays = s->any_emissive ? 1 : 0;
 
     for (uint32_t done = 0; done < (uint32_t)cfg->spp; done += k) {
         const uint32_t kk = ((uint32_t)cfg->spp - done) < k ? ((uint32_t)cfg->spp - done) : k;

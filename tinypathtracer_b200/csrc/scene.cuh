@@ -26,7 +26,7 @@ struct DeviceCounters {
     unsigned long long rays_primary, rays_extension, rays_shadow, rays_direct;
     unsigned long long node_visits, tri_tests;
     unsigned long long dropped_nonfinite;
-    unsigned long long pad;
+    unsigned long long rays_culled;   // camera samples answered by pixel-frustum culling (counted in rays_primary too)
 };
 
 struct BvhView {
@@ -96,6 +96,7 @@ struct tpt_scene {
     float4* tri_geom = nullptr;
     float4* tri_norm = nullptr;
     bool built = false;
+    bool any_emissive = false;    // some material has emission > 0 (else the reference's extra "direct" rays add nothing and are not traced)
     tpt::BvhView view() const { return tpt::BvhView{nodes, tri_geom, tri_norm, (int)n_faces}; }
 };
 

@@ -199,4 +199,47 @@ __device__ __forceinline__ void trav_leaf_step(TravState& s, const BvhView& bvh,
     else s.cur = stack[--s.sp];
 }
 
+// ---- pixel-frustum culling (k_primary) -------------------------------------------------------------------------
+// All camera samples of one pixel leave the same origin through the pixel's quadrilateral on the image plane, so
+// they lie inside a four-sided pyramid.  If that pyramid misses every leaf box of the tree, none of the pixel's
+// samples can hit anything and they need no traversal at all.  Conservative by construction: the footprint is grown
+// by 1/64 pixel on each side (rounding of the real ray directions is ~1e-7 of that), a box is rejected only when it
+// lies wholly outside one side plane, and a leaf counts as hit as soon as its BOX overlaps the pyramid.
+struct PixelFrustum {
+    float3 o;
+    float3 n[4];   // inward normals of the four side planes (all pass through o)
+};
+__device__ __forceinline__ bool frustum_box(const PixelFrustum& f, float lox, float hix, float loy, float hiy, float loz, float hiz) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const float3 n = f.n[k];
+        const float v = n.x * ((n.x >= 0.f ? hix : lox) - f.o.x) + n.y * ((n.y >= 0.f ? hiy : loy) - f.o.y) + n.z * ((n.z >= 0.f ? hiz : loz) - f.o.z);
+        if (v < 0.f) return false;   // even the most inward corner of the box is outside this plane
+    }
+    return true;
+}
+__device__ __forceinline__ bool frustum_may_hit(const BvhView& bvh, const PixelFrustum& f, int* stack) {
+    if (bvh.n_faces <= 1) return true;
+    int sp = 1, cur = 0;   // stack[0] holds the sentinel
+    while (cur != kStackSentinel) {
+        const float4* n = bvh.nodes + 4 * (size_t)cur;
+        const float4 n0 = __ldg(n), n1 = __ldg(n + 1), n2 = __ldg(n + 2);
+        const int2 n3 = __ldg(reinterpret_cast<const int2*>(n + 3));
+        const bool hL = frustum_box(f, n0.x, n0.y, n0.z, n0.w, n2.x, n2.y);
+        const bool hR = frustum_box(f, n1.x, n1.y, n1.z, n1.w, n2.z, n2.w);
+        if ((hL && n3.x < 0) || (hR && n3.y < 0)) return true;   // a leaf box overlaps the pyramid
+        if (hL && hR) {
+            stack[sp++] = n3.y;
+            cur = n3.x;
+        } else if (hL) {
+            cur = n3.x;
+        } else if (hR) {
+            cur = n3.y;
+        } else {
+            cur = stack[--sp];
+        }
+    }
+    return false;
+}
+
 }   // namespace tpt
