@@ -823,9 +823,10 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
     cudaStream_t st = ctx->stream;
     const int W = cfg->width, H = cfg->height;
     const uint32_t nPadded = tiles_x(W) * tiles_y(H) * 32u;
-    // default batch: as many camera samples as a 12 GiB queue budget allows (2 sides x (2+L) rays x 48 B each), at most 2^26
-    size_t target = ((size_t)12 << 30) / (96 * (2 + s->n_lights));
-    if (target > ((size_t)1 << 26)) target = (size_t)1 << 26;
+    // default batch: as many camera samples as a 32 GiB queue budget allows (2 sides x (2+L) rays x 48 B each), at most 2^27 —
+    // sized for 180 GB of HBM: fewer, larger batches mean fewer (mostly empty) deep-wave launches per frame
+    size_t target = ((size_t)32 << 30) / (96 * (2 + s->n_lights));
+    if (target > ((size_t)1 << 27)) target = (size_t)1 << 27;
     if (cfg->paths_in_flight > 0) target = (size_t)cfg->paths_in_flight;
     uint32_t k = (uint32_t)(target / nPadded);
     if (k < 1) k = 1;
