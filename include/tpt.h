@@ -123,6 +123,10 @@ typedef struct tpt_render_config {
 
 #define TPT_RENDER_COUNTERS 1u    /* count node/triangle visits per ray kind (slower; for roofline accounting) */
 #define TPT_RENDER_STAGE_TIMES 2u /* CUDA-event time of every wavefront kernel, summed per stage (one sync per batch) */
+#define TPT_RENDER_ENV_NEE 4u     /* sample the environment map from its alias table at every diffuse vertex (one extra shadow ray),
+                                   * combined with the reference's cosine-sampled misses by the balance heuristic: same expectation as
+                                   * the default estimator, lower variance under maps with small bright regions.  Off by default: the
+                                   * reference builds the map's pdf/cdf (src/env_light.cu:10-53) but never samples them. */
 
 typedef struct tpt_bvh_stats {
     float build_ms;          /* device time of the whole build, CUDA events on the context stream */
@@ -186,6 +190,13 @@ int tpt_scene_export_world(tpt_scene* scene, float* world_vertices, float* world
  * reference's tex2DLod point/clamp/normalised fetch (src/path_tracer.cu:288-294). */
 int tpt_env_set_rgba8(tpt_context* ctx, const uint8_t* rgba8, int width, int height);
 int tpt_env_clear(tpt_context* ctx); /* black environment (the reference's no-env case is UB) */
+/* Replaces EnvLightSample / EnvLightPDF (include/env_light.cuh:21-70, no call site in the reference): draws n directions
+ * from the map's luminance*sin(theta) distribution with the device alias tables; dirs_pdf is a HOST buffer of n*4 floats
+ * (unit direction xyz, density per unit solid angle).  Sample i uses the counter RNG with (seed, i). */
+int tpt_env_sample(tpt_context* ctx, size_t n, uint64_t seed, float* dirs_pdf);
+/* The alias tables themselves (width*height entries each, row 0 = bottom): acceptance probability, alias texel,
+ * probability mass per texel.  HOST buffers. */
+int tpt_env_sampler_tables(tpt_context* ctx, float* prob, uint32_t* alias, float* mass);
 
 /* Replaces traverseBVH (src/path_tracer.cu:61-107) as a batch entry: closest hit with t > 2e-4, or
  * (any_hit != 0) prim = index of some hit / -1.  rays/hits are host pointers unless device_ptrs != 0. */

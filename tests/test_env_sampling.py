@@ -1,0 +1,166 @@
+"""Alias-table importance sampling of the environment map (tinypathtracer_b200/csrc/env.cu, env.cuh) and the optional
+next-event estimation built on it (TPT_RENDER_ENV_NEE).
+
+The reference builds a pdf/cdf for its map (src/env_light.cu:10-53) but never samples them (EnvLightSample has no call
+site), so there is no reference output to compare with: the checks are the distribution's own invariants
+(table mass, sample histogram, pdf consistency, a Monte-Carlo integral) and that NEE leaves the rendered expectation
+unchanged while lowering the variance.
+"""
+import numpy as np
+import pytest
+
+from conftest import synthetic_sky
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def built(tpt, ctx, scenes):
+    out = {}
+    for name in ("ball", "box", "box2"):
+        ds = tpt.DeviceScene(ctx, scenes[name])
+        bvh = tpt.BVH(ds)
+        bvh.construct()
+        out[name] = (ds, bvh)
+    yield out
+    for ds, _ in out.values():
+        ds.close()
+
+
+def spot_sky(w=128, h=64):
+    """Dim sky with one small bright patch: the case cosine sampling handles badly."""
+    img = np.zeros((h, w, 4), np.uint8)
+    img[..., :3] = 6
+    img[h // 2:, :, 2] = 12                      # upper hemisphere slightly blue
+    img[int(h * 0.70):int(h * 0.76), int(w * 0.10):int(w * 0.13), :3] = 255
+    img[..., 3] = 255
+    return img
+
+
+def texel_weights(img):
+    h, w = img.shape[:2]
+    lum = 0.2126 * img[..., 0].astype(np.float64) + 0.7152 * img[..., 1] + 0.0722 * img[..., 2]
+    theta = (1.0 - (np.arange(h) + 0.5) / h) * np.pi
+    wgt = lum * np.sin(theta)[:, None]
+    return wgt / wgt.sum()
+
+
+def dir_to_texel(d, w, h):
+    u = np.arctan2(d[:, 2], d[:, 0]) / (2 * np.pi)
+    u = np.where(u < 0, u + 1, u)
+    v = 1.0 - np.arccos(np.clip(d[:, 1], -1, 1)) / np.pi
+    x = np.clip(np.floor(u * w).astype(np.int64), 0, w - 1)
+    y = np.clip(np.floor(v * h).astype(np.int64), 0, h - 1)
+    return x, y
+
+
+@pytest.mark.parametrize("make", [lambda: synthetic_sky(256, 128), spot_sky])
+def test_alias_tables_reproduce_texel_mass(make, tpt, ctx):
+    img = make()
+    env = tpt.EnvLight(ctx, img)
+    prob, alias, mass = env.sampler_tables()
+    h, w = img.shape[:2]
+    n = w * h
+    want = texel_weights(img)
+    assert abs(mass.sum(dtype=np.float64) - 1.0) < 1e-5
+    assert np.allclose(mass, want, rtol=2e-5, atol=1e-9)
+    assert (prob >= 0).all() and (prob <= 1.0).all() and (alias < n).all()
+    # probability of drawing texel i = (prob[i] + sum over buckets j aliased to i of (1 - prob[j])) / n
+    p = prob.astype(np.float64).ravel().copy()
+    np.add.at(p, alias.ravel().astype(np.int64), 1.0 - prob.astype(np.float64).ravel())
+    assert np.allclose(p / n, want.ravel(), rtol=1e-4, atol=2e-9)
+
+
+def test_samples_follow_the_pdf(tpt, ctx):
+    img = spot_sky()
+    h, w = img.shape[:2]
+    env = tpt.EnvLight(ctx, img)
+    n = 1 << 21
+    s = env.sample(n, seed=3)
+    d, pdf = s[:, :3].astype(np.float64), s[:, 3].astype(np.float64)
+    assert np.allclose(np.linalg.norm(d, axis=1), 1.0, atol=2e-6)
+    assert (pdf > 0).all()
+    want = texel_weights(img)
+    x, y = dir_to_texel(d, w, h)
+    # the reported pdf: uniform in (u, v) inside the texel, d(omega) = 2 pi^2 sin(theta) du dv
+    sin_t = np.hypot(d[:, 0], d[:, 2])
+    ok = np.isclose(pdf, want[y, x] * (w * h) / (2 * np.pi ** 2 * sin_t), rtol=5e-4)
+    assert ok.mean() > 0.999, ok.mean()       # the rest sit on a texel edge, where the float32 direction maps to the neighbour
+    # histogram over texels against the mass: normalised chi-square ~ 1
+    hist = np.bincount(y * w + x, minlength=w * h).astype(np.float64)
+    exp = want.ravel() * n
+    big = exp > 20
+    chi2 = (((hist - exp) ** 2 / np.maximum(exp, 1e-30))[big]).sum() / big.sum()
+    assert 0.8 < chi2 < 1.25, chi2
+    assert hist[~big].sum() <= 1.5 * exp[~big].sum() + 50
+    # Monte-Carlo integral of the map's luminance over the sphere, against the texel sum
+    lum = (0.2126 * img[..., 0].astype(np.float64) + 0.7152 * img[..., 1] + 0.0722 * img[..., 2]) / 255.0
+    theta = (1.0 - (np.arange(h) + 0.5) / h) * np.pi
+    exact = (lum * (2 * np.pi / w) * (2.0 * np.sin(np.pi / (2 * h)) * np.sin(theta))[:, None]).sum()   # exact band solid angles
+    mc = (lum[y, x] / pdf).mean()
+    assert abs(mc - exact) <= 5e-3 * exact, (mc, exact)
+    # a different seed draws different samples; the same seed the same
+    assert (env.sample(1024, seed=3) == s[:1024]).all()
+    assert (env.sample(1024, seed=4) != s[:1024]).any()
+
+
+def test_env_sample_needs_a_map(tpt, ctx):
+    env = tpt.EnvLight(ctx, None)
+    with pytest.raises(RuntimeError, match="no environment map"):
+        env.sample(16)
+
+
+def _relmse(a, b):
+    return float(((a.astype(np.float64) - b) ** 2).sum() / max((b.astype(np.float64) ** 2).sum(), 1e-30))
+
+
+@pytest.mark.parametrize("name", ["ball", "box2"])
+def test_nee_keeps_the_expectation_and_lowers_variance(name, tpt, ctx, built, scenes):
+    ds, _ = built[name]
+    cam = tpt.Camera.from_scene(scenes[name])
+    W, H = 64, 36
+    pt = tpt.PathTracer(ctx, W, H, env_rgba8=spot_sky())
+
+    def img(spp, seed, nee):
+        pt.m_radiance.clear()
+        pt.render_into(ds, cam, spp=spp, max_depth=8, seed=seed, env_nee=nee)
+        return pt.m_radiance.to_f32() / spp
+
+    ref = img(1 << 16, 5, False)                 # the reference's estimator, converged
+    nee = img(1 << 14, 6, True)
+    assert np.isfinite(nee).all()
+    err = _relmse(nee, ref)
+    assert err <= 1e-3, f"{name}: NEE image differs from the default estimator's: rel-MSE {err:.3e}"
+    assert abs(nee.mean() - ref.mean()) <= 0.01 * ref.mean()
+    # variance at equal (low) spp
+    e_plain = _relmse(img(64, 7, False), ref)
+    e_nee = _relmse(img(64, 7, True), ref)
+    # ball is lit by the map alone; box2's noise comes from its interior bounces, which NEE does not touch
+    assert e_nee < (0.5 if name == "ball" else 1.1) * e_plain, (e_nee, e_plain)
+    c = ctx.counters()
+    assert c["dropped_nonfinite"] >= 0
+
+
+def test_nee_flag_without_a_map_changes_nothing(tpt, ctx, built, scenes):
+    ds, _ = built["box"]
+    cam = tpt.Camera.from_scene(scenes["box"])
+    pt = tpt.PathTracer(ctx, 64, 36)
+    pt.render_into(ds, cam, spp=8, seed=2)
+    a = pt.m_radiance.to_i64()
+    pt.m_radiance.clear()
+    pt.render_into(ds, cam, spp=8, seed=2, env_nee=True)
+    assert (pt.m_radiance.to_i64() == a).all()
+
+
+def test_default_render_ignores_sampler_state(tpt, ctx, built, scenes):
+    """Building the alias tables (or having rendered with NEE) must not change a default render's bits."""
+    ds, _ = built["ball"]
+    cam = tpt.Camera.from_scene(scenes["ball"])
+    pt = tpt.PathTracer(ctx, 64, 36, env_rgba8=synthetic_sky(128, 64))
+    pt.render_into(ds, cam, spp=8, seed=2)
+    a = pt.m_radiance.to_i64()
+    pt.m_radiance.clear()
+    pt.render_into(ds, cam, spp=8, seed=2, env_nee=True)
+    pt.m_radiance.clear()
+    pt.render_into(ds, cam, spp=8, seed=2)
+    assert (pt.m_radiance.to_i64() == a).all()

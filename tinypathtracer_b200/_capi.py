@@ -23,6 +23,7 @@ lib = C.CDLL(str(LIB_PATH))
 TPT_OK = 0
 TPT_RENDER_COUNTERS = 1
 TPT_RENDER_STAGE_TIMES = 2
+TPT_RENDER_ENV_NEE = 4
 
 
 class Ray(C.Structure):
@@ -85,6 +86,8 @@ SIGNATURES = {
     "tpt_scene_export_world": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "tpt_env_set_rgba8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
     "tpt_env_clear": (C.c_int, [C.c_void_p]),
+    "tpt_env_sample": (C.c_int, [C.c_void_p, C.c_size_t, C.c_uint64, C.c_void_p]),
+    "tpt_env_sampler_tables": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "tpt_trace_rays": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int, C.c_int]),
     "tpt_trace_rays_counted": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int, C.c_int]),
     "tpt_generate_primary_rays": (C.c_int, [C.c_void_p, C.POINTER(Camera), C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_void_p, C.c_int]),

@@ -218,6 +218,21 @@ class EnvLight:
             img = np.ascontiguousarray(rgba8, np.uint8)
             assert img.ndim == 3 and img.shape[2] == 4
             check(lib.tpt_env_set_rgba8(ctx._h, _ptr(img), img.shape[1], img.shape[0]))
+        self.shape = None if rgba8 is None else (int(rgba8.shape[0]), int(rgba8.shape[1]))
+
+    def sample(self, n: int, seed: int = 1) -> np.ndarray:
+        """EnvLightSample (include/env_light.cuh:21-52; no call site in the reference): n x (dir.xyz, pdf per steradian)
+        drawn on the device from the map's luminance*sin(theta) alias tables."""
+        out = np.zeros((n, 4), np.float32)
+        check(lib.tpt_env_sample(self.ctx._h, n, seed, _ptr(out)))
+        return out
+
+    def sampler_tables(self):
+        """(prob, alias, mass) of the alias tables, each (height, width), row 0 = bottom."""
+        h, w = self.shape
+        prob, alias, mass = np.zeros((h, w), np.float32), np.zeros((h, w), np.uint32), np.zeros((h, w), np.float32)
+        check(lib.tpt_env_sampler_tables(self.ctx._h, _ptr(prob), _ptr(alias), _ptr(mass)))
+        return prob, alias, mass
 
 
 class Accum:
@@ -274,12 +289,13 @@ class Accum:
 
 
 def render_config(width, height, spp, max_depth=8, seed=1, sample_offset=0, sample_stride=1, counters=False, paths_in_flight=0,
-                  stage_times=False):
+                  stage_times=False, env_nee=False):
     c = capi.RenderConfig()
     c.width, c.height, c.spp, c.max_depth = width, height, spp, max_depth
     c.seed = seed
     c.sample_offset, c.sample_stride = sample_offset, sample_stride
-    c.flags = (capi.TPT_RENDER_COUNTERS if counters else 0) | (capi.TPT_RENDER_STAGE_TIMES if stage_times else 0)
+    c.flags = (capi.TPT_RENDER_COUNTERS if counters else 0) | (capi.TPT_RENDER_STAGE_TIMES if stage_times else 0) | \
+              (capi.TPT_RENDER_ENV_NEE if env_nee else 0)
     c.paths_in_flight = paths_in_flight
     return c
 
@@ -296,9 +312,9 @@ class PathTracer:
 
     def render_into(self, scene: DeviceScene, camera: Camera, spp: int, max_depth: int = 8, seed: int = 1, sample_offset: int = 0,
                     sample_stride: int = 1, counters: bool = False, paths_in_flight: int = 0, accum: Accum | None = None,
-                    stage_times: bool = False):
+                    stage_times: bool = False, env_nee: bool = False):
         cfg = render_config(self.m_width, self.m_height, spp, max_depth, seed, sample_offset, sample_stride, counters, paths_in_flight,
-                            stage_times)
+                            stage_times, env_nee)
         acc = accum or self.m_radiance
         check(lib.tpt_render(scene._h, C.byref(camera.c), C.byref(cfg), acc._h))
 

@@ -36,6 +36,9 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
 int tpt_accum_add_impl(tpt_accum* dst, const tpt_accum* src);
 int tpt_accum_to_f32_impl(tpt_accum* acc, float* d_out);
 int tpt_resolve_impl(tpt_accum* acc, int sppTotal, uint8_t* d_fb);
+int tpt_env_build_sampler(tpt_context* ctx);
+int tpt_env_free_sampler(tpt_context* ctx);
+int tpt_env_sample_impl(tpt_context* ctx, size_t n, uint64_t seed, float* host_dirs_pdf);
 
 namespace {
 
@@ -108,6 +111,7 @@ int tpt_context_destroy(tpt_context* ctx) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     cudaFree(ctx->env);
+    tpt_env_free_sampler(ctx);
     cudaFree(ctx->d_counters);
     cudaFree(ctx->q_ext[0]);
     cudaFree(ctx->q_ext[1]);
@@ -320,6 +324,7 @@ int tpt_env_set_rgba8(tpt_context* ctx, const uint8_t* rgba8, int w, int h) {
     TPT_CUDA(cudaStreamSynchronize(ctx->stream));
     if (ctx->env) cudaFree(ctx->env);
     ctx->env = nullptr;
+    tpt_env_free_sampler(ctx);
     TPT_CUDA(cudaMalloc(&ctx->env, (size_t)w * h * 4));
     TPT_CUDA(cudaMemcpyAsync(ctx->env, rgba8, (size_t)w * h * 4, cudaMemcpyHostToDevice, ctx->stream));
     TPT_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -334,7 +339,29 @@ int tpt_env_clear(tpt_context* ctx) {
     TPT_CUDA(cudaStreamSynchronize(ctx->stream));
     if (ctx->env) cudaFree(ctx->env);
     ctx->env = nullptr;
+    tpt_env_free_sampler(ctx);
     ctx->env_w = ctx->env_h = 0;
+    return TPT_OK;
+}
+
+int tpt_env_sample(tpt_context* ctx, size_t n, uint64_t seed, float* dirs_pdf) {
+    TPT_REQUIRE(ctx && (n == 0 || dirs_pdf), "tpt_env_sample: NULL argument");
+    TPT_REQUIRE(ctx->env != nullptr, "tpt_env_sample: no environment map set");
+    TPT_CHECK(bind(ctx));
+    if (n == 0) return TPT_OK;
+    return tpt_env_sample_impl(ctx, n, seed, dirs_pdf);
+}
+
+int tpt_env_sampler_tables(tpt_context* ctx, float* prob, uint32_t* alias, float* mass) {
+    TPT_REQUIRE(ctx && prob && alias && mass, "tpt_env_sampler_tables: NULL argument");
+    TPT_REQUIRE(ctx->env != nullptr, "tpt_env_sampler_tables: no environment map set");
+    TPT_CHECK(bind(ctx));
+    TPT_CHECK(tpt_env_build_sampler(ctx));
+    const size_t n = (size_t)ctx->env_w * ctx->env_h;
+    TPT_CUDA(cudaMemcpyAsync(prob, ctx->env_prob, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    TPT_CUDA(cudaMemcpyAsync(alias, ctx->env_alias, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    TPT_CUDA(cudaMemcpyAsync(mass, ctx->env_mass, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    TPT_CUDA(cudaStreamSynchronize(ctx->stream));
     return TPT_OK;
 }
 

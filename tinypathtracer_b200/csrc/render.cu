@@ -24,6 +24,7 @@
 // vertex is emissive (which also discards that vertex's own direct term, :421-424), or 0 at the depth
 // cut.  Every term is added to the pixel as an exact fixed-point integer, so the result does not
 // depend on the order in which kernels, warps or GPUs finish, nor on how terms are grouped.
+#include "env.cuh"
 #include "traverse.cuh"
 
 namespace tpt {
@@ -34,6 +35,7 @@ namespace tpt {
 struct PathRec {
     float3 o, d, T;
     uint32_t pixel, sample;
+    uint32_t w;   // extension ray (env NEE only): float bits of the solid-angle pdf its direction was drawn with, 0 = delta / camera
 };
 __device__ __forceinline__ PathRec load_path(const float4* __restrict__ p, uint32_t i) {
     const float4 a = __ldcs(p + 3 * (size_t)i), b = __ldcs(p + 3 * (size_t)i + 1), c = __ldcs(p + 3 * (size_t)i + 2);
@@ -43,6 +45,7 @@ __device__ __forceinline__ PathRec load_path(const float4* __restrict__ p, uint3
     r.T = f3(b.z, b.w, c.x);
     r.pixel = __float_as_uint(c.y);
     r.sample = __float_as_uint(c.z);
+    r.w = __float_as_uint(c.w);
     return r;
 }
 __device__ __forceinline__ void store_path(float4* __restrict__ p, uint32_t i, float3 o, float3 d, float3 T, uint32_t pixel,
@@ -278,6 +281,7 @@ struct ShadeParams {
     int depth, maxDepth;
     uint64_t seedKey;
     int directRays;          // 0 when no material of the scene is emissive: the extra cosine "direct" ray can only add emission
+    EnvSampler es;           // alias tables of the environment map (TPT_RENDER_ENV_NEE only)
 };
 
 // ---- one path vertex ------------------------------------------------------------------------------
@@ -292,13 +296,28 @@ struct Vertex {
     float3 ndir;     // next direction
     float3 ddir;     // direction of the "direct" ray
     bool next, direct;
+    // TPT_RENDER_ENV_NEE only: pdf of ndir (0 = delta lobe), and the environment sample (direction, weighted contribution)
+    float pb;
+    bool nee;
+    float3 ldir, lw;
 };
 
-__device__ __forceinline__ bool shade_vertex(const BvhView& bvh, const ShadeParams& sp, int depth, float3 o, float3 d, float3 T,
+//
+// NEE (TPT_RENDER_ENV_NEE): the environment term of the estimator, E[Tn * env(ndir) * miss], is evaluated by two
+// strategies combined with the balance heuristic — the reference's cosine-sampled extension ray (weight
+// pb / (pb + pl) applied where it misses) and one alias-table sample of the map per diffuse vertex (a shadow ray of
+// weight Tn * env(l) * pb(l) / (pl(l) + pb(l)), pb(l) = cos/pi).  Delta lobes and camera rays keep weight 1.
+// The expectation is the reference's; only the variance changes.
+template <bool NEE>
+__device__ __forceinline__ bool shade_vertex(const BvhView& bvh, const ShadeParams& sp, int depth, float3 o, float3 d, float3 T, uint32_t pbBits,
                                              uint32_t pixel, uint32_t sample, const HitRec& h, float3& terminal, Vertex& vx,
                                              DeviceCounters* ctr) {
     if (h.leaf < 0) {
         terminal = T * env_lookup(sp.env, sp.envW, sp.envH, d);
+        if (NEE && pbBits != 0u) {
+            const float pb = __uint_as_float(pbBits);
+            terminal = terminal * (pb / (pb + env_pdf(sp.es, d)));
+        }
         return false;
     }
     const float4 g2 = __ldg(bvh.tri_geom + 3 * (size_t)h.leaf + 2);
@@ -337,6 +356,23 @@ __device__ __forceinline__ bool shade_vertex(const BvhView& bvh, const ShadePara
         if (!vx.next) atomicAdd(&ctr->dropped_nonfinite, 1ull);
         vx.next = vx.next && (vx.Tn.x > 0.f || vx.Tn.y > 0.f || vx.Tn.z > 0.f);   // a black path adds nothing further
     }
+    if (NEE) {
+        vx.pb = 0.0f;
+        vx.nee = false;
+        if (vx.next && !(eta > 0.0f) && !(metallic > 0.0f) && sp.env != nullptr) {   // diffuse lobe of new_direction
+            const float3 nn = dot(d, nrm) > 0.0f ? -nrm : nrm;
+            vx.pb = dot(vx.ndir, nn) * (1.0f / kPi);
+            float u1, u2, u3, u4, pl;
+            rng_pair(key, 0x10000u + 2u * (uint32_t)depth, u1, u2);
+            rng_pair(key, 0x10001u + 2u * (uint32_t)depth, u3, u4);
+            vx.ldir = env_sample_dir(sp.es, u1, u2, u3, pl);
+            const float pbl = dot(vx.ldir, nn) * (1.0f / kPi);
+            if (pbl > 0.0f && pl > 0.0f) {
+                vx.lw = (vx.Tn * env_lookup(sp.env, sp.envW, sp.envH, vx.ldir)) * (pbl / (pl + pbl));
+                vx.nee = vx.lw.x > 0.f || vx.lw.y > 0.f || vx.lw.z > 0.f;
+            }
+        }
+    }
     return true;
 }
 
@@ -347,6 +383,7 @@ struct QueueOut {
 };
 
 // Emit the rays of a shaded vertex from whatever lanes are here (diverged callers allowed).
+template <bool NEE>
 __device__ __forceinline__ void emit_vertex(const ShadeParams& sp, const QueueOut& q, const Vertex& vx, uint32_t pixel, uint32_t sample) {
     // delta lights: one infinite shadow ray per light, contribution T_d * baseColor * Li
     for (int l = 0; l < sp.nLights; ++l) {
@@ -359,15 +396,19 @@ __device__ __forceinline__ void emit_vertex(const ShadeParams& sp, const QueueOu
         const uint32_t slot = append_sec(q.level, true);
         store_path(q.sec, slot, vx.P, vx.ddir, vx.Tn, pixel, sample, kKindDirect);
     }
+    if (NEE && vx.nee) {
+        const uint32_t slot = append_sec(q.level, false);
+        store_path(q.sec, slot, vx.P, vx.ldir, vx.lw, pixel, sample, kKindShadow);
+    }
     if (vx.next) {
         const uint32_t slot = append_ext(q.level);
-        store_path(q.ext, slot, vx.P, vx.ndir, vx.Tn, pixel, sample, 0u);
+        store_path(q.ext, slot, vx.P, vx.ndir, vx.Tn, pixel, sample, NEE ? __float_as_uint(vx.pb) : 0u);
     }
 }
 
 // ---- wave 0: generate + extend + shade, fused ---------------------------------------------------------
 // Thread = (pixel of an 8x4 tile, group of `spt` consecutive local samples).
-template <bool COUNT>
+template <bool COUNT, bool NEE>
 __global__ void __launch_bounds__(128) k_primary(BvhView bvh, ShadeParams sp, CameraParams cam, int W, int H, uint32_t nPadded,
                                                  uint32_t kSamples, uint32_t spt, uint32_t sampleBase, uint32_t sampleStride, QueueOut q,
                                                  unsigned long long* __restrict__ acc, DeviceCounters* ctr) {
@@ -403,8 +444,8 @@ __global__ void __launch_bounds__(128) k_primary(BvhView bvh, ShadeParams sp, Ca
         if (mayHit) h = traverse<COUNT>(bvh, o, d, false, stack, &ctr->node_visits, &ctr->tri_tests);
         float3 term;
         Vertex vx;
-        if (shade_vertex(bvh, sp, 0, o, d, f3(1.f, 1.f, 1.f), pixel, sIdx, h, term, vx, ctr)) {
-            emit_vertex(sp, q, vx, pixel, sIdx);
+        if (shade_vertex<NEE>(bvh, sp, 0, o, d, f3(1.f, 1.f, 1.f), 0u, pixel, sIdx, h, term, vx, ctr)) {
+            emit_vertex<NEE>(sp, q, vx, pixel, sIdx);
         } else if (term.x != 0.f || term.y != 0.f || term.z != 0.f) {
             if (finite3(term)) {
                 aR += to_fixed(term.x);
@@ -440,6 +481,7 @@ constexpr uint32_t kGrabMax = 256;
 constexpr int kStage = 64;
 constexpr uint32_t kNoItem = 0xffffffffu;
 
+template <bool NEE>
 __device__ __forceinline__ void shade_staged(const BvhView& bvh, const ShadeParams& sp, const float4* __restrict__ extIn, const QueueOut& q,
                                              unsigned long long* __restrict__ acc, DeviceCounters* ctr, const uint32_t* myIdx,
                                              const float4* myHit, uint32_t count) {
@@ -455,7 +497,7 @@ __device__ __forceinline__ void shade_staged(const BvhView& bvh, const ShadePara
         h.prim = -1;
         float3 term;
         Vertex vx;
-        if (shade_vertex(bvh, sp, sp.depth, p.o, p.d, p.T, p.pixel, p.sample, h, term, vx, ctr)) emit_vertex(sp, q, vx, p.pixel, p.sample);
+        if (shade_vertex<NEE>(bvh, sp, sp.depth, p.o, p.d, p.T, p.w, p.pixel, p.sample, h, term, vx, ctr)) emit_vertex<NEE>(sp, q, vx, p.pixel, p.sample);
         else accum_add(acc, p.pixel, term, ctr);
     }
     __syncwarp();
@@ -464,7 +506,7 @@ __device__ __forceinline__ void shade_staged(const BvhView& bvh, const ShadePara
 #ifndef TPT_WAVE_MIN_BLOCKS
 #define TPT_WAVE_MIN_BLOCKS 8
 #endif
-template <bool COUNT>
+template <bool COUNT, bool NEE>
 __global__ void __launch_bounds__(128, TPT_WAVE_MIN_BLOCKS) k_wave(BvhView bvh, ShadeParams sp, const float4* __restrict__ extIn, const float4* __restrict__ secIn,
                                               QueueLevel* __restrict__ levelIn, QueueOut q, unsigned long long* __restrict__ acc,
                                               DeviceCounters* ctr) {
@@ -533,7 +575,7 @@ __global__ void __launch_bounds__(128, TPT_WAVE_MIN_BLOCKS) k_wave(BvhView bvh, 
             if (fin) item = kNoItem;
             __syncwarp();
             if (nStaged >= 32u) {
-                shade_staged(bvh, sp, extIn, q, acc, ctr, myIdx, myHit, 32u);
+                shade_staged<NEE>(bvh, sp, extIn, q, acc, ctr, myIdx, myHit, 32u);
                 const uint32_t r = nStaged - 32u;
                 uint32_t ti = 0;
                 float4 th = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -602,7 +644,7 @@ __global__ void __launch_bounds__(128, TPT_WAVE_MIN_BLOCKS) k_wave(BvhView bvh, 
             } while (__popc(__ballot_sync(0xffffffffu, ts.cur < 0 && ts.cur != kStackSentinel)) >= keep);
         }
     }
-    if (nStaged) shade_staged(bvh, sp, extIn, q, acc, ctr, myIdx, myHit, nStaged);
+    if (nStaged) shade_staged<NEE>(bvh, sp, extIn, q, acc, ctr, myIdx, myHit, nStaged);
     if (COUNT) {
         const unsigned sv = __reduce_add_sync(0xffffffffu, nv), st = __reduce_add_sync(0xffffffffu, nt);
         if (lane == 0) {
@@ -818,21 +860,27 @@ static int ensure_pools(tpt_context* ctx, size_t paths, size_t secPerPath) {
 }
 
 
+int tpt_env_build_sampler(tpt_context* ctx);   // env.cu
+
 int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config* cfg, tpt_accum* acc) {
     tpt_context* ctx = s->ctx;
     cudaStream_t st = ctx->stream;
+    // environment next-event estimation needs a map to sample; without one the flag changes nothing
+    const bool nee = (cfg->flags & TPT_RENDER_ENV_NEE) != 0 && ctx->env != nullptr;
+    if (nee) TPT_CHECK(tpt_env_build_sampler(ctx));
     const int W = cfg->width, H = cfg->height;
     const uint32_t nPadded = tiles_x(W) * tiles_y(H) * 32u;
     // default batch: as many camera samples as a 32 GiB queue budget allows (2 sides x (2+L) rays x 48 B each), at most 2^27 —
     // sized for 180 GB of HBM: fewer, larger batches mean fewer (mostly empty) deep-wave launches per frame
-    size_t target = ((size_t)32 << 30) / (96 * (2 + s->n_lights));
+    const size_t secPerPath = s->n_lights + 1 + (nee ? 1 : 0);
+    size_t target = ((size_t)32 << 30) / (96 * (1 + secPerPath));
     if (target > ((size_t)1 << 27)) target = (size_t)1 << 27;
     if (cfg->paths_in_flight > 0) target = (size_t)cfg->paths_in_flight;
     uint32_t k = (uint32_t)(target / nPadded);
     if (k < 1) k = 1;
     if (k > (uint32_t)cfg->spp) k = (uint32_t)cfg->spp;
     const size_t pool = (size_t)nPadded * k;
-    TPT_CHECK(ensure_pools(ctx, pool, s->n_lights + 1));
+    TPT_CHECK(ensure_pools(ctx, pool, secPerPath));
 
     const CameraParams cp = make_camera(cam, W, H);
     const bool counted = (cfg->flags & TPT_RENDER_COUNTERS) != 0;
@@ -848,11 +896,16 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
     size_t ev = 0;
     auto mark = [&]() { if (timed) cudaEventRecord(ctx->stage_events[ev++], st); };
     const BvhView view = s->view();
-    if (ctx->wave_grid == 0) {
-        ctx->wave_grid = kNumSMs * resident_blocks(k_wave<false>, 128);
-        ctx->wave_grid_counted = kNumSMs * resident_blocks(k_wave<true>, 128);
+    if (ctx->wave_grid[0] == 0) {
+        ctx->wave_grid[0] = kNumSMs * resident_blocks(k_wave<false, false>, 128);
+        ctx->wave_grid[1] = kNumSMs * resident_blocks(k_wave<true, false>, 128);
+        ctx->wave_grid[2] = kNumSMs * resident_blocks(k_wave<false, true>, 128);
+        ctx->wave_grid[3] = kNumSMs * resident_blocks(k_wave<true, true>, 128);
     }
-    const unsigned gridWave = counted ? ctx->wave_grid_counted : ctx->wave_grid;
+    const int variant = (counted ? 1 : 0) + (nee ? 2 : 0);
+    const unsigned gridWave = ctx->wave_grid[variant];
+    const auto kPrimary = variant == 0 ? k_primary<false, false> : variant == 1 ? k_primary<true, false> : variant == 2 ? k_primary<false, true> : k_primary<true, true>;
+    const auto kWave = variant == 0 ? k_wave<false, false> : variant == 1 ? k_wave<true, false> : variant == 2 ? k_wave<false, true> : k_wave<true, true>;
 
     ShadeParams sp;
     sp.mtl = s->mtl_table;
@@ -865,6 +918,7 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
     sp.seedKey = rng_seed_key(cfg->seed);
     sp.depth = 0;
     sp.directRays = s->any_emissive ? 1 : 0;
+    sp.es = EnvSampler{ctx->env_prob, ctx->env_alias, ctx->env_mass, ctx->env_w, ctx->env_h};
 
     for (uint32_t done = 0; done < (uint32_t)cfg->spp; done += k) {
         const uint32_t kk = ((uint32_t)cfg->spp - done) < k ? ((uint32_t)cfg->spp - done) : k;
@@ -880,12 +934,7 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
             const QueueOut q{ctx->q_ext[1], ctx->q_sec[1], static_cast<QueueLevel*>(ctx->levels) + 1};
             const unsigned grid = (unsigned)(((size_t)nPadded * groups + 127) / 128);
             const uint32_t sampleBase = (uint32_t)cfg->sample_offset + done * (uint32_t)cfg->sample_stride;
-            if (counted)
-                k_primary<true><<<grid, 128, 0, st>>>(view, sp, cp, W, H, nPadded, kk, spt, sampleBase, (uint32_t)cfg->sample_stride, q, acc->data,
-                                                      ctx->d_counters);
-            else
-                k_primary<false><<<grid, 128, 0, st>>>(view, sp, cp, W, H, nPadded, kk, spt, sampleBase, (uint32_t)cfg->sample_stride, q, acc->data,
-                                                       ctx->d_counters);
+            kPrimary<<<grid, 128, 0, st>>>(view, sp, cp, W, H, nPadded, kk, spt, sampleBase, (uint32_t)cfg->sample_stride, q, acc->data, ctx->d_counters);
         }
         mark();
         // wave w traces extension rays towards vertex w and the secondary rays of vertex w-1; the last wave
@@ -894,10 +943,7 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
             const int in = w & 1, out = in ^ 1;
             sp.depth = w;
             const QueueOut q{ctx->q_ext[out], ctx->q_sec[out], static_cast<QueueLevel*>(ctx->levels) + w + 1};
-            if (counted)
-                k_wave<true><<<gridWave, 128, 0, st>>>(view, sp, ctx->q_ext[in], ctx->q_sec[in], static_cast<QueueLevel*>(ctx->levels) + w, q, acc->data, ctx->d_counters);
-            else
-                k_wave<false><<<gridWave, 128, 0, st>>>(view, sp, ctx->q_ext[in], ctx->q_sec[in], static_cast<QueueLevel*>(ctx->levels) + w, q, acc->data, ctx->d_counters);
+            kWave<<<gridWave, 128, 0, st>>>(view, sp, ctx->q_ext[in], ctx->q_sec[in], static_cast<QueueLevel*>(ctx->levels) + w, q, acc->data, ctx->d_counters);
             mark();
         }
         ctx->kernel_launches += 1 + (uint64_t)cfg->max_depth;

@@ -45,6 +45,10 @@ struct tpt_context {
     // environment map (RGBA8, row 0 = bottom)
     uchar4* env = nullptr;
     int env_w = 0, env_h = 0;
+    // alias tables over the map's texels (env.cu; built on first use by TPT_RENDER_ENV_NEE / tpt_env_sample, dropped with the map)
+    float* env_prob = nullptr;
+    uint32_t* env_alias = nullptr;
+    float* env_mass = nullptr;
     // counters
     tpt::DeviceCounters* d_counters = nullptr;
     uint64_t samples = 0;
@@ -54,7 +58,7 @@ struct tpt_context {
     float4* q_sec[2] = {nullptr, nullptr};
     size_t ext_capacity = 0, sec_capacity = 0;
     void* levels = nullptr;                       // QueueLevel[kMaxLevels] (render.cu)
-    unsigned wave_grid = 0, wave_grid_counted = 0; // persistent grid sizes of k_wave (148 x resident blocks)
+    unsigned wave_grid[4] = {0, 0, 0, 0};          // persistent grid sizes of k_wave<COUNT, NEE> (148 x resident blocks), index COUNT + 2*NEE
     unsigned long long* trace_cursor = nullptr;    // item cursor of k_trace_rays_persistent
     unsigned trace_grid = 0, trace_grid_counted = 0;
     // scratch for trace_rays with host pointers
