@@ -123,6 +123,8 @@ typedef struct tpt_render_config {
 
 #define TPT_RENDER_COUNTERS 1u    /* count node/triangle visits per ray kind (slower; for roofline accounting) */
 #define TPT_RENDER_STAGE_TIMES 2u /* CUDA-event time of every wavefront kernel, summed per stage (one sync per batch) */
+#define TPT_RENDER_NO_PIXEL_CANDIDATES 8u /* check switch: camera samples walk the tree one by one instead of testing their
+                                           * pixel's candidate triangles; the accumulation buffer is bit-identical either way */
 #define TPT_RENDER_ENV_NEE 4u     /* sample the environment map from its alias table at every diffuse vertex (one extra shadow ray),
                                    * combined with the reference's cosine-sampled misses by the balance heuristic: same expectation as
                                    * the default estimator, lower variance under maps with small bright regions.  Off by default: the

@@ -174,6 +174,7 @@ public:
     int m_width = 1920, m_height = 1080;
     int m_spp = 64, m_depth = 8, m_frames = 1;
     uint64_t m_seed = 1;
+    bool m_envNEE = false;   // TPT_RENDER_ENV_NEE: sample the environment map at diffuse vertices (same expectation, lower variance)
     std::string m_output;
     double m_lastFrameMs = 0.0;
     Context& context() { return *m_ctx; }

@@ -212,6 +212,22 @@ def test_slices_are_bit_identical(tpt, ctx, built, scenes):
     assert (pt.m_radiance.to_i64() == whole).all()
 
 
+@pytest.mark.parametrize("name", ["box", "ball", "light", "tir", "box2", "square"])
+def test_pixel_candidates_are_bit_identical_to_per_sample_traversal(name, tpt, ctx, built, scenes):
+    """k_primary tests each camera sample against its pixel's candidate triangles (one pyramid walk per pixel) instead
+    of walking the tree per sample; the closest hit, and with it every later decision of the path, must be the same bits."""
+    ds, _ = built[name]
+    cam = tpt.Camera.from_scene(scenes[name])
+    W, H, spp = 200, 120, 24
+    pt = tpt.PathTracer(ctx, W, H, env_rgba8=synthetic_sky(128, 64))
+    pt.render_into(ds, cam, spp=spp, seed=9)
+    a = pt.m_radiance.to_i64()
+    pt.m_radiance.clear()
+    pt.render_into(ds, cam, spp=spp, seed=9, pixel_candidates=False)
+    assert (pt.m_radiance.to_i64() == a).all()
+    assert a.any()
+
+
 def test_resolve_matches_reference_bytes(tpt, ctx, built, scenes, orc):
     """copyToFB (reference src/path_tracer.cu:451-471): truncation, BGR order, Y flip, alpha untouched."""
     ds, _ = built["box"]

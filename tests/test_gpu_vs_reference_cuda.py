@@ -25,7 +25,7 @@ def run_reference(scene, W, H, spp, env, out, exe="tpt_ref_headless"):
     return fb, info
 
 
-@pytest.mark.parametrize("scene,env,depth,spp", [("box", "black.png", 8, 16384), ("ball", "sky.png", 8, 1024), ("tir", "black.png", 8, 65536),
+@pytest.mark.parametrize("scene,env,depth,spp", [("box", "black.png", 8, 16384), ("ball", "sky.png", 8, 1024), ("tir", "black.png", 8, 262144),
                                                  ("box2", "sky.png", 8, 4096), ("light", "sky.png", 8, 1024), ("square", "black.png", 8, 1024)])
 def test_image_matches_reference_cuda_build(scene, env, depth, spp, tpt, ctx, scenes, tmp_path):
     if not (REF / "tpt_ref_headless").exists():

@@ -24,6 +24,7 @@ TPT_OK = 0
 TPT_RENDER_COUNTERS = 1
 TPT_RENDER_STAGE_TIMES = 2
 TPT_RENDER_ENV_NEE = 4
+TPT_RENDER_NO_PIXEL_CANDIDATES = 8
 
 
 class Ray(C.Structure):

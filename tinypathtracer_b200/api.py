@@ -289,13 +289,13 @@ class Accum:
 
 
 def render_config(width, height, spp, max_depth=8, seed=1, sample_offset=0, sample_stride=1, counters=False, paths_in_flight=0,
-                  stage_times=False, env_nee=False):
+                  stage_times=False, env_nee=False, pixel_candidates=True):
     c = capi.RenderConfig()
     c.width, c.height, c.spp, c.max_depth = width, height, spp, max_depth
     c.seed = seed
     c.sample_offset, c.sample_stride = sample_offset, sample_stride
     c.flags = (capi.TPT_RENDER_COUNTERS if counters else 0) | (capi.TPT_RENDER_STAGE_TIMES if stage_times else 0) | \
-              (capi.TPT_RENDER_ENV_NEE if env_nee else 0)
+              (capi.TPT_RENDER_ENV_NEE if env_nee else 0) | (0 if pixel_candidates else capi.TPT_RENDER_NO_PIXEL_CANDIDATES)
     c.paths_in_flight = paths_in_flight
     return c
 
@@ -312,9 +312,9 @@ class PathTracer:
 
     def render_into(self, scene: DeviceScene, camera: Camera, spp: int, max_depth: int = 8, seed: int = 1, sample_offset: int = 0,
                     sample_stride: int = 1, counters: bool = False, paths_in_flight: int = 0, accum: Accum | None = None,
-                    stage_times: bool = False, env_nee: bool = False):
+                    stage_times: bool = False, env_nee: bool = False, pixel_candidates: bool = True):
         cfg = render_config(self.m_width, self.m_height, spp, max_depth, seed, sample_offset, sample_stride, counters, paths_in_flight,
-                            stage_times, env_nee)
+                            stage_times, env_nee, pixel_candidates)
         acc = accum or self.m_radiance
         check(lib.tpt_render(scene._h, C.byref(camera.c), C.byref(cfg), acc._h))
 

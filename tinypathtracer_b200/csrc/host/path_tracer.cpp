@@ -56,6 +56,7 @@ void PathTracer::doTrace(DeviceScene& scene, Camera& camera, unsigned char* fram
     cfg.seed = m_seed;
     cfg.sample_offset = 0;
     cfg.sample_stride = 1;
+    cfg.flags = m_envNEE ? TPT_RENDER_ENV_NEE : 0u;
     const tpt_camera cam = camera.toABI();
     const auto t0 = std::chrono::steady_clock::now();
     check(tpt_do_trace(scene.handle.get(), &cam, &cfg, m_radiance, framebuffer), "tpt_do_trace");

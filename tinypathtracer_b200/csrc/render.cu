@@ -282,6 +282,7 @@ struct ShadeParams {
     uint64_t seedKey;
     int directRays;          // 0 when no material of the scene is emissive: the extra cosine "direct" ray can only add emission
     EnvSampler es;           // alias tables of the environment map (TPT_RENDER_ENV_NEE only)
+    int pixelCandidates;     // k_primary: per-pixel candidate triangles instead of one tree traversal per camera sample
 };
 
 // ---- one path vertex ------------------------------------------------------------------------------
@@ -426,8 +427,12 @@ __global__ void __launch_bounds__(128) k_primary(BvhView bvh, ShadeParams sp, Ca
     int stack[kStackSize];
     stack[0] = kStackSentinel;
     const float3 o = xmat4_point(cam.c2w, f3(0.f, 0.f, 0.f));   // the camera position: the same for every sample
-    // no sample of this pixel can hit anything when the pixel's pyramid misses every leaf box: skip their traversals
-    const bool mayHit = frustum_may_hit(bvh, pixel_frustum(cam, px, py, o), stack);
+    // One walk of the tree with the pixel's pyramid finds the candidate triangles of ALL its samples (traverse.cuh):
+    // nc == 0: no sample can hit anything; 1..kMaxCandidates: test those per sample; -1: too many, traverse per sample.
+    unsigned nv = 0, nt = 0;
+    const int nc = sp.pixelCandidates ? frustum_collect(bvh, pixel_frustum(cam, px, py, o), stack, nv)
+                                      : (frustum_may_hit(bvh, pixel_frustum(cam, px, py, o), stack) ? -1 : 0);
+    const bool mayHit = nc != 0;
     if (!mayHit) {
         const unsigned m = __activemask();
         const unsigned culled = __reduce_add_sync(m, s1 - s0);
@@ -441,7 +446,15 @@ __global__ void __launch_bounds__(128) k_primary(BvhView bvh, ShadeParams sp, Ca
         const float3 d = primary_dir(cam, px, py, ju, jv);
         HitRec h;
         h.leaf = -1;
-        if (mayHit) h = traverse<COUNT>(bvh, o, d, false, stack, &ctr->node_visits, &ctr->tri_tests);
+        if (nc > 0) {
+            h.t = FLT_MAX;
+            h.u = h.v = 0.0f;
+            h.prim = -1;
+            for (int k = 0; k < nc; ++k) leaf_test(bvh, stack[kStackSize - 1 - k], o, d, h);
+            if (COUNT) nt += (unsigned)nc;
+        } else if (nc < 0) {
+            h = traverse<COUNT>(bvh, o, d, false, stack, &ctr->node_visits, &ctr->tri_tests);
+        }
         float3 term;
         Vertex vx;
         if (shade_vertex<NEE>(bvh, sp, 0, o, d, f3(1.f, 1.f, 1.f), 0u, pixel, sIdx, h, term, vx, ctr)) {
@@ -454,6 +467,14 @@ __global__ void __launch_bounds__(128) k_primary(BvhView bvh, ShadeParams sp, Ca
             } else {
                 atomicAdd(&ctr->dropped_nonfinite, 1ull);
             }
+        }
+    }
+    if (COUNT) {
+        const unsigned m = __activemask();
+        const unsigned sv = __reduce_add_sync(m, nv), st = __reduce_add_sync(m, nt);
+        if ((threadIdx.x & 31) == __ffs(m) - 1) {
+            atomicAdd(&ctr->node_visits, (unsigned long long)sv);
+            atomicAdd(&ctr->tri_tests, (unsigned long long)st);
         }
     }
     unsigned long long* dst = acc + 3 * (size_t)pixel;
@@ -918,6 +939,7 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
     sp.seedKey = rng_seed_key(cfg->seed);
     sp.depth = 0;
     sp.directRays = s->any_emissive ? 1 : 0;
+    sp.pixelCandidates = (cfg->flags & TPT_RENDER_NO_PIXEL_CANDIDATES) ? 0 : 1;
     sp.es = EnvSampler{ctx->env_prob, ctx->env_alias, ctx->env_mass, ctx->env_w, ctx->env_h};
 
     for (uint32_t done = 0; done < (uint32_t)cfg->spp; done += k) {

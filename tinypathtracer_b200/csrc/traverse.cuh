@@ -242,4 +242,49 @@ __device__ __forceinline__ bool frustum_may_hit(const BvhView& bvh, const PixelF
     return false;
 }
 
+// The same walk, collecting instead of stopping: every leaf whose box overlaps the pyramid is a CANDIDATE, and a
+// camera sample of this pixel can only hit candidates.  Testing the candidates directly (leaf_test, the same exactly
+// rounded arithmetic and tie-break) gives bit for bit the closest hit a full traversal returns, without walking the
+// tree once per sample.  Candidates are written to the TOP of the caller's stack array (stack[kStackSize-1-k]), the
+// walk's own stack grows from the bottom.  Returns the number of candidates, or -1 when there are more than
+// kMaxCandidates (or the walk would collide with them): the caller then traverses per sample.
+constexpr int kMaxCandidates = 8;
+__device__ __forceinline__ int frustum_collect(const BvhView& bvh, const PixelFrustum& f, int* stack, unsigned& nodeVisits) {
+    if (bvh.n_faces <= 1) {
+        stack[kStackSize - 1] = 0;
+        return 1;
+    }
+    int sp = 1, cur = 0, nc = 0;   // stack[0] holds the sentinel
+    while (cur != kStackSentinel) {
+        const float4* n = bvh.nodes + 4 * (size_t)cur;
+        const float4 n0 = __ldg(n), n1 = __ldg(n + 1), n2 = __ldg(n + 2);
+        const int2 n3 = __ldg(reinterpret_cast<const int2*>(n + 3));
+        ++nodeVisits;
+        bool hL = frustum_box(f, n0.x, n0.y, n0.z, n0.w, n2.x, n2.y);
+        bool hR = frustum_box(f, n1.x, n1.y, n1.z, n1.w, n2.z, n2.w);
+        if (hL && n3.x < 0) {
+            if (nc == kMaxCandidates) return -1;
+            stack[kStackSize - 1 - nc++] = ~n3.x;
+            hL = false;
+        }
+        if (hR && n3.y < 0) {
+            if (nc == kMaxCandidates) return -1;
+            stack[kStackSize - 1 - nc++] = ~n3.y;
+            hR = false;
+        }
+        if (hL && hR) {
+            if (sp >= kStackSize - kMaxCandidates - 1) return -1;
+            stack[sp++] = n3.y;
+            cur = n3.x;
+        } else if (hL) {
+            cur = n3.x;
+        } else if (hR) {
+            cur = n3.y;
+        } else {
+            cur = stack[--sp];
+        }
+    }
+    return nc;
+}
+
 }   // namespace tpt
