@@ -257,7 +257,7 @@ def run_ours(args):
                     "avg_launch_us": round(1e3 * trav_ms / max(trav_launches, 1), 2),
                     "share_of_step": round(trav_ms / ms_step, 4),
                     "stage_ms": {k: round(v["ms"], 3) for k, v in st.items()},
-                    "rays": {k: c1[k] for k in ("rays_primary", "rays_culled", "rays_extension", "rays_shadow", "rays_direct")},
+                    "rays": {k: c1[k] for k in ("rays_primary", "rays_culled", "rays_candidates", "rays_extension", "rays_shadow", "rays_direct")},
                     "note": "BVH of this workload is L1/L2-resident; node fetches never reach HBM, the HBM fraction is an upper-bound accounting (SURVEY §8d)"}
         cpu = cpu_baseline(args, fixture, W, H, depth, env, seed) if world == 1 and not args.no_cpu_baseline else None
         line = {

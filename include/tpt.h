@@ -147,6 +147,8 @@ typedef struct tpt_counters {
     uint64_t kernel_launches;
     uint64_t rays_culled;                 /* camera samples (part of rays_primary) answered without a traversal: their pixel's
                                            * pyramid misses every leaf box of the tree (k_primary's pixel-frustum culling) */
+    uint64_t rays_candidates;             /* camera samples (part of rays_primary) answered by testing the 1..8 candidate triangles
+                                           * of their pixel's pyramid instead of walking the tree */
 } tpt_counters;
 
 /* Device time per wavefront stage since the last tpt_reset_counters, measured with CUDA events on the

@@ -162,6 +162,7 @@ int tpt_get_counters(tpt_context* ctx, tpt_counters* out) {
     out->dropped_nonfinite = h.dropped_nonfinite;
     out->kernel_launches = ctx->kernel_launches;
     out->rays_culled = h.rays_culled;
+    out->rays_candidates = h.rays_candidates;
     return TPT_OK;
 }
 

@@ -438,6 +438,10 @@ __global__ void __launch_bounds__(128) k_primary(BvhView bvh, ShadeParams sp, Ca
         const unsigned culled = __reduce_add_sync(m, s1 - s0);
         if ((threadIdx.x & 31) == __ffs(m) - 1) atomicAdd(&ctr->rays_culled, (unsigned long long)culled);
         if (sp.env == nullptr) return;   // black environment: nothing to add either
+    } else if (nc > 0) {
+        const unsigned m = __activemask();
+        const unsigned n = __reduce_add_sync(m, s1 - s0);
+        if ((threadIdx.x & 31) == __ffs(m) - 1) atomicAdd(&ctr->rays_candidates, (unsigned long long)n);
     }
     for (uint32_t sl = s0; sl < s1; ++sl) {
         const uint32_t sIdx = sampleBase + sl * sampleStride;
@@ -450,8 +454,11 @@ __global__ void __launch_bounds__(128) k_primary(BvhView bvh, ShadeParams sp, Ca
             h.t = FLT_MAX;
             h.u = h.v = 0.0f;
             h.prim = -1;
-            for (int k = 0; k < nc; ++k) leaf_test(bvh, stack[kStackSize - 1 - k], o, d, h);
-            if (COUNT) nt += (unsigned)nc;
+            for (int k = 0; k < nc; ++k) {   // sorted by a lower bound of t: nothing beyond the best hit needs testing
+                if (h.t < __int_as_float(stack[kStackSize - 1 - kMaxCandidates - k])) break;
+                leaf_test(bvh, stack[kStackSize - 1 - k], o, d, h);
+                if (COUNT) ++nt;
+            }
         } else if (nc < 0) {
             h = traverse<COUNT>(bvh, o, d, false, stack, &ctr->node_visits, &ctr->tri_tests);
         }

@@ -27,6 +27,7 @@ struct DeviceCounters {
     unsigned long long node_visits, tri_tests;
     unsigned long long dropped_nonfinite;
     unsigned long long rays_culled;   // camera samples answered by pixel-frustum culling (counted in rays_primary too)
+    unsigned long long rays_candidates;   // camera samples answered by testing their pixel's candidate triangles (in rays_primary too)
 };
 
 struct BvhView {

@@ -245,13 +245,41 @@ __device__ __forceinline__ bool frustum_may_hit(const BvhView& bvh, const PixelF
 // The same walk, collecting instead of stopping: every leaf whose box overlaps the pyramid is a CANDIDATE, and a
 // camera sample of this pixel can only hit candidates.  Testing the candidates directly (leaf_test, the same exactly
 // rounded arithmetic and tie-break) gives bit for bit the closest hit a full traversal returns, without walking the
-// tree once per sample.  Candidates are written to the TOP of the caller's stack array (stack[kStackSize-1-k]), the
-// walk's own stack grows from the bottom.  Returns the number of candidates, or -1 when there are more than
-// kMaxCandidates (or the walk would collide with them): the caller then traverses per sample.
-constexpr int kMaxCandidates = 8;
+// tree once per sample.  Candidates are kept sorted by a lower bound of the hit distance inside their box (distance
+// from the apex to the box, with slack for rounding), so the per-sample loop stops at the first candidate whose bound
+// exceeds the best t found.  They live at the TOP of the caller's stack array — leaf k at stack[kStackSize-1-k], its
+// bound (float bits) at stack[kStackSize-1-kMaxCandidates-k] — while the walk's own stack grows from the bottom.
+// Returns the number of candidates, or -1 when there are more than kMaxCandidates (or the walk would collide with
+// them): the caller then traverses per sample.
+#ifndef TPT_MAX_CANDIDATES
+#define TPT_MAX_CANDIDATES 24
+#endif
+constexpr int kMaxCandidates = TPT_MAX_CANDIDATES;
+__device__ __forceinline__ float box_distance_bound(float3 o, float lox, float hix, float loy, float hiy, float loz, float hiz) {
+    const float dx = fmaxf(fmaxf(lox - o.x, o.x - hix), 0.0f), dy = fmaxf(fmaxf(loy - o.y, o.y - hiy), 0.0f),
+                dz = fmaxf(fmaxf(loz - o.z, o.z - hiz), 0.0f);
+    const float mag = fmaxf(fmaxf(fmaxf(fabsf(lox), fabsf(hix)), fmaxf(fabsf(loy), fabsf(hiy))), fmaxf(fmaxf(fabsf(loz), fabsf(hiz)),
+                            fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z))));
+    // t is measured in units of |d| <= 1 (the reference's frsqrt never overestimates), so t >= distance; an accepted hit
+    // lies within ~1e-6 * mag of its triangle's box: 1e-4 relative + 3e-5 * mag absolute slack
+    return fmaxf(sqrtf(dx * dx + dy * dy + dz * dz) * 0.9999f - 3e-5f * mag, 0.0f);
+}
+__device__ __forceinline__ bool candidate_insert(int* stack, int& nc, int leaf, float bound) {
+    if (nc == kMaxCandidates) return false;
+    int k = nc++;
+    while (k > 0 && __int_as_float(stack[kStackSize - kMaxCandidates - k]) > bound) {   // entry k-1 moves to k
+        stack[kStackSize - 1 - k] = stack[kStackSize - k];
+        stack[kStackSize - 1 - kMaxCandidates - k] = stack[kStackSize - kMaxCandidates - k];
+        --k;
+    }
+    stack[kStackSize - 1 - k] = leaf;
+    stack[kStackSize - 1 - kMaxCandidates - k] = __float_as_int(bound);
+    return true;
+}
 __device__ __forceinline__ int frustum_collect(const BvhView& bvh, const PixelFrustum& f, int* stack, unsigned& nodeVisits) {
     if (bvh.n_faces <= 1) {
         stack[kStackSize - 1] = 0;
+        stack[kStackSize - 1 - kMaxCandidates] = 0;   // bound 0.0f
         return 1;
     }
     int sp = 1, cur = 0, nc = 0;   // stack[0] holds the sentinel
@@ -263,17 +291,15 @@ __device__ __forceinline__ int frustum_collect(const BvhView& bvh, const PixelFr
         bool hL = frustum_box(f, n0.x, n0.y, n0.z, n0.w, n2.x, n2.y);
         bool hR = frustum_box(f, n1.x, n1.y, n1.z, n1.w, n2.z, n2.w);
         if (hL && n3.x < 0) {
-            if (nc == kMaxCandidates) return -1;
-            stack[kStackSize - 1 - nc++] = ~n3.x;
+            if (!candidate_insert(stack, nc, ~n3.x, box_distance_bound(f.o, n0.x, n0.y, n0.z, n0.w, n2.x, n2.y))) return -1;
             hL = false;
         }
         if (hR && n3.y < 0) {
-            if (nc == kMaxCandidates) return -1;
-            stack[kStackSize - 1 - nc++] = ~n3.y;
+            if (!candidate_insert(stack, nc, ~n3.y, box_distance_bound(f.o, n1.x, n1.y, n1.z, n1.w, n2.z, n2.w))) return -1;
             hR = false;
         }
         if (hL && hR) {
-            if (sp >= kStackSize - kMaxCandidates - 1) return -1;
+            if (sp >= kStackSize - 2 * kMaxCandidates - 1) return -1;
             stack[sp++] = n3.y;
             cur = n3.x;
         } else if (hL) {
