@@ -76,33 +76,28 @@ __device__ __forceinline__ void accum_add(unsigned long long* __restrict__ acc, 
 }
 
 // ---- queues -----------------------------------------------------------------------------------------
-// Level w describes what wave w consumes: {nExt, cursor, nSec | nDirect << 32}.  Items are 3 float4
-// (PathRec above); secondary items carry the contribution weight in T and their kind in s2.w.
+// Every queue is split into kSegments independent SEGMENTS, each with its own counters on its own 128-B line: warps
+// of the whole GPU appending through one counter serialise in the L2 atomic unit (ncu: half of k_primary's stall
+// samples were the two append atomics), spread over a few lines they do not (8 segments measured as good as 64).  A path stays in the segment its camera
+// sample was born in (k_primary: blockIdx % kSegments), so segment s of any level holds at most as many extension
+// rays as segment s of level 1 can — the capacity bound that makes fixed segment sizes safe.
+// A segment's counter block describes what wave w consumes from it.  Items are 3 float4 (PathRec above); secondary
+// items carry the contribution weight in T and their kind in s2.w.  Both item counts live in ONE 64-bit word so
+// that a warp reserves the slots of everything a group of vertices emits with a single atomic round trip.
+#ifndef TPT_QUEUE_SEGMENTS
+#define TPT_QUEUE_SEGMENTS 8
+#endif
+constexpr int kSegments = TPT_QUEUE_SEGMENTS;   // power of two
+constexpr int kLevelStride = 128;               // bytes between the counter blocks of two segments
 struct QueueLevel {
-    uint32_t n_ext;                  // extension rays towards vertex w
-    uint32_t cursor;                 // next item not yet handed to a warp (k_wave)
-    unsigned long long n_sec;        // low 32 bits: secondary rays of vertex w-1; high 32 bits: how many are "direct" rays
+    unsigned long long counts;       // low 32 bits: extension rays towards vertex w; high 32 bits: secondary rays of vertex w-1
+    uint32_t cursor;                 // segment 0 only: next item of the whole level not yet handed to a warp (k_wave)
+    uint32_t n_direct;               // how many of the secondary rays are "direct" rays (statistics only)
 };
+__device__ __forceinline__ QueueLevel* seg_level(void* level, uint32_t seg) {
+    return reinterpret_cast<QueueLevel*>(static_cast<char*>(level) + (size_t)seg * kLevelStride);
+}
 constexpr uint32_t kKindShadow = 0u, kKindDirect = 1u;
-
-// Append from a possibly diverged warp: the lanes that are here together share one atomic.
-__device__ __forceinline__ uint32_t append_ext(QueueLevel* q) {
-    const unsigned m = __activemask();
-    const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
-    uint32_t base = 0;
-    if (lane == leader) base = atomicAdd(&q->n_ext, (uint32_t)__popc(m));
-    base = __shfl_sync(m, base, leader);
-    return base + __popc(m & ((1u << lane) - 1u));
-}
-__device__ __forceinline__ uint32_t append_sec(QueueLevel* q, bool direct) {
-    const unsigned m = __activemask();
-    const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
-    const unsigned long long n = (unsigned long long)__popc(m);
-    uint32_t base = 0;
-    if (lane == leader) base = (uint32_t)atomicAdd(&q->n_sec, direct ? (n | (n << 32)) : n);
-    base = __shfl_sync(m, base, leader);
-    return base + __popc(m & ((1u << lane) - 1u));
-}
 
 // ---- pixel enumeration: 8x4 tiles so that a warp's primary rays are coherent ---------------------
 __host__ __device__ __forceinline__ uint32_t tiles_x(int W) { return (uint32_t)(W + 7) >> 3; }
@@ -380,35 +375,104 @@ __device__ __forceinline__ bool shade_vertex(const BvhView& bvh, const ShadePara
 struct QueueOut {
     float4* ext;
     float4* sec;
-    QueueLevel* level;
+    void* level;                       // kSegments counter blocks of the level being produced
+    uint32_t extSegCap, secSegCap;     // items per segment
 };
 
-// Emit the rays of a shaded vertex from whatever lanes are here (diverged callers allowed).
-template <bool NEE>
-__device__ __forceinline__ void emit_vertex(const ShadeParams& sp, const QueueOut& q, const Vertex& vx, uint32_t pixel, uint32_t sample) {
+// Emit the rays of a shaded vertex from whatever lanes are here (diverged callers allowed): the lanes of one
+// segment that are here together reserve all their slots — one extension ray, one shadow ray per delta light, the
+// "direct" ray, the environment sample — with one atomic.  UNIFORM: every lane of the warp is in the same segment.
+template <bool NEE, bool UNIFORM>
+__device__ __forceinline__ void emit_vertex(const ShadeParams& sp, const QueueOut& q, uint32_t seg, const Vertex& vx, uint32_t pixel,
+                                            uint32_t sample) {
+    const unsigned here = __activemask();
+    const unsigned m = UNIFORM ? here : __match_any_sync(here, seg);
+    const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+    const unsigned lt = (1u << lane) - 1u;
+    const unsigned bExt = __ballot_sync(here, vx.next) & m, bDir = __ballot_sync(here, vx.direct) & m,
+                   bNee = NEE ? (__ballot_sync(here, vx.nee) & m) : 0u;
+    const uint32_t nL = (uint32_t)sp.nLights;
+    const uint32_t nExt = __popc(bExt), nSec = nL * __popc(m) + __popc(bDir) + __popc(bNee);
+    unsigned long long base = 0;
+    if (lane == leader && nExt + nSec != 0u) {
+        QueueLevel* level = seg_level(q.level, seg);
+        base = atomicAdd(&level->counts, (unsigned long long)nExt | ((unsigned long long)nSec << 32));
+        if (bDir) atomicAdd(&level->n_direct, (uint32_t)__popc(bDir));   // result unused: a fire-and-forget reduction
+    }
+    base = __shfl_sync(m, base, leader);
+    float4* ext = q.ext + 3 * (size_t)seg * q.extSegCap;
+    float4* sec = q.sec + 3 * (size_t)seg * q.secSegCap;
+    uint32_t slot = (uint32_t)(base >> 32) + nL * __popc(m & lt) + __popc(bDir & lt) + __popc(bNee & lt);
     // delta lights: one infinite shadow ray per light, contribution T_d * baseColor * Li
     for (int l = 0; l < sp.nLights; ++l) {
         float3 ldir, lrad;
         light_incoming(sp.lights[l], vx.P, ldir, lrad);
-        const uint32_t slot = append_sec(q.level, false);
-        store_path(q.sec, slot, vx.P, ldir, vx.Tn * (vx.base * lrad), pixel, sample, kKindShadow);
+        store_path(sec, slot++, vx.P, ldir, vx.Tn * (vx.base * lrad), pixel, sample, kKindShadow);
     }
-    if (vx.direct) {
-        const uint32_t slot = append_sec(q.level, true);
-        store_path(q.sec, slot, vx.P, vx.ddir, vx.Tn, pixel, sample, kKindDirect);
-    }
-    if (NEE && vx.nee) {
-        const uint32_t slot = append_sec(q.level, false);
-        store_path(q.sec, slot, vx.P, vx.ldir, vx.lw, pixel, sample, kKindShadow);
-    }
-    if (vx.next) {
-        const uint32_t slot = append_ext(q.level);
-        store_path(q.ext, slot, vx.P, vx.ndir, vx.Tn, pixel, sample, NEE ? __float_as_uint(vx.pb) : 0u);
-    }
+    if (vx.direct) store_path(sec, slot++, vx.P, vx.ddir, vx.Tn, pixel, sample, kKindDirect);
+    if (NEE && vx.nee) store_path(sec, slot++, vx.P, vx.ldir, vx.lw, pixel, sample, kKindShadow);
+    if (vx.next) store_path(ext, (uint32_t)base + __popc(bExt & lt), vx.P, vx.ndir, vx.Tn, pixel, sample, NEE ? __float_as_uint(vx.pb) : 0u);
 }
 
 // ---- wave 0: generate + extend + shade, fused ---------------------------------------------------------
-// Thread = (pixel of an 8x4 tile, group of `spt` consecutive local samples).
+// One camera sample: jitter, direction, closest hit among the pixel's candidates (cand/bound: nc entries sorted by a
+// lower bound of t) or by a tree walk (nc < 0) or none at all (nc == 0), then the first vertex.  Terminal
+// contributions are summed into (aR, aG, aB) in exact fixed point.
+template <bool COUNT, bool NEE>
+__device__ __forceinline__ void primary_sample(const BvhView& bvh, const ShadeParams& sp, const CameraParams& cam, const QueueOut& q, uint32_t seg,
+                                               int px, int py, uint32_t pixel, uint32_t sIdx, float3 o, int nc, const int* cand, const int* bound, int candStride,
+                                               int* stack, long long& aR, long long& aG, long long& aB, unsigned& nt, DeviceCounters* ctr) {
+    float ju, jv;
+    rng_pair(rng_path_key(sp.seedKey, pixel, sIdx), 0u, ju, jv);
+    const float3 d = primary_dir(cam, px, py, ju, jv);
+    HitRec h;
+    h.leaf = -1;
+    if (nc > 0) {
+        h.t = FLT_MAX;
+        h.u = h.v = 0.0f;
+        h.prim = -1;
+        for (int k = 0; k < nc; ++k) {   // sorted by a lower bound of t: nothing beyond the best hit needs testing
+            if (h.t < __int_as_float(bound[k * candStride])) break;
+            leaf_test(bvh, cand[k * candStride], o, d, h);
+            if (COUNT) ++nt;
+        }
+    } else if (nc < 0) {
+        h = traverse<COUNT>(bvh, o, d, false, stack, &ctr->node_visits, &ctr->tri_tests);
+    }
+    float3 term;
+    Vertex vx;
+    if (shade_vertex<NEE>(bvh, sp, 0, o, d, f3(1.f, 1.f, 1.f), 0u, pixel, sIdx, h, term, vx, ctr)) {
+        emit_vertex<NEE, true>(sp, q, seg, vx, pixel, sIdx);
+    } else if (term.x != 0.f || term.y != 0.f || term.z != 0.f) {
+        if (finite3(term)) {
+            aR += to_fixed(term.x);
+            aG += to_fixed(term.y);
+            aB += to_fixed(term.z);
+        } else {
+            atomicAdd(&ctr->dropped_nonfinite, 1ull);
+        }
+    }
+}
+
+// One walk of the tree with the pixel's pyramid finds the candidate triangles of ALL its samples (traverse.cuh):
+// 0: no sample can hit anything; 1..kMaxCandidates: test those per sample; -1: too many, traverse per sample.
+__device__ __forceinline__ int pixel_candidates(const BvhView& bvh, const ShadeParams& sp, const CameraParams& cam, int px, int py, float3 o,
+                                                int* stack, unsigned& nv) {
+    return sp.pixelCandidates ? frustum_collect(bvh, pixel_frustum(cam, px, py, o), stack, nv)
+                              : (frustum_may_hit(bvh, pixel_frustum(cam, px, py, o), stack) ? -1 : 0);
+}
+
+__device__ __forceinline__ void flush_trav_counters(unsigned nv, unsigned nt, DeviceCounters* ctr) {
+    const unsigned m = __activemask();
+    const unsigned sv = __reduce_add_sync(m, nv), st = __reduce_add_sync(m, nt);
+    if ((threadIdx.x & 31) == __ffs(m) - 1) {
+        atomicAdd(&ctr->node_visits, (unsigned long long)sv);
+        atomicAdd(&ctr->tri_tests, (unsigned long long)st);
+    }
+}
+
+// Form A (fewer than 32 samples per pixel in this launch): thread = (pixel of an 8x4 tile, group of `spt`
+// consecutive local samples); the candidates stay in the thread's own stack array.
 template <bool COUNT, bool NEE>
 __global__ void __launch_bounds__(128) k_primary(BvhView bvh, ShadeParams sp, CameraParams cam, int W, int H, uint32_t nPadded,
                                                  uint32_t kSamples, uint32_t spt, uint32_t sampleBase, uint32_t sampleStride, QueueOut q,
@@ -427,13 +491,9 @@ __global__ void __launch_bounds__(128) k_primary(BvhView bvh, ShadeParams sp, Ca
     int stack[kStackSize];
     stack[0] = kStackSentinel;
     const float3 o = xmat4_point(cam.c2w, f3(0.f, 0.f, 0.f));   // the camera position: the same for every sample
-    // One walk of the tree with the pixel's pyramid finds the candidate triangles of ALL its samples (traverse.cuh):
-    // nc == 0: no sample can hit anything; 1..kMaxCandidates: test those per sample; -1: too many, traverse per sample.
     unsigned nv = 0, nt = 0;
-    const int nc = sp.pixelCandidates ? frustum_collect(bvh, pixel_frustum(cam, px, py, o), stack, nv)
-                                      : (frustum_may_hit(bvh, pixel_frustum(cam, px, py, o), stack) ? -1 : 0);
-    const bool mayHit = nc != 0;
-    if (!mayHit) {
+    const int nc = pixel_candidates(bvh, sp, cam, px, py, o, stack, nv);
+    if (nc == 0) {
         const unsigned m = __activemask();
         const unsigned culled = __reduce_add_sync(m, s1 - s0);
         if ((threadIdx.x & 31) == __ffs(m) - 1) atomicAdd(&ctr->rays_culled, (unsigned long long)culled);
@@ -443,51 +503,85 @@ __global__ void __launch_bounds__(128) k_primary(BvhView bvh, ShadeParams sp, Ca
         const unsigned n = __reduce_add_sync(m, s1 - s0);
         if ((threadIdx.x & 31) == __ffs(m) - 1) atomicAdd(&ctr->rays_candidates, (unsigned long long)n);
     }
-    for (uint32_t sl = s0; sl < s1; ++sl) {
-        const uint32_t sIdx = sampleBase + sl * sampleStride;
-        float ju, jv;
-        rng_pair(rng_path_key(sp.seedKey, pixel, sIdx), 0u, ju, jv);
-        const float3 d = primary_dir(cam, px, py, ju, jv);
-        HitRec h;
-        h.leaf = -1;
-        if (nc > 0) {
-            h.t = FLT_MAX;
-            h.u = h.v = 0.0f;
-            h.prim = -1;
-            for (int k = 0; k < nc; ++k) {   // sorted by a lower bound of t: nothing beyond the best hit needs testing
-                if (h.t < __int_as_float(stack[kStackSize - 1 - kMaxCandidates - k])) break;
-                leaf_test(bvh, stack[kStackSize - 1 - k], o, d, h);
-                if (COUNT) ++nt;
-            }
-        } else if (nc < 0) {
-            h = traverse<COUNT>(bvh, o, d, false, stack, &ctr->node_visits, &ctr->tri_tests);
-        }
-        float3 term;
-        Vertex vx;
-        if (shade_vertex<NEE>(bvh, sp, 0, o, d, f3(1.f, 1.f, 1.f), 0u, pixel, sIdx, h, term, vx, ctr)) {
-            emit_vertex<NEE>(sp, q, vx, pixel, sIdx);
-        } else if (term.x != 0.f || term.y != 0.f || term.z != 0.f) {
-            if (finite3(term)) {
-                aR += to_fixed(term.x);
-                aG += to_fixed(term.y);
-                aB += to_fixed(term.z);
-            } else {
-                atomicAdd(&ctr->dropped_nonfinite, 1ull);
-            }
-        }
-    }
-    if (COUNT) {
-        const unsigned m = __activemask();
-        const unsigned sv = __reduce_add_sync(m, nv), st = __reduce_add_sync(m, nt);
-        if ((threadIdx.x & 31) == __ffs(m) - 1) {
-            atomicAdd(&ctr->node_visits, (unsigned long long)sv);
-            atomicAdd(&ctr->tri_tests, (unsigned long long)st);
-        }
-    }
+    for (uint32_t sl = s0; sl < s1; ++sl)
+        primary_sample<COUNT, NEE>(bvh, sp, cam, q, blockIdx.x & (kSegments - 1), px, py, pixel, sampleBase + sl * sampleStride, o, nc, stack + kStackSize - 1,
+                                   stack + kStackSize - 1 - kMaxCandidates, -1, stack, aR, aG, aB, nt, ctr);
+    if (COUNT) flush_trav_counters(nv, nt, ctr);
     unsigned long long* dst = acc + 3 * (size_t)pixel;
     if (aR) atomicAdd(dst + 0, (unsigned long long)aR);
     if (aG) atomicAdd(dst + 1, (unsigned long long)aG);
     if (aB) atomicAdd(dst + 2, (unsigned long long)aB);
+}
+
+// Form B (32 or more samples per pixel in this launch): warp = (8x4 pixel tile, group of `spt` local samples).
+// Each lane first walks the tree with ITS pixel's pyramid and leaves the candidates in shared memory; then the warp
+// takes the tile's pixels one at a time and its 32 lanes trace 32 samples of that pixel together.  Lanes of a warp
+// then share candidates, materials and (mostly) control flow, a pixel that needs no work costs the whole warp
+// nothing, and no lane waits for a neighbour whose pixel happens to be the expensive one.
+constexpr int kCoopCandidates = kMaxCandidates < 16 ? kMaxCandidates : 16;
+__device__ __forceinline__ long long warp_sum_ll(long long v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+#ifndef TPT_COOP_MIN_BLOCKS
+#define TPT_COOP_MIN_BLOCKS 7
+#endif
+template <bool COUNT, bool NEE>
+__global__ void __launch_bounds__(128, TPT_COOP_MIN_BLOCKS) k_primary_coop(BvhView bvh, ShadeParams sp, CameraParams cam, int W, int H, uint32_t nPadded,
+                                                      uint32_t kSamples, uint32_t spt, uint32_t sampleBase, uint32_t sampleStride, QueueOut q,
+                                                      unsigned long long* __restrict__ acc, DeviceCounters* ctr) {
+    __shared__ int sCand[4][kCoopCandidates][32];    // [warp][k][lane]: leaf k of the lane's pixel
+    __shared__ int sBound[4][kCoopCandidates][32];   //                   its lower bound of t (float bits)
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nPadded * ((kSamples + spt - 1) / spt)) return;    // whole warps: nPadded is a multiple of 32
+    if (i == 0) atomicAdd(&ctr->rays_primary, (unsigned long long)W * (unsigned long long)H * kSamples);
+    const uint32_t g = i / nPadded, p = i - g * nPadded;        // g is the same for the whole warp
+    const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    int px, py;
+    const bool inside = tile_decode(p, W, H, px, py);
+    const uint32_t s0 = g * spt, s1 = min(kSamples, s0 + spt);
+    int stack[kStackSize];
+    stack[0] = kStackSentinel;
+    const float3 o = xmat4_point(cam.c2w, f3(0.f, 0.f, 0.f));
+    unsigned nv = 0, nt = 0;
+    int nc = 0;
+    if (inside) {
+        nc = pixel_candidates(bvh, sp, cam, px, py, o, stack, nv);
+        if (nc > kCoopCandidates) nc = -1;
+        for (int k = 0; k < nc; ++k) {
+            sCand[wib][k][lane] = stack[kStackSize - 1 - k];
+            sBound[wib][k][lane] = stack[kStackSize - 1 - kMaxCandidates - k];
+        }
+    }
+    __syncwarp();
+    {   // statistics: camera samples answered without / with candidate tests
+        const unsigned nCulled = __popc(__ballot_sync(0xffffffffu, inside && nc == 0)), nCand = __popc(__ballot_sync(0xffffffffu, nc > 0));
+        if (lane == 0 && nCulled) atomicAdd(&ctr->rays_culled, (unsigned long long)nCulled * (s1 - s0));
+        if (lane == 0 && nCand) atomicAdd(&ctr->rays_candidates, (unsigned long long)nCand * (s1 - s0));
+    }
+    unsigned todo = __ballot_sync(0xffffffffu, inside && (nc != 0 || sp.env != nullptr));
+    while (todo) {
+        const int pl = __ffs(todo) - 1;
+        todo &= todo - 1;
+        const int ncp = __shfl_sync(0xffffffffu, nc, pl), pxp = __shfl_sync(0xffffffffu, px, pl), pyp = __shfl_sync(0xffffffffu, py, pl);
+        const uint32_t pixel = (uint32_t)(pxp + pyp * W);
+        long long aR = 0, aG = 0, aB = 0;
+        for (uint32_t sl = s0 + lane; sl < s1; sl += 32)
+            primary_sample<COUNT, NEE>(bvh, sp, cam, q, blockIdx.x & (kSegments - 1), pxp, pyp, pixel, sampleBase + sl * sampleStride, o, ncp, &sCand[wib][0][pl],
+                                       &sBound[wib][0][pl], 32, stack, aR, aG, aB, nt, ctr);
+        __syncwarp();
+        if (__ballot_sync(0xffffffffu, (aR | aG | aB) != 0)) {
+            aR = warp_sum_ll(aR);
+            aG = warp_sum_ll(aG);
+            aB = warp_sum_ll(aB);
+            unsigned long long* dst = acc + 3 * (size_t)pixel;
+            if (lane == 0 && aR) atomicAdd(dst + 0, (unsigned long long)aR);
+            if (lane == 1 && aG) atomicAdd(dst + 1, (unsigned long long)aG);
+            if (lane == 2 && aB) atomicAdd(dst + 2, (unsigned long long)aB);
+        }
+    }
+    if (COUNT) flush_trav_counters(nv, nt, ctr);
 }
 
 // ---- wave w >= 1: extension rays towards vertex w + secondary rays of vertex w-1 --------------------------
@@ -525,7 +619,8 @@ __device__ __forceinline__ void shade_staged(const BvhView& bvh, const ShadePara
         h.prim = -1;
         float3 term;
         Vertex vx;
-        if (shade_vertex<NEE>(bvh, sp, sp.depth, p.o, p.d, p.T, p.w, p.pixel, p.sample, h, term, vx, ctr)) emit_vertex<NEE>(sp, q, vx, p.pixel, p.sample);
+        if (shade_vertex<NEE>(bvh, sp, sp.depth, p.o, p.d, p.T, p.w, p.pixel, p.sample, h, term, vx, ctr))
+            emit_vertex<NEE, true>(sp, q, 0u, vx, p.pixel, p.sample);
         else accum_add(acc, p.pixel, term, ctr);
     }
     __syncwarp();
@@ -534,15 +629,74 @@ __device__ __forceinline__ void shade_staged(const BvhView& bvh, const ShadePara
 #ifndef TPT_WAVE_MIN_BLOCKS
 #define TPT_WAVE_MIN_BLOCKS 8
 #endif
-template <bool COUNT, bool NEE>
+// SEGIN: the input level is the segmented one k_primary wrote (wave 1); k_wave itself appends to segment 0 only — its
+// warps issue one atomic per 32 shaded vertices, far below what one counter sustains — so the levels it produces
+// are plain queues that use the whole pool.
+template <bool COUNT, bool NEE, bool SEGIN>
 __global__ void __launch_bounds__(128, TPT_WAVE_MIN_BLOCKS) k_wave(BvhView bvh, ShadeParams sp, const float4* __restrict__ extIn, const float4* __restrict__ secIn,
-                                              QueueLevel* __restrict__ levelIn, QueueOut q, unsigned long long* __restrict__ acc,
+                                              void* __restrict__ levelIn, QueueOut q, unsigned long long* __restrict__ acc,
                                               DeviceCounters* ctr) {
     __shared__ uint32_t sIdx[4][kStage];
     __shared__ float4 sHit[4][kStage];
-    const uint32_t nExt = levelIn->n_ext;
-    const unsigned long long secWord = levelIn->n_sec;
-    const uint32_t nSec = (uint32_t)secWord, nDirect = (uint32_t)(secWord >> 32);
+    // The level's items form one virtual queue: the extension rays of segment 0, 1, ... then the secondary rays of
+    // segment 0, 1, ...; sExtPre / sSecPre hold the exclusive prefix sums of the segment counts.
+    __shared__ uint32_t sExtPre[SEGIN ? kSegments + 1 : 1], sSecPre[SEGIN ? kSegments + 1 : 1], sDirect;
+    if (!SEGIN) {
+        if (threadIdx.x == 0) {
+            const unsigned long long w = seg_level(levelIn, 0)->counts;
+            sExtPre[0] = (uint32_t)w;
+            sSecPre[0] = (uint32_t)(w >> 32);
+            sDirect = seg_level(levelIn, 0)->n_direct;
+        }
+    } else if (threadIdx.x < 32) {
+        static_assert(kSegments % 32 == 0 || kSegments < 32, "kSegments: a power of two");
+        constexpr int per = kSegments >= 32 ? kSegments / 32 : 1;
+        const uint32_t l = threadIdx.x;
+        uint32_t e[per], c[per], sumE = 0, sumS = 0, sumD = 0;
+#pragma unroll
+        for (int k = 0; k < per; ++k) {
+            const uint32_t seg = l * per + k;
+            unsigned long long w = 0;
+            uint32_t d = 0;
+            if (seg < (uint32_t)kSegments) {
+                w = seg_level(levelIn, seg)->counts;
+                d = seg_level(levelIn, seg)->n_direct;
+            }
+            e[k] = (uint32_t)w;
+            c[k] = (uint32_t)(w >> 32);
+            sumE += e[k];
+            sumS += c[k];
+            sumD += d;
+        }
+        uint32_t incE = sumE, incS = sumS;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t a = __shfl_up_sync(0xffffffffu, incE, o), b = __shfl_up_sync(0xffffffffu, incS, o);
+            if (l >= (uint32_t)o) {
+                incE += a;
+                incS += b;
+            }
+        }
+        uint32_t runE = incE - sumE, runS = incS - sumS;
+#pragma unroll
+        for (int k = 0; k < per; ++k) {
+            const uint32_t seg = l * per + k;
+            if (seg < (uint32_t)kSegments) {
+                sExtPre[seg] = runE;
+                sSecPre[seg] = runS;
+            }
+            runE += e[k];
+            runS += c[k];
+        }
+        sumD = __reduce_add_sync(0xffffffffu, sumD);
+        if (l == 31) {
+            sExtPre[kSegments] = incE;
+            sSecPre[kSegments] = incS;
+            sDirect = sumD;
+        }
+    }
+    __syncthreads();
+    const uint32_t nExt = sExtPre[SEGIN ? kSegments : 0], nSec = sSecPre[SEGIN ? kSegments : 0], nDirect = sDirect;
     const uint32_t total = nExt + nSec;
     if (total == 0u) return;
     if (blockIdx.x == 0 && threadIdx.x == 0) {
@@ -550,6 +704,7 @@ __global__ void __launch_bounds__(128, TPT_WAVE_MIN_BLOCKS) k_wave(BvhView bvh, 
         atomicAdd(&ctr->rays_direct, (unsigned long long)nDirect);
         atomicAdd(&ctr->rays_shadow, (unsigned long long)(nSec - nDirect));
     }
+    uint32_t* cursor = &seg_level(levelIn, 0)->cursor;
     const uint32_t lane = threadIdx.x & 31, ltMask = (1u << lane) - 1u;
     // items taken from the global cursor at a time: large for big waves (few atomics), 32 for small ones so
     // that every resident warp gets work
@@ -563,6 +718,7 @@ __global__ void __launch_bounds__(128, TPT_WAVE_MIN_BLOCKS) k_wave(BvhView bvh, 
     ts.sp = 1;
     uint32_t item = kNoItem, kind = 0;   // kind: 0 extension, 1 shadow (any hit), 2 direct
     uint32_t lo = 0, hi = 0;             // warp-local range of items not yet dealt out
+    uint32_t gBase = 0, gEnd = 0;        // SEGIN: virtual index -> pool slot for the run of one segment the current grab starts in
     bool more = true;                    // the global cursor may still have items
     uint32_t nStaged = 0;
     unsigned nv = 0, nt = 0;
@@ -595,7 +751,7 @@ __global__ void __launch_bounds__(128, TPT_WAVE_MIN_BLOCKS) k_wave(BvhView bvh, 
                     }
                 }
                 if (add) {
-                    const size_t i = (size_t)(item - nExt);
+                    const size_t i = (size_t)item;
                     const float4 b = __ldcs(secIn + 3 * i + 1), c = __ldcs(secIn + 3 * i + 2);
                     accum_add(acc, __float_as_uint(c.y), f3(b.z, b.w, c.x) * e, ctr);
                 }
@@ -621,12 +777,22 @@ __global__ void __launch_bounds__(128, TPT_WAVE_MIN_BLOCKS) k_wave(BvhView bvh, 
             }
             // ---- deal new items to the idle lanes
             if (more && lo == hi) {
-                if (lane == 0) lo = atomicAdd(&levelIn->cursor, kGrab);
+                if (lane == 0) lo = atomicAdd(cursor, kGrab);
                 lo = __shfl_sync(0xffffffffu, lo, 0);
                 hi = min(lo + kGrab, total);
                 if (lo >= total) {
                     more = false;
                     lo = hi = 0;
+                } else if (SEGIN) {
+                    const bool isExt = lo < nExt;
+                    const uint32_t v = isExt ? lo : lo - nExt;
+                    const uint32_t* pre = isExt ? sExtPre : sSecPre;
+                    uint32_t seg = 0;
+#pragma unroll
+                    for (int step = kSegments >> 1; step > 0; step >>= 1)
+                        if (pre[seg + step] <= v) seg += step;
+                    gBase = seg * (isExt ? q.extSegCap : q.secSegCap) - pre[seg] - (isExt ? 0u : nExt);   // item = vi + gBase (mod 2^32)
+                    gEnd = pre[seg + 1] + (isExt ? 0u : nExt);
                 }
             }
             if (more) {
@@ -634,9 +800,24 @@ __global__ void __launch_bounds__(128, TPT_WAVE_MIN_BLOCKS) k_wave(BvhView bvh, 
                 const unsigned mEmpty = __ballot_sync(0xffffffffu, empty);
                 const uint32_t avail = hi - lo, rank = __popc(mEmpty & ltMask);
                 if (empty && rank < avail) {
-                    item = lo + rank;
-                    const bool isExt = item < nExt;
-                    const float4* src = isExt ? extIn + 3 * (size_t)item : secIn + 3 * (size_t)(item - nExt);
+                    // virtual index -> (segment, offset) -> slot in the extension or secondary pool
+                    const uint32_t vi = lo + rank;
+                    const bool isExt = vi < nExt;
+                    const uint32_t v = isExt ? vi : vi - nExt;
+                    item = v;
+                    if (SEGIN) {
+                        if (vi < gEnd) {   // same run of one segment as the first item of this grab (searched once per grab)
+                            item = vi + gBase;
+                        } else {
+                            const uint32_t* pre = isExt ? sExtPre : sSecPre;
+                            uint32_t seg = 0;
+#pragma unroll
+                            for (int step = kSegments >> 1; step > 0; step >>= 1)
+                                if (pre[seg + step] <= v) seg += step;
+                            item = seg * (isExt ? q.extSegCap : q.secSegCap) + (v - pre[seg]);
+                        }
+                    }
+                    const float4* src = (isExt ? extIn : secIn) + 3 * (size_t)item;
 #ifdef TPT_REFILL_LDCS
                     const float4 a = __ldcs(src), b = __ldcs(src + 1);
                     kind = isExt ? 0u : 1u + __float_as_uint(__ldcs(reinterpret_cast<const float*>(src + 2) + 3));
@@ -860,10 +1041,11 @@ int tpt_trace_rays_impl(tpt_scene* s, const tpt_ray* d_rays, size_t n, tpt_hit* 
 constexpr int kMaxLevels = 72;   // waves 0..max_depth (max_depth <= 64), see tpt_render's argument check
 
 // Queue pools: a batch of P camera samples can emit at most P extension rays and P*(L+1) secondary rays
-// per wave (every live path emits one ray of each sort and one shadow ray per light).
+// per wave (every live path emits one ray of each sort and one shadow ray per light).  `paths` = kSegments x the
+// segment capacity, which is what the k_primary blocks of one segment can emit (launch_plan below).
 static int ensure_pools(tpt_context* ctx, size_t paths, size_t secPerPath) {
     const size_t secNeed = paths * secPerPath;
-    if (!ctx->levels) TPT_CUDA(cudaMalloc(&ctx->levels, kMaxLevels * sizeof(QueueLevel)));
+    if (!ctx->levels) TPT_CUDA(cudaMalloc(&ctx->levels, (size_t)kMaxLevels * kSegments * kLevelStride));
     if (paths > ctx->ext_capacity) {
         TPT_CUDA(cudaStreamSynchronize(ctx->stream));
         for (int k = 0; k < 2; ++k) {
@@ -898,17 +1080,48 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
     if (nee) TPT_CHECK(tpt_env_build_sampler(ctx));
     const int W = cfg->width, H = cfg->height;
     const uint32_t nPadded = tiles_x(W) * tiles_y(H) * 32u;
-    // default batch: as many camera samples as a 32 GiB queue budget allows (2 sides x (2+L) rays x 48 B each), at most 2^27 —
+    // default batch: as many camera samples as a 40 GiB queue budget allows (2 sides x (2+L) rays x 48 B each), at most 2^27 —
     // sized for 180 GB of HBM: fewer, larger batches mean fewer (mostly empty) deep-wave launches per frame
     const size_t secPerPath = s->n_lights + 1 + (nee ? 1 : 0);
-    size_t target = ((size_t)32 << 30) / (96 * (1 + secPerPath));
+    size_t target = ((size_t)40 << 30) / (96 * (1 + secPerPath));
     if (target > ((size_t)1 << 27)) target = (size_t)1 << 27;
     if (cfg->paths_in_flight > 0) target = (size_t)cfg->paths_in_flight;
     uint32_t k = (uint32_t)(target / nPadded);
+    if (k > 32) k &= ~31u;   // whole warps of samples per pixel for k_primary_coop
     if (k < 1) k = 1;
     if (k > (uint32_t)cfg->spp) k = (uint32_t)cfg->spp;
-    const size_t pool = (size_t)nPadded * k;
-    TPT_CHECK(ensure_pools(ctx, pool, secPerPath));
+    // launch shape of k_primary for a batch of kk samples per pixel, and the segment capacity it needs: the blocks
+    // of one segment (blockIdx % kSegments) emit at most 128 * spt extension rays each
+    struct Plan {
+        uint32_t spt, groups;
+        unsigned grid;
+        bool coop;
+        size_t segCap;
+    };
+    auto launch_plan = [&](uint32_t kk) {
+        Plan pl;
+        // enough threads to fill the machine several times over, else as many samples per thread as possible
+        pl.spt = (uint32_t)(((size_t)nPadded * kk) / ((size_t)kNumSMs * 2048 * 4));
+        if (pl.spt < 1) pl.spt = 1;
+        static const int sptMax = getenv("TPT_SPT_MAX") ? atoi(getenv("TPT_SPT_MAX")) : 0;   // tuning switch
+        if (sptMax > 0 && pl.spt > (uint32_t)sptMax) pl.spt = (uint32_t)sptMax;
+        static const bool noCoop = getenv("TPT_NO_COOP") != nullptr;                          // tuning switch
+        pl.coop = kk >= 32 && !noCoop;   // a warp per pixel tile, 32 samples of one pixel at a time
+        if (pl.coop) pl.spt = (pl.spt + 31u) & ~31u;
+        if (pl.spt > kk) pl.spt = kk;
+        pl.groups = (kk + pl.spt - 1) / pl.spt;
+        pl.grid = (unsigned)(((size_t)nPadded * pl.groups + 127) / 128);
+        pl.segCap = (size_t)((pl.grid + kSegments - 1) / kSegments) * 128 * pl.spt;
+        return pl;
+    };
+    size_t extSegCap = launch_plan(k).segCap;
+    if ((uint32_t)cfg->spp % k) {
+        const size_t c = launch_plan((uint32_t)cfg->spp % k).segCap;
+        if (c > extSegCap) extSegCap = c;
+    }
+    const size_t secSegCap = extSegCap * secPerPath;
+    TPT_REQUIRE(secSegCap * kSegments < ((size_t)1 << 32), "tpt_render: paths_in_flight x (lights + 2) exceeds 2^32 queue slots");
+    TPT_CHECK(ensure_pools(ctx, extSegCap * kSegments, secPerPath));
 
     const CameraParams cp = make_camera(cam, W, H);
     const bool counted = (cfg->flags & TPT_RENDER_COUNTERS) != 0;
@@ -925,15 +1138,20 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
     auto mark = [&]() { if (timed) cudaEventRecord(ctx->stage_events[ev++], st); };
     const BvhView view = s->view();
     if (ctx->wave_grid[0] == 0) {
-        ctx->wave_grid[0] = kNumSMs * resident_blocks(k_wave<false, false>, 128);
-        ctx->wave_grid[1] = kNumSMs * resident_blocks(k_wave<true, false>, 128);
-        ctx->wave_grid[2] = kNumSMs * resident_blocks(k_wave<false, true>, 128);
-        ctx->wave_grid[3] = kNumSMs * resident_blocks(k_wave<true, true>, 128);
+        ctx->wave_grid[0] = kNumSMs * min(resident_blocks(k_wave<false, false, false>, 128), resident_blocks(k_wave<false, false, true>, 128));
+        ctx->wave_grid[1] = kNumSMs * min(resident_blocks(k_wave<true, false, false>, 128), resident_blocks(k_wave<true, false, true>, 128));
+        ctx->wave_grid[2] = kNumSMs * min(resident_blocks(k_wave<false, true, false>, 128), resident_blocks(k_wave<false, true, true>, 128));
+        ctx->wave_grid[3] = kNumSMs * min(resident_blocks(k_wave<true, true, false>, 128), resident_blocks(k_wave<true, true, true>, 128));
     }
     const int variant = (counted ? 1 : 0) + (nee ? 2 : 0);
     const unsigned gridWave = ctx->wave_grid[variant];
     const auto kPrimary = variant == 0 ? k_primary<false, false> : variant == 1 ? k_primary<true, false> : variant == 2 ? k_primary<false, true> : k_primary<true, true>;
-    const auto kWave = variant == 0 ? k_wave<false, false> : variant == 1 ? k_wave<true, false> : variant == 2 ? k_wave<false, true> : k_wave<true, true>;
+    const auto kPrimaryCoop = variant == 0   ? k_primary_coop<false, false>
+                              : variant == 1 ? k_primary_coop<true, false>
+                              : variant == 2 ? k_primary_coop<false, true>
+                                             : k_primary_coop<true, true>;
+    const auto kWave = variant == 0 ? k_wave<false, false, false> : variant == 1 ? k_wave<true, false, false> : variant == 2 ? k_wave<false, true, false> : k_wave<true, true, false>;
+    const auto kWave1 = variant == 0 ? k_wave<false, false, true> : variant == 1 ? k_wave<true, false, true> : variant == 2 ? k_wave<false, true, true> : k_wave<true, true, true>;
 
     ShadeParams sp;
     sp.mtl = s->mtl_table;
@@ -951,19 +1169,19 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
 
     for (uint32_t done = 0; done < (uint32_t)cfg->spp; done += k) {
         const uint32_t kk = ((uint32_t)cfg->spp - done) < k ? ((uint32_t)cfg->spp - done) : k;
-        // enough threads to fill the machine several times over, else as many samples per thread as possible
-        uint32_t spt = (uint32_t)(((size_t)nPadded * kk) / ((size_t)kNumSMs * 2048 * 4));
-        if (spt < 1) spt = 1;
-        if (spt > kk) spt = kk;
-        const uint32_t groups = (kk + spt - 1) / spt;
-        TPT_CUDA(cudaMemsetAsync(ctx->levels, 0, (size_t)(cfg->max_depth + 2) * sizeof(QueueLevel), st));
+        const Plan pl = launch_plan(kk);
+        char* levels = static_cast<char*>(ctx->levels);
+        const size_t levelBytes = (size_t)kSegments * kLevelStride;
+        TPT_CUDA(cudaMemsetAsync(levels, 0, (size_t)(cfg->max_depth + 2) * levelBytes, st));
         ev = 0;
         mark();
         {
-            const QueueOut q{ctx->q_ext[1], ctx->q_sec[1], static_cast<QueueLevel*>(ctx->levels) + 1};
-            const unsigned grid = (unsigned)(((size_t)nPadded * groups + 127) / 128);
+            const QueueOut q{ctx->q_ext[1], ctx->q_sec[1], levels + levelBytes, (uint32_t)extSegCap, (uint32_t)secSegCap};
             const uint32_t sampleBase = (uint32_t)cfg->sample_offset + done * (uint32_t)cfg->sample_stride;
-            kPrimary<<<grid, 128, 0, st>>>(view, sp, cp, W, H, nPadded, kk, spt, sampleBase, (uint32_t)cfg->sample_stride, q, acc->data, ctx->d_counters);
+            if (pl.coop)
+                kPrimaryCoop<<<pl.grid, 128, 0, st>>>(view, sp, cp, W, H, nPadded, kk, pl.spt, sampleBase, (uint32_t)cfg->sample_stride, q, acc->data, ctx->d_counters);
+            else
+                kPrimary<<<pl.grid, 128, 0, st>>>(view, sp, cp, W, H, nPadded, kk, pl.spt, sampleBase, (uint32_t)cfg->sample_stride, q, acc->data, ctx->d_counters);
         }
         mark();
         // wave w traces extension rays towards vertex w and the secondary rays of vertex w-1; the last wave
@@ -971,8 +1189,8 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
         for (int w = 1; w <= cfg->max_depth; ++w) {
             const int in = w & 1, out = in ^ 1;
             sp.depth = w;
-            const QueueOut q{ctx->q_ext[out], ctx->q_sec[out], static_cast<QueueLevel*>(ctx->levels) + w + 1};
-            kWave<<<gridWave, 128, 0, st>>>(view, sp, ctx->q_ext[in], ctx->q_sec[in], static_cast<QueueLevel*>(ctx->levels) + w, q, acc->data, ctx->d_counters);
+            const QueueOut q{ctx->q_ext[out], ctx->q_sec[out], levels + (size_t)(w + 1) * levelBytes, (uint32_t)extSegCap, (uint32_t)secSegCap};
+            (w == 1 ? kWave1 : kWave)<<<gridWave, 128, 0, st>>>(view, sp, ctx->q_ext[in], ctx->q_sec[in], levels + (size_t)w * levelBytes, q, acc->data, ctx->d_counters);
             mark();
         }
         ctx->kernel_launches += 1 + (uint64_t)cfg->max_depth;
