@@ -515,13 +515,17 @@ __global__ void __launch_bounds__(128) k_primary(BvhView bvh, ShadeParams sp, Ca
 
 // Form B (32 or more samples per pixel in this launch): warp = (8x4 pixel tile, group of `spt` local samples).
 // Each lane first walks the tree with ITS pixel's pyramid and leaves the candidates in shared memory; then the warp
-// takes the tile's pixels one at a time and its 32 lanes trace 32 samples of that pixel together.  Lanes of a warp
-// then share candidates, materials and (mostly) control flow, a pixel that needs no work costs the whole warp
-// nothing, and no lane waits for a neighbour whose pixel happens to be the expensive one.
+// takes the tile's pixels that have work a few at a time, kCoopLanes lanes tracing samples of the same pixel
+// together.  Lanes then share candidates, materials and (mostly) control flow, a pixel that needs no work costs
+// the warp nothing, and no lane waits long for a neighbour whose pixel happens to be the expensive one.
 constexpr int kCoopCandidates = kMaxCandidates < 16 ? kMaxCandidates : 16;
-__device__ __forceinline__ long long warp_sum_ll(long long v) {
+#ifndef TPT_COOP_LANES
+#define TPT_COOP_LANES 8
+#endif
+constexpr int kCoopLanes = TPT_COOP_LANES;   // lanes that share one pixel (power of two, >= 4)
+__device__ __forceinline__ long long group_sum_ll(long long v) {
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    for (int o = kCoopLanes >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     return v;
 }
 #ifndef TPT_COOP_MIN_BLOCKS
@@ -560,25 +564,31 @@ __global__ void __launch_bounds__(128, TPT_COOP_MIN_BLOCKS) k_primary_coop(BvhVi
         if (lane == 0 && nCulled) atomicAdd(&ctr->rays_culled, (unsigned long long)nCulled * (s1 - s0));
         if (lane == 0 && nCand) atomicAdd(&ctr->rays_candidates, (unsigned long long)nCand * (s1 - s0));
     }
+    // kCoopLanes lanes work on one pixel, 32 / kCoopLanes pixels at a time (the next ones that have work)
+    const uint32_t grp = lane / kCoopLanes, sub = lane % kCoopLanes;
     unsigned todo = __ballot_sync(0xffffffffu, inside && (nc != 0 || sp.env != nullptr));
     while (todo) {
-        const int pl = __ffs(todo) - 1;
-        todo &= todo - 1;
+        const unsigned src = __fns(todo, 0, (int)grp + 1);   // lane of my group's pixel; 0xffffffff when fewer pixels are left
+        const bool have = src != 0xffffffffu;
+        const int pl = have ? (int)src : 0;
+#pragma unroll
+        for (int k = 0; k < 32 / kCoopLanes; ++k) todo &= todo - 1;
         const int ncp = __shfl_sync(0xffffffffu, nc, pl), pxp = __shfl_sync(0xffffffffu, px, pl), pyp = __shfl_sync(0xffffffffu, py, pl);
         const uint32_t pixel = (uint32_t)(pxp + pyp * W);
         long long aR = 0, aG = 0, aB = 0;
-        for (uint32_t sl = s0 + lane; sl < s1; sl += 32)
-            primary_sample<COUNT, NEE>(bvh, sp, cam, q, blockIdx.x & (kSegments - 1), pxp, pyp, pixel, sampleBase + sl * sampleStride, o, ncp, &sCand[wib][0][pl],
-                                       &sBound[wib][0][pl], 32, stack, aR, aG, aB, nt, ctr);
+        if (have)
+            for (uint32_t sl = s0 + sub; sl < s1; sl += kCoopLanes)
+                primary_sample<COUNT, NEE>(bvh, sp, cam, q, blockIdx.x & (kSegments - 1), pxp, pyp, pixel, sampleBase + sl * sampleStride, o, ncp,
+                                           &sCand[wib][0][pl], &sBound[wib][0][pl], 32, stack, aR, aG, aB, nt, ctr);
         __syncwarp();
         if (__ballot_sync(0xffffffffu, (aR | aG | aB) != 0)) {
-            aR = warp_sum_ll(aR);
-            aG = warp_sum_ll(aG);
-            aB = warp_sum_ll(aB);
+            aR = group_sum_ll(aR);
+            aG = group_sum_ll(aG);
+            aB = group_sum_ll(aB);
             unsigned long long* dst = acc + 3 * (size_t)pixel;
-            if (lane == 0 && aR) atomicAdd(dst + 0, (unsigned long long)aR);
-            if (lane == 1 && aG) atomicAdd(dst + 1, (unsigned long long)aG);
-            if (lane == 2 && aB) atomicAdd(dst + 2, (unsigned long long)aB);
+            if (sub == 0 && aR) atomicAdd(dst + 0, (unsigned long long)aR);
+            if (sub == 1 % kCoopLanes && aG) atomicAdd(dst + 1, (unsigned long long)aG);
+            if (sub == 2 % kCoopLanes && aB) atomicAdd(dst + 2, (unsigned long long)aB);
         }
     }
     if (COUNT) flush_trav_counters(nv, nt, ctr);
