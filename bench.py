@@ -187,6 +187,8 @@ def run_ours(args):
     clk = clocks.stop() if rank == 0 else {}
     ctr = ctx.counters()
     launches = ctr["kernel_launches"]
+    if ctr["queue_overflow"] or ctr["dropped_nonfinite"] > 1e-6 * max(ctr["samples"], 1):
+        raise SystemExit(f"invalid run: queue_overflow={ctr['queue_overflow']} dropped_nonfinite={ctr['dropped_nonfinite']}")
     ms_step = ms_total / args.steps
     samples_step = W * H * spp                       # whole job, all ranks
     # rays actually traversed: camera samples whose pixel pyramid misses every leaf box are answered without a traversal

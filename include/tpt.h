@@ -149,6 +149,8 @@ typedef struct tpt_counters {
                                            * pyramid misses every leaf box of the tree (k_primary's pixel-frustum culling) */
     uint64_t rays_candidates;             /* camera samples (part of rays_primary) answered by testing the 1..8 candidate triangles
                                            * of their pixel's pyramid instead of walking the tree */
+    uint64_t queue_overflow;              /* vertices whose rays did not fit their queue and were dropped; 0 by construction (the
+                                           * pools hold the worst case), checked by the tests */
 } tpt_counters;
 
 /* Device time per wavefront stage since the last tpt_reset_counters, measured with CUDA events on the

@@ -210,6 +210,7 @@ def test_slices_are_bit_identical(tpt, ctx, built, scenes):
     pt.m_radiance.clear()
     pt.render_into(ds, cam, spp=S * per, seed=5, paths_in_flight=W * H * 3)
     assert (pt.m_radiance.to_i64() == whole).all()
+    assert ctx.counters()["queue_overflow"] == 0
 
 
 @pytest.mark.parametrize("name", ["box", "ball", "light", "tir", "box2", "square"])
@@ -226,6 +227,7 @@ def test_pixel_candidates_are_bit_identical_to_per_sample_traversal(name, tpt, c
     pt.render_into(ds, cam, spp=spp, seed=9, pixel_candidates=False)
     assert (pt.m_radiance.to_i64() == a).all()
     assert a.any()
+    assert ctx.counters()["queue_overflow"] == 0
 
 
 def test_resolve_matches_reference_bytes(tpt, ctx, built, scenes, orc):

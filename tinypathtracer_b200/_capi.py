@@ -61,7 +61,7 @@ class BvhStats(C.Structure):
 
 class Counters(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ("rays_primary", "rays_extension", "rays_shadow", "rays_direct", "node_visits",
-                                          "tri_tests", "samples", "dropped_nonfinite", "kernel_launches", "rays_culled", "rays_candidates")]
+                                          "tri_tests", "samples", "dropped_nonfinite", "kernel_launches", "rays_culled", "rays_candidates", "queue_overflow")]
 
 
 class StageTimes(C.Structure):

@@ -163,6 +163,7 @@ int tpt_get_counters(tpt_context* ctx, tpt_counters* out) {
     out->kernel_launches = ctx->kernel_launches;
     out->rays_culled = h.rays_culled;
     out->rays_candidates = h.rays_candidates;
+    out->queue_overflow = h.queue_overflow;
     return TPT_OK;
 }
 

@@ -377,6 +377,8 @@ struct QueueOut {
     float4* sec;
     void* level;                       // kSegments counter blocks of the level being produced
     uint32_t extSegCap, secSegCap;     // items per segment
+    uint32_t extCap, secCap;           // items the producing kernel may write per segment it uses: the segment for k_primary, the whole
+                                       // pool (k_wave writes segment 0 only and ignores the segment borders)
 };
 
 // Emit the rays of a shaded vertex from whatever lanes are here (diverged callers allowed): the lanes of one
@@ -384,7 +386,7 @@ struct QueueOut {
 // "direct" ray, the environment sample — with one atomic.  UNIFORM: every lane of the warp is in the same segment.
 template <bool NEE, bool UNIFORM>
 __device__ __forceinline__ void emit_vertex(const ShadeParams& sp, const QueueOut& q, uint32_t seg, const Vertex& vx, uint32_t pixel,
-                                            uint32_t sample) {
+                                            uint32_t sample, DeviceCounters* ctr) {
     const unsigned here = __activemask();
     const unsigned m = UNIFORM ? here : __match_any_sync(here, seg);
     const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
@@ -403,6 +405,14 @@ __device__ __forceinline__ void emit_vertex(const ShadeParams& sp, const QueueOu
     float4* ext = q.ext + 3 * (size_t)seg * q.extSegCap;
     float4* sec = q.sec + 3 * (size_t)seg * q.secSegCap;
     uint32_t slot = (uint32_t)(base >> 32) + nL * __popc(m & lt) + __popc(bDir & lt) + __popc(bNee & lt);
+    // The pools are sized for the most every path can emit, so a reservation cannot pass the end; should that ever
+    // be wrong, nothing is written out of bounds: the ray is dropped and counted, and the consumer clamps its counts.
+    const uint32_t extSlot = (uint32_t)base + __popc(bExt & lt);
+    const uint32_t mySec = nL + (vx.direct ? 1u : 0u) + ((NEE && vx.nee) ? 1u : 0u);
+    if (slot + mySec > q.secCap || (vx.next && extSlot >= q.extCap)) {
+        atomicAdd(&ctr->queue_overflow, 1ull);
+        return;
+    }
     // delta lights: one infinite shadow ray per light, contribution T_d * baseColor * Li
     for (int l = 0; l < sp.nLights; ++l) {
         float3 ldir, lrad;
@@ -411,7 +421,7 @@ __device__ __forceinline__ void emit_vertex(const ShadeParams& sp, const QueueOu
     }
     if (vx.direct) store_path(sec, slot++, vx.P, vx.ddir, vx.Tn, pixel, sample, kKindDirect);
     if (NEE && vx.nee) store_path(sec, slot++, vx.P, vx.ldir, vx.lw, pixel, sample, kKindShadow);
-    if (vx.next) store_path(ext, (uint32_t)base + __popc(bExt & lt), vx.P, vx.ndir, vx.Tn, pixel, sample, NEE ? __float_as_uint(vx.pb) : 0u);
+    if (vx.next) store_path(ext, extSlot, vx.P, vx.ndir, vx.Tn, pixel, sample, NEE ? __float_as_uint(vx.pb) : 0u);
 }
 
 // ---- wave 0: generate + extend + shade, fused ---------------------------------------------------------
@@ -442,7 +452,7 @@ __device__ __forceinline__ void primary_sample(const BvhView& bvh, const ShadePa
     float3 term;
     Vertex vx;
     if (shade_vertex<NEE>(bvh, sp, 0, o, d, f3(1.f, 1.f, 1.f), 0u, pixel, sIdx, h, term, vx, ctr)) {
-        emit_vertex<NEE, true>(sp, q, seg, vx, pixel, sIdx);
+        emit_vertex<NEE, true>(sp, q, seg, vx, pixel, sIdx, ctr);
     } else if (term.x != 0.f || term.y != 0.f || term.z != 0.f) {
         if (finite3(term)) {
             aR += to_fixed(term.x);
@@ -630,7 +640,7 @@ __device__ __forceinline__ void shade_staged(const BvhView& bvh, const ShadePara
         float3 term;
         Vertex vx;
         if (shade_vertex<NEE>(bvh, sp, sp.depth, p.o, p.d, p.T, p.w, p.pixel, p.sample, h, term, vx, ctr))
-            emit_vertex<NEE, true>(sp, q, 0u, vx, p.pixel, p.sample);
+            emit_vertex<NEE, true>(sp, q, 0u, vx, p.pixel, p.sample, ctr);
         else accum_add(acc, p.pixel, term, ctr);
     }
     __syncwarp();
@@ -654,8 +664,8 @@ __global__ void __launch_bounds__(128, TPT_WAVE_MIN_BLOCKS) k_wave(BvhView bvh, 
     if (!SEGIN) {
         if (threadIdx.x == 0) {
             const unsigned long long w = seg_level(levelIn, 0)->counts;
-            sExtPre[0] = (uint32_t)w;
-            sSecPre[0] = (uint32_t)(w >> 32);
+            sExtPre[0] = min((uint32_t)w, q.extCap);
+            sSecPre[0] = min((uint32_t)(w >> 32), q.secCap);
             sDirect = seg_level(levelIn, 0)->n_direct;
         }
     } else if (threadIdx.x < 32) {
@@ -672,8 +682,8 @@ __global__ void __launch_bounds__(128, TPT_WAVE_MIN_BLOCKS) k_wave(BvhView bvh, 
                 w = seg_level(levelIn, seg)->counts;
                 d = seg_level(levelIn, seg)->n_direct;
             }
-            e[k] = (uint32_t)w;
-            c[k] = (uint32_t)(w >> 32);
+            e[k] = min((uint32_t)w, q.extSegCap);
+            c[k] = min((uint32_t)(w >> 32), q.secSegCap);
             sumE += e[k];
             sumS += c[k];
             sumD += d;
@@ -1186,7 +1196,7 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
         ev = 0;
         mark();
         {
-            const QueueOut q{ctx->q_ext[1], ctx->q_sec[1], levels + levelBytes, (uint32_t)extSegCap, (uint32_t)secSegCap};
+            const QueueOut q{ctx->q_ext[1], ctx->q_sec[1], levels + levelBytes, (uint32_t)extSegCap, (uint32_t)secSegCap, (uint32_t)extSegCap, (uint32_t)secSegCap};
             const uint32_t sampleBase = (uint32_t)cfg->sample_offset + done * (uint32_t)cfg->sample_stride;
             if (pl.coop)
                 kPrimaryCoop<<<pl.grid, 128, 0, st>>>(view, sp, cp, W, H, nPadded, kk, pl.spt, sampleBase, (uint32_t)cfg->sample_stride, q, acc->data, ctx->d_counters);
@@ -1199,7 +1209,8 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
         for (int w = 1; w <= cfg->max_depth; ++w) {
             const int in = w & 1, out = in ^ 1;
             sp.depth = w;
-            const QueueOut q{ctx->q_ext[out], ctx->q_sec[out], levels + (size_t)(w + 1) * levelBytes, (uint32_t)extSegCap, (uint32_t)secSegCap};
+            const QueueOut q{ctx->q_ext[out], ctx->q_sec[out], levels + (size_t)(w + 1) * levelBytes, (uint32_t)extSegCap, (uint32_t)secSegCap,
+                             (uint32_t)(extSegCap * kSegments), (uint32_t)(secSegCap * kSegments)};
             (w == 1 ? kWave1 : kWave)<<<gridWave, 128, 0, st>>>(view, sp, ctx->q_ext[in], ctx->q_sec[in], levels + (size_t)w * levelBytes, q, acc->data, ctx->d_counters);
             mark();
         }

@@ -28,6 +28,7 @@ struct DeviceCounters {
     unsigned long long dropped_nonfinite;
     unsigned long long rays_culled;   // camera samples answered by pixel-frustum culling (counted in rays_primary too)
     unsigned long long rays_candidates;   // camera samples answered by testing their pixel's candidate triangles (in rays_primary too)
+    unsigned long long queue_overflow;    // vertices whose rays did not fit their queue (must stay 0: the pools hold the worst case)
 };
 
 struct BvhView {
