@@ -261,6 +261,17 @@ def run_ours(args):
                     "stage_ms": {k: round(v["ms"], 3) for k, v in st.items()},
                     "rays": {k: c1[k] for k in ("rays_primary", "rays_culled", "rays_candidates", "rays_extension", "rays_shadow", "rays_direct")},
                     "note": "BVH of this workload is L1/L2-resident; node fetches never reach HBM, the HBM fraction is an upper-bound accounting (SURVEY §8d)"}
+        # DRAM traffic of the dominant launch (k_wave, wave 1 of one batch) from the committed ncu --set full capture of this workload
+        prof = ROOT / "profiles" / f"r01_ncu_full_k_wave_{fixture}.csv"
+        if prof.exists() and world == 1:
+            try:
+                unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+                rows = {r[0]: r for r in (ln.split(",") for ln in prof.read_text().splitlines()) if len(r) >= 3}
+                tr = sum(float(rows[k][2]) * unit[rows[k][1]] for k in ("dram__bytes_read.sum", "dram__bytes_write.sum"))
+                roofline["traffic"] = round(tr)
+                roofline["traffic_of"] = f"one k_wave launch (wave 1 of a batch), ncu --set full, {prof.relative_to(ROOT)}"
+            except Exception:
+                pass
         cpu = cpu_baseline(args, fixture, W, H, depth, env, seed) if world == 1 and not args.no_cpu_baseline else None
         line = {
             "metric": "Msamples/s (whole frames: transform + BVH build + render + resolve)", "value": round(value, 3), "unit": "Msamples/s",
