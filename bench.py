@@ -396,6 +396,17 @@ def run_soup(args):
     bpr_pri = 56.0 * c_pri["node_visits"] / n + 40.0 * c_pri["tri_tests"] / n + 88.0
     ach = bpr_sec * ns / (ms_sec * 1e-3) / 1e9
     build_gbs = 408.0 * F / (build_ms * 1e-3) / 1e9
+    # DRAM traffic of the secondary-ray launch from the committed ncu --set full capture (launch2 of that file; full-size soup only)
+    traffic, traffic_of = None, None
+    prof = ROOT / "profiles" / "r01_ncu_full_k_trace_rays_soup.csv"
+    if prof.exists() and not args.soup_small:
+        try:
+            unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+            rows = {r[0]: r for r in (ln.split(",") for ln in prof.read_text().splitlines()) if len(r) >= 5}
+            traffic = round(sum(float(rows[k][4]) * unit[rows[k][1]] for k in ("dram__bytes_read.sum", "dram__bytes_write.sum")))
+            traffic_of = f"the secondary-ray k_trace_rays_persistent launch, ncu --set full, {prof.relative_to(ROOT)} (launch2)"
+        except Exception:
+            pass
     line = {
         "metric": "Mrays/s (tpt_trace_rays, primary + secondary ray sets; BVH build ms beside it)", "value": round((n + ns) / (ms_step * 1e-3) / 1e6, 2),
         "unit": "Mrays/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 3), "higher_is_better": True,
@@ -411,7 +422,7 @@ def run_soup(args):
         "gpu_launches": int(launches), "clocks": clk,
         "roofline": {"bound": "hbm", "kernel": "k_trace_rays (secondary ray set, incoherent)", "achieved": round(ach, 2), "peak": peak,
                      "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback (B200_PROFILING.md)", "unit": "GB/s", "frac": round(ach / peak, 5),
-                     "traffic": None, "bytes_per_ray": round(bpr_sec, 1), "n_int_per_ray": round(c_sec["node_visits"] / ns, 2),
+                     "traffic": traffic, "traffic_of": traffic_of, "bytes_per_ray": round(bpr_sec, 1), "n_int_per_ray": round(c_sec["node_visits"] / ns, 2),
                      "n_leaf_per_ray": round(c_sec["tri_tests"] / ns, 2), "rays_per_launch": ns, "avg_launch_us": round(ms_sec * 1e3, 1),
                      "primary": {"bytes_per_ray": round(bpr_pri, 1), "n_int_per_ray": round(c_pri["node_visits"] / n, 2),
                                  "n_leaf_per_ray": round(c_pri["tri_tests"] / n, 2), "achieved": round(bpr_pri * n / (ms_pri * 1e-3) / 1e9, 2)},
