@@ -49,11 +49,16 @@ class Transform {
 public:
     Transform() = default;
     Transform(Vec3 loc, Quat quat, Vec3 s) : m_location(loc), m_rotation(quat), m_scale(s) {}
-    Mat4 localToParent() const;   // Translate * Rotate * Scale, include/transform.h:28-33
-    Mat4 localToWorld() const { return localToParent(); }   // the reference never sets a parent (src/mesh.cu:265 TODO)
+    Mat4 localToParent() const;   // Translate * Rotate * Scale, include/transform.h:28-33 (or the node's `matrix`, "gltf-full" only)
+    // The reference declares m_parent (include/transform.h:55) but never sets it (src/mesh.cu:265 TODO), so with its loader
+    // ("gltf") this is localToParent(); the "gltf-full" loader links the node hierarchy.
+    Mat4 localToWorld() const { return m_parent ? m_parent->localToWorld() * localToParent() : localToParent(); }
     Vec3 m_location{0, 0, 0};
     Quat m_rotation;
     Vec3 m_scale{1, 1, 1};
+    std::shared_ptr<Transform> m_parent;
+    bool m_hasMatrix = false;     // glTF `matrix` property given instead of TRS
+    Mat4 m_matrix;
 };
 Mat4 normalToWorld(const Mat4& localToWorld);   // inverse transpose of the upper 3x3, src/mesh.cu:371-378
 
@@ -116,7 +121,12 @@ struct DeviceScene {
 class Scene {
 public:
     Scene() = default;
-    Scene(const std::string& filename, const std::string& type);   // type must be "gltf" (src/mesh.cu:68-78)
+    // type "gltf": the reference's loader, quirks included (src/mesh.cu:68-307: flat node list, TRS only, primitives[0] only,
+    // materials and lights keyed by name).  type "gltf-full" (SURVEY §8(f)-1): the scene graph of `scenes[scene]` with parent
+    // transforms and `matrix` nodes, every triangle primitive of a mesh, instanced meshes, bufferView.byteStride,
+    // non-indexed primitives, computed normals where NORMAL is absent, materials and lights keyed by index.
+    // Both accept the .glb container as well as .gltf + external / base64 buffers.
+    Scene(const std::string& filename, const std::string& type);
     DeviceScene flatten() const;                                   // host part of copySceneToDevice (src/mesh.cu:309-397)
     DeviceScene copySceneToDevice(Context& ctx) const;             // + tpt_scene_create
     Camera m_camera;
@@ -125,7 +135,7 @@ public:
     const std::map<std::string, DeltaLight>& lights() const { return m_lights; }
 
 private:
-    void readFromGLTF(const std::string& filename);
+    void readFromGLTF(const std::string& filename, bool full);
     std::vector<Mesh> m_meshes;
     std::map<std::string, Material> m_materials;   // std::map: name order, as uploaded by the reference (src/mesh.cu:326-333)
     std::map<std::string, DeltaLight> m_lights;
@@ -174,6 +184,7 @@ public:
     int m_width = 1920, m_height = 1080;
     int m_spp = 64, m_depth = 8, m_frames = 1;
     uint64_t m_seed = 1;
+    std::string m_sceneType = "gltf";   // "gltf" = the reference's loader; "gltf-full" = scene graph, all primitives (Scene)
     bool m_envNEE = false;   // TPT_RENDER_ENV_NEE: sample the environment map at diffuse vertices (same expectation, lower variance)
     std::string m_output;
     double m_lastFrameMs = 0.0;

@@ -20,6 +20,8 @@ def host():
     lib = C.CDLL(str(LIB))
     lib.tpt_host_load_gltf.restype = C.c_void_p
     lib.tpt_host_load_gltf.argtypes = [C.c_char_p]
+    lib.tpt_host_load_scene.restype = C.c_void_p
+    lib.tpt_host_load_scene.argtypes = [C.c_char_p, C.c_char_p]
     lib.tpt_host_last_error.restype = C.c_char_p
     lib.tpt_host_scene_free.argtypes = [C.c_void_p]
     lib.tpt_host_scene_sizes.argtypes = [C.c_void_p, C.c_void_p]
@@ -29,9 +31,9 @@ def host():
     return lib
 
 
-def _load(host, path, tpt_dtypes):
+def _load(host, path, tpt_dtypes, kind=None):
     MATERIAL_DTYPE, MTL_INTERVAL_DTYPE, LIGHT_DTYPE = tpt_dtypes
-    h = host.tpt_host_load_gltf(str(path).encode())
+    h = host.tpt_host_load_gltf(str(path).encode()) if kind is None else host.tpt_host_load_scene(str(path).encode(), kind.encode())
     assert h, host.tpt_host_last_error().decode()
     sizes = np.zeros(5, np.uint64)
     host.tpt_host_scene_sizes(h, sizes.ctypes.data)
@@ -75,6 +77,146 @@ def test_loader_errors_are_exceptions_with_the_reference_messages(host, tmp_path
     bad.write_text('{"nodes": [{"extensions": {"KHR_lights_punctual": {"light": 0}}}], "extensions": {"KHR_lights_punctual": {"lights": [{"type": "area"}]}}}')
     assert not host.tpt_host_load_gltf(str(bad).encode())
     assert b"Unsupported light type" in host.tpt_host_last_error()
+
+
+# ---- "gltf-full": SURVEY §8(f)-1 loader hardening -------------------------------------------------------------------
+def _trs(t=(0, 0, 0), q=(0, 0, 0, 1), s=(1, 1, 1)):
+    x, y, z, w = q
+    R = np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y)],
+                  [2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x)],
+                  [2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)]])
+    M = np.eye(4)
+    M[:3, :3] = R @ np.diag(s)
+    M[:3, 3] = t
+    return M
+
+
+def _hierarchy_gltf(tmp_path, glb):
+    """Two meshes: mesh 0 has two primitives (an indexed quad with interleaved, strided POSITION/NORMAL and u16 indices; a
+    non-indexed triangle without normals) plus a LINES primitive that must be skipped; mesh 0 is instanced by two nodes
+    under a rotated + scaled parent, one of them through a `matrix`; a camera hangs under a translated node; a light
+    under the parent."""
+    import base64
+    import json
+    import struct
+    quad_p = np.array([[0, 0, 0], [1, 0, 0], [1, 1, 0], [0, 1, 0]], np.float32)
+    quad_n = np.array([[0, 0, 1]] * 4, np.float32)
+    inter = np.concatenate([quad_p, quad_n], axis=1).astype(np.float32).tobytes()     # stride 24
+    idx = np.array([0, 1, 2, 0, 2, 3], np.uint16).tobytes()
+    tri = np.array([[0, 0, 1], [2, 0, 1], [0, 2, 1]], np.float32).tobytes()
+    blob = inter + idx + tri
+    views = [dict(buffer=0, byteOffset=0, byteLength=len(inter), byteStride=24),
+             dict(buffer=0, byteOffset=len(inter), byteLength=len(idx)),
+             dict(buffer=0, byteOffset=len(inter) + len(idx), byteLength=len(tri))]
+    acc = [dict(bufferView=0, byteOffset=0, componentType=5126, count=4, type="VEC3"),
+           dict(bufferView=0, byteOffset=12, componentType=5126, count=4, type="VEC3"),
+           dict(bufferView=1, componentType=5123, count=6, type="SCALAR"),
+           dict(bufferView=2, componentType=5126, count=3, type="VEC3")]
+    parent_q = (0.0, float(np.sin(np.pi / 8)), 0.0, float(np.cos(np.pi / 8)))
+    child_m = _trs(t=(0.5, -1, 2), q=(float(np.sin(0.3)), 0, 0, float(np.cos(0.3))), s=(1, 2, 1))
+    doc = dict(
+        asset=dict(version="2.0"), scene=0, scenes=[dict(nodes=[0, 4])],
+        nodes=[dict(name="parent", translation=[1, 2, 3], rotation=list(parent_q), scale=[2, 2, 2], children=[1, 2, 3]),
+               dict(name="inst_a", mesh=0, translation=[0, 0, -1]),
+               dict(name="inst_b", mesh=0, matrix=[float(v) for v in child_m.T.reshape(-1)]),
+               dict(name="lamp", translation=[0, 3, 0], extensions=dict(KHR_lights_punctual=dict(light=0))),
+               dict(name="rig", translation=[0, 1, 8], children=[5]),
+               dict(name="cam", camera=0, rotation=[0, 0, 0, 1]),
+               dict(name="orphan_not_in_scene", mesh=0)],
+        meshes=[dict(primitives=[dict(attributes=dict(POSITION=0, NORMAL=1), indices=2, material=1),
+                                 dict(attributes=dict(POSITION=3), material=0),
+                                 dict(attributes=dict(POSITION=3), mode=1)])],
+        materials=[dict(name="same", pbrMetallicRoughness=dict(baseColorFactor=[0.1, 0.2, 0.3, 1], metallicFactor=0)),
+                   dict(name="same", pbrMetallicRoughness=dict(baseColorFactor=[0.9, 0.8, 0.7, 1], metallicFactor=0))],
+        cameras=[dict(type="perspective", perspective=dict(yfov=0.8, aspectRatio=1.5, znear=0.05))],
+        extensions=dict(KHR_lights_punctual=dict(lights=[dict(type="point", intensity=683.0, color=[1, 0.5, 0.25])])),
+        accessors=acc, bufferViews=views)
+    if glb:
+        doc["buffers"] = [dict(byteLength=len(blob))]
+        js = json.dumps(doc).encode()
+        js += b" " * (-len(js) % 4)
+        bn = blob + b"\0" * (-len(blob) % 4)
+        body = struct.pack("<II", len(js), 0x4E4F534A) + js + struct.pack("<II", len(bn), 0x004E4942) + bn
+        path = tmp_path / "h.glb"
+        path.write_bytes(b"glTF" + struct.pack("<II", 2, 12 + len(body)) + body)
+    else:
+        doc["buffers"] = [dict(byteLength=len(blob), uri="data:application/octet-stream;base64," + base64.b64encode(blob).decode())]
+        path = tmp_path / "h.gltf"
+        path.write_text(json.dumps(doc))
+    parent = _trs((1, 2, 3), parent_q, (2, 2, 2))
+    worlds = [parent @ _trs(t=(0, 0, -1)), parent @ child_m]
+    return path, quad_p, np.frombuffer(tri, np.float32).reshape(3, 3), worlds, parent
+
+
+@pytest.mark.parametrize("glb", [False, True])
+def test_full_loader_walks_the_scene_graph(glb, host, tmp_path):
+    from oracle.pyoracle import LIGHT_DTYPE, MATERIAL_DTYPE, MTL_INTERVAL_DTYPE
+    path, quad_p, tri_p, worlds, parent = _hierarchy_gltf(tmp_path, glb)
+    got = _load(host, path, (MATERIAL_DTYPE, MTL_INTERVAL_DTYPE, LIGHT_DTYPE), "gltf-full")
+    # 2 instances x (quad + triangle); the LINES primitive and the node outside the scene are not loaded
+    assert got["objects"].shape[0] == 4 and got["indices"].size == 2 * (6 + 3) and got["vertices"].shape[0] == 2 * (4 + 3)
+    np.testing.assert_array_equal(got["indices"], [0, 1, 2, 0, 2, 3, 4, 5, 6, 7, 8, 9, 7, 9, 10, 11, 12, 13])
+    np.testing.assert_array_equal(got["vertices"], np.concatenate([quad_p, tri_p, quad_p, tri_p]))
+    np.testing.assert_array_equal(got["normals"][:4], [[0, 0, 1]] * 4)
+    np.testing.assert_allclose(got["normals"][4:7], [[0, 0, 1]] * 3, atol=1e-7)          # computed: the triangle's face normal
+    for k, w in enumerate([worlds[0], worlds[0], worlds[1], worlds[1]]):
+        np.testing.assert_allclose(got["vert_trans"][k].reshape(4, 4).T, w, rtol=1e-5, atol=1e-6)
+        nt = got["normal_trans"][k].reshape(4, 4).T[:3, :3]
+        np.testing.assert_allclose(nt, np.linalg.inv(w[:3, :3]).T, rtol=1e-4, atol=1e-6)
+    # materials keyed by index (two materials share a name): quad -> material 1, triangle -> material 0
+    assert got["materials"].shape[0] == 2
+    np.testing.assert_allclose(got["materials"]["base"], [[0.1, 0.2, 0.3], [0.9, 0.8, 0.7]], rtol=1e-6)
+    np.testing.assert_array_equal(got["objects"]["mtl"], [1, 0, 1, 0])
+    np.testing.assert_array_equal(got["objects"]["begin"], [0, 2, 3, 5])
+    # camera under "rig", light under "parent"
+    cam = got["cam"]
+    assert cam[0] == np.float32(0.8) and cam[1] == np.float32(1.5) and cam[2] == np.float32(0.05)
+    np.testing.assert_allclose(cam[3:].reshape(4, 4).T, _trs(t=(0, 1, 8)), atol=1e-6)
+    assert got["lights"].shape[0] == 1 and got["lights"]["type"][0] == 0
+    np.testing.assert_allclose(got["lights"]["a"][0], (parent @ np.array([0, 3, 0, 1.0]))[:3], rtol=1e-5)
+    np.testing.assert_allclose(got["lights"]["intensity"][0], 1.0, rtol=1e-6)
+
+
+def test_reference_loader_reads_the_same_file_its_own_way(host, tmp_path):
+    """type "gltf" keeps the reference's reading of the same file: every node of the flat list (the orphan too), local TRS
+    only (no parents, no `matrix`), primitives[0] only, materials keyed by name (first definition wins)."""
+    from oracle.pyoracle import LIGHT_DTYPE, MATERIAL_DTYPE, MTL_INTERVAL_DTYPE
+    path, quad_p, _, _, _ = _hierarchy_gltf(tmp_path, False)
+    got = _load(host, path, (MATERIAL_DTYPE, MTL_INTERVAL_DTYPE, LIGHT_DTYPE), "gltf")
+    assert got["objects"].shape[0] == 3 and got["indices"].size == 18 and got["materials"].shape[0] == 1
+    np.testing.assert_allclose(got["vert_trans"][0].reshape(4, 4).T, _trs(t=(0, 0, -1)), atol=1e-7)
+    np.testing.assert_allclose(got["vert_trans"][1].reshape(4, 4).T, np.eye(4), atol=1e-7)
+    np.testing.assert_allclose(got["materials"]["base"][0], [0.9, 0.8, 0.7], rtol=1e-6)
+    # ... and it misreads the strided accessor as tightly packed, as the reference does (src/mesh.cu:165-170)
+    assert not np.array_equal(got["vertices"][:4], quad_p)
+
+
+def test_glb_container_in_reference_mode(host, tmp_path, scenes):
+    """The reference's scenes repacked as .glb load to the same arrays as their .gltf."""
+    import json
+    import struct
+    from oracle.pyoracle import LIGHT_DTYPE, MATERIAL_DTYPE, MTL_INTERVAL_DTYPE
+    src = next((d / "box.gltf" for d in GLTF_DIRS if (d / "box.gltf").exists()), None)
+    if src is None:
+        pytest.skip("no .gltf inputs on this machine")
+    doc = json.loads(src.read_text())
+    assert len(doc["buffers"]) == 1
+    uri = doc["buffers"][0].pop("uri")
+    if uri.startswith("data:"):
+        import base64
+        blob = base64.b64decode(uri.split(",", 1)[1])
+    else:
+        blob = (src.parent / uri).read_bytes()
+    js = json.dumps(doc).encode()
+    js += b" " * (-len(js) % 4)
+    bn = blob + b"\0" * (-len(blob) % 4)
+    body = struct.pack("<II", len(js), 0x4E4F534A) + js + struct.pack("<II", len(bn), 0x004E4942) + bn
+    path = tmp_path / "box.glb"
+    path.write_bytes(b"glTF" + struct.pack("<II", 2, 12 + len(body)) + body)
+    dt = (MATERIAL_DTYPE, MTL_INTERVAL_DTYPE, LIGHT_DTYPE)
+    a, b = _load(host, path, dt), _load(host, src, dt)
+    for k in a:
+        assert a[k].tobytes() == b[k].tobytes(), k
 
 
 def test_png_codecs_round_trip(host, tmp_path):

@@ -30,6 +30,7 @@ Mat4 operator*(const Mat4& a, const Mat4& b) {
 }
 
 Mat4 Transform::localToParent() const {
+    if (m_hasMatrix) return m_matrix;
     const Real x = m_rotation.x, y = m_rotation.y, z = m_rotation.z, w = m_rotation.w;
     const Real x2 = x * x, y2 = y * y, z2 = z * z, xy = x * y, xz = x * z, yz = y * z, wx = w * x, wy = w * y, wz = w * z;
     Mat4 R, T, S;
@@ -149,8 +150,9 @@ namespace {
 struct Gltf {
     json::Value root;
     std::vector<std::vector<uint8_t>> buffers;
-    // tightly packed view of an accessor: buffer + accessor.byteOffset + bufferView.byteOffset (src/mesh.cu:165-170)
-    const uint8_t* data(int accessor, size_t bytesNeeded) const {
+    // Element `i` of an accessor lives at base + i * stride.  The reference assumes tightly packed data
+    // (src/mesh.cu:165-170); `strided` (gltf-full) honours bufferView.byteStride.
+    const uint8_t* data(int accessor, size_t elemBytes, size_t count, bool strided, size_t* stride) const {
         const json::Value& acc = root["accessors"][(size_t)accessor];
         if (!acc.is_object()) throw std::runtime_error("glTF: accessor index out of range");
         const json::Value& bv = root["bufferViews"][(size_t)acc["bufferView"].integer(-1)];
@@ -158,25 +160,49 @@ struct Gltf {
         const size_t b = (size_t)bv["buffer"].integer(0);
         if (b >= buffers.size()) throw std::runtime_error("glTF: buffer index out of range");
         const size_t off = (size_t)acc["byteOffset"].number(0) + (size_t)bv["byteOffset"].number(0);
-        if (off + bytesNeeded > buffers[b].size()) throw std::runtime_error("glTF: accessor reads past the end of its buffer");
+        const size_t bs = strided ? (size_t)bv["byteStride"].number(0) : 0;
+        *stride = bs ? bs : elemBytes;
+        if (count && off + (count - 1) * *stride + elemBytes > buffers[b].size()) throw std::runtime_error("glTF: accessor reads past the end of its buffer");
         return buffers[b].data() + off;
     }
     size_t count(int accessor) const { return (size_t)root["accessors"][(size_t)accessor]["count"].number(0); }
 };
-}   // namespace
 
-Scene::Scene(const std::string& filename, const std::string& type) {
-    if (type == "gltf") readFromGLTF(filename);
-    else throw std::runtime_error("Unsupported file type!");   // src/mesh.cu:76
+uint32_t le32(const std::string& s, size_t off) {
+    uint32_t v;
+    std::memcpy(&v, s.data() + off, 4);
+    return v;
 }
 
-void Scene::readFromGLTF(const std::string& filename) {
-    Gltf g;
-    g.root = json::parse(readFile(filename));
+// .gltf (JSON + external or base64 buffers) or .glb (12-byte header, JSON chunk, optional BIN chunk = buffer without uri)
+void loadContainer(const std::string& filename, Gltf& g) {
+    const std::string file = readFile(filename);
+    std::string glbBin;
+    bool hasBin = false;
+    if (file.size() >= 12 && file.compare(0, 4, "glTF") == 0) {
+        if (le32(file, 4) != 2) throw std::runtime_error("Failed to load .gltf : only GLB version 2 is supported");
+        size_t off = 12;
+        std::string jsonText;
+        while (off + 8 <= file.size()) {
+            const uint32_t len = le32(file, off), type = le32(file, off + 4);
+            if (off + 8 + len > file.size()) throw std::runtime_error("Failed to load .gltf : truncated GLB chunk");
+            if (type == 0x4E4F534Au) jsonText = file.substr(off + 8, len);                    // "JSON"
+            else if (type == 0x004E4942u && !hasBin) { glbBin = file.substr(off + 8, len); hasBin = true; }   // "BIN\0"
+            off += 8 + (size_t)len;
+        }
+        if (jsonText.empty()) throw std::runtime_error("Failed to load .gltf : GLB has no JSON chunk");
+        g.root = json::parse(jsonText);
+    } else {
+        g.root = json::parse(file);
+    }
     const std::string dir = filename.find_last_of("/\\") == std::string::npos ? "" : filename.substr(0, filename.find_last_of("/\\") + 1);
     for (size_t i = 0; i < g.root["buffers"].size(); ++i) {
-        const std::string& uri = g.root["buffers"][i]["uri"].string("");
-        if (uri.compare(0, 5, "data:") == 0) {
+        const json::Value& uriV = g.root["buffers"][i]["uri"];
+        const std::string uri = uriV.string("");
+        if (uri.empty()) {
+            if (!hasBin) throw std::runtime_error("glTF: buffer without uri and no GLB BIN chunk");
+            g.buffers.emplace_back(glbBin.begin(), glbBin.end());
+        } else if (uri.compare(0, 5, "data:") == 0) {
             const size_t comma = uri.find(',');
             g.buffers.push_back(base64Decode(uri, comma == std::string::npos ? 5 : comma + 1));
         } else {
@@ -184,108 +210,231 @@ void Scene::readFromGLTF(const std::string& filename) {
             g.buffers.emplace_back(raw.begin(), raw.end());
         }
     }
+}
+
+Material readMaterial(const json::Value& gm) {   // src/mesh.cu:228-257
+    Material m = defaultMaterial();
+    const json::Value& pbr = gm["pbrMetallicRoughness"];
+    m.unused[2] = (Real)pbr["roughnessFactor"].number(1.0);
+    m.metallic = (Real)pbr["metallicFactor"].number(1.0);   // glTF default 1.0 -> a material that omits it is a mirror
+    const json::Value& bc = pbr["baseColorFactor"];
+    m.base_color[0] = bc.is_array() ? (Real)bc[0].num : 1.0f;
+    m.base_color[1] = bc.is_array() ? (Real)bc[1].num : 1.0f;
+    m.base_color[2] = bc.is_array() ? (Real)bc[2].num : 1.0f;
+    const json::Value& ext = gm["extensions"];   // src/mesh.cu:243-257
+    if (ext.has("KHR_materials_transmission")) m.unused[1] = 1.0f - (Real)ext["KHR_materials_transmission"]["transmissionFactor"].number(0) / 5.0f;
+    if (ext.has("KHR_materials_emissive_strength")) m.emission = (Real)ext["KHR_materials_emissive_strength"]["emissiveStrength"].number(0);
+    if (ext.has("KHR_materials_ior")) m.eta = (Real)ext["KHR_materials_ior"]["ior"].number(0);
+    return m;
+}
+
+DeltaLight readLight(const json::Value& L, const Mat4& m) {   // src/mesh.cu:267-304
+    const float wattsPerLumen = 1.0f / 683.0f;   // include/delta_light.h:7
+    DeltaLight d;
+    std::memset(&d, 0, sizeof d);
+    const json::Value& col = L["color"];
+    for (int k = 0; k < 3; ++k) d.color[k] = col.is_array() ? (Real)col[(size_t)k].num : 1.0f;
+    const Real inten = (Real)L["intensity"].number(1.0);
+    const std::string type = L["type"].string("");
+    const Vec3 pos = mulPoint(m, Vec3(0, 0, 0), 1.0f), dirv = mulPoint(m, Vec3(0, 0, -1), 0.0f);
+    if (type == "point") {
+        d.type = 0;
+        d.intensity = inten * wattsPerLumen;       // src/mesh.cu:276
+        d.a[0] = pos.x; d.a[1] = pos.y; d.a[2] = pos.z;
+    } else if (type == "directional") {
+        d.type = 1;
+        d.intensity = inten;                       // src/mesh.cu:283 (not scaled)
+        d.a[0] = dirv.x; d.a[1] = dirv.y; d.a[2] = dirv.z;
+    } else if (type == "spot") {
+        d.type = 2;
+        d.intensity = inten * wattsPerLumen;       // src/mesh.cu:290
+        const Real inner = (Real)L["spot"]["innerConeAngle"].number(0.0);
+        const Real outer = (Real)L["spot"]["outerConeAngle"].number(0.7853981633974483);
+        const Real co = std::cos(outer), ci = std::cos(inner);
+        d.cos_outer = co;
+        d.inv_cone_diff = 1.0f / (ci - co);
+        d.a[0] = pos.x; d.a[1] = pos.y; d.a[2] = pos.z;
+        d.b[0] = dirv.x; d.b[1] = dirv.y; d.b[2] = dirv.z;
+    } else {
+        throw std::runtime_error("Unsupported light type");   // src/mesh.cu:303
+    }
+    return d;
+}
+
+// One primitive -> Mesh arrays.  `full` == false is the reference's reading (tight accessors, POSITION + NORMAL +
+// indices required).  Returns false for a primitive that is not a triangle list (gltf-full skips those).
+bool readPrimitive(const Gltf& g, const json::Value& prim, bool full, Mesh& mesh) {
+    if (full && prim["mode"].integer(4) != 4) return false;
+    const json::Value& attrs = prim["attributes"];
+    const int aPos = attrs["POSITION"].integer(-1), aNrm = attrs["NORMAL"].integer(-1), aTex = attrs["TEXCOORD_0"].integer(-1);
+    const int aIdx = prim["indices"].integer(-1);
+    if (!full && (aPos < 0 || aNrm < 0 || aIdx < 0)) throw std::runtime_error("glTF: a mesh primitive needs POSITION, NORMAL and indices");
+    if (aPos < 0) throw std::runtime_error("glTF: a mesh primitive needs POSITION");
+    if (full && g.root["accessors"][(size_t)aPos]["componentType"].integer(5126) != 5126) throw std::runtime_error("glTF: POSITION must be float");
+    const size_t nv = g.count(aPos);
+    size_t sp = 12, sn = 12, st = 8;
+    const uint8_t* pos = g.data(aPos, 12, nv, full, &sp);   // buffers are byte arrays: no alignment assumed
+    mesh.m_vertexCoords.resize(nv);
+    mesh.m_vertexNormals.assign(nv, Vec3(0, 0, 0));
+    mesh.m_vertexTexCoords.resize(nv);
+    for (size_t i = 0; i < nv; ++i) {
+        Real p3[3];
+        std::memcpy(p3, pos + sp * i, 12);
+        mesh.m_vertexCoords[i] = Vec3(p3[0], p3[1], p3[2]);
+    }
+    if (aNrm >= 0) {
+        const uint8_t* nrm = g.data(aNrm, 12, nv, full, &sn);
+        for (size_t i = 0; i < nv; ++i) {
+            Real n3[3];
+            std::memcpy(n3, nrm + sn * i, 12);
+            mesh.m_vertexNormals[i] = Vec3(n3[0], n3[1], n3[2]);
+        }
+    }
+    if (aTex >= 0 && (!full || g.root["accessors"][(size_t)aTex]["componentType"].integer(5126) == 5126)) {
+        const uint8_t* tex = g.data(aTex, 8, nv, full, &st);
+        for (size_t i = 0; i < nv; ++i) std::memcpy(&mesh.m_vertexTexCoords[i], tex + st * i, 8);
+    }
+    if (aIdx >= 0) {
+        const size_t ni = g.count(aIdx);
+        const int ctype = g.root["accessors"][(size_t)aIdx]["componentType"].integer(5125);
+        const size_t isz = ctype == 5121 ? 1 : (ctype == 5123 ? 2 : 4);
+        size_t si = isz;
+        const uint8_t* idx = g.data(aIdx, isz, ni, full, &si);
+        mesh.m_polygons.resize(ni);
+        for (size_t i = 0; i < ni; ++i) {
+            uint32_t v = 0;
+            std::memcpy(&v, idx + si * i, isz);
+            if (full && v >= nv) throw std::runtime_error("glTF: index out of range");
+            mesh.m_polygons[i] = v;
+        }
+    } else {   // non-indexed triangle list
+        mesh.m_polygons.resize(nv - nv % 3);
+        for (size_t i = 0; i < mesh.m_polygons.size(); ++i) mesh.m_polygons[i] = (uint32_t)i;
+    }
+    if (aNrm < 0) {   // area-weighted vertex normals from the faces
+        for (size_t f = 0; f + 2 < mesh.m_polygons.size(); f += 3) {
+            const Vec3 &a = mesh.m_vertexCoords[mesh.m_polygons[f]], &b = mesh.m_vertexCoords[mesh.m_polygons[f + 1]], &c = mesh.m_vertexCoords[mesh.m_polygons[f + 2]];
+            const Vec3 e1(b.x - a.x, b.y - a.y, b.z - a.z), e2(c.x - a.x, c.y - a.y, c.z - a.z);
+            const Vec3 n(e1.y * e2.z - e1.z * e2.y, e1.z * e2.x - e1.x * e2.z, e1.x * e2.y - e1.y * e2.x);
+            for (int k = 0; k < 3; ++k) {
+                Vec3& dst = mesh.m_vertexNormals[mesh.m_polygons[f + k]];
+                dst.x += n.x; dst.y += n.y; dst.z += n.z;
+            }
+        }
+        for (Vec3& n : mesh.m_vertexNormals) {
+            const Real len = std::sqrt(n.x * n.x + n.y * n.y + n.z * n.z);
+            if (len > 0) { n.x /= len; n.y /= len; n.z /= len; } else n = Vec3(0, 1, 0);
+        }
+    }
+    return true;
+}
+
+std::string indexedKey(int idx, const std::string& name) {   // sorts by index, keeps the name readable
+    char buf[16];
+    std::snprintf(buf, sizeof buf, "%06d:", idx);
+    return buf + name;
+}
+}   // namespace
+
+Scene::Scene(const std::string& filename, const std::string& type) {
+    if (type == "gltf") readFromGLTF(filename, false);
+    else if (type == "gltf-full") readFromGLTF(filename, true);
+    else throw std::runtime_error("Unsupported file type!");   // src/mesh.cu:76
+}
+
+void Scene::readFromGLTF(const std::string& filename, bool full) {
+    Gltf g;
+    loadContainer(filename, g);
     const json::Value& glMaterials = g.root["materials"];
     const json::Value& glLights = g.root["extensions"]["KHR_lights_punctual"]["lights"];
-    const float wattsPerLumen = 1.0f / 683.0f;   // include/delta_light.h:7
-
     const json::Value& nodes = g.root["nodes"];
-    for (size_t ni = 0; ni < nodes.size(); ++ni) {
-        const json::Value& node = nodes[ni];
-        const int lightIdx = node["extensions"]["KHR_lights_punctual"]["light"].integer(-1);
-        if (node["camera"].integer(-1) > -1) {
-            const json::Value& cam = g.root["cameras"][(size_t)node["camera"].integer(0)];
-            if (cam["type"].string("") == "perspective") {   // src/mesh.cu:146-156
-                const json::Value& p = cam["perspective"];
-                m_camera = Camera((Real)p["yfov"].number(0), (Real)p["aspectRatio"].number(0), (Real)p["znear"].number(0), readTransform(node));
+
+    if (!full) {   // the reference's loop over the flat node list (src/mesh.cu:97-306)
+        for (size_t ni = 0; ni < nodes.size(); ++ni) {
+            const json::Value& node = nodes[ni];
+            const int lightIdx = node["extensions"]["KHR_lights_punctual"]["light"].integer(-1);
+            if (node["camera"].integer(-1) > -1) {
+                const json::Value& cam = g.root["cameras"][(size_t)node["camera"].integer(0)];
+                if (cam["type"].string("") == "perspective") {   // src/mesh.cu:146-156
+                    const json::Value& p = cam["perspective"];
+                    m_camera = Camera((Real)p["yfov"].number(0), (Real)p["aspectRatio"].number(0), (Real)p["znear"].number(0), readTransform(node));
+                }
+            } else if (node["mesh"].integer(-1) > -1) {
+                const json::Value& prim = g.root["meshes"][(size_t)node["mesh"].integer(0)]["primitives"][0];   // primitives[0] only, src/mesh.cu:165
+                Mesh mesh;
+                readPrimitive(g, prim, false, mesh);
+                if (glMaterials.size() > 0) {
+                    const json::Value& gm = glMaterials[(size_t)prim["material"].integer(0)];
+                    mesh.m_material = gm["name"].string("");
+                    if (!m_materials.count(mesh.m_material)) m_materials[mesh.m_material] = readMaterial(gm);   // first definition wins, src/mesh.cu:228
+                }
+                mesh.m_transform = std::make_shared<Transform>(readTransform(node));
+                m_meshes.push_back(std::move(mesh));
+            } else if (lightIdx > -1) {
+                m_lights[node["name"].string("")] = readLight(glLights[(size_t)lightIdx], readTransform(node).localToWorld());
             }
-        } else if (node["mesh"].integer(-1) > -1) {
-            const json::Value& prim = g.root["meshes"][(size_t)node["mesh"].integer(0)]["primitives"][0];   // primitives[0] only, src/mesh.cu:165
-            const json::Value& attrs = prim["attributes"];
-            Mesh mesh;
-            const int aPos = attrs["POSITION"].integer(-1), aNrm = attrs["NORMAL"].integer(-1), aTex = attrs["TEXCOORD_0"].integer(-1);
-            const int aIdx = prim["indices"].integer(-1);
-            if (aPos < 0 || aNrm < 0 || aIdx < 0) throw std::runtime_error("glTF: a mesh primitive needs POSITION, NORMAL and indices");
-            const size_t nv = g.count(aPos);
-            const float* pos = reinterpret_cast<const float*>(g.data(aPos, nv * 12));
-            const float* nrm = reinterpret_cast<const float*>(g.data(aNrm, nv * 12));
-            mesh.m_vertexCoords.resize(nv);
-            mesh.m_vertexNormals.resize(nv);
-            mesh.m_vertexTexCoords.resize(nv);
-            for (size_t i = 0; i < nv; ++i) {
-                Real p3[3], n3[3];
-                std::memcpy(p3, reinterpret_cast<const uint8_t*>(pos) + 12 * i, 12);   // buffers are byte arrays: no alignment assumed
-                std::memcpy(n3, reinterpret_cast<const uint8_t*>(nrm) + 12 * i, 12);
-                mesh.m_vertexCoords[i] = Vec3(p3[0], p3[1], p3[2]);
-                mesh.m_vertexNormals[i] = Vec3(n3[0], n3[1], n3[2]);
+        }
+    } else {   // scene graph: roots of scenes[scene], parents before children
+        std::vector<int> roots;
+        const json::Value& sceneNodes = g.root["scenes"][(size_t)g.root["scene"].integer(0)]["nodes"];
+        if (sceneNodes.is_array()) {
+            for (size_t i = 0; i < sceneNodes.size(); ++i) roots.push_back(sceneNodes[i].integer(-1));
+        } else {   // no scenes: every node that is nobody's child
+            std::vector<char> isChild(nodes.size(), 0);
+            for (size_t i = 0; i < nodes.size(); ++i)
+                for (size_t c = 0; c < nodes[i]["children"].size(); ++c) {
+                    const int ch = nodes[i]["children"][c].integer(-1);
+                    if (ch >= 0 && (size_t)ch < nodes.size()) isChild[(size_t)ch] = 1;
+                }
+            for (size_t i = 0; i < nodes.size(); ++i) if (!isChild[i]) roots.push_back((int)i);
+        }
+        bool haveCamera = false;
+        struct Item { int node; std::shared_ptr<Transform> parent; int depth; };
+        std::vector<Item> stack;
+        for (auto it = roots.rbegin(); it != roots.rend(); ++it) stack.push_back({*it, nullptr, 0});
+        while (!stack.empty()) {
+            const Item item = stack.back();
+            stack.pop_back();
+            if (item.node < 0 || (size_t)item.node >= nodes.size()) throw std::runtime_error("glTF: node index out of range");
+            if (item.depth > 256) throw std::runtime_error("glTF: node hierarchy deeper than 256 (cycle?)");
+            const json::Value& node = nodes[(size_t)item.node];
+            auto t = std::make_shared<Transform>(readTransform(node));
+            t->m_parent = item.parent;
+            const json::Value& mat = node["matrix"];
+            if (mat.is_array() && mat.size() == 16) {
+                t->m_hasMatrix = true;
+                for (size_t k = 0; k < 16; ++k) t->m_matrix.m[k] = (Real)mat[k].num;
             }
-            if (aTex >= 0) {
-                const uint8_t* tex = g.data(aTex, nv * 8);
-                for (size_t i = 0; i < nv; ++i) std::memcpy(&mesh.m_vertexTexCoords[i], tex + 8 * i, 8);
-            }
-            const size_t ni2 = g.count(aIdx);
-            const int ctype = g.root["accessors"][(size_t)aIdx]["componentType"].integer(5125);
-            const size_t isz = ctype == 5121 ? 1 : (ctype == 5123 ? 2 : 4);
-            const uint8_t* idx = g.data(aIdx, ni2 * isz);
-            mesh.m_polygons.resize(ni2);
-            for (size_t i = 0; i < ni2; ++i) {
-                uint32_t v = 0;
-                std::memcpy(&v, idx + isz * i, isz);
-                mesh.m_polygons[i] = v;
-            }
-            if (glMaterials.size() > 0) {
-                const json::Value& gm = glMaterials[(size_t)prim["material"].integer(0)];
-                mesh.m_material = gm["name"].string("");
-                if (!m_materials.count(mesh.m_material)) {   // first definition wins, src/mesh.cu:228
-                    Material m = defaultMaterial();
-                    const json::Value& pbr = gm["pbrMetallicRoughness"];
-                    m.unused[2] = (Real)pbr["roughnessFactor"].number(1.0);
-                    m.metallic = (Real)pbr["metallicFactor"].number(1.0);   // glTF default 1.0 -> a material that omits it is a mirror
-                    const json::Value& bc = pbr["baseColorFactor"];
-                    m.base_color[0] = bc.is_array() ? (Real)bc[0].num : 1.0f;
-                    m.base_color[1] = bc.is_array() ? (Real)bc[1].num : 1.0f;
-                    m.base_color[2] = bc.is_array() ? (Real)bc[2].num : 1.0f;
-                    const json::Value& ext = gm["extensions"];   // src/mesh.cu:243-257
-                    if (ext.has("KHR_materials_transmission"))
-                        m.unused[1] = 1.0f - (Real)ext["KHR_materials_transmission"]["transmissionFactor"].number(0) / 5.0f;
-                    if (ext.has("KHR_materials_emissive_strength")) m.emission = (Real)ext["KHR_materials_emissive_strength"]["emissiveStrength"].number(0);
-                    if (ext.has("KHR_materials_ior")) m.eta = (Real)ext["KHR_materials_ior"]["ior"].number(0);
-                    m_materials[mesh.m_material] = m;
+            if (node["camera"].integer(-1) > -1 && !haveCamera) {
+                const json::Value& cam = g.root["cameras"][(size_t)node["camera"].integer(0)];
+                if (cam["type"].string("") == "perspective") {
+                    const json::Value& p = cam["perspective"];
+                    m_camera = Camera((Real)p["yfov"].number(0), (Real)p["aspectRatio"].number(1.77778), (Real)p["znear"].number(0.1), Transform());
+                    m_camera.m_transform = t;
+                    haveCamera = true;
                 }
             }
-            mesh.m_transform = std::make_shared<Transform>(readTransform(node));
-            m_meshes.push_back(std::move(mesh));
-        } else if (lightIdx > -1) {
-            const json::Value& L = glLights[(size_t)lightIdx];
-            DeltaLight d;
-            std::memset(&d, 0, sizeof d);
-            const json::Value& col = L["color"];
-            for (int k = 0; k < 3; ++k) d.color[k] = col.is_array() ? (Real)col[(size_t)k].num : 1.0f;
-            const Real inten = (Real)L["intensity"].number(1.0);
-            const Mat4 m = readTransform(node).localToWorld();
-            const std::string& type = L["type"].string("");
-            const Vec3 pos = mulPoint(m, Vec3(0, 0, 0), 1.0f), dirv = mulPoint(m, Vec3(0, 0, -1), 0.0f);
-            if (type == "point") {
-                d.type = 0;
-                d.intensity = inten * wattsPerLumen;       // src/mesh.cu:276
-                d.a[0] = pos.x; d.a[1] = pos.y; d.a[2] = pos.z;
-            } else if (type == "directional") {
-                d.type = 1;
-                d.intensity = inten;                       // src/mesh.cu:283 (not scaled)
-                d.a[0] = dirv.x; d.a[1] = dirv.y; d.a[2] = dirv.z;
-            } else if (type == "spot") {
-                d.type = 2;
-                d.intensity = inten * wattsPerLumen;       // src/mesh.cu:290
-                const Real inner = (Real)L["spot"]["innerConeAngle"].number(0.0);
-                const Real outer = (Real)L["spot"]["outerConeAngle"].number(0.7853981633974483);
-                const Real co = std::cos(outer), ci = std::cos(inner);
-                d.cos_outer = co;
-                d.inv_cone_diff = 1.0f / (ci - co);
-                d.a[0] = pos.x; d.a[1] = pos.y; d.a[2] = pos.z;
-                d.b[0] = dirv.x; d.b[1] = dirv.y; d.b[2] = dirv.z;
-            } else {
-                throw std::runtime_error("Unsupported light type");   // src/mesh.cu:303
+            if (node["mesh"].integer(-1) > -1) {
+                const json::Value& prims = g.root["meshes"][(size_t)node["mesh"].integer(0)]["primitives"];
+                for (size_t pi = 0; pi < prims.size(); ++pi) {
+                    Mesh mesh;
+                    if (!readPrimitive(g, prims[pi], true, mesh) || mesh.m_polygons.empty()) continue;
+                    const int mi = prims[pi]["material"].integer(-1);
+                    if (mi >= 0 && (size_t)mi < glMaterials.size()) {
+                        mesh.m_material = indexedKey(mi, glMaterials[(size_t)mi]["name"].string(""));
+                        if (!m_materials.count(mesh.m_material)) m_materials[mesh.m_material] = readMaterial(glMaterials[(size_t)mi]);
+                    } else {
+                        mesh.m_material = "";   // sorts first: the default material
+                        if (!m_materials.count("")) m_materials[""] = defaultMaterial();
+                    }
+                    mesh.m_transform = t;
+                    m_meshes.push_back(std::move(mesh));
+                }
             }
-            m_lights[node["name"].string("")] = d;
+            const int lightIdx = node["extensions"]["KHR_lights_punctual"]["light"].integer(-1);
+            if (lightIdx > -1) m_lights[indexedKey(item.node, node["name"].string(""))] = readLight(glLights[(size_t)lightIdx], t->localToWorld());
+            const json::Value& ch = node["children"];
+            for (size_t c = ch.size(); c-- > 0;) stack.push_back({ch[c].integer(-1), t, item.depth + 1});
         }
     }
     // declared deviation: a file without a `materials` array makes the reference read materials[0] of an empty vector

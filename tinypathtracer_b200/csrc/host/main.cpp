@@ -11,7 +11,7 @@ int main(int argc, char** argv) {
     std::string scene, env, out;
     int w = 1920, h = 1080, spp = 64, depth = 8, frames = 1;
     unsigned long long seed = 1;
-    bool envNee = false;
+    bool envNee = false, fullGltf = false;
     for (int i = 1; i < argc; ++i) {
         const std::string k = argv[i];
         auto val = [&]() -> const char* {
@@ -28,10 +28,11 @@ int main(int argc, char** argv) {
         else if (k == "--frames") frames = std::atoi(val());
         else if (k == "--seed") seed = std::strtoull(val(), nullptr, 10);
         else if (k == "--env-nee") envNee = true;
+        else if (k == "--full-gltf") fullGltf = true;
         else { std::fprintf(stderr, "unknown argument %s\n", k.c_str()); return 2; }
     }
     if (scene.empty()) {
-        std::fprintf(stderr, "usage: tpt_render --scene file.gltf [--env sky.png] [--w 1920 --h 1080 --spp 64 --depth 8 --frames 1 --seed 1 --env-nee --out frame.png]\n");
+        std::fprintf(stderr, "usage: tpt_render --scene file.gltf [--env sky.png] [--w 1920 --h 1080 --spp 64 --depth 8 --frames 1 --seed 1 --env-nee --full-gltf --out frame.png]\n");
         return 2;
     }
     try {
@@ -43,6 +44,7 @@ int main(int argc, char** argv) {
         pathTracer.m_frames = frames;
         pathTracer.m_seed = seed;
         pathTracer.m_envNEE = envNee;
+        if (fullGltf) pathTracer.m_sceneType = "gltf-full";
         pathTracer.m_output = out;
         pathTracer.render(scene);          // src/main.cu:12
         const tpt_counters c = pathTracer.context().counters();

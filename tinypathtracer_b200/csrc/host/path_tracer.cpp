@@ -64,7 +64,7 @@ void PathTracer::doTrace(DeviceScene& scene, Camera& camera, unsigned char* fram
 }
 
 void PathTracer::render(const std::string& meshFile) {
-    Scene scene(meshFile, "gltf");                            // src/path_tracer.cu:558
+    Scene scene(meshFile, m_sceneType);                       // src/path_tracer.cu:558 ("gltf")
     DeviceScene d_scene = scene.copySceneToDevice(*m_ctx);    // :560
     Camera& camera = scene.m_camera;                          // :562
     std::vector<unsigned char> fb((size_t)m_width * m_height * 4, 0);
@@ -102,6 +102,19 @@ const char* tpt_host_last_error(void) { return g_host_error.c_str(); }
 tpt_host_scene* tpt_host_load_gltf(const char* path) {
     try {
         tpt::Scene scene(path, "gltf");
+        tpt_host_scene* h = new tpt_host_scene();
+        h->d = scene.flatten();
+        h->cam = scene.m_camera;
+        h->abi = h->cam.toABI();
+        return h;
+    } catch (const std::exception& e) {
+        g_host_error = e.what();
+        return nullptr;
+    }
+}
+tpt_host_scene* tpt_host_load_scene(const char* path, const char* type) {   // type: "gltf" | "gltf-full"
+    try {
+        tpt::Scene scene(path, type);
         tpt_host_scene* h = new tpt_host_scene();
         h->d = scene.flatten();
         h->cam = scene.m_camera;
