@@ -184,6 +184,15 @@ public:
     int m_width = 1920, m_height = 1080;
     int m_spp = 64, m_depth = 8, m_frames = 1;
     uint64_t m_seed = 1;
+    // Progressive mode (the reference restarts every frame, src/path_tracer.cu:534): frames ADD their samples —
+    // frame f renders sample indices [f*spp, (f+1)*spp) with the same seed, and the framebuffer shows the mean of all samples so
+    // far.  Accumulation is exact (int64), so N progressive frames equal one frame of N*spp samples bit for bit.
+    bool m_progressive = false;
+    uint64_t m_samplesDone = 0;          // samples per pixel in the accumulator (progressive mode / after loadCheckpoint)
+    // Checkpoint = the int64 accumulation buffer + {width, height, samples done, seed}; resuming continues the sample sequence
+    // (SURVEY §8(f)-2), so an interrupted render finishes with the image an uninterrupted one gives.
+    void saveCheckpoint(const std::string& file);
+    void loadCheckpoint(const std::string& file);   // switches to progressive mode
     std::string m_sceneType = "gltf";   // "gltf" = the reference's loader; "gltf-full" = scene graph, all primitives (Scene)
     bool m_envNEE = false;   // TPT_RENDER_ENV_NEE: sample the environment map at diffuse vertices (same expectation, lower variance)
     std::string m_output;
@@ -191,6 +200,7 @@ public:
     Context& context() { return *m_ctx; }
 
 private:
+    void ensureAccumulator();
     std::unique_ptr<Context> m_ctx;
     std::string m_envFile;
     tpt_accum* m_radiance = nullptr;

@@ -266,3 +266,36 @@ def test_tpt_render_cli_matches_the_python_binding(tpt, ctx, scenes, tmp_path):
     assert img.mean() > 5
     bad = subprocess.run([str(exe), "--scene", str(tmp_path / "nope.gltf")], capture_output=True, text=True)
     assert bad.returncode == 1 and "Failed to load .gltf" in bad.stderr
+
+
+@pytest.mark.gpu
+def test_progressive_frames_and_checkpoint_resume_equal_one_shot(tmp_path):
+    """frames that ADD samples (same seed, continuing sample indices) and a render resumed from a
+    checkpoint give the image of one uninterrupted frame with all the samples — the same bytes, since accumulation is exact."""
+    import subprocess
+    from PIL import Image
+    exe = ROOT / "tinypathtracer_b200" / "lib" / "tpt_render"
+    src = next((d / "box.gltf" for d in GLTF_DIRS if (d / "box.gltf").exists()), None)
+    if src is None:
+        pytest.skip("no .gltf inputs on this machine")
+    base = [str(exe), "--scene", str(src), "--w", "128", "--h", "72", "--depth", "8", "--seed", "5"]
+
+    def run(*extra):
+        r = subprocess.run(base + list(extra), capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr[-2000:]
+        return r
+
+    run("--spp", "32", "--out", str(tmp_path / "one.png"))
+    run("--spp", "8", "--frames", "4", "--progressive", "--out", str(tmp_path / "prog.png"))
+    run("--spp", "8", "--frames", "2", "--progressive", "--checkpoint", str(tmp_path / "half.ckpt"), "--out", str(tmp_path / "half.png"))
+    run("--spp", "16", "--resume", str(tmp_path / "half.ckpt"), "--seed", "777", "--out", str(tmp_path / "resumed.png"))   # seed comes from the checkpoint
+    one = np.asarray(Image.open(tmp_path / "one.png"))
+    assert one.mean() > 5
+    np.testing.assert_array_equal(np.asarray(Image.open(tmp_path / "prog.png")), one)
+    np.testing.assert_array_equal(np.asarray(Image.open(tmp_path / "resumed.png")), one)
+    assert not np.array_equal(np.asarray(Image.open(tmp_path / "half.png")), one)
+    # without --progressive every frame restarts with a new seed, as the reference does
+    run("--spp", "8", "--frames", "4", "--out", str(tmp_path / "restart.png"))
+    assert not np.array_equal(np.asarray(Image.open(tmp_path / "restart.png")), one)
+    bad = subprocess.run(base + ["--w", "64", "--spp", "8", "--resume", str(tmp_path / "half.ckpt")], capture_output=True, text=True)
+    assert bad.returncode == 1 and "checkpoint is 128x72" in bad.stderr

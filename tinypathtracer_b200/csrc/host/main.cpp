@@ -11,7 +11,8 @@ int main(int argc, char** argv) {
     std::string scene, env, out;
     int w = 1920, h = 1080, spp = 64, depth = 8, frames = 1;
     unsigned long long seed = 1;
-    bool envNee = false, fullGltf = false;
+    bool envNee = false, fullGltf = false, progressive = false;
+    std::string checkpoint, resume;
     for (int i = 1; i < argc; ++i) {
         const std::string k = argv[i];
         auto val = [&]() -> const char* {
@@ -29,10 +30,13 @@ int main(int argc, char** argv) {
         else if (k == "--seed") seed = std::strtoull(val(), nullptr, 10);
         else if (k == "--env-nee") envNee = true;
         else if (k == "--full-gltf") fullGltf = true;
+        else if (k == "--progressive") progressive = true;
+        else if (k == "--checkpoint") checkpoint = val();
+        else if (k == "--resume") resume = val();
         else { std::fprintf(stderr, "unknown argument %s\n", k.c_str()); return 2; }
     }
     if (scene.empty()) {
-        std::fprintf(stderr, "usage: tpt_render --scene file.gltf [--env sky.png] [--w 1920 --h 1080 --spp 64 --depth 8 --frames 1 --seed 1 --env-nee --full-gltf --out frame.png]\n");
+        std::fprintf(stderr, "usage: tpt_render --scene file.gltf [--env sky.png] [--w 1920 --h 1080 --spp 64 --depth 8 --frames 1 --seed 1 --env-nee --full-gltf --progressive --checkpoint file --resume file --out frame.png]\n");
         return 2;
     }
     try {
@@ -45,8 +49,11 @@ int main(int argc, char** argv) {
         pathTracer.m_seed = seed;
         pathTracer.m_envNEE = envNee;
         if (fullGltf) pathTracer.m_sceneType = "gltf-full";
+        pathTracer.m_progressive = progressive;
+        if (!resume.empty()) pathTracer.loadCheckpoint(resume);   // continues its sample sequence and seed
         pathTracer.m_output = out;
         pathTracer.render(scene);          // src/main.cu:12
+        if (!checkpoint.empty()) pathTracer.saveCheckpoint(checkpoint);
         const tpt_counters c = pathTracer.context().counters();
         std::printf("{\"ms_last_frame\": %.3f, \"samples\": %llu, \"rays\": %llu, \"kernel_launches\": %llu}\n", pathTracer.m_lastFrameMs,
                     (unsigned long long)c.samples, (unsigned long long)(c.rays_primary + c.rays_extension + c.rays_shadow + c.rays_direct),

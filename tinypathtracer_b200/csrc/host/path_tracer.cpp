@@ -38,15 +38,71 @@ PathTracer::~PathTracer() {
     if (m_radiance) tpt_accum_destroy(m_radiance);
 }
 
-// One frame exactly as src/path_tracer.cu:491-554: transform + BVH rebuild, clear, trace, copyToFB.
-void PathTracer::doTrace(DeviceScene& scene, Camera& camera, unsigned char* framebuffer, int nSamplesPerPixel) {
+void PathTracer::ensureAccumulator() {
     if (!m_radiance || m_accW != m_width || m_accH != m_height) {
         if (m_radiance) tpt_accum_destroy(m_radiance);
         m_radiance = nullptr;
         check(tpt_accum_create(m_ctx->handle(), m_width, m_height, &m_radiance), "tpt_accum_create");
         m_accW = m_width;
         m_accH = m_height;
+        m_samplesDone = 0;
     }
+}
+
+namespace {
+struct CheckpointHeader {
+    char magic[8];   // "TPTACC1\0"
+    int32_t width, height;
+    uint64_t samples, seed;
+};
+}   // namespace
+
+void PathTracer::saveCheckpoint(const std::string& file) {
+    if (!m_radiance) throw std::runtime_error("saveCheckpoint: nothing rendered yet");
+    std::vector<int64_t> acc((size_t)m_accW * m_accH * 3);
+    check(tpt_accum_export_i64(m_radiance, acc.data()), "tpt_accum_export_i64");
+    CheckpointHeader h;
+    std::memset(&h, 0, sizeof h);
+    std::memcpy(h.magic, "TPTACC1", 8);
+    h.width = m_accW;
+    h.height = m_accH;
+    h.samples = m_samplesDone;
+    h.seed = m_seed;
+    FILE* f = std::fopen(file.c_str(), "wb");
+    if (!f) throw std::runtime_error("saveCheckpoint: cannot create " + file);
+    const bool ok = std::fwrite(&h, sizeof h, 1, f) == 1 && std::fwrite(acc.data(), sizeof(int64_t), acc.size(), f) == acc.size();
+    std::fclose(f);
+    if (!ok) throw std::runtime_error("saveCheckpoint: short write to " + file);
+}
+
+void PathTracer::loadCheckpoint(const std::string& file) {
+    FILE* f = std::fopen(file.c_str(), "rb");
+    if (!f) throw std::runtime_error("loadCheckpoint: cannot open " + file);
+    CheckpointHeader h;
+    if (std::fread(&h, sizeof h, 1, f) != 1 || std::memcmp(h.magic, "TPTACC1", 8) != 0) {
+        std::fclose(f);
+        throw std::runtime_error("loadCheckpoint: " + file + " is not a checkpoint");
+    }
+    if (h.width != m_width || h.height != m_height) {
+        std::fclose(f);
+        throw std::runtime_error("loadCheckpoint: checkpoint is " + std::to_string(h.width) + "x" + std::to_string(h.height) + ", renderer is " +
+                                 std::to_string(m_width) + "x" + std::to_string(m_height));
+    }
+    std::vector<int64_t> acc((size_t)h.width * h.height * 3);
+    const bool ok = std::fread(acc.data(), sizeof(int64_t), acc.size(), f) == acc.size();
+    std::fclose(f);
+    if (!ok) throw std::runtime_error("loadCheckpoint: truncated checkpoint " + file);
+    ensureAccumulator();
+    check(tpt_accum_import_i64(m_radiance, acc.data()), "tpt_accum_import_i64");
+    m_samplesDone = h.samples;
+    m_seed = h.seed;
+    m_progressive = true;
+}
+
+// One frame exactly as src/path_tracer.cu:491-554: transform + BVH rebuild, clear, trace, copyToFB.  Progressive mode
+// skips the clear, continues the sample sequence and resolves the mean of everything accumulated.
+void PathTracer::doTrace(DeviceScene& scene, Camera& camera, unsigned char* framebuffer, int nSamplesPerPixel) {
+    ensureAccumulator();
     tpt_render_config cfg;
     std::memset(&cfg, 0, sizeof cfg);
     cfg.width = m_width;
@@ -59,7 +115,16 @@ void PathTracer::doTrace(DeviceScene& scene, Camera& camera, unsigned char* fram
     cfg.flags = m_envNEE ? TPT_RENDER_ENV_NEE : 0u;
     const tpt_camera cam = camera.toABI();
     const auto t0 = std::chrono::steady_clock::now();
-    check(tpt_do_trace(scene.handle.get(), &cam, &cfg, m_radiance, framebuffer), "tpt_do_trace");
+    if (!m_progressive) {
+        check(tpt_do_trace(scene.handle.get(), &cam, &cfg, m_radiance, framebuffer), "tpt_do_trace");
+        m_samplesDone = (uint64_t)nSamplesPerPixel;
+    } else {
+        cfg.sample_offset = (uint32_t)m_samplesDone;
+        check(tpt_bvh_build(scene.handle.get(), nullptr), "tpt_bvh_build");
+        check(tpt_render(scene.handle.get(), &cam, &cfg, m_radiance), "tpt_render");
+        m_samplesDone += (uint64_t)nSamplesPerPixel;
+        check(tpt_resolve_bgra8(m_radiance, (int)m_samplesDone, framebuffer, 0), "tpt_resolve_bgra8");
+    }
     m_lastFrameMs = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
 }
 
@@ -73,7 +138,7 @@ void PathTracer::render(const std::string& meshFile) {
     for (int f = 0; f < m_frames; ++f) {
         doTrace(d_scene, camera, fb.data(), m_spp);
         std::printf("1 frame: %.3f ms\n", m_lastFrameMs);     // src/vkEngine.cu:300 prints "1 frame"
-        ++m_seed;
+        if (!m_progressive) ++m_seed;
     }
     if (!m_output.empty()) {
         std::vector<uint8_t> rgb((size_t)m_width * m_height * 3);
