@@ -305,4 +305,17 @@ def test_degenerate_inputs(tpt, ctx, scenes, orc):
         ref = orc.trace_rays(s["vertices"], s["indices"], rays, mode=0)
         assert (got["prim"] == ref["prim"]).all(), (got, ref)      # equal-t ties -> lowest primitive id on both sides
         assert np.allclose(got["t"][ref["prim"] >= 0], ref["t"][ref["prim"] >= 0], rtol=1e-6)
+        # the renderer's three camera-ray forms agree on them too: per-thread candidates (< 32 spp), warp-cooperative
+        # candidates (>= 32 spp), per-sample traversal; equal-t duplicates must resolve to the same primitive in all of them
+        cam = tpt.Camera.from_scene(s)
+        pt = tpt.PathTracer(ctx, 64, 36, env_rgba8=synthetic_sky(64, 32))
+        imgs = []
+        for spp_chunks, cand in (([40], True), ([40], False), ([8] * 5, True)):
+            pt.m_radiance.clear()
+            off = 0
+            for n in spp_chunks:
+                pt.render_into(ds, cam, spp=n, seed=3, sample_offset=off, pixel_candidates=cand)
+                off += n
+            imgs.append(pt.m_radiance.to_i64())
+        assert (imgs[0] == imgs[1]).all() and (imgs[0] == imgs[2]).all() and imgs[0].any()
         ds.close()
