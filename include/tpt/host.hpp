@@ -159,7 +159,7 @@ private:
     std::shared_ptr<tpt_scene> m_scene;
 };
 
-// 8-bit image, top-down rows, 3 or 4 channels (include/picture.h loads through FreeImage; here: PNG and binary PPM).
+// 8-bit image, top-down rows, 3 or 4 channels (include/picture.h loads through FreeImage; here: PNG, baseline JPEG, binary PPM).
 struct Picture {
     int width = 0, height = 0, channels = 0;
     std::vector<uint8_t> pixels;

@@ -238,6 +238,44 @@ def test_png_codecs_round_trip(host, tmp_path):
         np.testing.assert_array_equal(out2, img)
 
 
+def _read_image(host, path):
+    whc = np.zeros(3, np.int32)
+    assert host.tpt_host_read_image(str(path).encode(), None, 0, whc.ctypes.data) == 0, host.tpt_host_last_error().decode()
+    out = np.zeros((whc[1], whc[0], whc[2]), np.uint8)
+    assert host.tpt_host_read_image(str(path).encode(), out.ctypes.data, out.nbytes, whc.ctypes.data) == 0
+    return out
+
+
+def test_jpeg_decoder_agrees_with_an_independent_one(host, tmp_path):
+    """The reference's environment maps are .jpg (src/main.cu:11, README): baseline JPEG decodes to what libjpeg (PIL)
+    gives, up to IDCT rounding (4:4:4, 4:2:2, 4:2:0 with libjpeg's triangle-filter chroma upsampling, grey)."""
+    from PIL import Image
+    rng = np.random.default_rng(5)
+    h, w = 75, 133                                   # not multiples of the MCU size
+    yy, xx = np.mgrid[0:h, 0:w]
+    img = np.stack([128 + 100 * np.sin(xx / 17.0), 128 + 100 * np.cos(yy / 11.0), (xx * 2 + yy * 3) % 256], axis=-1)
+    img = np.clip(img + rng.normal(0, 6, img.shape), 0, 255).astype(np.uint8)
+    cases = [("444.jpg", dict(quality=92, subsampling=0), 4, 0.6), ("420.jpg", dict(quality=90, subsampling=2), 4, 0.6),
+             ("422.jpg", dict(quality=85, subsampling=1), 4, 0.6), ("opt.jpg", dict(quality=75, subsampling=0, optimize=True), 4, 0.6)]
+    for name, kw, max_tol, mean_tol in cases:
+        Image.fromarray(img).save(tmp_path / name, **kw)
+        ref = np.asarray(Image.open(tmp_path / name).convert("RGB")).astype(int)
+        got = _read_image(host, tmp_path / name).astype(int)
+        assert got.shape == ref.shape == (h, w, 3)
+        d = np.abs(got - ref)
+        assert d.max() <= max_tol and d.mean() <= mean_tol, (name, d.max(), d.mean())
+    Image.fromarray(img[..., 0]).save(tmp_path / "grey.jpg", quality=90)
+    got = _read_image(host, tmp_path / "grey.jpg").astype(int)
+    ref = np.asarray(Image.open(tmp_path / "grey.jpg")).astype(int)
+    assert got.shape == (h, w, 3) and np.abs(got[..., 0] - ref).max() <= 4 and (got[..., 0] == got[..., 2]).all()
+    Image.fromarray(img).save(tmp_path / "prog.jpg", progressive=True)
+    whc = np.zeros(3, np.int32)
+    assert host.tpt_host_read_image(str(tmp_path / "prog.jpg").encode(), None, 0, whc.ctypes.data) != 0
+    assert b"progressive JPEG is not supported" in host.tpt_host_last_error()
+    (tmp_path / "trunc.jpg").write_bytes((tmp_path / "444.jpg").read_bytes()[:300])
+    assert host.tpt_host_read_image(str(tmp_path / "trunc.jpg").encode(), None, 0, whc.ctypes.data) != 0
+
+
 @pytest.mark.gpu
 def test_tpt_render_cli_matches_the_python_binding(tpt, ctx, scenes, tmp_path):
     """src/main.cu's PathTracer(env).render(gltf) through the C++ classes: same seed -> the same framebuffer, byte for byte,
