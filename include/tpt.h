@@ -125,6 +125,7 @@ typedef struct tpt_render_config {
 #define TPT_RENDER_STAGE_TIMES 2u /* CUDA-event time of every wavefront kernel, summed per stage (one sync per batch) */
 #define TPT_RENDER_NO_PIXEL_CANDIDATES 8u /* check switch: camera samples walk the tree one by one instead of testing their
                                            * pixel's candidate triangles; the accumulation buffer is bit-identical either way */
+#define TPT_RENDER_REFIT 16u      /* tpt_do_trace only: refit (tpt_bvh_refit) instead of rebuilding when the scene has a hierarchy */
 #define TPT_RENDER_ENV_NEE 4u     /* sample the environment map from its alias table at every diffuse vertex (one extra shadow ray),
                                    * combined with the reference's cosine-sampled misses by the balance heuristic: same expectation as
                                    * the default estimator, lower variance under maps with small bright regions.  Off by default: the
@@ -185,6 +186,12 @@ int tpt_scene_set_transforms(tpt_scene* scene, const float* vert_trans, const fl
  * (src/bvh.cu:304-331, called :541-542): object->world vertices/normals, Morton keys, radix sort,
  * hierarchy, refit.  Asynchronous when stats == NULL. */
 int tpt_bvh_build(tpt_scene* scene, tpt_bvh_stats* stats);
+/* After tpt_scene_set_transforms on an unchanged mesh: keep the hierarchy of the last tpt_bvh_build (leaf order, children,
+ * parents) and redo only what depends on the matrices — object->world transform, triangle/normal records, bottom-up boxes.
+ * The reference has no such call (it rebuilds per frame, src/path_tracer.cu:540-542).  Hits are those of a
+ * rebuild (the boxes are exact again and the closest hit under the tie rule does not depend on the tree); tree quality follows
+ * the motion.  TPT_ERR_STATE when the scene was never built.  Asynchronous when stats == NULL. */
+int tpt_bvh_refit(tpt_scene* scene, tpt_bvh_stats* stats);
 /* Structural export in the reference's layout (include/bvh.cuh:34-58, 36-byte BVHNode, internal nodes
  * [0,F-1) then leaves [F-1,2F-1), child indices global, leaf k holds its face id): n_nodes must be 2F-1. */
 int tpt_bvh_export_reference_nodes(tpt_scene* scene, void* out_nodes36, size_t n_nodes);

@@ -116,6 +116,9 @@ struct DeviceScene {
     std::vector<DeltaLight> lights;
     std::shared_ptr<tpt_scene> handle;   // tpt_scene_create / tpt_scene_destroy
     size_t nFaces() const { return indices.size() / 3; }
+    // push the current vertTrans / normalTrans to the device (the reference re-reads them every frame, src/path_tracer.cu:536-537);
+    // follow with BVH::construct() or BVH::refit()
+    void uploadTransforms();
 };
 
 class Scene {
@@ -152,6 +155,8 @@ public:
     explicit BVH(DeviceScene& scene) : m_scene(scene.handle) {}
     void construct();                       // `transform` kernel + BVH::construct of the reference
     tpt_bvh_stats constructWithStats();
+    void refit();                           // after new object matrices on the same mesh: keeps the hierarchy
+    tpt_bvh_stats refitWithStats();
     std::vector<BVHNode36> exportReferenceLayout(size_t nFaces);
     void traceRays(const tpt_ray* rays, size_t n, tpt_hit* hits, bool anyHit = false);   // host buffers
 

@@ -83,6 +83,7 @@ SIGNATURES = {
     "tpt_scene_destroy": (C.c_int, [C.c_void_p]),
     "tpt_scene_set_transforms": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "tpt_bvh_build": (C.c_int, [C.c_void_p, C.POINTER(BvhStats)]),
+    "tpt_bvh_refit": (C.c_int, [C.c_void_p, C.POINTER(BvhStats)]),
     "tpt_bvh_export_reference_nodes": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
     "tpt_scene_export_world": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "tpt_env_set_rgba8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),

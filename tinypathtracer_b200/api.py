@@ -172,14 +172,19 @@ class BVH:
         self.scene = scene
         self.stats = None
 
-    def construct(self, stats: bool = True):
+    def refit(self, stats: bool = True):
+        """After DeviceScene.set_transforms: reuse the hierarchy of the last construct(), redo transform + leaf records + boxes."""
+        return self.construct(stats, _fn=lib.tpt_bvh_refit)
+
+    def construct(self, stats: bool = True, _fn=None):
+        build = _fn or lib.tpt_bvh_build
         if stats:
             st = capi.BvhStats()
-            check(lib.tpt_bvh_build(self.scene._h, C.byref(st)))
+            check(build(self.scene._h, C.byref(st)))
             self.stats = dict(build_ms=st.build_ms, n_faces=st.n_faces, n_nodes=st.n_nodes, max_depth=st.max_depth,
                               sah_cost=st.sah_cost, bounds_min=tuple(st.bounds_min), bounds_max=tuple(st.bounds_max))
         else:
-            check(lib.tpt_bvh_build(self.scene._h, None))
+            check(build(self.scene._h, None))
         return self.stats
 
     @property

@@ -415,6 +415,33 @@ int tpt_bvh_build_impl(tpt_scene* s) {
     TPT_CUDA(cudaGetLastError());
     ctx->kernel_launches += 6 + 8;   // + radix sort passes (library, counted nominally)
     s->built = true;
+    s->topology = true;
+    return TPT_OK;
+}
+
+// Refit: new object->world matrices (tpt_scene_set_transforms) on an unchanged mesh.  The reference rebuilds everything per
+// frame (src/path_tracer.cu:540-542); here the sorted leaf order, children, parents and range ends of the last full build are
+// kept and only the geometry-dependent part runs again: transform, triangle/normal records, bottom-up boxes.  No Morton keys,
+// no sort, no hierarchy.  The boxes are again the exact bounds of their triangles, so traversal results are those of a rebuild
+// (closest hit under the tie rule does not depend on the tree shape); only the tree quality can drift with large motion.
+int tpt_bvh_refit_impl(tpt_scene* s) {
+    tpt_context* ctx = s->ctx;
+    cudaStream_t st = ctx->stream;
+    const int F = (int)s->n_faces;
+    const uint32_t V = (uint32_t)s->n_vertices;
+    const int persistent = kNumSMs * 8;
+    k_init_bounds<<<1, 32, 0, st>>>(s->bounds);
+    k_transform<<<min(persistent, (int)grid_for(V, 256)), 256, 0, st>>>(s->obj_verts, s->obj_norms, s->vert_obj, s->vert_trans,
+                                                                         s->normal_trans, V, s->world_verts, s->world_norms, s->bounds);
+    if (F > 1) TPT_CUDA(cudaMemsetAsync(s->flags, 0, (size_t)(F - 1) * sizeof(uint32_t), st));
+    int* frontier = reinterpret_cast<int*>(s->keys[0]);
+    k_leaves_refit<<<grid_for(F, kRefitBlock), kRefitBlock, 0, st>>>(s->vals[1], s->indices, s->world_verts, s->world_norms, s->face_mtl, F,
+                                                                     s->parent_int, s->parent_leaf, reinterpret_cast<const int*>(s->vals[0]),
+                                                                     s->flags, s->nodes, s->tri_geom, s->tri_norm, frontier, s->bounds + 6);
+    if (F > 1) k_refit_upper<<<grid_for((size_t)F / 2 + 1, 256), 256, 0, st>>>(frontier, s->bounds + 6, s->parent_int, s->flags, s->nodes);
+    TPT_CUDA(cudaGetLastError());
+    ctx->kernel_launches += 4;
+    s->built = true;
     return TPT_OK;
 }
 

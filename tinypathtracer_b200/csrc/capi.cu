@@ -28,6 +28,7 @@ using namespace tpt;
 // implemented in bvh.cu / render.cu
 int tpt_scene_build_tables(tpt_scene* s);
 int tpt_bvh_build_impl(tpt_scene* s);
+int tpt_bvh_refit_impl(tpt_scene* s);
 int tpt_bvh_stats_impl(tpt_scene* s, tpt_bvh_stats* stats);
 int tpt_bvh_export_reference_impl(tpt_scene* s, void* out, size_t nNodes);
 int tpt_primary_rays_impl(tpt_context* ctx, const tpt_camera* cam, int W, int H, int jitter, uint64_t seed, tpt_ray* d_rays);
@@ -295,6 +296,26 @@ int tpt_bvh_build(tpt_scene* s, tpt_bvh_stats* stats) {
     return TPT_OK;
 }
 
+int tpt_bvh_refit(tpt_scene* s, tpt_bvh_stats* stats) {
+    TPT_REQUIRE(s, "tpt_bvh_refit: scene is NULL");
+    if (!s->topology) {
+        set_error("tpt_bvh_refit: no hierarchy to reuse, call tpt_bvh_build first");
+        return TPT_ERR_STATE;
+    }
+    tpt_context* ctx = s->ctx;
+    TPT_CHECK(bind(ctx));
+    if (stats) TPT_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
+    TPT_CHECK(tpt_bvh_refit_impl(s));
+    if (stats) {
+        TPT_CUDA(cudaEventRecord(ctx->ev1, ctx->stream));
+        TPT_CUDA(cudaEventSynchronize(ctx->ev1));
+        memset(stats, 0, sizeof *stats);
+        TPT_CHECK(tpt_bvh_stats_impl(s, stats));
+        TPT_CUDA(cudaEventElapsedTime(&stats->build_ms, ctx->ev0, ctx->ev1));
+    }
+    return TPT_OK;
+}
+
 int tpt_bvh_export_reference_nodes(tpt_scene* s, void* out_nodes36, size_t n_nodes) {
     TPT_REQUIRE(s && out_nodes36, "tpt_bvh_export_reference_nodes: NULL argument");
     if (!s->built) {
@@ -536,7 +557,8 @@ int tpt_resolve_bgra8(tpt_accum* a, int spp_total, uint8_t* fb, int device_ptr) 
 
 int tpt_do_trace(tpt_scene* s, const tpt_camera* cam, const tpt_render_config* cfg, tpt_accum* acc, uint8_t* host_fb) {
     TPT_REQUIRE(s && cam && cfg && acc && host_fb, "tpt_do_trace: NULL argument");
-    TPT_CHECK(tpt_bvh_build(s, nullptr));
+    if ((cfg->flags & TPT_RENDER_REFIT) && s->topology) TPT_CHECK(tpt_bvh_refit(s, nullptr));
+    else TPT_CHECK(tpt_bvh_build(s, nullptr));
     TPT_CHECK(tpt_accum_clear(acc));
     TPT_CHECK(tpt_render(s, cam, cfg, acc));
     return tpt_resolve_bgra8(acc, cfg->spp, host_fb, 0);

@@ -494,11 +494,26 @@ DeviceScene Scene::copySceneToDevice(Context& ctx) const {
     return d;
 }
 
+void DeviceScene::uploadTransforms() {
+    if (!handle) throw std::runtime_error("DeviceScene::uploadTransforms: scene is not on a device");
+    if (vertTrans.size() != materialsLUT.size() || normalTrans.size() != materialsLUT.size())
+        throw std::runtime_error("DeviceScene::uploadTransforms: one matrix pair per object expected");
+    check(tpt_scene_set_transforms(handle.get(), reinterpret_cast<const float*>(vertTrans.data()),
+                                   reinterpret_cast<const float*>(normalTrans.data())),
+          "tpt_scene_set_transforms");
+}
+
 // ---- BVH -------------------------------------------------------------------------------------------------------
 void BVH::construct() { check(tpt_bvh_build(m_scene.get(), nullptr), "tpt_bvh_build"); }
 tpt_bvh_stats BVH::constructWithStats() {
     tpt_bvh_stats st;
     check(tpt_bvh_build(m_scene.get(), &st), "tpt_bvh_build");
+    return st;
+}
+void BVH::refit() { check(tpt_bvh_refit(m_scene.get(), nullptr), "tpt_bvh_refit"); }
+tpt_bvh_stats BVH::refitWithStats() {
+    tpt_bvh_stats st;
+    check(tpt_bvh_refit(m_scene.get(), &st), "tpt_bvh_refit");
     return st;
 }
 std::vector<BVHNode36> BVH::exportReferenceLayout(size_t nFaces) {

@@ -102,6 +102,7 @@ struct tpt_scene {
     float4* tri_geom = nullptr;
     float4* tri_norm = nullptr;
     bool built = false;
+    bool topology = false;        // hierarchy (children, parents, leaf order, range ends) of the last full build is intact: tpt_bvh_refit may reuse it
     bool any_emissive = false;    // some material has emission > 0 (else the reference's extra "direct" rays add nothing and are not traced)
     tpt::BvhView view() const { return tpt::BvhView{nodes, tri_geom, tri_norm, (int)n_faces}; }
 };
