@@ -202,6 +202,10 @@ int tpt_scene_export_world(tpt_scene* scene, float* world_vertices, float* world
  * rgba8: host pointer, w*h*4 bytes, row 0 = BOTTOM scanline (FreeImage order), RGBA.  The lookup is the
  * reference's tex2DLod point/clamp/normalised fetch (src/path_tracer.cu:288-294). */
 int tpt_env_set_rgba8(tpt_context* ctx, const uint8_t* rgba8, int width, int height);
+/* HDR environment (the reference's Texture is 8-bit only, src/texture.cu:79-82): linear float RGB, host pointer,
+ * w*h*3 floats, row 0 = BOTTOM scanline, same lat-long lookup.  Texels must be finite and in [0, 65536] (TPT_ERR_INVALID
+ * otherwise).  Replaces a map set by tpt_env_set_rgba8 and vice versa. */
+int tpt_env_set_rgb32f(tpt_context* ctx, const float* rgb, int width, int height);
 int tpt_env_clear(tpt_context* ctx); /* black environment (the reference's no-env case is UB) */
 /* Replaces EnvLightSample / EnvLightPDF (include/env_light.cuh:21-70, no call site in the reference): draws n directions
  * from the map's luminance*sin(theta) distribution with the device alias tables; dirs_pdf is a HOST buffer of n*4 floats

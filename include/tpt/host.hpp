@@ -173,6 +173,17 @@ struct Picture {
 };
 void writePNG(const std::string& filename, const uint8_t* rgba, int width, int height, int channels);
 
+// Float image, top-down rows, linear RGB (HDR environment maps and float dumps of the accumulation buffer; the
+// reference's Picture/Texture are 8-bit only).  Reads Radiance RGBE (.hdr, flat or run-length coded scanlines) and PFM.
+struct PictureF {
+    int width = 0, height = 0;
+    std::vector<float> pixels;   // width * height * 3
+    PictureF() = default;
+    explicit PictureF(const std::string& filename);
+    static bool isFloatFile(const std::string& filename);   // by magic: "#?" (Radiance) or "PF"/"Pf"
+};
+void writePFM(const std::string& filename, const float* rgbTopDown, int width, int height);   // little-endian "PF"
+
 class EnvLight {
 public:
     EnvLight(Context& ctx, const std::string& file);   // "" -> black environment (the reference: uninitialised texture)
@@ -201,6 +212,7 @@ public:
     std::string m_sceneType = "gltf";   // "gltf" = the reference's loader; "gltf-full" = scene graph, all primitives (Scene)
     bool m_envNEE = false;   // TPT_RENDER_ENV_NEE: sample the environment map at diffuse vertices (same expectation, lower variance)
     std::string m_output;
+    std::string m_outputFloat;   // PFM of the linear mean radiance (accumulator / samples), unclamped; empty = none
     double m_lastFrameMs = 0.0;
     Context& context() { return *m_ctx; }
 

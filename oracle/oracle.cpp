@@ -610,13 +610,19 @@ inline void vec2uv(V3 d, float& u, float& v) {
 // path_tracer.cu:288-294 + texture.cu:160-168: tex2DLod<uchar4>, normalised coordinates, point
 // filter, clamp addressing, level 0: texel = clamp(floor(u*W)), clamp(floor(v*H)).  Row 0 of the
 // texture is the bottom scanline of the file (FreeImage is bottom-up, include/picture.h:41-42).
-inline V3 sample_env(const uint8_t* rgba, int ew, int eh, V3 dir) {
-    if (!rgba) return v3(0, 0, 0);
+// `rgbf` (not in the reference, whose Texture is 8-bit only): linear float RGB, 3 floats per texel, same lookup — the HDR
+// maps of SURVEY §8f-2.
+inline V3 sample_env(const uint8_t* rgba, int ew, int eh, V3 dir, const float* rgbf = nullptr) {
+    if (!rgba && !rgbf) return v3(0, 0, 0);
     float u, v;
     vec2uv(dir, u, v);
     int x = (int)floorf(u * (float)ew), y = (int)floorf(v * (float)eh);
     x = std::min(std::max(x, 0), ew - 1);
     y = std::min(std::max(y, 0), eh - 1);
+    if (rgbf) {
+        const float* t = rgbf + 3 * ((size_t)y * ew + x);
+        return v3(t[0], t[1], t[2]);
+    }
     const uint8_t* t = rgba + 4 * ((size_t)y * ew + x);
     return v3((float)t[0], (float)t[1], (float)t[2]) / 255.0f;
 }
@@ -635,6 +641,7 @@ struct SceneView {
     const RefNode* nodes;
     const uint8_t* env;
     int ew, eh;
+    const float* envf = nullptr;   // float RGB map instead of `env` (HDR)
 };
 
 struct Counters {
@@ -668,7 +675,7 @@ V3 trace_sample(const SceneView& S, const Camera& cam, int px, int py, int W, in
         Hit status = no_hit();
         traverse(ray, status);
         if (status.idx < 0) {
-            radiance = sample_env(S.env, S.ew, S.eh, ray.d);
+            radiance = sample_env(S.env, S.ew, S.eh, ray.d, S.envf);
             break;
         }
         uint32_t i0 = S.indices[status.idx * 3 + 0], i1 = S.indices[status.idx * 3 + 1], i2 = S.indices[status.idx * 3 + 2];
@@ -951,13 +958,25 @@ int orc_retest_triangle(const float* wverts, const uint32_t* indices, int fid, c
 // order exactly as the kernel does (totalRad += radiance; color += totalRad).
 // Region [x0,x1) x [y0,y1) only (bounded CPU samples); pixels outside are left untouched.
 // counters (optional): [rays, nInt, nLeaf].
+void orc_render_env(const uint32_t* indices, int F, const float* wverts, const float* wnormals, const void* materials, int M,
+                    const void* lut, int O, const void* lights, int L, const void* nodes36, const uint8_t* env, const float* envf,
+                    int ew, int eh, const float* cam19, int W, int H, int x0, int y0, int x1, int y1, int spp, int sampleOffset,
+                    int sampleStride, int maxDepth, uint64_t seed, float* out, uint64_t* counters);
 void orc_render(const uint32_t* indices, int F, const float* wverts, const float* wnormals, const void* materials, int M,
                 const void* lut, int O, const void* lights, int L, const void* nodes36, const uint8_t* env, int ew, int eh,
                 const float* cam19, int W, int H, int x0, int y0, int x1, int y1, int spp, int sampleOffset, int sampleStride,
                 int maxDepth, uint64_t seed, float* out, uint64_t* counters) {
+    orc_render_env(indices, F, wverts, wnormals, materials, M, lut, O, lights, L, nodes36, env, nullptr, ew, eh, cam19, W, H, x0, y0,
+                   x1, y1, spp, sampleOffset, sampleStride, maxDepth, seed, out, counters);
+}
+// the same with either texel format of the environment: `env` RGBA8 (the reference's) or `envf` float RGB (HDR)
+void orc_render_env(const uint32_t* indices, int F, const float* wverts, const float* wnormals, const void* materials, int M,
+                    const void* lut, int O, const void* lights, int L, const void* nodes36, const uint8_t* env, const float* envf,
+                    int ew, int eh, const float* cam19, int W, int H, int x0, int y0, int x1, int y1, int spp, int sampleOffset,
+                    int sampleStride, int maxDepth, uint64_t seed, float* out, uint64_t* counters) {
     SceneView S{indices, F, wverts, wnormals, reinterpret_cast<const Material*>(materials), M,
                 reinterpret_cast<const MtlInterval*>(lut), O, reinterpret_cast<const DeltaLight*>(lights), L,
-                reinterpret_cast<const RefNode*>(nodes36), env, ew, eh};
+                reinterpret_cast<const RefNode*>(nodes36), env, ew, eh, envf};
     Camera cam;
     cam.vfov = cam19[0]; cam.aspect = cam19[1]; cam.nearPlane = cam19[2];
     std::memcpy(cam.c2w, cam19 + 3, 64);

@@ -62,6 +62,9 @@ def lib() -> C.CDLL:
         L.orc_render.argtypes = ([C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int,
                                   C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
                                  + [C.c_int] * 10 + [C.c_uint64, C.c_void_p, C.c_void_p])
+        L.orc_render_env.argtypes = ([C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int,
+                                      C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+                                     + [C.c_int] * 10 + [C.c_uint64, C.c_void_p, C.c_void_p])
         L.orc_resolve_bgra8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
         L.orc_sample_env.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         _lib = L
@@ -230,15 +233,21 @@ def render(scene: dict, W: int, H: int, spp: int, max_depth: int = 8, seed: int 
     x0, y0, x1, y1 = region if region is not None else (0, 0, W, H)
     ew = eh = 0
     envp = None
-    if env is not None:
+    envfp = None
+    if env is not None and np.asarray(env).dtype.kind == "f":      # HDR: linear float RGB [h, w, 3]
+        env = np.ascontiguousarray(env, np.float32)
+        assert env.ndim == 3 and env.shape[2] == 3
+        eh, ew = env.shape[:2]
+        envfp = _p(env)
+    elif env is not None:
         env = np.ascontiguousarray(env, np.uint8)
         eh, ew = env.shape[:2]
         envp = _p(env)
     cnt = np.zeros(3, np.uint64)
     F = scene["indices"].size // 3
-    lib().orc_render(_p(scene["indices"]), F, _p(wv), _p(wn), _p(scene["materials"]), scene["materials"].shape[0],
+    lib().orc_render_env(_p(scene["indices"]), F, _p(wv), _p(wn), _p(scene["materials"]), scene["materials"].shape[0],
                      _p(scene["objects"]), scene["objects"].shape[0], _p(scene["lights"]), scene["lights"].shape[0],
-                     _p(nodes), envp, ew, eh, _p(camera19(scene)), W, H, x0, y0, x1, y1, spp, sample_offset, sample_stride,
+                     _p(nodes), envp, envfp, ew, eh, _p(camera19(scene)), W, H, x0, y0, x1, y1, spp, sample_offset, sample_stride,
                      max_depth, seed, _p(out), _p(cnt) if counters else None)
     return (out, cnt) if counters else out
 

@@ -164,3 +164,85 @@ def test_default_render_ignores_sampler_state(tpt, ctx, built, scenes):
     pt.m_radiance.clear()
     pt.render_into(ds, cam, spp=8, seed=2)
     assert (pt.m_radiance.to_i64() == a).all()
+
+
+# ---- HDR (float) environment maps: tpt_env_set_rgb32f, SURVEY §8f-2 ---------------------------------------------------
+def hdr_sky(w=128, h=64):
+    """Linear float map with a sun 300x the 8-bit ceiling (what an 8-bit map cannot hold)."""
+    img = np.zeros((h, w, 3), np.float32)
+    img[...] = (0.05, 0.07, 0.12)
+    img[h // 2:] = (0.25, 0.45, 0.9)
+    img[int(h * 0.70):int(h * 0.76), int(w * 0.10):int(w * 0.13)] = (300.0, 270.0, 220.0)
+    return img
+
+
+def test_float_map_with_8bit_values_gives_the_8bit_maps_bits(tpt, ctx, built, scenes):
+    """A float map holding exactly u8 * (1/255) (one fp32 product, what the RGBA8 lookup computes) must render the same
+    accumulator bits as the RGBA8 map: the two texel formats share one lookup."""
+    ds, _ = built["ball"]
+    cam = tpt.Camera.from_scene(scenes["ball"])
+    sky8 = synthetic_sky(128, 64)
+    skyf = sky8[..., :3].astype(np.float32) * np.float32(1.0 / 255.0)
+    W, H = 96, 54
+    pa = tpt.PathTracer(ctx, W, H, env_rgba8=sky8)
+    pa.render_into(ds, cam, spp=40, seed=4)
+    a = pa.m_radiance.to_i64()
+    pb = tpt.PathTracer(ctx, W, H, env_rgba8=skyf)
+    pb.render_into(ds, cam, spp=40, seed=4)
+    assert (pb.m_radiance.to_i64() == a).all() and a.any()
+    # and switching back replaces the float map
+    pc = tpt.PathTracer(ctx, W, H, env_rgba8=sky8)
+    pc.render_into(ds, cam, spp=40, seed=4)
+    assert (pc.m_radiance.to_i64() == a).all()
+
+
+@pytest.mark.parametrize("name", ["ball", "box2"])
+def test_hdr_map_render_vs_oracle(name, tpt, ctx, built, scenes, orc):
+    """Same RNG on both sides (as test_render_same_rng_vs_oracle) under a float map with a 300x sun."""
+    ds, _ = built[name]
+    env = hdr_sky()
+    W, H, spp = 96, 54, 32
+    pt = tpt.PathTracer(ctx, W, H, env_rgba8=env)
+    pt.render_into(ds, tpt.Camera.from_scene(scenes[name]), spp=spp, max_depth=8, seed=11)
+    img = pt.m_radiance.to_f32() / spp
+    ref = orc.render(scenes[name], W, H, spp, max_depth=8, seed=11, env=env) / spp
+    assert np.isfinite(img).all() and img.max() > 2.0          # values above the 8-bit ceiling reach the image
+    err = _relmse(img, ref)
+    assert err <= 2e-2, f"{name}: rel-MSE at {spp} spp with shared RNG under an HDR map = {err:.3e}"
+    assert ctx.counters()["dropped_nonfinite"] == 0
+
+
+def test_hdr_map_sampler_and_nee(tpt, ctx, built, scenes):
+    """Alias tables are built from the float texels (mass = luminance * sin(theta)); NEE keeps the expectation under the HDR sun
+    and cuts the error at equal spp."""
+    env = hdr_sky()
+    el = tpt.EnvLight(ctx, env)
+    _, _, mass = el.sampler_tables()
+    lum = 0.2126 * env[..., 0].astype(np.float64) + 0.7152 * env[..., 1] + 0.0722 * env[..., 2]
+    theta = (1.0 - (np.arange(env.shape[0]) + 0.5) / env.shape[0]) * np.pi
+    want = lum * np.sin(theta)[:, None]
+    want /= want.sum()
+    np.testing.assert_allclose(mass, want, rtol=2e-5, atol=1e-12)
+    ds, _ = built["ball"]
+    cam = tpt.Camera.from_scene(scenes["ball"])
+    W, H = 64, 36
+    pt = tpt.PathTracer(ctx, W, H, env_rgba8=env)
+
+    def img(spp, seed, nee):
+        pt.m_radiance.clear()
+        pt.render_into(ds, cam, spp=spp, max_depth=8, seed=seed, env_nee=nee)
+        return pt.m_radiance.to_f32() / spp
+
+    ref = img(1 << 18, 5, False)                 # the reference's estimator; the sun makes it converge slowly
+    nee = img(1 << 16, 6, True)
+    assert _relmse(nee, ref) <= 3e-3
+    assert _relmse(img(64, 7, True), ref) < 0.5 * _relmse(img(64, 7, False), ref)
+
+
+def test_float_map_rejects_bad_texels(tpt, ctx):
+    bad = hdr_sky(16, 8)
+    for v in (np.nan, np.inf, -1.0, 1e6):
+        b = bad.copy()
+        b[3, 5, 1] = v
+        with pytest.raises(tpt.TptError):
+            tpt.EnvLight(ctx, b)

@@ -337,3 +337,131 @@ def test_progressive_frames_and_checkpoint_resume_equal_one_shot(tmp_path):
     assert not np.array_equal(np.asarray(Image.open(tmp_path / "restart.png")), one)
     bad = subprocess.run(base + ["--w", "64", "--spp", "8", "--resume", str(tmp_path / "half.ckpt")], capture_output=True, text=True)
     assert bad.returncode == 1 and "checkpoint is 128x72" in bad.stderr
+
+
+# ---- float images: Radiance .hdr and PFM --------------------------------------------------------------
+def _read_f32(host, path):
+    host.tpt_host_read_image_f32.argtypes = [C.c_char_p, C.c_void_p, C.c_size_t, C.c_void_p]
+    wh = np.zeros(2, np.int32)
+    assert host.tpt_host_read_image_f32(str(path).encode(), None, 0, wh.ctypes.data) == 0, host.tpt_host_last_error().decode()
+    out = np.zeros((wh[1], wh[0], 3), np.float32)
+    assert host.tpt_host_read_image_f32(str(path).encode(), out.ctypes.data, out.size, wh.ctypes.data) == 0
+    return out
+
+
+def _rgbe_to_float(rgbe):
+    """rgbe.c convention (the one FreeImage's HDR plugin uses): mantissa * 2^(e - 136), e = 0 -> 0."""
+    e = rgbe[..., 3].astype(np.int32)
+    f = np.where(e > 0, np.ldexp(np.float32(1.0), e - 136), np.float32(0.0)).astype(np.float32)
+    return rgbe[..., :3].astype(np.float32) * f[..., None]
+
+
+def _rle_channel(vals):
+    """Radiance new-style run-length coding of one channel of one scanline."""
+    out, i, n = bytearray(), 0, len(vals)
+    while i < n:
+        run = 1
+        while i + run < n and run < 127 and vals[i + run] == vals[i]:
+            run += 1
+        if run >= 4:
+            out += bytes([128 + run, vals[i]])
+            i += run
+        else:
+            j = i
+            while j < n and j - i < 128:
+                r = 1
+                while j + r < n and r < 4 and vals[j + r] == vals[j]:
+                    r += 1
+                if r >= 4:
+                    break
+                j += 1
+            out += bytes([j - i]) + bytes(vals[i:j])
+            i = j
+    return bytes(out)
+
+
+def test_radiance_hdr_reader_flat_and_rle(host, tmp_path):
+    rng = np.random.default_rng(5)
+    W, H = 67, 19
+    rgbe = rng.integers(0, 256, (H, W, 4), dtype=np.uint8)
+    rgbe[..., 3] = rng.integers(100, 150, (H, W))          # exponents around 1.0
+    rgbe[2, 5:40] = (200, 100, 50, 140)                    # long runs, so the RLE path sees both kinds of packet
+    rgbe[7, :, 3] = 0                                      # e = 0 -> black
+    rgbe[9, 10:30, 0] = 77
+    want = _rgbe_to_float(rgbe)
+    hdr = b"#?RADIANCE\n# made by the test\nFORMAT=32-bit_rle_rgbe\nEXPOSURE=1.0\n\n-Y %d +X %d\n" % (H, W)
+    flat = tmp_path / "flat.hdr"
+    flat.write_bytes(hdr + rgbe.tobytes())
+    np.testing.assert_array_equal(_read_f32(host, flat), want)
+    body = bytearray()
+    for y in range(H):
+        body += bytes([2, 2, W >> 8, W & 255])
+        for c in range(4):
+            body += _rle_channel(rgbe[y, :, c].tolist())
+    rle = tmp_path / "rle.hdr"
+    rle.write_bytes(hdr + bytes(body))
+    assert len(body) < rgbe.nbytes + 4 * H + H * W // 16    # it really is run-length coded
+    np.testing.assert_array_equal(_read_f32(host, rle), want)
+    # errors are exceptions (-> -1 + message through the C hook)
+    (tmp_path / "cut.hdr").write_bytes(hdr + bytes(body[:len(body) // 2]))
+    wh = np.zeros(2, np.int32)
+    assert host.tpt_host_read_image_f32(str(tmp_path / "cut.hdr").encode(), None, 0, wh.ctypes.data) == -1
+    assert b"truncated" in host.tpt_host_last_error()
+    (tmp_path / "fmt.hdr").write_bytes(hdr.replace(b"rle_rgbe", b"rle_xyze") + rgbe.tobytes())
+    assert host.tpt_host_read_image_f32(str(tmp_path / "fmt.hdr").encode(), None, 0, wh.ctypes.data) == -1
+
+
+def test_pfm_round_trip_and_foreign_files(host, tmp_path):
+    host.tpt_host_write_pfm.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_int]
+    rng = np.random.default_rng(6)
+    img = (rng.random((23, 41, 3), dtype=np.float32) * 1000.0).astype(np.float32)
+    p = tmp_path / "a.pfm"
+    assert host.tpt_host_write_pfm(str(p).encode(), img.ctypes.data, 41, 23) == 0
+    raw = p.read_bytes()
+    assert raw.startswith(b"PF\n41 23\n-1.0\n")
+    body = np.frombuffer(raw[len(b"PF\n41 23\n-1.0\n"):], "<f4").reshape(23, 41, 3)
+    np.testing.assert_array_equal(body[::-1], img)          # PFM rows run bottom to top
+    np.testing.assert_array_equal(_read_f32(host, p), img)
+    # big-endian colour and little-endian grey files from another writer
+    (tmp_path / "be.pfm").write_bytes(b"PF\n41 23\n1.0\n" + img[::-1].astype(">f4").tobytes())
+    np.testing.assert_array_equal(_read_f32(host, tmp_path / "be.pfm"), img)
+    grey = img[..., 0]
+    (tmp_path / "g.pfm").write_bytes(b"Pf\n41 23\n-1.0\n" + grey[::-1].astype("<f4").tobytes())
+    np.testing.assert_array_equal(_read_f32(host, tmp_path / "g.pfm"), np.repeat(grey[..., None], 3, axis=2))
+
+
+@pytest.mark.gpu
+def test_cli_hdr_environment_and_float_output(tpt, ctx, scenes, tmp_path):
+    """tpt_render --env sky.hdr --out-float frame.pfm: the Radiance map reaches the device as float texels (same accumulator as
+    the binding given the decoded floats) and the PFM holds the unclamped linear mean radiance."""
+    import subprocess
+    exe = ROOT / "tinypathtracer_b200" / "lib" / "tpt_render"
+    src = next((d / "ball.gltf" for d in GLTF_DIRS if (d / "ball.gltf").exists()), None)
+    if src is None:
+        pytest.skip("no .gltf inputs on this machine")
+    rng = np.random.default_rng(8)
+    EW, EH = 64, 32
+    rgbe = np.zeros((EH, EW, 4), np.uint8)
+    rgbe[..., :3] = rng.integers(64, 256, (EH, EW, 3))
+    rgbe[..., 3] = 127                                       # mantissa / 512: a dim sky
+    rgbe[4:8, 20:24] = (255, 240, 200, 138)                  # sun, top-down rows: ~1000
+    env_file = tmp_path / "sky.hdr"
+    env_file.write_bytes(b"#?RADIANCE\nFORMAT=32-bit_rle_rgbe\n\n-Y %d +X %d\n" % (EH, EW) + rgbe.tobytes())
+    env = _rgbe_to_float(rgbe)[::-1].copy()                  # the device map is bottom-up
+    W, H, spp = 128, 72, 16
+    out = tmp_path / "frame.pfm"
+    r = subprocess.run([str(exe), "--scene", str(src), "--env", str(env_file), "--w", str(W), "--h", str(H), "--spp", str(spp), "--seed", "4",
+                        "--out-float", str(out)], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    raw = out.read_bytes()
+    head = b"PF\n%d %d\n-1.0\n" % (W, H)
+    assert raw.startswith(head)
+    got = np.frombuffer(raw[len(head):], "<f4").reshape(H, W, 3)       # bottom-up, like the accumulator
+    ds = tpt.DeviceScene(ctx, scenes["ball"])
+    tpt.BVH(ds).construct()
+    pt = tpt.PathTracer(ctx, W, H, env_rgba8=env)
+    pt.render_into(ds, tpt.Camera.from_scene(scenes["ball"]), spp=spp, max_depth=8, seed=4)
+    want = pt.m_radiance.to_f32() * np.float32(1.0 / spp)
+    ds.close()
+    np.testing.assert_array_equal(got, want)
+    assert got.max() > 1.5                                   # above anything an 8-bit map or framebuffer can hold

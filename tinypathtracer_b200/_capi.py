@@ -87,6 +87,7 @@ SIGNATURES = {
     "tpt_bvh_export_reference_nodes": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
     "tpt_scene_export_world": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "tpt_env_set_rgba8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
+    "tpt_env_set_rgb32f": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
     "tpt_env_clear": (C.c_int, [C.c_void_p]),
     "tpt_env_sample": (C.c_int, [C.c_void_p, C.c_size_t, C.c_uint64, C.c_void_p]),
     "tpt_env_sampler_tables": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),

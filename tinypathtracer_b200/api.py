@@ -213,12 +213,17 @@ class BVH:
 
 
 class EnvLight:
-    """include/env_light.cuh:9-19: RGBA8 radiance texture, row 0 = bottom scanline."""
+    """include/env_light.cuh:9-19: RGBA8 radiance texture, row 0 = bottom scanline; or a linear float RGB
+    map [h, w, 3] for HDR environments."""
 
     def __init__(self, ctx: Context, rgba8: np.ndarray | None):
         self.ctx = ctx
         if rgba8 is None:
             check(lib.tpt_env_clear(ctx._h))
+        elif np.asarray(rgba8).dtype.kind == "f":
+            img = np.ascontiguousarray(rgba8, np.float32)
+            assert img.ndim == 3 and img.shape[2] == 3
+            check(lib.tpt_env_set_rgb32f(ctx._h, _ptr(img), img.shape[1], img.shape[0]))
         else:
             img = np.ascontiguousarray(rgba8, np.uint8)
             assert img.ndim == 3 and img.shape[2] == 4

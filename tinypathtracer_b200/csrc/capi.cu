@@ -112,6 +112,7 @@ int tpt_context_destroy(tpt_context* ctx) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     cudaFree(ctx->env);
+    cudaFree(ctx->envf);
     tpt_env_free_sampler(ctx);
     cudaFree(ctx->d_counters);
     cudaFree(ctx->q_ext[0]);
@@ -340,16 +341,48 @@ int tpt_scene_export_world(tpt_scene* s, float* wv, float* wn) {
     return TPT_OK;
 }
 
+static int env_drop(tpt_context* ctx) {
+    TPT_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (ctx->env) cudaFree(ctx->env);
+    if (ctx->envf) cudaFree(ctx->envf);
+    ctx->env = nullptr;
+    ctx->envf = nullptr;
+    ctx->env_w = ctx->env_h = 0;
+    tpt_env_free_sampler(ctx);
+    return TPT_OK;
+}
+
 int tpt_env_set_rgba8(tpt_context* ctx, const uint8_t* rgba8, int w, int h) {
     TPT_REQUIRE(ctx && rgba8, "tpt_env_set_rgba8: NULL argument");
     TPT_REQUIRE(w > 0 && h > 0, "tpt_env_set_rgba8: bad size");
     TPT_CHECK(bind(ctx));
-    TPT_CUDA(cudaStreamSynchronize(ctx->stream));
-    if (ctx->env) cudaFree(ctx->env);
-    ctx->env = nullptr;
-    tpt_env_free_sampler(ctx);
+    TPT_CHECK(env_drop(ctx));
     TPT_CUDA(cudaMalloc(&ctx->env, (size_t)w * h * 4));
     TPT_CUDA(cudaMemcpyAsync(ctx->env, rgba8, (size_t)w * h * 4, cudaMemcpyHostToDevice, ctx->stream));
+    TPT_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->env_w = w;
+    ctx->env_h = h;
+    return TPT_OK;
+}
+
+int tpt_env_set_rgb32f(tpt_context* ctx, const float* rgb, int w, int h) {
+    TPT_REQUIRE(ctx && rgb, "tpt_env_set_rgb32f: NULL argument");
+    TPT_REQUIRE(w > 0 && h > 0, "tpt_env_set_rgb32f: bad size");
+    const size_t n = (size_t)w * h;
+    // texels must be finite and in [0, 65536]: one sample's contribution then stays far inside the int64 fixed-point range
+    std::vector<float4> staged(n);
+    for (size_t i = 0; i < n; ++i) {
+        const float r = rgb[3 * i], g = rgb[3 * i + 1], b = rgb[3 * i + 2];
+        if (!(r >= 0.0f && r <= 65536.0f && g >= 0.0f && g <= 65536.0f && b >= 0.0f && b <= 65536.0f)) {
+            set_error("tpt_env_set_rgb32f: texel " + std::to_string(i) + " is negative, non-finite or above 65536");
+            return TPT_ERR_INVALID;
+        }
+        staged[i] = make_float4(r, g, b, 0.0f);
+    }
+    TPT_CHECK(bind(ctx));
+    TPT_CHECK(env_drop(ctx));
+    TPT_CUDA(cudaMalloc(&ctx->envf, n * sizeof(float4)));
+    TPT_CUDA(cudaMemcpyAsync(ctx->envf, staged.data(), n * sizeof(float4), cudaMemcpyHostToDevice, ctx->stream));
     TPT_CUDA(cudaStreamSynchronize(ctx->stream));
     ctx->env_w = w;
     ctx->env_h = h;
@@ -359,17 +392,12 @@ int tpt_env_set_rgba8(tpt_context* ctx, const uint8_t* rgba8, int w, int h) {
 int tpt_env_clear(tpt_context* ctx) {
     TPT_REQUIRE(ctx, "tpt_env_clear: ctx is NULL");
     TPT_CHECK(bind(ctx));
-    TPT_CUDA(cudaStreamSynchronize(ctx->stream));
-    if (ctx->env) cudaFree(ctx->env);
-    ctx->env = nullptr;
-    tpt_env_free_sampler(ctx);
-    ctx->env_w = ctx->env_h = 0;
-    return TPT_OK;
+    return env_drop(ctx);
 }
 
 int tpt_env_sample(tpt_context* ctx, size_t n, uint64_t seed, float* dirs_pdf) {
     TPT_REQUIRE(ctx && (n == 0 || dirs_pdf), "tpt_env_sample: NULL argument");
-    TPT_REQUIRE(ctx->env != nullptr, "tpt_env_sample: no environment map set");
+    TPT_REQUIRE(ctx->env != nullptr || ctx->envf != nullptr, "tpt_env_sample: no environment map set");
     TPT_CHECK(bind(ctx));
     if (n == 0) return TPT_OK;
     return tpt_env_sample_impl(ctx, n, seed, dirs_pdf);
@@ -377,7 +405,7 @@ int tpt_env_sample(tpt_context* ctx, size_t n, uint64_t seed, float* dirs_pdf) {
 
 int tpt_env_sampler_tables(tpt_context* ctx, float* prob, uint32_t* alias, float* mass) {
     TPT_REQUIRE(ctx && prob && alias && mass, "tpt_env_sampler_tables: NULL argument");
-    TPT_REQUIRE(ctx->env != nullptr, "tpt_env_sampler_tables: no environment map set");
+    TPT_REQUIRE(ctx->env != nullptr || ctx->envf != nullptr, "tpt_env_sampler_tables: no environment map set");
     TPT_CHECK(bind(ctx));
     TPT_CHECK(tpt_env_build_sampler(ctx));
     const size_t n = (size_t)ctx->env_w * ctx->env_h;

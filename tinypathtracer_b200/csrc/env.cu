@@ -11,12 +11,20 @@
 namespace tpt {
 
 // weight(texel) = luminance(rgb) * sin(theta of the texel's centre row); row 0 = bottom <-> v = 0 <-> theta = pi
-__global__ void __launch_bounds__(256) k_env_weights(const uchar4* __restrict__ env, int w, int h, float* __restrict__ weight) {
+__global__ void __launch_bounds__(256) k_env_weights(const uchar4* __restrict__ env, const float4* __restrict__ envf, int w, int h,
+                                                     float* __restrict__ weight) {
     const size_t n = (size_t)w * h;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
         const int y = (int)(i / (size_t)w);
-        const uchar4 t = env[i];
-        const float lum = 0.2126f * (float)t.x + 0.7152f * (float)t.y + 0.0722f * (float)t.z;
+        float3 c;
+        if (envf != nullptr) {
+            const float4 t = envf[i];
+            c = f3(t.x, t.y, t.z);
+        } else {
+            const uchar4 t = env[i];
+            c = f3((float)t.x, (float)t.y, (float)t.z);
+        }
+        const float lum = 0.2126f * c.x + 0.7152f * c.y + 0.0722f * c.z;
         weight[i] = lum * sinf((1.0f - ((float)y + 0.5f) / (float)h) * kPi);
     }
 }
@@ -49,11 +57,11 @@ int tpt_env_free_sampler(tpt_context* ctx) {
 // Vose's alias method: buckets of height 1/n, each holding at most two texels.
 int tpt_env_build_sampler(tpt_context* ctx) {
     if (ctx->env_prob) return TPT_OK;
-    TPT_REQUIRE(ctx->env != nullptr, "environment importance sampling needs an environment map (tpt_env_set_rgba8)");
+    TPT_REQUIRE(ctx->env != nullptr || ctx->envf != nullptr, "environment importance sampling needs an environment map (tpt_env_set_rgba8 / tpt_env_set_rgb32f)");
     const size_t n = (size_t)ctx->env_w * ctx->env_h;
     float* d_weight = nullptr;
     TPT_CUDA(cudaMalloc(&d_weight, n * sizeof(float)));
-    k_env_weights<<<kNumSMs * 8, 256, 0, ctx->stream>>>(ctx->env, ctx->env_w, ctx->env_h, d_weight);
+    k_env_weights<<<kNumSMs * 8, 256, 0, ctx->stream>>>(ctx->env, ctx->envf, ctx->env_w, ctx->env_h, d_weight);
     ctx->kernel_launches += 1;
     std::vector<float> wgt(n);
     cudaError_t e = cudaMemcpyAsync(wgt.data(), d_weight, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream);

@@ -418,6 +418,129 @@ Picture::Picture(const std::string& filename) {
     if (channels != 3 && channels != 4) throw std::runtime_error("Unsupported image format");   // src/texture.cu:79-82
 }
 
+// ---- float images: Radiance RGBE (.hdr) and PFM ---------------------------------------------------------
+// The reference reads environment maps through FreeImage into an 8-bit Texture only (include/picture.h:25-44,
+// src/texture.cu:79-82).  RGBE -> float follows the rgbe.c convention FreeImage's HDR plugin uses: mantissa * 2^(e - 136),
+// e = 0 -> black (no +0.5 bias).
+static bool nextLine(const std::string& d, size_t& pos, std::string& line) {
+    if (pos >= d.size()) return false;
+    const size_t e = d.find('\n', pos);
+    line = d.substr(pos, e == std::string::npos ? std::string::npos : e - pos);
+    pos = e == std::string::npos ? d.size() : e + 1;
+    if (!line.empty() && line.back() == '\r') line.pop_back();
+    return true;
+}
+
+static void loadHDR(const std::string& d, PictureF& pic) {
+    size_t pos = 0;
+    std::string line;
+    bool format = false;
+    nextLine(d, pos, line);   // "#?RADIANCE" / "#?RGBE"
+    while (nextLine(d, pos, line) && !line.empty())
+        if (line.rfind("FORMAT=", 0) == 0) {
+            if (line != "FORMAT=32-bit_rle_rgbe") throw std::runtime_error("PictureF: unsupported Radiance format " + line);
+            format = true;
+        }
+    if (!format) throw std::runtime_error("PictureF: Radiance header without FORMAT=32-bit_rle_rgbe");
+    if (!nextLine(d, pos, line)) throw std::runtime_error("PictureF: Radiance file without a resolution line");
+    int h = 0, w = 0;
+    if (std::sscanf(line.c_str(), "-Y %d +X %d", &h, &w) != 2 || w <= 0 || h <= 0 || w > 65535 || h > 65535)
+        throw std::runtime_error("PictureF: only the standard '-Y h +X w' orientation is supported");
+    pic.width = w;
+    pic.height = h;
+    pic.pixels.assign((size_t)w * h * 3, 0.0f);
+    std::vector<uint8_t> row((size_t)w * 4);
+    const uint8_t* p = reinterpret_cast<const uint8_t*>(d.data()) + pos;
+    const uint8_t* end = reinterpret_cast<const uint8_t*>(d.data()) + d.size();
+    auto need = [&](size_t n) { if ((size_t)(end - p) < n) throw std::runtime_error("PictureF: truncated Radiance file"); };
+    for (int y = 0; y < h; ++y) {
+        need(4);
+        if (w >= 8 && w < 32768 && p[0] == 2 && p[1] == 2 && !(p[2] & 0x80)) {   // new RLE: each of the 4 channels run-length coded
+            if (((int)p[2] << 8 | p[3]) != w) throw std::runtime_error("PictureF: Radiance scanline width mismatch");
+            p += 4;
+            for (int c = 0; c < 4; ++c)
+                for (int x = 0; x < w;) {
+                    need(1);
+                    int n = *p++;
+                    if (n > 128) {   // run
+                        n -= 128;
+                        need(1);
+                        if (x + n > w) throw std::runtime_error("PictureF: Radiance run overflows its scanline");
+                        const uint8_t v = *p++;
+                        while (n--) row[4 * (size_t)x++ + c] = v;
+                    } else {         // literals
+                        if (n == 0 || x + n > w) throw std::runtime_error("PictureF: bad Radiance literal count");
+                        need((size_t)n);
+                        while (n--) row[4 * (size_t)x++ + c] = *p++;
+                    }
+                }
+        } else {   // flat RGBE pixels (old-style repeat markers are not produced by any current writer)
+            need((size_t)w * 4);
+            std::memcpy(row.data(), p, (size_t)w * 4);
+            p += (size_t)w * 4;
+        }
+        float* out = &pic.pixels[(size_t)y * w * 3];
+        for (int x = 0; x < w; ++x) {
+            const uint8_t* q = &row[4 * (size_t)x];
+            const float f = q[3] ? std::ldexp(1.0f, (int)q[3] - 136) : 0.0f;
+            out[3 * x + 0] = q[0] * f;
+            out[3 * x + 1] = q[1] * f;
+            out[3 * x + 2] = q[2] * f;
+        }
+    }
+}
+
+// PFM: "PF" (RGB) or "Pf" (grey), "w h", scale (negative = little endian), then rows BOTTOM to top.
+static void loadPFM(const std::string& d, PictureF& pic) {
+    int w = 0, h = 0, used = 0;
+    float scale = 0.0f;
+    char kind = 0;
+    if (std::sscanf(d.c_str(), "P%c %d %d %f%n", &kind, &w, &h, &scale, &used) != 4 || (kind != 'F' && kind != 'f') || w <= 0 || h <= 0 ||
+        scale == 0.0f)
+        throw std::runtime_error("PictureF: bad PFM header");
+    const size_t pos = (size_t)used + 1;   // exactly one whitespace byte after the scale
+    const int ch = kind == 'F' ? 3 : 1;
+    if (d.size() < pos + (size_t)w * h * ch * 4) throw std::runtime_error("PictureF: truncated PFM file");
+    pic.width = w;
+    pic.height = h;
+    pic.pixels.resize((size_t)w * h * 3);
+    const uint8_t* p = reinterpret_cast<const uint8_t*>(d.data()) + pos;
+    const bool little = scale < 0.0f;
+    for (int y = 0; y < h; ++y)
+        for (int x = 0; x < w; ++x)
+            for (int c = 0; c < 3; ++c) {
+                const uint8_t* q = p + 4 * (((size_t)(h - 1 - y) * w + x) * ch + (ch == 3 ? c : 0));
+                const uint32_t bits = little ? ((uint32_t)q[0] | (uint32_t)q[1] << 8 | (uint32_t)q[2] << 16 | (uint32_t)q[3] << 24) : be32(q);
+                float v;
+                std::memcpy(&v, &bits, 4);
+                pic.pixels[((size_t)y * w + x) * 3 + c] = v;
+            }
+}
+
+bool PictureF::isFloatFile(const std::string& filename) {
+    FILE* f = std::fopen(filename.c_str(), "rb");
+    if (!f) return false;
+    char m[2] = {0, 0};
+    const size_t n = std::fread(m, 1, 2, f);
+    std::fclose(f);
+    return n == 2 && ((m[0] == '#' && m[1] == '?') || (m[0] == 'P' && (m[1] == 'F' || m[1] == 'f')));
+}
+
+PictureF::PictureF(const std::string& filename) {
+    const std::string data = slurp(filename);
+    if (data.size() > 2 && data[0] == '#' && data[1] == '?') loadHDR(data, *this);
+    else if (data.size() > 2 && data[0] == 'P' && (data[1] == 'F' || data[1] == 'f')) loadPFM(data, *this);
+    else throw std::runtime_error("PictureF: " + filename + " is not a Radiance .hdr or PFM file");
+}
+
+void writePFM(const std::string& filename, const float* rgbTopDown, int width, int height) {
+    FILE* f = std::fopen(filename.c_str(), "wb");
+    if (!f) throw std::runtime_error("writePFM: cannot create " + filename);
+    std::fprintf(f, "PF\n%d %d\n-1.0\n", width, height);   // little endian
+    for (int y = height - 1; y >= 0; --y) std::fwrite(rgbTopDown + (size_t)y * width * 3, sizeof(float), (size_t)width * 3, f);
+    std::fclose(f);
+}
+
 static void chunk(std::vector<uint8_t>& out, const char* type, const uint8_t* body, size_t len) {
     const uint8_t l[4] = {(uint8_t)(len >> 24), (uint8_t)(len >> 16), (uint8_t)(len >> 8), (uint8_t)len};
     out.insert(out.end(), l, l + 4);

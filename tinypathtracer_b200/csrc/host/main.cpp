@@ -8,7 +8,7 @@
 #include "tpt/host.hpp"
 
 int main(int argc, char** argv) {
-    std::string scene, env, out;
+    std::string scene, env, out, outFloat;
     int w = 1920, h = 1080, spp = 64, depth = 8, frames = 1;
     unsigned long long seed = 1;
     bool envNee = false, fullGltf = false, progressive = false;
@@ -22,6 +22,7 @@ int main(int argc, char** argv) {
         if (k == "--scene") scene = val();
         else if (k == "--env") env = val();
         else if (k == "--out") out = val();
+        else if (k == "--out-float") outFloat = val();
         else if (k == "--w" || k == "--width") w = std::atoi(val());
         else if (k == "--h" || k == "--height") h = std::atoi(val());
         else if (k == "--spp") spp = std::atoi(val());
@@ -36,7 +37,7 @@ int main(int argc, char** argv) {
         else { std::fprintf(stderr, "unknown argument %s\n", k.c_str()); return 2; }
     }
     if (scene.empty()) {
-        std::fprintf(stderr, "usage: tpt_render --scene file.gltf [--env sky.png] [--w 1920 --h 1080 --spp 64 --depth 8 --frames 1 --seed 1 --env-nee --full-gltf --progressive --checkpoint file --resume file --out frame.png]\n");
+        std::fprintf(stderr, "usage: tpt_render --scene file.gltf [--env sky.png|sky.jpg|sky.hdr|sky.pfm] [--w 1920 --h 1080 --spp 64 --depth 8 --frames 1 --seed 1 --env-nee --full-gltf --progressive --checkpoint file --resume file --out frame.png --out-float frame.pfm]\n");
         return 2;
     }
     try {
@@ -52,6 +53,7 @@ int main(int argc, char** argv) {
         pathTracer.m_progressive = progressive;
         if (!resume.empty()) pathTracer.loadCheckpoint(resume);   // continues its sample sequence and seed
         pathTracer.m_output = out;
+        pathTracer.m_outputFloat = outFloat;
         pathTracer.render(scene);          // src/main.cu:12
         if (!checkpoint.empty()) pathTracer.saveCheckpoint(checkpoint);
         const tpt_counters c = pathTracer.context().counters();

@@ -1,5 +1,6 @@
 // path_tracer.cpp — EnvLight and PathTracer of the reference (include/env_light.cuh:9-19, include/path_tracer.h:16-35,
 // src/path_tracer.cu:477-579) over the C ABI, plus the extern "C" hooks the tests use to read the loader's output.
+#include <algorithm>
 #include <chrono>
 #include <cstdio>
 #include <cstring>
@@ -13,6 +14,18 @@ namespace tpt {
 EnvLight::EnvLight(Context& ctx, const std::string& file) {
     if (file.empty()) {
         check(tpt_env_clear(ctx.handle()), "tpt_env_clear");
+        return;
+    }
+    if (PictureF::isFloatFile(file)) {   // HDR map: linear float texels, rows flipped to the reference's bottom-up order
+        const PictureF pic(file);
+        std::vector<float> rgb((size_t)pic.width * pic.height * 3);
+        for (int y = 0; y < pic.height; ++y) {
+            const float* src = &pic.pixels[(size_t)(pic.height - 1 - y) * pic.width * 3];
+            float* dst = &rgb[(size_t)y * pic.width * 3];
+            // the C ABI takes finite texels in [0, 65536]; files may hold negative or larger values (or NaN)
+            for (int i = 0; i < 3 * pic.width; ++i) dst[i] = src[i] >= 0.0f ? std::min(src[i], 65536.0f) : 0.0f;
+        }
+        check(tpt_env_set_rgb32f(ctx.handle(), rgb.data(), pic.width, pic.height), "tpt_env_set_rgb32f");
         return;
     }
     const Picture pic(file);
@@ -149,6 +162,15 @@ void PathTracer::render(const std::string& meshFile) {
         }
         writePNG(m_output, rgb.data(), m_width, m_height, 3);
     }
+    if (!m_outputFloat.empty()) {
+        std::vector<float> sum((size_t)m_width * m_height * 3), img(sum.size());
+        check(tpt_accum_export_f32(m_radiance, sum.data()), "tpt_accum_export_f32");   // radiance SUM, row 0 = bottom
+        const float inv = 1.0f / (float)(m_samplesDone ? m_samplesDone : 1);
+        for (int y = 0; y < m_height; ++y)
+            for (size_t i = 0; i < (size_t)m_width * 3; ++i)
+                img[(size_t)y * m_width * 3 + i] = sum[(size_t)(m_height - 1 - y) * m_width * 3 + i] * inv;
+        writePFM(m_outputFloat, img.data(), m_width, m_height);
+    }
 }
 
 }   // namespace tpt
@@ -223,6 +245,32 @@ int tpt_host_write_png(const char* path, const uint8_t* px, int w, int h, int ch
         return -1;
     }
 }
+int tpt_host_read_image_f32(const char* path, float* out, size_t capacityFloats, int* wh2) {
+    try {
+        const tpt::PictureF pic(path);
+        wh2[0] = pic.width;
+        wh2[1] = pic.height;
+        if (out) {
+            if (capacityFloats < pic.pixels.size()) throw std::runtime_error("tpt_host_read_image_f32: buffer too small");
+            std::memcpy(out, pic.pixels.data(), pic.pixels.size() * sizeof(float));
+        }
+        return 0;
+    } catch (const std::exception& e) {
+        g_host_error = e.what();
+        return -1;
+    }
+}
+
+int tpt_host_write_pfm(const char* path, const float* rgbTopDown, int w, int h) {
+    try {
+        tpt::writePFM(path, rgbTopDown, w, h);
+        return 0;
+    } catch (const std::exception& e) {
+        g_host_error = e.what();
+        return -1;
+    }
+}
+
 int tpt_host_read_image(const char* path, uint8_t* out, size_t capacity, int* whc3) {
     try {
         tpt::Picture p(path);

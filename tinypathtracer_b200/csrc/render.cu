@@ -254,15 +254,20 @@ __device__ __forceinline__ void light_incoming(const tpt_delta_light& L, float3 
 }
 
 // sampleEnvLights + Vec2UV, src/path_tracer.cu:288-294, include/env_light.cuh:72-78; point filter,
-// clamp addressing, normalised coordinates (src/texture.cu:160-168).
-__device__ __forceinline__ float3 env_lookup(const uchar4* __restrict__ env, int ew, int eh, float3 d) {
-    if (env == nullptr) return f3(0.f, 0.f, 0.f);
+// clamp addressing, normalised coordinates (src/texture.cu:160-168).  Two texel formats: the reference's RGBA8
+// (value / 255) and linear float RGB for HDR maps (tpt_env_set_rgb32f; one 128-bit load per lookup).
+__device__ __forceinline__ float3 env_lookup(const uchar4* __restrict__ env, const float4* __restrict__ envf, int ew, int eh, float3 d) {
+    if (env == nullptr && envf == nullptr) return f3(0.f, 0.f, 0.f);
     float u = atan2f(d.z, d.x) / (2.0f * kPi);
     if (u < 0.0f) u += 1.0f;
     const float v = 1.0f - acosf(fmaxf(fminf(d.y, 1.0f), -1.0f)) / kPi;
     int x = (int)floorf(u * (float)ew), y = (int)floorf(v * (float)eh);
     x = min(max(x, 0), ew - 1);
     y = min(max(y, 0), eh - 1);
+    if (envf != nullptr) {
+        const float4 t = __ldg(envf + (size_t)y * ew + x);
+        return f3(t.x, t.y, t.z);
+    }
     const uchar4 t = __ldg(env + (size_t)y * ew + x);
     return f3((float)t.x, (float)t.y, (float)t.z) * (1.0f / 255.0f);
 }
@@ -271,8 +276,10 @@ struct ShadeParams {
     const float4* mtl;       // 2 float4 per material
     const tpt_delta_light* lights;
     int nLights;
-    const uchar4* env;
+    const uchar4* env;       // RGBA8 map (the reference's format) or
+    const float4* envf;      // float RGB map (HDR); at most one of the two is set
     int envW, envH;
+    __device__ __forceinline__ bool has_env() const { return env != nullptr || envf != nullptr; }
     int depth, maxDepth;
     uint64_t seedKey;
     int directRays;          // 0 when no material of the scene is emissive: the extra cosine "direct" ray can only add emission
@@ -309,7 +316,7 @@ __device__ __forceinline__ bool shade_vertex(const BvhView& bvh, const ShadePara
                                              uint32_t pixel, uint32_t sample, const HitRec& h, float3& terminal, Vertex& vx,
                                              DeviceCounters* ctr) {
     if (h.leaf < 0) {
-        terminal = T * env_lookup(sp.env, sp.envW, sp.envH, d);
+        terminal = T * env_lookup(sp.env, sp.envf, sp.envW, sp.envH, d);
         if (NEE && pbBits != 0u) {
             const float pb = __uint_as_float(pbBits);
             terminal = terminal * (pb / (pb + env_pdf(sp.es, d)));
@@ -355,7 +362,7 @@ __device__ __forceinline__ bool shade_vertex(const BvhView& bvh, const ShadePara
     if (NEE) {
         vx.pb = 0.0f;
         vx.nee = false;
-        if (vx.next && !(eta > 0.0f) && !(metallic > 0.0f) && sp.env != nullptr) {   // diffuse lobe of new_direction
+        if (vx.next && !(eta > 0.0f) && !(metallic > 0.0f) && sp.has_env()) {   // diffuse lobe of new_direction
             const float3 nn = dot(d, nrm) > 0.0f ? -nrm : nrm;
             vx.pb = dot(vx.ndir, nn) * (1.0f / kPi);
             float u1, u2, u3, u4, pl;
@@ -364,7 +371,7 @@ __device__ __forceinline__ bool shade_vertex(const BvhView& bvh, const ShadePara
             vx.ldir = env_sample_dir(sp.es, u1, u2, u3, pl);
             const float pbl = dot(vx.ldir, nn) * (1.0f / kPi);
             if (pbl > 0.0f && pl > 0.0f) {
-                vx.lw = (vx.Tn * env_lookup(sp.env, sp.envW, sp.envH, vx.ldir)) * (pbl / (pl + pbl));
+                vx.lw = (vx.Tn * env_lookup(sp.env, sp.envf, sp.envW, sp.envH, vx.ldir)) * (pbl / (pl + pbl));
                 vx.nee = vx.lw.x > 0.f || vx.lw.y > 0.f || vx.lw.z > 0.f;
             }
         }
@@ -507,7 +514,7 @@ __global__ void __launch_bounds__(128) k_primary(BvhView bvh, ShadeParams sp, Ca
         const unsigned m = __activemask();
         const unsigned culled = __reduce_add_sync(m, s1 - s0);
         if ((threadIdx.x & 31) == __ffs(m) - 1) atomicAdd(&ctr->rays_culled, (unsigned long long)culled);
-        if (sp.env == nullptr) return;   // black environment: nothing to add either
+        if (!sp.has_env()) return;   // black environment: nothing to add either
     } else if (nc > 0) {
         const unsigned m = __activemask();
         const unsigned n = __reduce_add_sync(m, s1 - s0);
@@ -576,7 +583,7 @@ __global__ void __launch_bounds__(128, TPT_COOP_MIN_BLOCKS) k_primary_coop(BvhVi
     }
     // kCoopLanes lanes work on one pixel, 32 / kCoopLanes pixels at a time (the next ones that have work)
     const uint32_t grp = lane / kCoopLanes, sub = lane % kCoopLanes;
-    unsigned todo = __ballot_sync(0xffffffffu, inside && (nc != 0 || sp.env != nullptr));
+    unsigned todo = __ballot_sync(0xffffffffu, inside && (nc != 0 || sp.has_env()));
     while (todo) {
         const unsigned src = __fns(todo, 0, (int)grp + 1);   // lane of my group's pixel; 0xffffffff when fewer pixels are left
         const bool have = src != 0xffffffffu;
@@ -1096,7 +1103,7 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
     tpt_context* ctx = s->ctx;
     cudaStream_t st = ctx->stream;
     // environment next-event estimation needs a map to sample; without one the flag changes nothing
-    const bool nee = (cfg->flags & TPT_RENDER_ENV_NEE) != 0 && ctx->env != nullptr;
+    const bool nee = (cfg->flags & TPT_RENDER_ENV_NEE) != 0 && (ctx->env != nullptr || ctx->envf != nullptr);
     if (nee) TPT_CHECK(tpt_env_build_sampler(ctx));
     const int W = cfg->width, H = cfg->height;
     const uint32_t nPadded = tiles_x(W) * tiles_y(H) * 32u;
@@ -1178,6 +1185,7 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
     sp.lights = s->lights;
     sp.nLights = (int)s->n_lights;
     sp.env = ctx->env;
+    sp.envf = ctx->envf;
     sp.envW = ctx->env_w;
     sp.envH = ctx->env_h;
     sp.maxDepth = cfg->max_depth;

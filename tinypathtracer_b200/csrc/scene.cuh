@@ -46,6 +46,7 @@ struct tpt_context {
     bool own_stream = false;
     // environment map (RGBA8, row 0 = bottom)
     uchar4* env = nullptr;
+    float4* envf = nullptr;   // or linear float RGB (HDR, tpt_env_set_rgb32f); at most one of env / envf is set
     int env_w = 0, env_h = 0;
     // alias tables over the map's texels (env.cu; built on first use by TPT_RENDER_ENV_NEE / tpt_env_sample, dropped with the map)
     float* env_prob = nullptr;
