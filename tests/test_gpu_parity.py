@@ -402,3 +402,35 @@ def test_refit_equals_rebuild(name, tpt, ctx, scenes, orc):
         ds2.close()
     assert ctx.counters()["queue_overflow"] == 0
     ds.close()
+
+
+def test_live_pixel_batches_change_nothing(tpt, ctx, built, scenes):
+    """A frame too big for one worst-case batch (1080p x 128 spp = 265 M camera samples > 2^27) is sized by its LIVE pixels
+    (k_tile_live: tir.gltf has ~10 %) and runs as one batch; forcing the old worst-case batches gives the same accumulator
+    bits, nothing overflows, and a changed camera re-measures."""
+    ds, _ = built["tir"]
+    W, H, spp = 1920, 1080, 128
+    cam = tpt.Camera.from_scene(scenes["tir"])
+    pt = tpt.PathTracer(ctx, W, H)
+    n0 = ctx.counters()["kernel_launches"]
+    pt.render_into(ds, cam, spp=spp, max_depth=32, seed=3)
+    one = ctx.counters()["kernel_launches"] - n0
+    a = pt.m_radiance.to_i64()
+    pt.m_radiance.clear()
+    n0 = ctx.counters()["kernel_launches"]
+    pt.render_into(ds, cam, spp=spp, max_depth=32, seed=3, paths_in_flight=W * H * 32)
+    four = ctx.counters()["kernel_launches"] - n0
+    assert (pt.m_radiance.to_i64() == a).all() and a.any()
+    assert one <= 35 and four >= 4 * 33                      # 1 + 1 + 32 launches against 4 x (1 + 32)
+    # another camera (closer: more live pixels) must not reuse the first camera's table
+    sc = scenes["tir"]
+    c2w = np.array(sc["c2w"], np.float32).reshape(16).copy()
+    c2w[12:15] *= np.float32(0.6)                            # column-major: the translation column
+    cam2 = tpt.Camera(sc["vfov"], sc["aspect"], sc["near"], c2w)
+    pt.m_radiance.clear()
+    pt.render_into(ds, cam2, spp=spp, max_depth=32, seed=3)
+    b = pt.m_radiance.to_i64()
+    pt.m_radiance.clear()
+    pt.render_into(ds, cam2, spp=spp, max_depth=32, seed=3, paths_in_flight=W * H * 32)
+    assert (pt.m_radiance.to_i64() == b).all() and not (a == b).all()
+    assert ctx.counters()["queue_overflow"] == 0

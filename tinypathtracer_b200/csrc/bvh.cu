@@ -13,6 +13,8 @@
 //                       root with one atomic arrival counter per node; the second arrival owns the
 //                       node.  Grid-wide, replaces the reference's single 1024-thread block
 //                       (computeBBox, src/bvh.cu:220-302).
+#include <atomic>
+
 #include <cub/device/device_radix_sort.cuh>
 
 #include "scene.cuh"
@@ -363,6 +365,7 @@ __global__ void k_bvh_stats(const float4* __restrict__ nodes, const int* __restr
 
 using namespace tpt;
 
+static std::atomic<uint64_t> g_geom_epoch{0};   // one counter for all scenes and contexts
 static inline unsigned grid_for(size_t n, int block) { return (unsigned)((n + block - 1) / block); }
 
 int tpt_scene_build_tables(tpt_scene* s) {
@@ -415,6 +418,7 @@ int tpt_bvh_build_impl(tpt_scene* s) {
     TPT_CUDA(cudaGetLastError());
     ctx->kernel_launches += 6 + 8;   // + radix sort passes (library, counted nominally)
     s->built = true;
+    s->geom_epoch = ++g_geom_epoch;   // unique across scenes: a new scene at a recycled address never matches a cached key
     s->topology = true;
     return TPT_OK;
 }
@@ -442,6 +446,7 @@ int tpt_bvh_refit_impl(tpt_scene* s) {
     TPT_CUDA(cudaGetLastError());
     ctx->kernel_launches += 4;
     s->built = true;
+    s->geom_epoch = ++g_geom_epoch;   // unique across scenes: a new scene at a recycled address never matches a cached key
     return TPT_OK;
 }
 

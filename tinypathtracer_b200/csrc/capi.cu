@@ -121,6 +121,7 @@ int tpt_context_destroy(tpt_context* ctx) {
     cudaFree(ctx->q_sec[1]);
     cudaFree(ctx->levels);
     cudaFree(ctx->trace_cursor);
+    cudaFree(ctx->d_tile_live);
     cudaFree(ctx->io_rays);
     cudaFree(ctx->io_hits);
     for (cudaEvent_t e : ctx->stage_events) cudaEventDestroy(e);

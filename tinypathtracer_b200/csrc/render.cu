@@ -24,6 +24,9 @@
 // vertex is emissive (which also discards that vertex's own direct term, :421-424), or 0 at the depth
 // cut.  Every term is added to the pixel as an exact fixed-point integer, so the result does not
 // depend on the order in which kernels, warps or GPUs finish, nor on how terms are grouped.
+#include <algorithm>
+#include <cstring>
+
 #include "env.cuh"
 #include "traverse.cuh"
 
@@ -611,6 +614,25 @@ __global__ void __launch_bounds__(128, TPT_COOP_MIN_BLOCKS) k_primary_coop(BvhVi
     if (COUNT) flush_trav_counters(nv, nt, ctr);
 }
 
+// Pre-pass for the batch size: how many pixels of each 8x4 tile can emit a path at all (the same pyramid walk k_primary does,
+// so "0 candidates" here is "0 candidates" there).  The queue pools are sized for what the live pixels can emit, not for
+// every pixel of the frame: ball.gltf has 22 % live pixels, tir.gltf 10 %, and their 256 spp then fit ONE batch (one
+// k_primary + max_depth k_wave launches per frame instead of four of each).
+__global__ void __launch_bounds__(128) k_tile_live(BvhView bvh, ShadeParams sp, CameraParams cam, int W, int H, uint32_t nPadded,
+                                                   uint8_t* __restrict__ tileLive) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nPadded) return;   // whole warps: nPadded is a multiple of 32
+    int px, py;
+    const bool inside = tile_decode(i, W, H, px, py);
+    int stack[kStackSize];
+    stack[0] = kStackSentinel;
+    const float3 o = xmat4_point(cam.c2w, f3(0.f, 0.f, 0.f));
+    unsigned nv = 0;
+    const int nc = inside ? pixel_candidates(bvh, sp, cam, px, py, o, stack, nv) : 0;
+    const unsigned live = __ballot_sync(0xffffffffu, nc != 0);
+    if ((threadIdx.x & 31) == 0) tileLive[i >> 5] = (uint8_t)__popc(live);
+}
+
 // ---- wave w >= 1: extension rays towards vertex w + secondary rays of vertex w-1 --------------------------
 // Persistent warps.  Incoherent rays finish after very different numbers of steps, and a lane that waits
 // for the slowest ray of its warp is a wasted lane, so each lane runs the traversal state machine of
@@ -1107,18 +1129,75 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
     if (nee) TPT_CHECK(tpt_env_build_sampler(ctx));
     const int W = cfg->width, H = cfg->height;
     const uint32_t nPadded = tiles_x(W) * tiles_y(H) * 32u;
-    // default batch: as many camera samples as a 40 GiB queue budget allows (2 sides x (2+L) rays x 48 B each), at most 2^27 —
-    // sized for 180 GB of HBM: fewer, larger batches mean fewer (mostly empty) deep-wave launches per frame
+    const CameraParams cp = make_camera(cam, W, H);
+    ShadeParams sp;
+    sp.mtl = s->mtl_table;
+    sp.lights = s->lights;
+    sp.nLights = (int)s->n_lights;
+    sp.env = ctx->env;
+    sp.envf = ctx->envf;
+    sp.envW = ctx->env_w;
+    sp.envH = ctx->env_h;
+    sp.maxDepth = cfg->max_depth;
+    sp.seedKey = rng_seed_key(cfg->seed);
+    sp.depth = 0;
+    sp.directRays = s->any_emissive ? 1 : 0;
+    sp.pixelCandidates = (cfg->flags & TPT_RENDER_NO_PIXEL_CANDIDATES) ? 0 : 1;
+    sp.es = EnvSampler{ctx->env_prob, ctx->env_alias, ctx->env_mass, ctx->env_w, ctx->env_h};
+    const BvhView view = s->view();
+
+    // batch budget: as many LIVE camera samples as a 40 GiB queue budget allows (2 sides x (2+L) rays x 48 B each), at most
+    // 2^27 — sized for 180 GB of HBM: fewer, larger batches mean fewer (mostly empty) deep-wave launches per frame
     const size_t secPerPath = s->n_lights + 1 + (nee ? 1 : 0);
     size_t target = ((size_t)40 << 30) / (96 * (1 + secPerPath));
     if (target > ((size_t)1 << 27)) target = (size_t)1 << 27;
     if (cfg->paths_in_flight > 0) target = (size_t)cfg->paths_in_flight;
-    uint32_t k = (uint32_t)(target / nPadded);
+    // Live pixels per 8x4 tile (k_tile_live): only they can put rays into the queues.  One small kernel, one 1-byte-per-tile
+    // copy and one stream sync per (geometry, camera, resolution); frames that change none of them reuse the result.
+    const uint32_t nTiles = nPadded / 32u;
+    static const bool noLiveBound = getenv("TPT_NO_LIVE_BOUND") != nullptr;   // tuning switch: size the pools for every pixel
+    {
+        LiveKey key;
+        memset(&key, 0, sizeof key);
+        key.scene = s;
+        key.epoch = s->geom_epoch;
+        key.cam = *cam;
+        key.w = W;
+        key.h = H;
+        key.candidates = sp.pixelCandidates;
+        // the pre-pass costs a stream sync: only worth it when the frame would otherwise need more than one batch
+        key.measured = (!noLiveBound && cfg->paths_in_flight <= 0 && (size_t)nPadded * (size_t)cfg->spp > target) ? 1 : 0;
+        if (ctx->tile_live_host.size() != nTiles || memcmp(&key, &ctx->live_key, sizeof key) != 0) {
+            if (nTiles > ctx->tile_live_capacity) {
+                TPT_CUDA(cudaStreamSynchronize(st));
+                if (ctx->d_tile_live) cudaFree(ctx->d_tile_live);
+                ctx->d_tile_live = nullptr;
+                ctx->tile_live_capacity = 0;
+                TPT_CUDA(cudaMalloc(&ctx->d_tile_live, nTiles));
+                ctx->tile_live_capacity = nTiles;
+            }
+            ctx->tile_live_host.resize(nTiles);
+            if (!key.measured) {
+                std::fill(ctx->tile_live_host.begin(), ctx->tile_live_host.end(), (uint8_t)32);
+            } else {
+                k_tile_live<<<(nPadded + 127) / 128, 128, 0, st>>>(view, sp, cp, W, H, nPadded, ctx->d_tile_live);
+                ctx->kernel_launches += 1;
+                TPT_CUDA(cudaMemcpyAsync(ctx->tile_live_host.data(), ctx->d_tile_live, nTiles, cudaMemcpyDeviceToHost, st));
+                TPT_CUDA(cudaStreamSynchronize(st));
+            }
+            ctx->live_key = key;
+        }
+    }
+    const uint8_t* tileLive = ctx->tile_live_host.data();
+    size_t livePixels = 0;
+    for (uint32_t t = 0; t < nTiles; ++t) livePixels += tileLive[t];
+    // an explicit paths_in_flight keeps its old meaning (camera samples per batch, live or not): the tests use it to force batching
+    uint32_t k = (uint32_t)std::min<size_t>(target / (cfg->paths_in_flight > 0 ? (size_t)nPadded : std::max<size_t>(livePixels, 1)), 1u << 20);
     if (k > 32) k &= ~31u;   // whole warps of samples per pixel for k_primary_coop
     if (k < 1) k = 1;
     if (k > (uint32_t)cfg->spp) k = (uint32_t)cfg->spp;
-    // launch shape of k_primary for a batch of kk samples per pixel, and the segment capacity it needs: the blocks
-    // of one segment (blockIdx % kSegments) emit at most 128 * spt extension rays each
+    // launch shape of k_primary for a batch of kk samples per pixel, and the segment capacity it needs: what the live pixels
+    // of the blocks of one segment (blockIdx % kSegments) can emit, one extension ray per live pixel and sample
     struct Plan {
         uint32_t spt, groups;
         unsigned grid;
@@ -1138,7 +1217,15 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
         if (pl.spt > kk) pl.spt = kk;
         pl.groups = (kk + pl.spt - 1) / pl.spt;
         pl.grid = (unsigned)(((size_t)nPadded * pl.groups + 127) / 128);
-        pl.segCap = (size_t)((pl.grid + kSegments - 1) / kSegments) * 128 * pl.spt;
+        // warp w of the grid = (sample group w / nTiles, tile w % nTiles), block w / 4, segment block % kSegments
+        size_t segSum[kSegments];
+        for (int q = 0; q < kSegments; ++q) segSum[q] = 0;
+        for (uint32_t g = 0; g < pl.groups; ++g) {
+            const size_t ns = std::min(kk, (g + 1) * pl.spt) - g * pl.spt;
+            for (uint32_t t = 0; t < nTiles; ++t) segSum[(((size_t)g * nTiles + t) >> 2) & (kSegments - 1)] += tileLive[t] * ns;
+        }
+        pl.segCap = 32;
+        for (int q = 0; q < kSegments; ++q) pl.segCap = std::max(pl.segCap, segSum[q]);
         return pl;
     };
     size_t extSegCap = launch_plan(k).segCap;
@@ -1150,7 +1237,6 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
     TPT_REQUIRE(secSegCap * kSegments < ((size_t)1 << 32), "tpt_render: paths_in_flight x (lights + 2) exceeds 2^32 queue slots");
     TPT_CHECK(ensure_pools(ctx, extSegCap * kSegments, secPerPath));
 
-    const CameraParams cp = make_camera(cam, W, H);
     const bool counted = (cfg->flags & TPT_RENDER_COUNTERS) != 0;
     const bool timed = (cfg->flags & TPT_RENDER_STAGE_TIMES) != 0;
     const size_t nEvents = 3 + (size_t)cfg->max_depth;
@@ -1163,7 +1249,6 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
     }
     size_t ev = 0;
     auto mark = [&]() { if (timed) cudaEventRecord(ctx->stage_events[ev++], st); };
-    const BvhView view = s->view();
     if (ctx->wave_grid[0] == 0) {
         ctx->wave_grid[0] = kNumSMs * min(resident_blocks(k_wave<false, false, false>, 128), resident_blocks(k_wave<false, false, true>, 128));
         ctx->wave_grid[1] = kNumSMs * min(resident_blocks(k_wave<true, false, false>, 128), resident_blocks(k_wave<true, false, true>, 128));
@@ -1179,21 +1264,6 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
                                              : k_primary_coop<true, true>;
     const auto kWave = variant == 0 ? k_wave<false, false, false> : variant == 1 ? k_wave<true, false, false> : variant == 2 ? k_wave<false, true, false> : k_wave<true, true, false>;
     const auto kWave1 = variant == 0 ? k_wave<false, false, true> : variant == 1 ? k_wave<true, false, true> : variant == 2 ? k_wave<false, true, true> : k_wave<true, true, true>;
-
-    ShadeParams sp;
-    sp.mtl = s->mtl_table;
-    sp.lights = s->lights;
-    sp.nLights = (int)s->n_lights;
-    sp.env = ctx->env;
-    sp.envf = ctx->envf;
-    sp.envW = ctx->env_w;
-    sp.envH = ctx->env_h;
-    sp.maxDepth = cfg->max_depth;
-    sp.seedKey = rng_seed_key(cfg->seed);
-    sp.depth = 0;
-    sp.directRays = s->any_emissive ? 1 : 0;
-    sp.pixelCandidates = (cfg->flags & TPT_RENDER_NO_PIXEL_CANDIDATES) ? 0 : 1;
-    sp.es = EnvSampler{ctx->env_prob, ctx->env_alias, ctx->env_mass, ctx->env_w, ctx->env_h};
 
     for (uint32_t done = 0; done < (uint32_t)cfg->spp; done += k) {
         const uint32_t kk = ((uint32_t)cfg->spp - done) < k ? ((uint32_t)cfg->spp - done) : k;

@@ -40,6 +40,15 @@ struct BvhView {
 
 }   // namespace tpt
 
+struct tpt_scene;
+// what the live-pixel table of a context was computed for (render.cu: k_tile_live)
+struct LiveKey {
+    const tpt_scene* scene;
+    uint64_t epoch;
+    tpt_camera cam;
+    int w, h, candidates, measured;
+};
+
 struct tpt_context {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -69,6 +78,11 @@ struct tpt_context {
     void* io_hits = nullptr;
     size_t io_capacity = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // live pixels per 8x4 tile of the last (scene geometry, camera, resolution) rendered: bounds what a batch can emit
+    uint8_t* d_tile_live = nullptr;
+    size_t tile_live_capacity = 0;
+    std::vector<uint8_t> tile_live_host;
+    LiveKey live_key = {};
     // per-stage timing (TPT_RENDER_STAGE_TIMES)
     std::vector<cudaEvent_t> stage_events;
     double stage_ms[4] = {0, 0, 0, 0};
@@ -103,6 +117,7 @@ struct tpt_scene {
     float4* tri_geom = nullptr;
     float4* tri_norm = nullptr;
     bool built = false;
+    uint64_t geom_epoch = 0;      // bumped by every build / refit: world-space geometry may have changed
     bool topology = false;        // hierarchy (children, parents, leaf order, range ends) of the last full build is intact: tpt_bvh_refit may reuse it
     bool any_emissive = false;    // some material has emission > 0 (else the reference's extra "direct" rays add nothing and are not traced)
     tpt::BvhView view() const { return tpt::BvhView{nodes, tri_geom, tri_norm, (int)n_faces}; }
