@@ -57,7 +57,8 @@ typedef struct tpt_hit {
 } tpt_hit;
 
 /* include/material.h:86-120 `Material` (60 bytes; only base_color, emission, eta, metallic are read
- * by the reference's kernels, src/path_tracer.cu:187-225,374-412) */
+ * by the reference's kernels, src/path_tracer.cu:187-225,374-412); unused[2] is `roughness`, read only
+ * under TPT_RENDER_ROUGH_METALS */
 typedef struct tpt_material {
     float base_color[3];
     float emission;
@@ -125,6 +126,10 @@ typedef struct tpt_render_config {
 #define TPT_RENDER_STAGE_TIMES 2u /* CUDA-event time of every wavefront kernel, summed per stage (one sync per batch) */
 #define TPT_RENDER_NO_PIXEL_CANDIDATES 8u /* check switch: camera samples walk the tree one by one instead of testing their
                                            * pixel's candidate triangles; the accumulation buffer is bit-identical either way */
+#define TPT_RENDER_ROUGH_METALS 32u /* metals (metallic > 0, eta = 0) use their `roughness` (Material float 8, loaded by the
+                                    * reference at src/mesh.cu:231 but read by none of its kernels): GGX microfacet reflection, visible-normal
+                                    * sampling, alpha = roughness^2, Fresnel = baseColor as for the mirror; alpha < 1e-3 is the reference's
+                                    * mirror, bit for bit.  Off by default: the reference's metals are perfect mirrors. */
 #define TPT_RENDER_REFIT 16u      /* tpt_do_trace only: refit (tpt_bvh_refit) instead of rebuilding when the scene has a hierarchy */
 #define TPT_RENDER_ENV_NEE 4u     /* sample the environment map from its alias table at every diffuse vertex (one extra shadow ray),
                                    * combined with the reference's cosine-sampled misses by the balance heuristic: same expectation as

@@ -536,11 +536,41 @@ inline float hemisphere_cosine_pdf(V3 dir, V3 n) {   // sampler.h:91-96
     float f = c > 0.0f ? 1.0f : 0.0f;
     return (c / kPi) * f;
 }
+// NOT in the reference (TPT_RENDER_ROUGH_METALS): GGX reflection for metals with alpha = roughness^2 >= 1e-3,
+// half vector from the distribution of visible normals (Heitz 2018), weight G1(wi) on top of baseColor; same local frame as
+// hemisphere_cosine.  Returns G1(wi) (0 below the surface).
+inline float rough_metal_direction(V3 rayDir, V3 n, float alpha, float xi1, float xi2, V3& out) {
+    V3 nn = dot(rayDir, n) > 0.0f ? n * -1.0f : n;
+    V3 xBase = nn.z == 0.0f ? v3(0, 0, 1) : v3(1.0f, 0.0f, -nn.x / nn.z);
+    xBase = xBase / norm(xBase);
+    V3 zBase = cross(xBase, nn);
+    V3 wo = v3(-dot(rayDir, xBase), -dot(rayDir, zBase), -dot(rayDir, nn));
+    V3 vh = v3(alpha * wo.x, alpha * wo.y, wo.z);
+    vh = vh / norm(vh);
+    float lensq = vh.x * vh.x + vh.y * vh.y;
+    V3 t1 = lensq > 0.0f ? v3(-vh.y, vh.x, 0.0f) / sqrtf(lensq) : v3(1, 0, 0);
+    V3 t2 = cross(vh, t1);
+    float r = sqrtf(xi1), phi = 2.0f * kPi * xi2;
+    float p1 = r * cosf(phi), sh = 0.5f * (1.0f + vh.z);
+    float p2 = (1.0f - sh) * sqrtf(std::max(1.0f - p1 * p1, 0.0f)) + sh * (r * sinf(phi));
+    V3 nh = p1 * t1 + p2 * t2 + sqrtf(std::max(1.0f - p1 * p1 - p2 * p2, 0.0f)) * vh;
+    V3 ne = v3(alpha * nh.x, alpha * nh.y, std::max(nh.z, 0.0f));
+    ne = ne / norm(ne);
+    V3 wi = (2.0f * dot(wo, ne)) * ne - wo;
+    out = wi.x * xBase + wi.y * zBase + wi.z * nn;
+    if (!(wi.z > 0.0f)) return 0.0f;
+    return 2.0f * wi.z / (wi.z + sqrtf(alpha * alpha + (1.0f - alpha * alpha) * wi.z * wi.z));
+}
 // path_tracer.cu:187-225.  xi1/xi2 are the pair of uniforms reserved for this call (a dielectric
 // consumes xi1 only, a mirror none, a diffuse surface both, in that order).
-inline float get_new_direction(V3 rayDir, V3 n, const Material& m, float xi1, float xi2, V3& nextDir, float& attenFactor) {
+inline float get_new_direction(V3 rayDir, V3 n, const Material& m, float xi1, float xi2, V3& nextDir, float& attenFactor,
+                               bool roughMetals = false) {
     float prob;
-    if (m.eta > 0.0f) {
+    const float alpha = m.unused[2] * m.unused[2];   // roughness (include/material.h:113), read only by the rough-metal extension
+    if (roughMetals && m.metallic > 0.0f && !(m.eta > 0.0f) && alpha >= 1e-3f) {
+        attenFactor = rough_metal_direction(rayDir, n, alpha, xi1, xi2, nextDir);
+        prob = 1.0f;
+    } else if (m.eta > 0.0f) {
         bool tir = false;
         float eta, cosI;
         V3 refr = refract(rayDir, n, m.eta, cosI, eta, tir);
@@ -642,6 +672,7 @@ struct SceneView {
     const uint8_t* env;
     int ew, eh;
     const float* envf = nullptr;   // float RGB map instead of `env` (HDR)
+    bool roughMetals = false;      // TPT_RENDER_ROUGH_METALS
 };
 
 struct Counters {
@@ -690,7 +721,7 @@ V3 trace_sample(const SceneView& S, const Camera& cam, int px, int py, int W, in
         draw_pair(key, 1u + 2u * (uint32_t)depth, xi1, xi2);
         V3 newDir;
         float attenFactor;
-        float prob = get_new_direction(ray.d, normal, mtl, xi1, xi2, newDir, attenFactor);
+        float prob = get_new_direction(ray.d, normal, mtl, xi1, xi2, newDir, attenFactor, S.roughMetals);
         attenuation[depth] = base * attenFactor;
         pStack[depth] = prob;
 
@@ -958,6 +989,9 @@ int orc_retest_triangle(const float* wverts, const uint32_t* indices, int fid, c
 // order exactly as the kernel does (totalRad += radiance; color += totalRad).
 // Region [x0,x1) x [y0,y1) only (bounded CPU samples); pixels outside are left untouched.
 // counters (optional): [rays, nInt, nLeaf].
+static bool g_rough_metals = false;
+// estimator extensions beyond the reference, off by default (bit 0: TPT_RENDER_ROUGH_METALS); applies to later orc_render* calls
+void orc_set_extensions(int flags) { g_rough_metals = (flags & 1) != 0; }
 void orc_render_env(const uint32_t* indices, int F, const float* wverts, const float* wnormals, const void* materials, int M,
                     const void* lut, int O, const void* lights, int L, const void* nodes36, const uint8_t* env, const float* envf,
                     int ew, int eh, const float* cam19, int W, int H, int x0, int y0, int x1, int y1, int spp, int sampleOffset,
@@ -976,7 +1010,7 @@ void orc_render_env(const uint32_t* indices, int F, const float* wverts, const f
                     int sampleStride, int maxDepth, uint64_t seed, float* out, uint64_t* counters) {
     SceneView S{indices, F, wverts, wnormals, reinterpret_cast<const Material*>(materials), M,
                 reinterpret_cast<const MtlInterval*>(lut), O, reinterpret_cast<const DeltaLight*>(lights), L,
-                reinterpret_cast<const RefNode*>(nodes36), env, ew, eh, envf};
+                reinterpret_cast<const RefNode*>(nodes36), env, ew, eh, envf, g_rough_metals};
     Camera cam;
     cam.vfov = cam19[0]; cam.aspect = cam19[1]; cam.nearPlane = cam19[2];
     std::memcpy(cam.c2w, cam19 + 3, 64);

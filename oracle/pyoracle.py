@@ -216,7 +216,8 @@ def retest_triangle(wverts, indices, fid, ray6, eps=1e-5):
 
 
 def render(scene: dict, W: int, H: int, spp: int, max_depth: int = 8, seed: int = 1, env: np.ndarray | None = None,
-           region=None, sample_offset: int = 0, sample_stride: int = 1, prepared=None, counters: bool = False):
+           region=None, sample_offset: int = 0, sample_stride: int = 1, prepared=None, counters: bool = False,
+           rough_metals: bool = False):
     """Restates src/path_tracer.cu:491-554 doTrace up to (not including) copyToFB.
 
     Returns the float32 radiance SUM buffer [H, W, 3] (row 0 = bottom of the image, as in the
@@ -245,11 +246,20 @@ def render(scene: dict, W: int, H: int, spp: int, max_depth: int = 8, seed: int 
         envp = _p(env)
     cnt = np.zeros(3, np.uint64)
     F = scene["indices"].size // 3
+    lib().orc_set_extensions(1 if rough_metals else 0)
+    try:
+        _render_env(scene, F, wv, wn, nodes, envp, envfp, ew, eh, W, H, x0, y0, x1, y1, spp, sample_offset, sample_stride, max_depth, seed,
+                    out, cnt if counters else None)
+    finally:
+        lib().orc_set_extensions(0)
+    return (out, cnt) if counters else out
+
+
+def _render_env(scene, F, wv, wn, nodes, envp, envfp, ew, eh, W, H, x0, y0, x1, y1, spp, sample_offset, sample_stride, max_depth, seed, out, cnt):
     lib().orc_render_env(_p(scene["indices"]), F, _p(wv), _p(wn), _p(scene["materials"]), scene["materials"].shape[0],
                      _p(scene["objects"]), scene["objects"].shape[0], _p(scene["lights"]), scene["lights"].shape[0],
                      _p(nodes), envp, envfp, ew, eh, _p(camera19(scene)), W, H, x0, y0, x1, y1, spp, sample_offset, sample_stride,
-                     max_depth, seed, _p(out), _p(cnt) if counters else None)
-    return (out, cnt) if counters else out
+                     max_depth, seed, _p(out), _p(cnt))
 
 
 def resolve_bgra8(radiance: np.ndarray, spp: int, fb: np.ndarray | None = None) -> np.ndarray:

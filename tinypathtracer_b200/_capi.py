@@ -25,6 +25,8 @@ TPT_RENDER_COUNTERS = 1
 TPT_RENDER_STAGE_TIMES = 2
 TPT_RENDER_ENV_NEE = 4
 TPT_RENDER_NO_PIXEL_CANDIDATES = 8
+TPT_RENDER_REFIT = 16
+TPT_RENDER_ROUGH_METALS = 32
 
 
 class Ray(C.Structure):

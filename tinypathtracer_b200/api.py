@@ -299,13 +299,14 @@ class Accum:
 
 
 def render_config(width, height, spp, max_depth=8, seed=1, sample_offset=0, sample_stride=1, counters=False, paths_in_flight=0,
-                  stage_times=False, env_nee=False, pixel_candidates=True):
+                  stage_times=False, env_nee=False, pixel_candidates=True, rough_metals=False, refit=False):
     c = capi.RenderConfig()
     c.width, c.height, c.spp, c.max_depth = width, height, spp, max_depth
     c.seed = seed
     c.sample_offset, c.sample_stride = sample_offset, sample_stride
     c.flags = (capi.TPT_RENDER_COUNTERS if counters else 0) | (capi.TPT_RENDER_STAGE_TIMES if stage_times else 0) | \
-              (capi.TPT_RENDER_ENV_NEE if env_nee else 0) | (0 if pixel_candidates else capi.TPT_RENDER_NO_PIXEL_CANDIDATES)
+              (capi.TPT_RENDER_ENV_NEE if env_nee else 0) | (0 if pixel_candidates else capi.TPT_RENDER_NO_PIXEL_CANDIDATES) | \
+              (capi.TPT_RENDER_ROUGH_METALS if rough_metals else 0) | (capi.TPT_RENDER_REFIT if refit else 0)
     c.paths_in_flight = paths_in_flight
     return c
 
@@ -322,14 +323,15 @@ class PathTracer:
 
     def render_into(self, scene: DeviceScene, camera: Camera, spp: int, max_depth: int = 8, seed: int = 1, sample_offset: int = 0,
                     sample_stride: int = 1, counters: bool = False, paths_in_flight: int = 0, accum: Accum | None = None,
-                    stage_times: bool = False, env_nee: bool = False, pixel_candidates: bool = True):
+                    stage_times: bool = False, env_nee: bool = False, pixel_candidates: bool = True, rough_metals: bool = False):
         cfg = render_config(self.m_width, self.m_height, spp, max_depth, seed, sample_offset, sample_stride, counters, paths_in_flight,
-                            stage_times, env_nee, pixel_candidates)
+                            stage_times, env_nee, pixel_candidates, rough_metals)
         acc = accum or self.m_radiance
         check(lib.tpt_render(scene._h, C.byref(camera.c), C.byref(cfg), acc._h))
 
-    def doTrace(self, scene: DeviceScene, camera: Camera, framebuffer: np.ndarray, nSamplesPerPixel: int, max_depth: int = 8, seed: int = 1):
+    def doTrace(self, scene: DeviceScene, camera: Camera, framebuffer: np.ndarray, nSamplesPerPixel: int, max_depth: int = 8, seed: int = 1,
+                refit: bool = False):
         """One frame exactly as src/path_tracer.cu:491-554: transform + BVH rebuild, clear, trace, copyToFB."""
-        cfg = render_config(self.m_width, self.m_height, nSamplesPerPixel, max_depth, seed)
+        cfg = render_config(self.m_width, self.m_height, nSamplesPerPixel, max_depth, seed, refit=refit)
         check(lib.tpt_do_trace(scene._h, C.byref(camera.c), C.byref(cfg), self.m_radiance._h, _ptr(framebuffer)))
         return framebuffer

@@ -238,7 +238,7 @@ int tpt_scene_create(tpt_context* ctx, const tpt_scene_desc* d, tpt_scene** out)
     for (size_t m = 0; m < d->n_materials; ++m) {
         const tpt_material& M = d->materials[m];
         mtl[2 * m] = make_float4(M.base_color[0], M.base_color[1], M.base_color[2], M.emission);
-        mtl[2 * m + 1] = make_float4(M.eta, M.metallic, 0.f, 0.f);
+        mtl[2 * m + 1] = make_float4(M.eta, M.metallic, M.unused[2] /* roughness (include/material.h:113) */, 0.f);
     }
     int rc = TPT_OK;
     auto A = [&](int r) { if (rc == TPT_OK) rc = r; };

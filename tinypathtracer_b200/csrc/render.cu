@@ -197,6 +197,35 @@ __device__ __forceinline__ float3 hemisphere_cosine(float xi1, float xi2, float3
     return (cp * sinT) * xBase + cosT * n + (sp * sinT) * zBase;
 }
 
+// Rough metal lobe (TPT_RENDER_ROUGH_METALS; not in the reference, whose metals are mirrors): GGX with alpha = roughness^2,
+// half-vector drawn from the distribution of VISIBLE normals (Heitz 2018) around the shading normal facing the ray, reflection
+// about it.  With Fresnel = baseColor (as for the mirror) the sample weight is baseColor * G1(wi), G1 the Smith masking term;
+// a direction below the surface has weight 0.  Returns G1(wi).  Local frame = the one hemisphere_cosine builds.
+__device__ __forceinline__ float rough_metal_direction(float3 rayDir, float3 n, float alpha, float xi1, float xi2, float3& out) {
+    const float3 nn = dot(rayDir, n) > 0.0f ? -n : n;
+    float3 xBase = (nn.z == 0.0f) ? f3(0.f, 0.f, 1.f) : f3(1.0f, 0.0f, -nn.x / nn.z);
+    xBase = (1.0f / sqrtf(dot(xBase, xBase))) * xBase;
+    const float3 zBase = cross(xBase, nn);
+    const float3 wo = f3(-dot(rayDir, xBase), -dot(rayDir, zBase), -dot(rayDir, nn));   // towards the viewer, local (x, y, z = normal)
+    float3 vh = f3(alpha * wo.x, alpha * wo.y, wo.z);
+    vh = (1.0f / sqrtf(dot(vh, vh))) * vh;
+    const float lensq = vh.x * vh.x + vh.y * vh.y;
+    const float3 t1 = lensq > 0.0f ? (1.0f / sqrtf(lensq)) * f3(-vh.y, vh.x, 0.0f) : f3(1.0f, 0.0f, 0.0f);
+    const float3 t2 = cross(vh, t1);
+    const float r = sqrtf(xi1), phi = 2.0f * kPi * xi2;
+    float sphi, cphi;
+    sincosf(phi, &sphi, &cphi);
+    const float p1 = r * cphi, sh = 0.5f * (1.0f + vh.z);
+    const float p2 = (1.0f - sh) * sqrtf(fmaxf(1.0f - p1 * p1, 0.0f)) + sh * (r * sphi);
+    const float3 nh = p1 * t1 + p2 * t2 + sqrtf(fmaxf(1.0f - p1 * p1 - p2 * p2, 0.0f)) * vh;
+    float3 ne = f3(alpha * nh.x, alpha * nh.y, fmaxf(nh.z, 0.0f));
+    ne = (1.0f / sqrtf(dot(ne, ne))) * ne;
+    const float3 wi = 2.0f * dot(wo, ne) * ne - wo;
+    out = wi.x * xBase + wi.y * zBase + wi.z * nn;
+    if (!(wi.z > 0.0f)) return 0.0f;
+    return 2.0f * wi.z / (wi.z + sqrtf(alpha * alpha + (1.0f - alpha * alpha) * wi.z * wi.z));
+}
+
 // getNewDirection, src/path_tracer.cu:187-225.  Returns false when the reference's pdf would be 0
 // (cosine sample below the horizon after rounding: its result is Inf/NaN; we drop the sub-path).
 __device__ __forceinline__ bool new_direction(float3 rayDir, float3 n, float eta_m, float metallic, float xi1, float xi2, float3& out) {
@@ -287,6 +316,7 @@ struct ShadeParams {
     uint64_t seedKey;
     int directRays;          // 0 when no material of the scene is emissive: the extra cosine "direct" ray can only add emission
     EnvSampler es;           // alias tables of the environment map (TPT_RENDER_ENV_NEE only)
+    int roughMetals;         // TPT_RENDER_ROUGH_METALS: metals with roughness^2 >= 1e-3 scatter by GGX instead of mirroring
     int pixelCandidates;     // k_primary: per-pixel candidate triangles instead of one tree traversal per camera sample
 };
 
@@ -355,7 +385,15 @@ __device__ __forceinline__ bool shade_vertex(const BvhView& bvh, const ShadePara
         vx.direct = new_direction(d, nrm, eta, metallic, a, b, vx.ddir);
         if (!vx.direct) atomicAdd(&ctr->dropped_nonfinite, 1ull);
     }
-    if (vx.next) {
+    const float alpha = m1.z * m1.z;
+    if (sp.roughMetals && metallic > 0.0f && !(eta > 0.0f) && alpha >= 1e-3f) {
+        // drawn at the last vertex too: G1 is the estimator's attenuation at this vertex and scales its light terms as well,
+        // as every attenuation does in the reference's unwind (src/path_tracer.cu:417-430)
+        float a, b;
+        rng_pair(key, 1u + 2u * (uint32_t)depth, a, b);
+        vx.Tn = vx.Tn * rough_metal_direction(d, nrm, alpha, a, b, vx.ndir);
+        vx.next = vx.next && (vx.Tn.x > 0.f || vx.Tn.y > 0.f || vx.Tn.z > 0.f);
+    } else if (vx.next) {
         float a, b;
         rng_pair(key, 1u + 2u * (uint32_t)depth, a, b);
         vx.next = new_direction(d, nrm, eta, metallic, a, b, vx.ndir);
@@ -1143,6 +1181,7 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
     sp.depth = 0;
     sp.directRays = s->any_emissive ? 1 : 0;
     sp.pixelCandidates = (cfg->flags & TPT_RENDER_NO_PIXEL_CANDIDATES) ? 0 : 1;
+    sp.roughMetals = (cfg->flags & TPT_RENDER_ROUGH_METALS) ? 1 : 0;
     sp.es = EnvSampler{ctx->env_prob, ctx->env_alias, ctx->env_mass, ctx->env_w, ctx->env_h};
     const BvhView view = s->view();
 
