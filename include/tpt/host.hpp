@@ -210,6 +210,8 @@ public:
     void saveCheckpoint(const std::string& file);
     void loadCheckpoint(const std::string& file);   // switches to progressive mode
     std::string m_sceneType = "gltf";   // "gltf" = the reference's loader; "gltf-full" = scene graph, all primitives (Scene)
+    bool m_roughMetals = false;   // TPT_RENDER_ROUGH_METALS: metals scatter by GGX from Material::roughness (the reference: mirrors)
+    bool m_refit = false;         // TPT_RENDER_REFIT: frames after the first keep the BVH hierarchy and refit it (the reference rebuilds)
     bool m_envNEE = false;   // TPT_RENDER_ENV_NEE: sample the environment map at diffuse vertices (same expectation, lower variance)
     std::string m_output;
     std::string m_outputFloat;   // PFM of the linear mean radiance (accumulator / samples), unclamped; empty = none

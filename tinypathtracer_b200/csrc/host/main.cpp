@@ -11,7 +11,7 @@ int main(int argc, char** argv) {
     std::string scene, env, out, outFloat;
     int w = 1920, h = 1080, spp = 64, depth = 8, frames = 1;
     unsigned long long seed = 1;
-    bool envNee = false, fullGltf = false, progressive = false;
+    bool envNee = false, fullGltf = false, progressive = false, roughMetals = false, refit = false;
     std::string checkpoint, resume;
     for (int i = 1; i < argc; ++i) {
         const std::string k = argv[i];
@@ -30,6 +30,8 @@ int main(int argc, char** argv) {
         else if (k == "--frames") frames = std::atoi(val());
         else if (k == "--seed") seed = std::strtoull(val(), nullptr, 10);
         else if (k == "--env-nee") envNee = true;
+        else if (k == "--rough-metals") roughMetals = true;
+        else if (k == "--refit") refit = true;
         else if (k == "--full-gltf") fullGltf = true;
         else if (k == "--progressive") progressive = true;
         else if (k == "--checkpoint") checkpoint = val();
@@ -37,7 +39,7 @@ int main(int argc, char** argv) {
         else { std::fprintf(stderr, "unknown argument %s\n", k.c_str()); return 2; }
     }
     if (scene.empty()) {
-        std::fprintf(stderr, "usage: tpt_render --scene file.gltf [--env sky.png|sky.jpg|sky.hdr|sky.pfm] [--w 1920 --h 1080 --spp 64 --depth 8 --frames 1 --seed 1 --env-nee --full-gltf --progressive --checkpoint file --resume file --out frame.png --out-float frame.pfm]\n");
+        std::fprintf(stderr, "usage: tpt_render --scene file.gltf [--env sky.png|sky.jpg|sky.hdr|sky.pfm] [--w 1920 --h 1080 --spp 64 --depth 8 --frames 1 --seed 1 --env-nee --rough-metals --refit --full-gltf --progressive --checkpoint file --resume file --out frame.png --out-float frame.pfm]\n");
         return 2;
     }
     try {
@@ -49,6 +51,8 @@ int main(int argc, char** argv) {
         pathTracer.m_frames = frames;
         pathTracer.m_seed = seed;
         pathTracer.m_envNEE = envNee;
+        pathTracer.m_roughMetals = roughMetals;
+        pathTracer.m_refit = refit;
         if (fullGltf) pathTracer.m_sceneType = "gltf-full";
         pathTracer.m_progressive = progressive;
         if (!resume.empty()) pathTracer.loadCheckpoint(resume);   // continues its sample sequence and seed

@@ -125,7 +125,7 @@ void PathTracer::doTrace(DeviceScene& scene, Camera& camera, unsigned char* fram
     cfg.seed = m_seed;
     cfg.sample_offset = 0;
     cfg.sample_stride = 1;
-    cfg.flags = m_envNEE ? TPT_RENDER_ENV_NEE : 0u;
+    cfg.flags = (m_envNEE ? TPT_RENDER_ENV_NEE : 0u) | (m_roughMetals ? TPT_RENDER_ROUGH_METALS : 0u) | (m_refit ? TPT_RENDER_REFIT : 0u);
     const tpt_camera cam = camera.toABI();
     const auto t0 = std::chrono::steady_clock::now();
     if (!m_progressive) {
