@@ -9,6 +9,11 @@ ROOT = Path(__file__).resolve().parents[1]
 if str(ROOT) not in sys.path:
     sys.path.insert(0, str(ROOT))
 
+# k_primary's specular continuation is limited to shallow trees by default (a speed heuristic, csrc/render.cu); the tests lift
+# the limit so that the continuation is exercised on every fixture — results are bit-identical either way, which is what
+# test_specular_continuation_is_bit_identical_to_queued_paths asserts against the queued form.
+os.environ.setdefault("TPT_SPEC_MAX_FACES", "100000000")
+
 SCENES = ["box", "box1", "box2", "tir", "ball", "light", "square"]
 GOLDEN = ROOT / "tests" / "golden"
 

@@ -434,3 +434,57 @@ def test_live_pixel_batches_change_nothing(tpt, ctx, built, scenes):
     pt.render_into(ds, cam2, spp=spp, max_depth=32, seed=3, paths_in_flight=W * H * 32)
     assert (pt.m_radiance.to_i64() == b).all() and not (a == b).all()
     assert ctx.counters()["queue_overflow"] == 0
+
+
+@pytest.mark.parametrize("name,depth", [("light", 8), ("tir", 32), ("box", 8), ("box2", 8), ("box1", 8)])
+def test_specular_continuation_is_bit_identical_to_queued_paths(name, depth, tpt, ctx, built, scenes):
+    """k_primary follows mirror / glass bounces of a camera path in registers (while-while traversal, no queue round trip)
+    until the first diffuse vertex, which is queued with the number of vertices it is ahead of its wave.  Same hits, same
+    RNG dimensions, exact integer accumulation: the accumulator and the ray counts must equal those of the queued form,
+    in both camera-ray forms (per-thread < 32 spp, warp-cooperative >= 32 spp)."""
+    ds, _ = built[name]
+    cam = tpt.Camera.from_scene(scenes[name])
+    W, H = 200, 120
+    pt = tpt.PathTracer(ctx, W, H, env_rgba8=synthetic_sky(128, 64))
+    for spp in (8, 40):
+        res = []
+        for cont in (True, False):
+            pt.m_radiance.clear()
+            ctx.reset_counters()
+            pt.render_into(ds, cam, spp=spp, max_depth=depth, seed=13, specular_continuation=cont)
+            c = ctx.counters()
+            res.append((pt.m_radiance.to_i64(), c["rays_extension"], c["rays_shadow"], c["rays_direct"], c["kernel_launches"]))
+            assert c["queue_overflow"] == 0
+        assert (res[0][0] == res[1][0]).all() and res[0][0].any()
+        assert res[0][1:4] == res[1][1:4], (res[0][1:], res[1][1:])
+
+
+def test_specular_continuation_with_delta_lights(tpt, ctx, scenes, orc):
+    """No fixture has both a delta light and a mirror / glass surface; box.gltf plus a point light has.  The shadow rays of the
+    vertices passed in registers are traced there too: accumulator and counters equal the queued form, and the image agrees
+    with the oracle (shared RNG)."""
+    s = dict(scenes["box"])
+    L = np.zeros(1, s["lights"].dtype)
+    L["type"] = 0                                     # point light inside the box
+    L["color"] = (1.0, 0.9, 0.8)
+    L["intensity"] = 0.6
+    wv, _ = orc.transform(s)
+    L["a"] = (wv.min(axis=0) + wv.max(axis=0)) * 0.5 + np.array([0.1, 0.2, 0.05], np.float32)
+    s["lights"] = L
+    ds = tpt.DeviceScene(ctx, s)
+    tpt.BVH(ds).construct()
+    cam = tpt.Camera.from_scene(s)
+    W, H, spp = 96, 54, 32
+    pt = tpt.PathTracer(ctx, W, H)
+    out = []
+    for cont in (True, False):
+        pt.m_radiance.clear()
+        ctx.reset_counters()
+        pt.render_into(ds, cam, spp=spp, seed=17, specular_continuation=cont)
+        c = ctx.counters()
+        out.append((pt.m_radiance.to_i64(), c["rays_extension"], c["rays_shadow"], c["rays_direct"]))
+    assert (out[0][0] == out[1][0]).all() and out[0][1:] == out[1][1:] and out[0][2] > 0
+    img = pt.m_radiance.to_f32() / spp
+    ref = orc.render(s, W, H, spp, seed=17) / spp
+    assert _relmse(img, ref) <= 2e-2
+    ds.close()

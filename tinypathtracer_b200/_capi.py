@@ -27,6 +27,7 @@ TPT_RENDER_ENV_NEE = 4
 TPT_RENDER_NO_PIXEL_CANDIDATES = 8
 TPT_RENDER_REFIT = 16
 TPT_RENDER_ROUGH_METALS = 32
+TPT_RENDER_NO_SPECULAR_CONTINUATION = 64
 
 
 class Ray(C.Structure):

@@ -299,14 +299,15 @@ class Accum:
 
 
 def render_config(width, height, spp, max_depth=8, seed=1, sample_offset=0, sample_stride=1, counters=False, paths_in_flight=0,
-                  stage_times=False, env_nee=False, pixel_candidates=True, rough_metals=False, refit=False):
+                  stage_times=False, env_nee=False, pixel_candidates=True, rough_metals=False, refit=False, specular_continuation=True):
     c = capi.RenderConfig()
     c.width, c.height, c.spp, c.max_depth = width, height, spp, max_depth
     c.seed = seed
     c.sample_offset, c.sample_stride = sample_offset, sample_stride
     c.flags = (capi.TPT_RENDER_COUNTERS if counters else 0) | (capi.TPT_RENDER_STAGE_TIMES if stage_times else 0) | \
               (capi.TPT_RENDER_ENV_NEE if env_nee else 0) | (0 if pixel_candidates else capi.TPT_RENDER_NO_PIXEL_CANDIDATES) | \
-              (capi.TPT_RENDER_ROUGH_METALS if rough_metals else 0) | (capi.TPT_RENDER_REFIT if refit else 0)
+              (capi.TPT_RENDER_ROUGH_METALS if rough_metals else 0) | (capi.TPT_RENDER_REFIT if refit else 0) | \
+              (0 if specular_continuation else capi.TPT_RENDER_NO_SPECULAR_CONTINUATION)
     c.paths_in_flight = paths_in_flight
     return c
 
@@ -323,9 +324,10 @@ class PathTracer:
 
     def render_into(self, scene: DeviceScene, camera: Camera, spp: int, max_depth: int = 8, seed: int = 1, sample_offset: int = 0,
                     sample_stride: int = 1, counters: bool = False, paths_in_flight: int = 0, accum: Accum | None = None,
-                    stage_times: bool = False, env_nee: bool = False, pixel_candidates: bool = True, rough_metals: bool = False):
+                    stage_times: bool = False, env_nee: bool = False, pixel_candidates: bool = True, rough_metals: bool = False,
+                    specular_continuation: bool = True):
         cfg = render_config(self.m_width, self.m_height, spp, max_depth, seed, sample_offset, sample_stride, counters, paths_in_flight,
-                            stage_times, env_nee, pixel_candidates, rough_metals)
+                            stage_times, env_nee, pixel_candidates, rough_metals, specular_continuation=specular_continuation)
         acc = accum or self.m_radiance
         check(lib.tpt_render(scene._h, C.byref(camera.c), C.byref(cfg), acc._h))
 

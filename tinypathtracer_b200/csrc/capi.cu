@@ -233,6 +233,7 @@ int tpt_scene_create(tpt_context* ctx, const tpt_scene_desc* d, tpt_scene** out)
     s->n_materials = d->n_materials;
     s->n_lights = d->n_lights;
     for (size_t m = 0; m < d->n_materials; ++m) s->any_emissive = s->any_emissive || d->materials[m].emission > 0.0f;
+    for (size_t m = 0; m < d->n_materials; ++m) s->any_specular = s->any_specular || d->materials[m].eta > 0.0f || d->materials[m].metallic > 0.0f;
     const size_t V = d->n_vertices, O = d->n_objects;
     std::vector<float4> mtl(2 * d->n_materials);
     for (size_t m = 0; m < d->n_materials; ++m) {

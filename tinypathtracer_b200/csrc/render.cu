@@ -38,7 +38,9 @@ namespace tpt {
 struct PathRec {
     float3 o, d, T;
     uint32_t pixel, sample;
-    uint32_t w;   // extension ray (env NEE only): float bits of the solid-angle pdf its direction was drawn with, 0 = delta / camera
+    uint32_t w;   // extension ray, env NEE kernels: float bits of the solid-angle pdf its direction was drawn with, 0 = delta / camera;
+                  // other kernels: how many vertices AHEAD of its wave the path is (k_primary follows specular chains in registers,
+                  // so the ray consumed by wave w heads for vertex w + ahead)
 };
 __device__ __forceinline__ PathRec load_path(const float4* __restrict__ p, uint32_t i) {
     const float4 a = __ldcs(p + 3 * (size_t)i), b = __ldcs(p + 3 * (size_t)i + 1), c = __ldcs(p + 3 * (size_t)i + 2);
@@ -316,6 +318,8 @@ struct ShadeParams {
     uint64_t seedKey;
     int directRays;          // 0 when no material of the scene is emissive: the extra cosine "direct" ray can only add emission
     EnvSampler es;           // alias tables of the environment map (TPT_RENDER_ENV_NEE only)
+    int continueSpecular;    // how many mirror / glass bounces after the camera vertex k_primary<SPEC> follows in registers
+    int continueVote;        // ... when at least continueVote / 4 of the lanes that are there together want to
     int roughMetals;         // TPT_RENDER_ROUGH_METALS: metals with roughness^2 >= 1e-3 scatter by GGX instead of mirroring
     int pixelCandidates;     // k_primary: per-pixel candidate triangles instead of one tree traversal per camera sample
 };
@@ -332,6 +336,7 @@ struct Vertex {
     float3 ndir;     // next direction
     float3 ddir;     // direction of the "direct" ray
     bool next, direct;
+    bool delta;      // ndir came from a mirror / glass lobe: one determined direction, nothing to stage or sort
     // TPT_RENDER_ENV_NEE only: pdf of ndir (0 = delta lobe), and the environment sample (direction, weighted contribution)
     float pb;
     bool nee;
@@ -386,7 +391,9 @@ __device__ __forceinline__ bool shade_vertex(const BvhView& bvh, const ShadePara
         if (!vx.direct) atomicAdd(&ctr->dropped_nonfinite, 1ull);
     }
     const float alpha = m1.z * m1.z;
+    vx.delta = eta > 0.0f || metallic > 0.0f;
     if (sp.roughMetals && metallic > 0.0f && !(eta > 0.0f) && alpha >= 1e-3f) {
+        vx.delta = false;
         // drawn at the last vertex too: G1 is the estimator's attenuation at this vertex and scales its light terms as well,
         // as every attenuation does in the reference's unwind (src/path_tracer.cu:417-430)
         float a, b;
@@ -434,7 +441,7 @@ struct QueueOut {
 // "direct" ray, the environment sample — with one atomic.  UNIFORM: every lane of the warp is in the same segment.
 template <bool NEE, bool UNIFORM>
 __device__ __forceinline__ void emit_vertex(const ShadeParams& sp, const QueueOut& q, uint32_t seg, const Vertex& vx, uint32_t pixel,
-                                            uint32_t sample, DeviceCounters* ctr) {
+                                            uint32_t sample, uint32_t ahead, DeviceCounters* ctr) {
     const unsigned here = __activemask();
     const unsigned m = UNIFORM ? here : __match_any_sync(here, seg);
     const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
@@ -469,17 +476,18 @@ __device__ __forceinline__ void emit_vertex(const ShadeParams& sp, const QueueOu
     }
     if (vx.direct) store_path(sec, slot++, vx.P, vx.ddir, vx.Tn, pixel, sample, kKindDirect);
     if (NEE && vx.nee) store_path(sec, slot++, vx.P, vx.ldir, vx.lw, pixel, sample, kKindShadow);
-    if (vx.next) store_path(ext, extSlot, vx.P, vx.ndir, vx.Tn, pixel, sample, NEE ? __float_as_uint(vx.pb) : 0u);
+    if (vx.next) store_path(ext, extSlot, vx.P, vx.ndir, vx.Tn, pixel, sample, NEE ? __float_as_uint(vx.pb) : ahead);
 }
 
 // ---- wave 0: generate + extend + shade, fused ---------------------------------------------------------
 // One camera sample: jitter, direction, closest hit among the pixel's candidates (cand/bound: nc entries sorted by a
 // lower bound of t) or by a tree walk (nc < 0) or none at all (nc == 0), then the first vertex.  Terminal
 // contributions are summed into (aR, aG, aB) in exact fixed point.
-template <bool COUNT, bool NEE>
+template <bool COUNT, bool NEE, bool SPEC>
 __device__ __forceinline__ void primary_sample(const BvhView& bvh, const ShadeParams& sp, const CameraParams& cam, const QueueOut& q, uint32_t seg,
                                                int px, int py, uint32_t pixel, uint32_t sIdx, float3 o, int nc, const int* cand, const int* bound, int candStride,
-                                               int* stack, long long& aR, long long& aG, long long& aB, unsigned& nt, DeviceCounters* ctr) {
+                                               int* stack, long long& aR, long long& aG, long long& aB, unsigned& nt, unsigned& nExt, unsigned& nShadow,
+                                               DeviceCounters* ctr) {
     float ju, jv;
     rng_pair(rng_path_key(sp.seedKey, pixel, sIdx), 0u, ju, jv);
     const float3 d = primary_dir(cam, px, py, ju, jv);
@@ -497,18 +505,75 @@ __device__ __forceinline__ void primary_sample(const BvhView& bvh, const ShadePa
     } else if (nc < 0) {
         h = traverse<COUNT>(bvh, o, d, false, stack, &ctr->node_visits, &ctr->tri_tests);
     }
-    float3 term;
-    Vertex vx;
-    if (shade_vertex<NEE>(bvh, sp, 0, o, d, f3(1.f, 1.f, 1.f), 0u, pixel, sIdx, h, term, vx, ctr)) {
-        emit_vertex<NEE, true>(sp, q, seg, vx, pixel, sIdx, ctr);
-    } else if (term.x != 0.f || term.y != 0.f || term.z != 0.f) {
-        if (finite3(term)) {
-            aR += to_fixed(term.x);
-            aG += to_fixed(term.y);
-            aB += to_fixed(term.z);
-        } else {
-            atomicAdd(&ctr->dropped_nonfinite, 1ull);
+    if (!SPEC) {
+        float3 term;
+        Vertex vx;
+        if (shade_vertex<NEE>(bvh, sp, 0, o, d, f3(1.f, 1.f, 1.f), 0u, pixel, sIdx, h, term, vx, ctr)) {
+            emit_vertex<NEE, true>(sp, q, seg, vx, pixel, sIdx, 0u, ctr);
+        } else if (term.x != 0.f || term.y != 0.f || term.z != 0.f) {
+            if (finite3(term)) {
+                aR += to_fixed(term.x);
+                aG += to_fixed(term.y);
+                aB += to_fixed(term.z);
+            } else {
+                atomicAdd(&ctr->dropped_nonfinite, 1ull);
+            }
         }
+        return;
+    }
+    // SPEC (scenes with mirror / glass materials; not the env-NEE kernels): specular continuation.  A path that leaves a vertex
+    // through a mirror / glass lobe is one determined ray; when (nearly) all lanes that are here together want to go on that
+    // way — a warp whose pixels lie on a mirror — the ray is traced right here with the while-while traversal instead of going
+    // through a queue and the next wave, for at most sp.continueSpecular bounces (further down a chain the lanes have drifted
+    // apart and k_wave's self-scheduling warps do better).  The first vertex not passed this way is queued with the number of
+    // vertices it is AHEAD of its wave; terminal contributions stay in registers.  Delta-light shadow rays of the vertices
+    // passed are traced here too, so a camera sample still emits the rays of at most one vertex (the pool bound).
+    float3 ro = o, rd = d, T = f3(1.f, 1.f, 1.f);
+    int depth = 0;
+    while (true) {
+        float3 term;
+        Vertex vx;
+        if (!shade_vertex<NEE>(bvh, sp, depth, ro, rd, T, 0u, pixel, sIdx, h, term, vx, ctr)) {
+            if (term.x != 0.f || term.y != 0.f || term.z != 0.f) {
+                if (finite3(term)) {
+                    aR += to_fixed(term.x);
+                    aG += to_fixed(term.y);
+                    aB += to_fixed(term.z);
+                } else {
+                    atomicAdd(&ctr->dropped_nonfinite, 1ull);
+                }
+            }
+            break;
+        }
+        const bool want = vx.delta && vx.next && depth < sp.continueSpecular;
+        const unsigned here = __activemask();
+        const unsigned wants = __ballot_sync(here, want);
+        if (!want || 4 * __popc(wants) < sp.continueVote * __popc(here)) {   // a heuristic only: either way gives the same sums
+            emit_vertex<NEE, true>(sp, q, seg, vx, pixel, sIdx, (uint32_t)depth, ctr);
+            break;
+        }
+        for (int l = 0; l < sp.nLights; ++l) {   // what wave depth+1 would do with this vertex's shadow rays
+            float3 ldir, lrad;
+            light_incoming(sp.lights[l], vx.P, ldir, lrad);
+            const HitRec sh = traverse<COUNT>(bvh, vx.P, ldir, true, stack, &ctr->node_visits, &ctr->tri_tests);
+            ++nShadow;
+            if (sh.leaf < 0) {
+                const float3 c = vx.Tn * (vx.base * lrad);
+                if (finite3(c)) {
+                    if (c.x != 0.f) aR += to_fixed(c.x);
+                    if (c.y != 0.f) aG += to_fixed(c.y);
+                    if (c.z != 0.f) aB += to_fixed(c.z);
+                } else {
+                    atomicAdd(&ctr->dropped_nonfinite, 1ull);
+                }
+            }
+        }
+        ro = vx.P;
+        rd = vx.ndir;
+        T = vx.Tn;
+        ++depth;
+        ++nExt;
+        h = traverse<COUNT>(bvh, ro, rd, false, stack, &ctr->node_visits, &ctr->tri_tests);
     }
 }
 
@@ -518,6 +583,16 @@ __device__ __forceinline__ int pixel_candidates(const BvhView& bvh, const ShadeP
                                                 int* stack, unsigned& nv) {
     return sp.pixelCandidates ? frustum_collect(bvh, pixel_frustum(cam, px, py, o), stack, nv)
                               : (frustum_may_hit(bvh, pixel_frustum(cam, px, py, o), stack) ? -1 : 0);
+}
+
+// rays k_primary traced in registers (specular continuation) never see a queue, where k_wave counts its rays
+__device__ __forceinline__ void flush_ray_counters(unsigned nExt, unsigned nShadow, DeviceCounters* ctr) {
+    const unsigned m = __activemask();
+    const unsigned se = __reduce_add_sync(m, nExt), ss = __reduce_add_sync(m, nShadow);
+    if ((threadIdx.x & 31) == __ffs(m) - 1) {
+        if (se) atomicAdd(&ctr->rays_extension, (unsigned long long)se);
+        if (ss) atomicAdd(&ctr->rays_shadow, (unsigned long long)ss);
+    }
 }
 
 __device__ __forceinline__ void flush_trav_counters(unsigned nv, unsigned nt, DeviceCounters* ctr) {
@@ -531,7 +606,7 @@ __device__ __forceinline__ void flush_trav_counters(unsigned nv, unsigned nt, De
 
 // Form A (fewer than 32 samples per pixel in this launch): thread = (pixel of an 8x4 tile, group of `spt`
 // consecutive local samples); the candidates stay in the thread's own stack array.
-template <bool COUNT, bool NEE>
+template <bool COUNT, bool NEE, bool SPEC>
 __global__ void __launch_bounds__(128) k_primary(BvhView bvh, ShadeParams sp, CameraParams cam, int W, int H, uint32_t nPadded,
                                                  uint32_t kSamples, uint32_t spt, uint32_t sampleBase, uint32_t sampleStride, QueueOut q,
                                                  unsigned long long* __restrict__ acc, DeviceCounters* ctr) {
@@ -549,7 +624,7 @@ __global__ void __launch_bounds__(128) k_primary(BvhView bvh, ShadeParams sp, Ca
     int stack[kStackSize];
     stack[0] = kStackSentinel;
     const float3 o = xmat4_point(cam.c2w, f3(0.f, 0.f, 0.f));   // the camera position: the same for every sample
-    unsigned nv = 0, nt = 0;
+    unsigned nv = 0, nt = 0, nExt = 0, nShadow = 0;
     const int nc = pixel_candidates(bvh, sp, cam, px, py, o, stack, nv);
     if (nc == 0) {
         const unsigned m = __activemask();
@@ -562,9 +637,10 @@ __global__ void __launch_bounds__(128) k_primary(BvhView bvh, ShadeParams sp, Ca
         if ((threadIdx.x & 31) == __ffs(m) - 1) atomicAdd(&ctr->rays_candidates, (unsigned long long)n);
     }
     for (uint32_t sl = s0; sl < s1; ++sl)
-        primary_sample<COUNT, NEE>(bvh, sp, cam, q, blockIdx.x & (kSegments - 1), px, py, pixel, sampleBase + sl * sampleStride, o, nc, stack + kStackSize - 1,
-                                   stack + kStackSize - 1 - kMaxCandidates, -1, stack, aR, aG, aB, nt, ctr);
+        primary_sample<COUNT, NEE, SPEC>(bvh, sp, cam, q, blockIdx.x & (kSegments - 1), px, py, pixel, sampleBase + sl * sampleStride, o, nc, stack + kStackSize - 1,
+                                   stack + kStackSize - 1 - kMaxCandidates, -1, stack, aR, aG, aB, nt, nExt, nShadow, ctr);
     if (COUNT) flush_trav_counters(nv, nt, ctr);
+    flush_ray_counters(nExt, nShadow, ctr);
     unsigned long long* dst = acc + 3 * (size_t)pixel;
     if (aR) atomicAdd(dst + 0, (unsigned long long)aR);
     if (aG) atomicAdd(dst + 1, (unsigned long long)aG);
@@ -589,7 +665,7 @@ __device__ __forceinline__ long long group_sum_ll(long long v) {
 #ifndef TPT_COOP_MIN_BLOCKS
 #define TPT_COOP_MIN_BLOCKS 7
 #endif
-template <bool COUNT, bool NEE>
+template <bool COUNT, bool NEE, bool SPEC>
 __global__ void __launch_bounds__(128, TPT_COOP_MIN_BLOCKS) k_primary_coop(BvhView bvh, ShadeParams sp, CameraParams cam, int W, int H, uint32_t nPadded,
                                                       uint32_t kSamples, uint32_t spt, uint32_t sampleBase, uint32_t sampleStride, QueueOut q,
                                                       unsigned long long* __restrict__ acc, DeviceCounters* ctr) {
@@ -606,7 +682,7 @@ __global__ void __launch_bounds__(128, TPT_COOP_MIN_BLOCKS) k_primary_coop(BvhVi
     int stack[kStackSize];
     stack[0] = kStackSentinel;
     const float3 o = xmat4_point(cam.c2w, f3(0.f, 0.f, 0.f));
-    unsigned nv = 0, nt = 0;
+    unsigned nv = 0, nt = 0, nExt = 0, nShadow = 0;
     int nc = 0;
     if (inside) {
         nc = pixel_candidates(bvh, sp, cam, px, py, o, stack, nv);
@@ -636,8 +712,8 @@ __global__ void __launch_bounds__(128, TPT_COOP_MIN_BLOCKS) k_primary_coop(BvhVi
         long long aR = 0, aG = 0, aB = 0;
         if (have)
             for (uint32_t sl = s0 + sub; sl < s1; sl += kCoopLanes)
-                primary_sample<COUNT, NEE>(bvh, sp, cam, q, blockIdx.x & (kSegments - 1), pxp, pyp, pixel, sampleBase + sl * sampleStride, o, ncp,
-                                           &sCand[wib][0][pl], &sBound[wib][0][pl], 32, stack, aR, aG, aB, nt, ctr);
+                primary_sample<COUNT, NEE, SPEC>(bvh, sp, cam, q, blockIdx.x & (kSegments - 1), pxp, pyp, pixel, sampleBase + sl * sampleStride, o, ncp,
+                                           &sCand[wib][0][pl], &sBound[wib][0][pl], 32, stack, aR, aG, aB, nt, nExt, nShadow, ctr);
         __syncwarp();
         if (__ballot_sync(0xffffffffu, (aR | aG | aB) != 0)) {
             aR = group_sum_ll(aR);
@@ -650,6 +726,7 @@ __global__ void __launch_bounds__(128, TPT_COOP_MIN_BLOCKS) k_primary_coop(BvhVi
         }
     }
     if (COUNT) flush_trav_counters(nv, nt, ctr);
+    flush_ray_counters(nExt, nShadow, ctr);
 }
 
 // Pre-pass for the batch size: how many pixels of each 8x4 tile can emit a path at all (the same pyramid walk k_primary does,
@@ -706,8 +783,9 @@ __device__ __forceinline__ void shade_staged(const BvhView& bvh, const ShadePara
         h.prim = -1;
         float3 term;
         Vertex vx;
-        if (shade_vertex<NEE>(bvh, sp, sp.depth, p.o, p.d, p.T, p.w, p.pixel, p.sample, h, term, vx, ctr))
-            emit_vertex<NEE, true>(sp, q, 0u, vx, p.pixel, p.sample, ctr);
+        const uint32_t ahead = NEE ? 0u : p.w;
+        if (shade_vertex<NEE>(bvh, sp, sp.depth + (int)ahead, p.o, p.d, p.T, NEE ? p.w : 0u, p.pixel, p.sample, h, term, vx, ctr))
+            emit_vertex<NEE, true>(sp, q, 0u, vx, p.pixel, p.sample, ahead, ctr);
         else accum_add(acc, p.pixel, term, ctr);
     }
     __syncwarp();
@@ -1182,6 +1260,10 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
     sp.directRays = s->any_emissive ? 1 : 0;
     sp.pixelCandidates = (cfg->flags & TPT_RENDER_NO_PIXEL_CANDIDATES) ? 0 : 1;
     sp.roughMetals = (cfg->flags & TPT_RENDER_ROUGH_METALS) ? 1 : 0;
+    static const int specChain = getenv("TPT_SPEC_CHAIN") ? atoi(getenv("TPT_SPEC_CHAIN")) : 4;   // tuning switches
+    static const int specVote = getenv("TPT_SPEC_VOTE") ? atoi(getenv("TPT_SPEC_VOTE")) : 3;
+    sp.continueSpecular = (cfg->flags & TPT_RENDER_NO_SPECULAR_CONTINUATION) ? 0 : specChain;
+    sp.continueVote = specVote;
     sp.es = EnvSampler{ctx->env_prob, ctx->env_alias, ctx->env_mass, ctx->env_w, ctx->env_h};
     const BvhView view = s->view();
 
@@ -1296,11 +1378,18 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
     }
     const int variant = (counted ? 1 : 0) + (nee ? 2 : 0);
     const unsigned gridWave = ctx->wave_grid[variant];
-    const auto kPrimary = variant == 0 ? k_primary<false, false> : variant == 1 ? k_primary<true, false> : variant == 2 ? k_primary<false, true> : k_primary<true, true>;
-    const auto kPrimaryCoop = variant == 0   ? k_primary_coop<false, false>
-                              : variant == 1 ? k_primary_coop<true, false>
-                              : variant == 2 ? k_primary_coop<false, true>
-                                             : k_primary_coop<true, true>;
+    // SPEC kernels (specular continuation) only where they pay: the scene has a mirror / glass material, no env NEE, and the
+    // tree is shallow.  Following a ray in k_primary saves a queue round trip and k_wave's scheduling (a fixed cost per ray) but
+    // walks the tree in lock-step with the warp's other rays; measured: light.gltf (80 triangles) 18.1 -> 14.7 ms, tir.gltf
+    // (6) 6.37 -> 6.21 ms, box.gltf (1 932, long divergent walks inside the box) 10.7 -> 11.1 ms, hence the limit.
+    static const size_t specMaxFaces = getenv("TPT_SPEC_MAX_FACES") ? (size_t)atoll(getenv("TPT_SPEC_MAX_FACES")) : 512;   // tuning switch
+    const bool spec = s->any_specular && !nee && sp.continueSpecular > 0 && s->n_faces <= specMaxFaces;
+    const auto kPrimary = spec ? (counted ? k_primary<true, false, true> : k_primary<false, false, true>)
+                          : variant == 0 ? k_primary<false, false, false> : variant == 1 ? k_primary<true, false, false>
+                          : variant == 2 ? k_primary<false, true, false> : k_primary<true, true, false>;
+    const auto kPrimaryCoop = spec ? (counted ? k_primary_coop<true, false, true> : k_primary_coop<false, false, true>)
+                              : variant == 0 ? k_primary_coop<false, false, false> : variant == 1 ? k_primary_coop<true, false, false>
+                              : variant == 2 ? k_primary_coop<false, true, false> : k_primary_coop<true, true, false>;
     const auto kWave = variant == 0 ? k_wave<false, false, false> : variant == 1 ? k_wave<true, false, false> : variant == 2 ? k_wave<false, true, false> : k_wave<true, true, false>;
     const auto kWave1 = variant == 0 ? k_wave<false, false, true> : variant == 1 ? k_wave<true, false, true> : variant == 2 ? k_wave<false, true, true> : k_wave<true, true, true>;
 

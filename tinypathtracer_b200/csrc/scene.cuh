@@ -119,6 +119,7 @@ struct tpt_scene {
     bool built = false;
     uint64_t geom_epoch = 0;      // bumped by every build / refit: world-space geometry may have changed
     bool topology = false;        // hierarchy (children, parents, leaf order, range ends) of the last full build is intact: tpt_bvh_refit may reuse it
+    bool any_specular = false;    // some material is a mirror or glass (metallic > 0 or eta > 0): k_primary's specular continuation can apply
     bool any_emissive = false;    // some material has emission > 0 (else the reference's extra "direct" rays add nothing and are not traced)
     tpt::BvhView view() const { return tpt::BvhView{nodes, tri_geom, tri_norm, (int)n_faces}; }
 };
