@@ -130,8 +130,9 @@ typedef struct tpt_render_config {
                                     * reference at src/mesh.cu:231 but read by none of its kernels): GGX microfacet reflection, visible-normal
                                     * sampling, alpha = roughness^2, Fresnel = baseColor as for the mirror; alpha < 1e-3 is the reference's
                                     * mirror, bit for bit.  Off by default: the reference's metals are perfect mirrors. */
-#define TPT_RENDER_NO_SPECULAR_CONTINUATION 64u /* check switch: k_primary queues the ray that leaves a mirror / glass camera vertex like any
-                                                * other instead of following the specular chain in registers; same accumulator bits */
+#define TPT_RENDER_NO_SPECULAR_CONTINUATION 64u /* check switch: k_primary queues every ray of the camera vertex (the ray that leaves a mirror /
+                                                * glass vertex, the delta-light shadow rays) instead of tracing them itself in registers;
+                                                * same accumulator bits, same ray counts */
 #define TPT_RENDER_REFIT 16u      /* tpt_do_trace only: refit (tpt_bvh_refit) instead of rebuilding when the scene has a hierarchy */
 #define TPT_RENDER_ENV_NEE 4u     /* sample the environment map from its alias table at every diffuse vertex (one extra shadow ray),
                                    * combined with the reference's cosine-sampled misses by the balance heuristic: same expectation as

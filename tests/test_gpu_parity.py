@@ -436,7 +436,7 @@ def test_live_pixel_batches_change_nothing(tpt, ctx, built, scenes):
     assert ctx.counters()["queue_overflow"] == 0
 
 
-@pytest.mark.parametrize("name,depth", [("light", 8), ("tir", 32), ("box", 8), ("box2", 8), ("box1", 8)])
+@pytest.mark.parametrize("name,depth", [("light", 8), ("tir", 32), ("box", 8), ("box2", 8), ("box1", 8), ("ball", 8)])
 def test_specular_continuation_is_bit_identical_to_queued_paths(name, depth, tpt, ctx, built, scenes):
     """k_primary follows mirror / glass bounces of a camera path in registers (while-while traversal, no queue round trip)
     until the first diffuse vertex, which is queued with the number of vertices it is ahead of its wave.  Same hits, same

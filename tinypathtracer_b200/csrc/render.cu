@@ -439,7 +439,7 @@ struct QueueOut {
 // Emit the rays of a shaded vertex from whatever lanes are here (diverged callers allowed): the lanes of one
 // segment that are here together reserve all their slots — one extension ray, one shadow ray per delta light, the
 // "direct" ray, the environment sample — with one atomic.  UNIFORM: every lane of the warp is in the same segment.
-template <bool NEE, bool UNIFORM>
+template <bool NEE, bool UNIFORM, bool LIGHTS = true>
 __device__ __forceinline__ void emit_vertex(const ShadeParams& sp, const QueueOut& q, uint32_t seg, const Vertex& vx, uint32_t pixel,
                                             uint32_t sample, uint32_t ahead, DeviceCounters* ctr) {
     const unsigned here = __activemask();
@@ -448,7 +448,7 @@ __device__ __forceinline__ void emit_vertex(const ShadeParams& sp, const QueueOu
     const unsigned lt = (1u << lane) - 1u;
     const unsigned bExt = __ballot_sync(here, vx.next) & m, bDir = __ballot_sync(here, vx.direct) & m,
                    bNee = NEE ? (__ballot_sync(here, vx.nee) & m) : 0u;
-    const uint32_t nL = (uint32_t)sp.nLights;
+    const uint32_t nL = LIGHTS ? (uint32_t)sp.nLights : 0u;   // !LIGHTS: the caller has traced the vertex's light shadow rays itself
     const uint32_t nExt = __popc(bExt), nSec = nL * __popc(m) + __popc(bDir) + __popc(bNee);
     unsigned long long base = 0;
     if (lane == leader && nExt + nSec != 0u) {
@@ -469,7 +469,7 @@ __device__ __forceinline__ void emit_vertex(const ShadeParams& sp, const QueueOu
         return;
     }
     // delta lights: one infinite shadow ray per light, contribution T_d * baseColor * Li
-    for (int l = 0; l < sp.nLights; ++l) {
+    for (int l = 0; l < (int)nL; ++l) {
         float3 ldir, lrad;
         light_incoming(sp.lights[l], vx.P, ldir, lrad);
         store_path(sec, slot++, vx.P, ldir, vx.Tn * (vx.base * lrad), pixel, sample, kKindShadow);
@@ -479,15 +479,41 @@ __device__ __forceinline__ void emit_vertex(const ShadeParams& sp, const QueueOu
     if (vx.next) store_path(ext, extSlot, vx.P, vx.ndir, vx.Tn, pixel, sample, NEE ? __float_as_uint(vx.pb) : ahead);
 }
 
+// The delta-light shadow rays of one vertex, traced where the vertex was shaded (k_primary): the lanes of a pixel group sit at
+// neighbouring points and aim at the same light, so the while-while any-hit walk stays coherent, and the rays never cost a
+// queue item, a second read and k_wave's scheduling.  Adds exactly what k_wave would add for them.
+template <bool COUNT>
+__device__ __forceinline__ void light_shadows_here(const BvhView& bvh, const ShadeParams& sp, const Vertex& vx, int* stack, long long& aR, long long& aG,
+                                                   long long& aB, unsigned& nShadow, DeviceCounters* ctr) {
+    for (int l = 0; l < sp.nLights; ++l) {
+        float3 ldir, lrad;
+        light_incoming(sp.lights[l], vx.P, ldir, lrad);
+        const HitRec sh = traverse<COUNT>(bvh, vx.P, ldir, true, stack, &ctr->node_visits, &ctr->tri_tests);
+        ++nShadow;
+        if (sh.leaf < 0) {
+            const float3 c = vx.Tn * (vx.base * lrad);
+            if (finite3(c)) {
+                if (c.x != 0.f) aR += to_fixed(c.x);
+                if (c.y != 0.f) aG += to_fixed(c.y);
+                if (c.z != 0.f) aB += to_fixed(c.z);
+            } else {
+                atomicAdd(&ctr->dropped_nonfinite, 1ull);
+            }
+        }
+    }
+}
+
 // ---- wave 0: generate + extend + shade, fused ---------------------------------------------------------
 // One camera sample: jitter, direction, closest hit among the pixel's candidates (cand/bound: nc entries sorted by a
 // lower bound of t) or by a tree walk (nc < 0) or none at all (nc == 0), then the first vertex.  Terminal
 // contributions are summed into (aR, aG, aB) in exact fixed point.
-template <bool COUNT, bool NEE, bool SPEC>
+// MODE bit 0 (SPEC): specular continuation; bit 1 (LHERE): the camera-side vertices' light shadow rays are traced here.
+template <bool COUNT, bool NEE, int MODE>
 __device__ __forceinline__ void primary_sample(const BvhView& bvh, const ShadeParams& sp, const CameraParams& cam, const QueueOut& q, uint32_t seg,
                                                int px, int py, uint32_t pixel, uint32_t sIdx, float3 o, int nc, const int* cand, const int* bound, int candStride,
                                                int* stack, long long& aR, long long& aG, long long& aB, unsigned& nt, unsigned& nExt, unsigned& nShadow,
                                                DeviceCounters* ctr) {
+    constexpr bool SPEC = (MODE & 1) != 0, LHERE = (MODE & 2) != 0;
     float ju, jv;
     rng_pair(rng_path_key(sp.seedKey, pixel, sIdx), 0u, ju, jv);
     const float3 d = primary_dir(cam, px, py, ju, jv);
@@ -509,7 +535,8 @@ __device__ __forceinline__ void primary_sample(const BvhView& bvh, const ShadePa
         float3 term;
         Vertex vx;
         if (shade_vertex<NEE>(bvh, sp, 0, o, d, f3(1.f, 1.f, 1.f), 0u, pixel, sIdx, h, term, vx, ctr)) {
-            emit_vertex<NEE, true>(sp, q, seg, vx, pixel, sIdx, 0u, ctr);
+            if (LHERE) light_shadows_here<COUNT>(bvh, sp, vx, stack, aR, aG, aB, nShadow, ctr);
+            emit_vertex<NEE, true, !LHERE>(sp, q, seg, vx, pixel, sIdx, 0u, ctr);
         } else if (term.x != 0.f || term.y != 0.f || term.z != 0.f) {
             if (finite3(term)) {
                 aR += to_fixed(term.x);
@@ -549,25 +576,11 @@ __device__ __forceinline__ void primary_sample(const BvhView& bvh, const ShadePa
         const unsigned here = __activemask();
         const unsigned wants = __ballot_sync(here, want);
         if (!want || 4 * __popc(wants) < sp.continueVote * __popc(here)) {   // a heuristic only: either way gives the same sums
-            emit_vertex<NEE, true>(sp, q, seg, vx, pixel, sIdx, (uint32_t)depth, ctr);
+            if (LHERE) light_shadows_here<COUNT>(bvh, sp, vx, stack, aR, aG, aB, nShadow, ctr);
+            emit_vertex<NEE, true, !LHERE>(sp, q, seg, vx, pixel, sIdx, (uint32_t)depth, ctr);
             break;
         }
-        for (int l = 0; l < sp.nLights; ++l) {   // what wave depth+1 would do with this vertex's shadow rays
-            float3 ldir, lrad;
-            light_incoming(sp.lights[l], vx.P, ldir, lrad);
-            const HitRec sh = traverse<COUNT>(bvh, vx.P, ldir, true, stack, &ctr->node_visits, &ctr->tri_tests);
-            ++nShadow;
-            if (sh.leaf < 0) {
-                const float3 c = vx.Tn * (vx.base * lrad);
-                if (finite3(c)) {
-                    if (c.x != 0.f) aR += to_fixed(c.x);
-                    if (c.y != 0.f) aG += to_fixed(c.y);
-                    if (c.z != 0.f) aB += to_fixed(c.z);
-                } else {
-                    atomicAdd(&ctr->dropped_nonfinite, 1ull);
-                }
-            }
-        }
+        light_shadows_here<COUNT>(bvh, sp, vx, stack, aR, aG, aB, nShadow, ctr);   // what wave depth+1 would do with this vertex's shadow rays
         ro = vx.P;
         rd = vx.ndir;
         T = vx.Tn;
@@ -606,7 +619,7 @@ __device__ __forceinline__ void flush_trav_counters(unsigned nv, unsigned nt, De
 
 // Form A (fewer than 32 samples per pixel in this launch): thread = (pixel of an 8x4 tile, group of `spt`
 // consecutive local samples); the candidates stay in the thread's own stack array.
-template <bool COUNT, bool NEE, bool SPEC>
+template <bool COUNT, bool NEE, int MODE>
 __global__ void __launch_bounds__(128) k_primary(BvhView bvh, ShadeParams sp, CameraParams cam, int W, int H, uint32_t nPadded,
                                                  uint32_t kSamples, uint32_t spt, uint32_t sampleBase, uint32_t sampleStride, QueueOut q,
                                                  unsigned long long* __restrict__ acc, DeviceCounters* ctr) {
@@ -637,7 +650,7 @@ __global__ void __launch_bounds__(128) k_primary(BvhView bvh, ShadeParams sp, Ca
         if ((threadIdx.x & 31) == __ffs(m) - 1) atomicAdd(&ctr->rays_candidates, (unsigned long long)n);
     }
     for (uint32_t sl = s0; sl < s1; ++sl)
-        primary_sample<COUNT, NEE, SPEC>(bvh, sp, cam, q, blockIdx.x & (kSegments - 1), px, py, pixel, sampleBase + sl * sampleStride, o, nc, stack + kStackSize - 1,
+        primary_sample<COUNT, NEE, MODE>(bvh, sp, cam, q, blockIdx.x & (kSegments - 1), px, py, pixel, sampleBase + sl * sampleStride, o, nc, stack + kStackSize - 1,
                                    stack + kStackSize - 1 - kMaxCandidates, -1, stack, aR, aG, aB, nt, nExt, nShadow, ctr);
     if (COUNT) flush_trav_counters(nv, nt, ctr);
     flush_ray_counters(nExt, nShadow, ctr);
@@ -665,7 +678,7 @@ __device__ __forceinline__ long long group_sum_ll(long long v) {
 #ifndef TPT_COOP_MIN_BLOCKS
 #define TPT_COOP_MIN_BLOCKS 7
 #endif
-template <bool COUNT, bool NEE, bool SPEC>
+template <bool COUNT, bool NEE, int MODE>
 __global__ void __launch_bounds__(128, TPT_COOP_MIN_BLOCKS) k_primary_coop(BvhView bvh, ShadeParams sp, CameraParams cam, int W, int H, uint32_t nPadded,
                                                       uint32_t kSamples, uint32_t spt, uint32_t sampleBase, uint32_t sampleStride, QueueOut q,
                                                       unsigned long long* __restrict__ acc, DeviceCounters* ctr) {
@@ -712,7 +725,7 @@ __global__ void __launch_bounds__(128, TPT_COOP_MIN_BLOCKS) k_primary_coop(BvhVi
         long long aR = 0, aG = 0, aB = 0;
         if (have)
             for (uint32_t sl = s0 + sub; sl < s1; sl += kCoopLanes)
-                primary_sample<COUNT, NEE, SPEC>(bvh, sp, cam, q, blockIdx.x & (kSegments - 1), pxp, pyp, pixel, sampleBase + sl * sampleStride, o, ncp,
+                primary_sample<COUNT, NEE, MODE>(bvh, sp, cam, q, blockIdx.x & (kSegments - 1), pxp, pyp, pixel, sampleBase + sl * sampleStride, o, ncp,
                                            &sCand[wib][0][pl], &sBound[wib][0][pl], 32, stack, aR, aG, aB, nt, nExt, nShadow, ctr);
         __syncwarp();
         if (__ballot_sync(0xffffffffu, (aR | aG | aB) != 0)) {
@@ -1384,12 +1397,19 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
     // (6) 6.37 -> 6.21 ms, box.gltf (1 932, long divergent walks inside the box) 10.7 -> 11.1 ms, hence the limit.
     static const size_t specMaxFaces = getenv("TPT_SPEC_MAX_FACES") ? (size_t)atoll(getenv("TPT_SPEC_MAX_FACES")) : 512;   // tuning switch
     const bool spec = s->any_specular && !nee && sp.continueSpecular > 0 && s->n_faces <= specMaxFaces;
-    const auto kPrimary = spec ? (counted ? k_primary<true, false, true> : k_primary<false, false, true>)
-                          : variant == 0 ? k_primary<false, false, false> : variant == 1 ? k_primary<true, false, false>
-                          : variant == 2 ? k_primary<false, true, false> : k_primary<true, true, false>;
-    const auto kPrimaryCoop = spec ? (counted ? k_primary_coop<true, false, true> : k_primary_coop<false, false, true>)
-                              : variant == 0 ? k_primary_coop<false, false, false> : variant == 1 ? k_primary_coop<true, false, false>
-                              : variant == 2 ? k_primary_coop<false, true, false> : k_primary_coop<true, true, false>;
+    // LHERE kernels: the camera vertex's delta-light shadow rays are traced in k_primary (coherent: one light, neighbouring points)
+    static const bool noLightsHere = getenv("TPT_NO_LIGHTS_HERE") != nullptr;   // tuning switch
+    const bool lhere = s->n_lights > 0 && !nee && !noLightsHere && !(cfg->flags & TPT_RENDER_NO_SPECULAR_CONTINUATION);
+    const int mode = (spec ? 1 : 0) | (lhere ? 2 : 0);
+    using PrimaryKernel = void (*)(BvhView, ShadeParams, CameraParams, int, int, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, QueueOut,
+                                   unsigned long long*, DeviceCounters*);
+    static const PrimaryKernel primaryTable[2][4] = {{k_primary<false, false, 0>, k_primary<false, false, 1>, k_primary<false, false, 2>, k_primary<false, false, 3>},
+                                                     {k_primary<true, false, 0>, k_primary<true, false, 1>, k_primary<true, false, 2>, k_primary<true, false, 3>}};
+    static const PrimaryKernel coopTable[2][4] = {
+        {k_primary_coop<false, false, 0>, k_primary_coop<false, false, 1>, k_primary_coop<false, false, 2>, k_primary_coop<false, false, 3>},
+        {k_primary_coop<true, false, 0>, k_primary_coop<true, false, 1>, k_primary_coop<true, false, 2>, k_primary_coop<true, false, 3>}};
+    const PrimaryKernel kPrimary = nee ? (counted ? k_primary<true, true, 0> : k_primary<false, true, 0>) : primaryTable[counted ? 1 : 0][mode];
+    const PrimaryKernel kPrimaryCoop = nee ? (counted ? k_primary_coop<true, true, 0> : k_primary_coop<false, true, 0>) : coopTable[counted ? 1 : 0][mode];
     const auto kWave = variant == 0 ? k_wave<false, false, false> : variant == 1 ? k_wave<true, false, false> : variant == 2 ? k_wave<false, true, false> : k_wave<true, true, false>;
     const auto kWave1 = variant == 0 ? k_wave<false, false, true> : variant == 1 ? k_wave<true, false, true> : variant == 2 ? k_wave<false, true, true> : k_wave<true, true, true>;
 
