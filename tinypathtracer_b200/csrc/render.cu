@@ -667,9 +667,12 @@ __global__ void __launch_bounds__(128) k_primary(BvhView bvh, ShadeParams sp, Ca
 // the warp nothing, and no lane waits long for a neighbour whose pixel happens to be the expensive one.
 constexpr int kCoopCandidates = kMaxCandidates < 16 ? kMaxCandidates : 16;
 #ifndef TPT_COOP_LANES
-#define TPT_COOP_LANES 8
+#define TPT_COOP_LANES 32
 #endif
-constexpr int kCoopLanes = TPT_COOP_LANES;   // lanes that share one pixel (power of two, >= 4)
+// Lanes that share one pixel (power of two, 4..32).  Measured (ms per frame, 8 / 16 / 32 lanes): ball 34.8 / 33.2 / 32.8, box 10.67 /
+// 10.54 / 10.42, tir 6.21 / 6.23 / 6.21, light 14.74 / 14.86 / 15.08: since k_primary also traces shadow and mirror rays in
+// registers, rays that start at the same pixel's surface points walk the tree together best when the whole warp has one pixel.
+constexpr int kCoopLanes = TPT_COOP_LANES;
 __device__ __forceinline__ long long group_sum_ll(long long v) {
 #pragma unroll
     for (int o = kCoopLanes >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
