@@ -290,11 +290,47 @@ __device__ __forceinline__ void light_incoming(const tpt_delta_light& L, float3 
 // sampleEnvLights + Vec2UV, src/path_tracer.cu:288-294, include/env_light.cuh:72-78; point filter,
 // clamp addressing, normalised coordinates (src/texture.cu:160-168).  Two texel formats: the reference's RGBA8
 // (value / 255) and linear float RGB for HDR maps (tpt_env_set_rgb32f; one 128-bit load per lookup).
+// The two inverse trigonometric functions only choose a texel, so they are polynomials here (|error| < 3e-7 rad, i.e. < 2e-4 of a
+// texel of a 4096 x 2048 map; libm's atan2f + acosf were 11 % of k_primary's instructions on ball.gltf):
+//   atan(t), t in [0,1]: t * P8(t^2), Chebyshev fit, max error 1.1e-7;  acos(x), x in [0,1]: sqrt(1-x) * P7(x) (Abramowitz & Stegun
+//   4.4.46), max error 2.5e-7 in fp32.
+__device__ __forceinline__ float atan2_turns(float y, float x) {   // atan2(y, x) / 2pi in [0, 1)
+    const float ax = fabsf(x), ay = fabsf(y);
+    const float mx = fmaxf(ax, ay), mn = fminf(ax, ay);
+    const float t = mx > 0.0f ? __fdividef(mn, mx) : 0.0f;
+    const float z = t * t;
+    float p = 0.0028340641874819994f;
+    p = fmaf(p, z, -0.016005029901862144f);
+    p = fmaf(p, z, 0.042587608098983765f);
+    p = fmaf(p, z, -0.07495445758104324f);
+    p = fmaf(p, z, 0.10636754333972931f);
+    p = fmaf(p, z, -0.14202570915222168f);
+    p = fmaf(p, z, 0.19992484152317047f);
+    p = fmaf(p, z, -0.3333306610584259f);
+    p = fmaf(p, z, 1.0f);
+    float a = p * t;                            // [0, pi/4]
+    if (ay > ax) a = 0.5f * kPi - a;            // [0, pi/2]
+    if (x < 0.0f) a = kPi - a;                  // [0, pi]
+    const float u = a * (0.5f / kPi);
+    return y < 0.0f ? 1.0f - u : u;             // atan2 < 0 -> + 1 turn
+}
+__device__ __forceinline__ float acos_fast(float x) {   // x in [-1, 1]
+    const float ax = fabsf(x);
+    float p = -0.0012624911f;
+    p = fmaf(p, ax, 0.0066700901f);
+    p = fmaf(p, ax, -0.0170881256f);
+    p = fmaf(p, ax, 0.0308918810f);
+    p = fmaf(p, ax, -0.0501743046f);
+    p = fmaf(p, ax, 0.0889789874f);
+    p = fmaf(p, ax, -0.2145988016f);
+    p = fmaf(p, ax, 1.5707963050f);
+    const float r = sqrtf(1.0f - ax) * p;
+    return x < 0.0f ? kPi - r : r;
+}
 __device__ __forceinline__ float3 env_lookup(const uchar4* __restrict__ env, const float4* __restrict__ envf, int ew, int eh, float3 d) {
     if (env == nullptr && envf == nullptr) return f3(0.f, 0.f, 0.f);
-    float u = atan2f(d.z, d.x) / (2.0f * kPi);
-    if (u < 0.0f) u += 1.0f;
-    const float v = 1.0f - acosf(fmaxf(fminf(d.y, 1.0f), -1.0f)) / kPi;
+    const float u = atan2_turns(d.z, d.x);
+    const float v = 1.0f - acos_fast(fmaxf(fminf(d.y, 1.0f), -1.0f)) * (1.0f / kPi);
     int x = (int)floorf(u * (float)ew), y = (int)floorf(v * (float)eh);
     x = min(max(x, 0), ew - 1);
     y = min(max(y, 0), eh - 1);
@@ -758,9 +794,10 @@ __global__ void __launch_bounds__(128) k_tile_live(BvhView bvh, ShadeParams sp, 
     int stack[kStackSize];
     stack[0] = kStackSentinel;
     const float3 o = xmat4_point(cam.c2w, f3(0.f, 0.f, 0.f));
-    unsigned nv = 0;
-    const int nc = inside ? pixel_candidates(bvh, sp, cam, px, py, o, stack, nv) : 0;
-    const unsigned live = __ballot_sync(0xffffffffu, nc != 0);
+    // "some leaf box meets the pyramid" is exactly "pixel_candidates(...) != 0" (same walk, same plane-box test), and stops at the
+    // first such leaf instead of collecting and sorting them all
+    const bool hit = inside && frustum_may_hit(bvh, pixel_frustum(cam, px, py, o), stack);
+    const unsigned live = __ballot_sync(0xffffffffu, hit);
     if ((threadIdx.x & 31) == 0) tileLive[i >> 5] = (uint8_t)__popc(live);
 }
 
