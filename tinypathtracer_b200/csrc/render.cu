@@ -929,8 +929,11 @@ __global__ void __launch_bounds__(128, TPT_WAVE_MIN_BLOCKS) k_wave(BvhView bvh, 
     const uint32_t kGrab = min(max((total / (gridDim.x * 8u)) & ~31u, 32u), kGrabMax);
     uint32_t* myIdx = sIdx[threadIdx.x >> 5];
     float4* myHit = sHit[threadIdx.x >> 5];
-    int stack[kStackSize];
-    stack[0] = kStackSentinel;
+    // local-memory stack here: the shared-memory one (HybridStack, used by k_trace_rays_persistent) measured 2-4 % SLOWER on
+    // the bundled scenes' waves (its depth test costs issue slots, and these waves are as much issue- as data-pipe-bound)
+    int stackArr[kStackSize];
+    stackArr[0] = kStackSentinel;
+    const LocalStack stack{stackArr};
     TravState ts;
     ts.cur = kStackSentinel;
     ts.sp = 1;
@@ -1089,8 +1092,16 @@ __global__ void __launch_bounds__(128, 10) k_trace_rays_persistent(BvhView bvh, 
     const uint32_t lane = threadIdx.x & 31, ltMask = (1u << lane) - 1u;
     const unsigned long long perWarp = n / ((unsigned long long)gridDim.x * 8ull);
     const unsigned long long grab = perWarp >= kGrabMax ? kGrabMax : (perWarp >= 32ull ? (perWarp & ~31ull) : 32ull);
-    int stack[kStackSize];
-    stack[0] = kStackSentinel;
+#if TPT_SMEM_STACK > 0
+    __shared__ int sStack[kSmemStack][128];
+    int stackDeep[kStackSize - kSmemStack];
+    const HybridStack stack{&sStack[0][threadIdx.x], stackDeep};
+    sStack[0][threadIdx.x] = kStackSentinel;
+#else
+    int stackArr[kStackSize];
+    stackArr[0] = kStackSentinel;
+    const LocalStack stack{stackArr};
+#endif
     TravState ts;
     ts.cur = kStackSentinel;
     ts.sp = 1;
