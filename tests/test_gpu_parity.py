@@ -488,3 +488,24 @@ def test_specular_continuation_with_delta_lights(tpt, ctx, scenes, orc):
     ref = orc.render(s, W, H, spp, seed=17) / spp
     assert _relmse(img, ref) <= 2e-2
     ds.close()
+
+
+def test_host_pointer_trace_is_pipelined_in_chunks_with_the_same_hits(built, scenes, orc):
+    """tpt_trace_rays with host buffers cuts batches above 2^20 rays into chunks (copy-in, traversal and copy-out of
+    neighbouring chunks overlap on three streams); the hits must be those of the same rays traced in single-chunk calls."""
+    ds, bvh = built["box"]
+    wv, _ = orc.transform(scenes["box"])
+    rng = np.random.default_rng(99)
+    n = 2_600_000                                            # 3 chunks, the last one ragged
+    lo, hi = wv.min(axis=0) - 0.5, wv.max(axis=0) + 0.5
+    o = rng.uniform(lo, hi, size=(n, 3)).astype(np.float32)
+    d = rng.normal(size=(n, 3)).astype(np.float32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    rays = np.concatenate([o, d], axis=1).astype(np.float32)
+    whole = bvh.trace(rays)
+    parts = np.concatenate([bvh.trace(rays[i:i + 650_000]) for i in range(0, n, 650_000)])
+    for k in ("prim", "t", "u", "v"):
+        assert np.array_equal(whole[k], parts[k]), k
+    ref = orc.trace_rays(wv, scenes["box"]["indices"], rays[:20000], mode=0)
+    assert np.array_equal(whole["prim"][:20000], ref["prim"]) and np.array_equal(whole["t"][:20000], ref["t"])
+    assert (whole["prim"] >= 0).mean() > 0.2

@@ -3,6 +3,7 @@
 // Host-side orchestration only: argument checks, device memory ownership, host<->device staging and
 // kernel sequencing.  There is no CPU implementation of any entry point: when no CUDA device is
 // usable, tpt_context_create fails and nothing else can be called.
+#include <algorithm>
 #include <cstring>
 #include <new>
 #include <vector>
@@ -122,6 +123,9 @@ int tpt_context_destroy(tpt_context* ctx) {
     cudaFree(ctx->levels);
     cudaFree(ctx->trace_cursor);
     cudaFree(ctx->d_tile_live);
+    if (ctx->io_in) cudaStreamDestroy(ctx->io_in);
+    if (ctx->io_out) cudaStreamDestroy(ctx->io_out);
+    for (cudaEvent_t e : ctx->io_events) cudaEventDestroy(e);
     cudaFree(ctx->io_rays);
     cudaFree(ctx->io_hits);
     for (cudaEvent_t e : ctx->stage_events) cudaEventDestroy(e);
@@ -429,9 +433,36 @@ static int trace_common(tpt_scene* s, const tpt_ray* rays, size_t n, tpt_hit* hi
     TPT_CHECK(bind(ctx));
     if (device_ptrs) return tpt_trace_rays_impl(s, rays, n, hits, any_hit, counted);
     TPT_CHECK(ensure_io(ctx, n));
-    TPT_CUDA(cudaMemcpyAsync(ctx->io_rays, rays, n * sizeof(tpt_ray), cudaMemcpyHostToDevice, ctx->stream));
-    TPT_CHECK(tpt_trace_rays_impl(s, static_cast<const tpt_ray*>(ctx->io_rays), n, static_cast<tpt_hit*>(ctx->io_hits), any_hit, counted));
-    TPT_CUDA(cudaMemcpyAsync(hits, ctx->io_hits, n * sizeof(tpt_hit), cudaMemcpyDeviceToHost, ctx->stream));
+    // Host buffers: the batch is cut into chunks and pipelined over three streams — chunk i+1 goes up while chunk i is traced
+    // and the hits of chunk i-1 come down (PCIe is full duplex; with pinned host memory the call costs about
+    // max(copy in + copy out of one direction's worth, traversal) instead of their sum).  Results do not depend on the cut.
+    if (!ctx->io_in) {
+        TPT_CUDA(cudaStreamCreateWithFlags(&ctx->io_in, cudaStreamNonBlocking));
+        TPT_CUDA(cudaStreamCreateWithFlags(&ctx->io_out, cudaStreamNonBlocking));
+    }
+    const size_t chunk = std::max<size_t>((size_t)1 << 20, (n + 7) / 8);
+    const size_t nChunks = (n + chunk - 1) / chunk;
+    while (ctx->io_events.size() < 2 * nChunks + 1) {
+        cudaEvent_t e;
+        TPT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        ctx->io_events.push_back(e);
+    }
+    tpt_ray* dRays = static_cast<tpt_ray*>(ctx->io_rays);
+    tpt_hit* dHits = static_cast<tpt_hit*>(ctx->io_hits);
+    // the staging buffers may still be in use by earlier work on the context stream
+    TPT_CUDA(cudaEventRecord(ctx->io_events[2 * nChunks], ctx->stream));
+    TPT_CUDA(cudaStreamWaitEvent(ctx->io_in, ctx->io_events[2 * nChunks], 0));
+    for (size_t c = 0; c < nChunks; ++c) {
+        const size_t off = c * chunk, cnt = std::min(chunk, n - off);
+        TPT_CUDA(cudaMemcpyAsync(dRays + off, rays + off, cnt * sizeof(tpt_ray), cudaMemcpyHostToDevice, ctx->io_in));
+        TPT_CUDA(cudaEventRecord(ctx->io_events[2 * c], ctx->io_in));
+        TPT_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->io_events[2 * c], 0));
+        TPT_CHECK(tpt_trace_rays_impl(s, dRays + off, cnt, dHits + off, any_hit, counted));
+        TPT_CUDA(cudaEventRecord(ctx->io_events[2 * c + 1], ctx->stream));
+        TPT_CUDA(cudaStreamWaitEvent(ctx->io_out, ctx->io_events[2 * c + 1], 0));
+        TPT_CUDA(cudaMemcpyAsync(hits + off, dHits + off, cnt * sizeof(tpt_hit), cudaMemcpyDeviceToHost, ctx->io_out));
+    }
+    TPT_CUDA(cudaStreamSynchronize(ctx->io_out));
     TPT_CUDA(cudaStreamSynchronize(ctx->stream));
     return TPT_OK;
 }

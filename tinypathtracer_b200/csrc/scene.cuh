@@ -77,6 +77,10 @@ struct tpt_context {
     void* io_rays = nullptr;
     void* io_hits = nullptr;
     size_t io_capacity = 0;
+    // host-pointer tpt_trace_rays: copy-in and copy-out streams + per-chunk events, so that PCIe transfers in both directions
+    // overlap the traversal of the neighbouring chunks
+    cudaStream_t io_in = nullptr, io_out = nullptr;
+    std::vector<cudaEvent_t> io_events;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     // live pixels per 8x4 tile of the last (scene geometry, camera, resolution) rendered: bounds what a batch can emit
     uint8_t* d_tile_live = nullptr;
