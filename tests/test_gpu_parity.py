@@ -509,3 +509,23 @@ def test_host_pointer_trace_is_pipelined_in_chunks_with_the_same_hits(built, sce
     ref = orc.trace_rays(wv, scenes["box"]["indices"], rays[:20000], mode=0)
     assert np.array_equal(whole["prim"][:20000], ref["prim"]) and np.array_equal(whole["t"][:20000], ref["t"])
     assert (whole["prim"] >= 0).mean() > 0.2
+
+
+def test_do_trace_with_refit_flag_equals_rebuild(tpt, ctx, scenes):
+    """TPT_RENDER_REFIT: tpt_do_trace builds on the first frame and refits afterwards; frames equal those of per-frame rebuilds,
+    also after the objects have moved."""
+    s = scenes["box2"]
+    W, H = 96, 54
+    cam = tpt.Camera.from_scene(s)
+    a, b = tpt.DeviceScene(ctx, s), tpt.DeviceScene(ctx, s)
+    pt = tpt.PathTracer(ctx, W, H, env_rgba8=synthetic_sky(64, 32))
+    for step, (angle, shift) in enumerate([(0.0, 0.0), (0.2, 0.1), (0.5, 0.25)]):
+        moved = _moved(s, angle, shift)
+        fa, fb = np.zeros((H, W, 4), np.uint8), np.zeros((H, W, 4), np.uint8)
+        a.set_transforms(moved["vert_trans"], moved["normal_trans"])
+        b.set_transforms(moved["vert_trans"], moved["normal_trans"])
+        pt.doTrace(a, cam, fa, 8, seed=4, refit=True)      # frame 0 builds (no hierarchy yet), later frames refit
+        pt.doTrace(b, cam, fb, 8, seed=4)
+        assert (fa == fb).all() and fa[..., :3].any(), step
+    a.close()
+    b.close()

@@ -1370,7 +1370,7 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
                 TPT_CUDA(cudaMemcpyAsync(ctx->tile_live_host.data(), ctx->d_tile_live, nTiles, cudaMemcpyDeviceToHost, st));
                 TPT_CUDA(cudaStreamSynchronize(st));
             }
-            ctx->live_key = key;
+            memcpy(&ctx->live_key, &key, sizeof key);   // padding included: the comparison above is a memcmp
         }
     }
     const uint8_t* tileLive = ctx->tile_live_host.data();
