@@ -120,6 +120,9 @@ def run_ours(args):
         raise SystemExit("bench.py: no CUDA device — the hot path has no CPU fallback")
     torch.cuda.set_device(local)
     if world > 1:
+        # NCCL prints "NCCL version ..." on STDOUT at NCCL_DEBUG=VERSION (some boxes export that): the contract is ONE JSON line
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     fixture, W, H, spp, depth, envkind, seed = WORKLOADS[args.workload]
     if args.spp:
