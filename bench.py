@@ -120,9 +120,6 @@ def run_ours(args):
         raise SystemExit("bench.py: no CUDA device — the hot path has no CPU fallback")
     torch.cuda.set_device(local)
     if world > 1:
-        # NCCL prints "NCCL version ..." on STDOUT at NCCL_DEBUG=VERSION (some boxes export that): the contract is ONE JSON line
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     fixture, W, H, spp, depth, envkind, seed = WORKLOADS[args.workload]
     if args.spp:
@@ -622,7 +619,18 @@ def run_reference_cuda(args, exe, ref_scene, W, H, spp, depth, envkind, cfg):
             "e2e": {"value": round(v, 3), "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
 
 
+def _json_only_stdout():
+    """The contract is ONE JSON line on stdout, but native libraries write there too (NCCL prints its version banner on fd 1 at
+    any NCCL_DEBUG level above NONE).  File descriptor 1 is pointed at stderr for the whole run; Python's sys.stdout — where the
+    JSON line is printed — keeps the original stdout."""
+    sys.stdout.flush()
+    real = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real, "w", buffering=1)
+
+
 def main():
+    _json_only_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
