@@ -241,6 +241,14 @@ int tpt_accum_create(tpt_context* ctx, int width, int height, tpt_accum** out);
 int tpt_accum_wrap(tpt_context* ctx, void* device_i64, int width, int height, tpt_accum** out);
 int tpt_accum_destroy(tpt_accum* acc);
 int tpt_accum_clear(tpt_accum* acc);                      /* thrust::fill at src/path_tracer.cu:534 */
+/* Multi-GPU from ONE process (the reference drives its single GPU from one host thread).  tpt_comm_init_all creates
+ * one context per GPU 0..ngpu-1 and enables peer access between all of them.  tpt_accum_allreduce leaves in EVERY accumulator
+ * (one per context, same size) the exact integer sum of all of them: each GPU reduces 1/n of the buffer by reading its peers'
+ * memory over NVLink, then fetches the other reduced parts — no library collective; asynchronous, ordered after the work already
+ * queued on each context's stream and before whatever is queued next.  With one process PER GPU (torch.distributed) wrap the
+ * buffer instead (tpt_accum_wrap / tpt_accum_device_ptr) and use the framework's all-reduce: int64 sums are exact either way. */
+int tpt_comm_init_all(int ngpu, tpt_context** out_contexts);
+int tpt_accum_allreduce(tpt_accum** per_gpu, int n);
 int tpt_accum_add(tpt_accum* dst, const tpt_accum* src);   /* dst += src (same context) */
 void* tpt_accum_device_ptr(tpt_accum* acc);               /* int64[height][width][3], row 0 = bottom */
 int tpt_accum_export_f32(tpt_accum* acc, float* host_rgb); /* radiance SUM, float[height][width][3] */

@@ -95,6 +95,9 @@ class Context {
 public:
     explicit Context(int device = 0);
     ~Context();
+    // one process, several GPUs: contexts for GPUs 0..n-1 with peer access between all of them (tpt_comm_init_all);
+    // sum per-GPU accumulators with tpt_accum_allreduce
+    static std::vector<std::unique_ptr<Context>> initAll(int nGpus);
     Context(const Context&) = delete;
     Context& operator=(const Context&) = delete;
     tpt_context* handle() const { return m_ctx; }
@@ -102,6 +105,7 @@ public:
     tpt_counters counters();
 
 private:
+    explicit Context(tpt_context* adopted) : m_ctx(adopted) {}
     tpt_context* m_ctx = nullptr;
 };
 

@@ -89,6 +89,8 @@ SIGNATURES = {
     "tpt_bvh_refit": (C.c_int, [C.c_void_p, C.POINTER(BvhStats)]),
     "tpt_bvh_export_reference_nodes": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
     "tpt_scene_export_world": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
+    "tpt_comm_init_all": (C.c_int, [C.c_int, C.c_void_p]),
+    "tpt_accum_allreduce": (C.c_int, [C.c_void_p, C.c_int]),
     "tpt_env_set_rgba8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
     "tpt_env_set_rgb32f": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
     "tpt_env_clear": (C.c_int, [C.c_void_p]),

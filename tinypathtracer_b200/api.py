@@ -35,9 +35,12 @@ def _ptr(a):
 
 
 class Context:
-    def __init__(self, device: int = 0):
+    def __init__(self, device: int = 0, _handle=None):
         h = C.c_void_p()
-        check(lib.tpt_context_create(device, C.byref(h)))
+        if _handle is None:
+            check(lib.tpt_context_create(device, C.byref(h)))
+        else:
+            h = _handle
         self._h = h
         self.device = device
         self._children = weakref.WeakSet()   # scenes / accumulators must be destroyed before their context
@@ -109,6 +112,19 @@ class Camera:
 
     def getNearPlane(self):
         return self.c.near_plane
+
+
+def comm_init_all(ngpu: int) -> list:
+    """tpt_comm_init_all: one Context per GPU 0..ngpu-1 of THIS process, peer access enabled between all of them."""
+    arr = (C.c_void_p * ngpu)()
+    check(lib.tpt_comm_init_all(ngpu, arr))
+    return [Context(d, _handle=C.c_void_p(arr[d])) for d in range(ngpu)]
+
+
+def accum_allreduce(accums: list):
+    """tpt_accum_allreduce: every accumulator (one per context) ends up holding the exact sum of all of them."""
+    arr = (C.c_void_p * len(accums))(*[a._h for a in accums])
+    check(lib.tpt_accum_allreduce(arr, len(accums)))
 
 
 class DeviceScene:

@@ -10,7 +10,7 @@ PKG = Path(__file__).resolve().parent
 ROOT = PKG.parent
 CSRC = PKG / "csrc"
 LIB = PKG / "lib" / "libtpt_b200.so"
-SOURCES = ["capi.cu", "bvh.cu", "render.cu", "env.cu"]
+SOURCES = ["capi.cu", "bvh.cu", "render.cu", "env.cu", "comm.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC",
               "-ccbin", "/usr/bin/g++", f"-I{ROOT / 'include'}", "--expt-relaxed-constexpr"]
 

@@ -95,6 +95,13 @@ tpt_camera Camera::toABI() const {
 // ---- context -------------------------------------------------------------------------------------------------
 Context::Context(int device) { check(tpt_context_create(device, &m_ctx), "tpt_context_create"); }
 Context::~Context() { tpt_context_destroy(m_ctx); }
+std::vector<std::unique_ptr<Context>> Context::initAll(int nGpus) {
+    std::vector<tpt_context*> raw((size_t)std::max(nGpus, 1), nullptr);
+    check(tpt_comm_init_all(nGpus, raw.data()), "tpt_comm_init_all");
+    std::vector<std::unique_ptr<Context>> out;
+    for (tpt_context* c : raw) out.emplace_back(new Context(c));
+    return out;
+}
 void Context::synchronize() { check(tpt_context_synchronize(m_ctx), "tpt_context_synchronize"); }
 tpt_counters Context::counters() {
     tpt_counters c;
