@@ -216,6 +216,10 @@ public:
     std::string m_sceneType = "gltf";   // "gltf" = the reference's loader; "gltf-full" = scene graph, all primitives (Scene)
     bool m_roughMetals = false;   // TPT_RENDER_ROUGH_METALS: metals scatter by GGX from Material::roughness (the reference: mirrors)
     bool m_refit = false;         // TPT_RENDER_REFIT: frames after the first keep the BVH hierarchy and refit it (the reference rebuilds)
+    // Several GPUs from this one host thread: device ids, one context each (an id may repeat: several contexts on one
+    // GPU, which is how the single-GPU test runs it).  Rank g renders the sample indices = g (mod n); the accumulators are summed
+    // by tpt_accum_allreduce (peer-memory kernel) and GPU m_devices[0] resolves: the frame is bit-identical for any n.
+    std::vector<int> m_devices;
     bool m_envNEE = false;   // TPT_RENDER_ENV_NEE: sample the environment map at diffuse vertices (same expectation, lower variance)
     std::string m_output;
     std::string m_outputFloat;   // PFM of the linear mean radiance (accumulator / samples), unclamped; empty = none
@@ -223,6 +227,8 @@ public:
     Context& context() { return *m_ctx; }
 
 private:
+    void renderMulti(const std::string& meshFile);
+    void writeOutputs(const std::vector<unsigned char>& fb, tpt_accum* acc, uint64_t samples);
     void ensureAccumulator();
     std::unique_ptr<Context> m_ctx;
     std::string m_envFile;

@@ -465,3 +465,29 @@ def test_cli_hdr_environment_and_float_output(tpt, ctx, scenes, tmp_path):
     ds.close()
     np.testing.assert_array_equal(got, want)
     assert got.max() > 1.5                                   # above anything an 8-bit map or framebuffer can hold
+
+
+@pytest.mark.gpu
+def test_cli_single_process_multi_gpu_is_bit_identical(tmp_path):
+    """tpt_render --devices a,b,c: one host thread drives one context per entry (here three contexts on GPU 0; on a multi-GPU box
+    `--gpus N`), rank g renders the samples = g (mod n), tpt_accum_allreduce sums the buffers with its peer-memory kernel.
+    The PNG and the float dump must equal the single-context run's byte for byte."""
+    import subprocess
+    exe = ROOT / "tinypathtracer_b200" / "lib" / "tpt_render"
+    src = next((d / "box2.gltf" for d in GLTF_DIRS if (d / "box2.gltf").exists()), None)
+    if src is None:
+        pytest.skip("no .gltf inputs on this machine")
+    from tinypathtracer_b200.sky import synthetic_sky
+    from PIL import Image
+    sky = tmp_path / "sky.png"
+    Image.fromarray(synthetic_sky(64, 32)[::-1, :, :3].copy()).save(sky)
+    outs = []
+    for tag, extra in (("one", []), ("three", ["--devices", "0,0,0"])):
+        png, pfm = tmp_path / f"{tag}.png", tmp_path / f"{tag}.pfm"
+        r = subprocess.run([str(exe), "--scene", str(src), "--env", str(sky), "--w", "96", "--h", "54", "--spp", "24", "--seed", "3", "--frames", "2",
+                            "--out", str(png), "--out-float", str(pfm), *extra], capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr[-2000:]
+        outs.append((png.read_bytes(), pfm.read_bytes()))
+    assert outs[0][0] == outs[1][0] and outs[0][1] == outs[1][1]
+    bad = subprocess.run([str(exe), "--scene", str(src), "--spp", "25", "--devices", "0,0,0"], capture_output=True, text=True, timeout=300)
+    assert bad.returncode == 1 and "multiple of the number of GPUs" in bad.stderr

@@ -95,6 +95,24 @@ int tpt_accum_allreduce(tpt_accum** acc, int n) {
         for (int q = 0; q < r; ++q) TPT_REQUIRE(acc[q] != acc[r], "tpt_accum_allreduce: the same accumulator twice");
     }
     if (n == 1) return TPT_OK;
+    // contexts made one by one (tpt_context_create) instead of by tpt_comm_init_all: enable peer access on first use
+    static bool peerOk[64][64];
+    for (int a = 0; a < n; ++a)
+        for (int b = 0; b < n; ++b) {
+            const int da = acc[a]->ctx->device, db = acc[b]->ctx->device;
+            if (da == db || da >= 64 || db >= 64 || peerOk[da][db]) continue;
+            int can = 0;
+            TPT_CUDA(cudaDeviceCanAccessPeer(&can, da, db));
+            if (!can) {
+                set_error("tpt_accum_allreduce: GPU " + std::to_string(da) + " cannot access GPU " + std::to_string(db) + " as a peer");
+                return TPT_ERR_CUDA;
+            }
+            TPT_CUDA(cudaSetDevice(da));
+            const cudaError_t e = cudaDeviceEnablePeerAccess(db, 0);
+            if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+            else if (e != cudaSuccess) return cuda_fail(e, "cudaDeviceEnablePeerAccess", __FILE__, __LINE__);
+            peerOk[da][db] = true;
+        }
     const size_t total = (size_t)acc[0]->width * acc[0]->height * 3;
     const size_t per = ((total + n - 1) / n + 1) & ~(size_t)1;   // even slice length: slices start 16-byte aligned
     PeerPtrs src;

@@ -12,7 +12,8 @@ int main(int argc, char** argv) {
     int w = 1920, h = 1080, spp = 64, depth = 8, frames = 1;
     unsigned long long seed = 1;
     bool envNee = false, fullGltf = false, progressive = false, roughMetals = false, refit = false;
-    std::string checkpoint, resume;
+    std::string checkpoint, resume, devices;
+    int gpus = 1;
     for (int i = 1; i < argc; ++i) {
         const std::string k = argv[i];
         auto val = [&]() -> const char* {
@@ -30,6 +31,8 @@ int main(int argc, char** argv) {
         else if (k == "--frames") frames = std::atoi(val());
         else if (k == "--seed") seed = std::strtoull(val(), nullptr, 10);
         else if (k == "--env-nee") envNee = true;
+        else if (k == "--gpus") gpus = std::atoi(val());
+        else if (k == "--devices") devices = val();   // e.g. 0,1,2,3 (an id may repeat)
         else if (k == "--rough-metals") roughMetals = true;
         else if (k == "--refit") refit = true;
         else if (k == "--full-gltf") fullGltf = true;
@@ -39,7 +42,7 @@ int main(int argc, char** argv) {
         else { std::fprintf(stderr, "unknown argument %s\n", k.c_str()); return 2; }
     }
     if (scene.empty()) {
-        std::fprintf(stderr, "usage: tpt_render --scene file.gltf [--env sky.png|sky.jpg|sky.hdr|sky.pfm] [--w 1920 --h 1080 --spp 64 --depth 8 --frames 1 --seed 1 --env-nee --rough-metals --refit --full-gltf --progressive --checkpoint file --resume file --out frame.png --out-float frame.pfm]\n");
+        std::fprintf(stderr, "usage: tpt_render --scene file.gltf [--env sky.png|sky.jpg|sky.hdr|sky.pfm] [--w 1920 --h 1080 --spp 64 --depth 8 --frames 1 --seed 1 --gpus N | --devices 0,1,.. --env-nee --rough-metals --refit --full-gltf --progressive --checkpoint file --resume file --out frame.png --out-float frame.pfm]\n");
         return 2;
     }
     try {
@@ -51,6 +54,16 @@ int main(int argc, char** argv) {
         pathTracer.m_frames = frames;
         pathTracer.m_seed = seed;
         pathTracer.m_envNEE = envNee;
+        if (!devices.empty()) {
+            for (size_t pos = 0; pos <= devices.size();) {
+                const size_t c = devices.find(',', pos);
+                pathTracer.m_devices.push_back(std::atoi(devices.substr(pos, c == std::string::npos ? std::string::npos : c - pos).c_str()));
+                if (c == std::string::npos) break;
+                pos = c + 1;
+            }
+        } else {
+            for (int g = 0; g < gpus && gpus > 1; ++g) pathTracer.m_devices.push_back(g);
+        }
         pathTracer.m_roughMetals = roughMetals;
         pathTracer.m_refit = refit;
         if (fullGltf) pathTracer.m_sceneType = "gltf-full";

@@ -141,18 +141,7 @@ void PathTracer::doTrace(DeviceScene& scene, Camera& camera, unsigned char* fram
     m_lastFrameMs = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
 }
 
-void PathTracer::render(const std::string& meshFile) {
-    Scene scene(meshFile, m_sceneType);                       // src/path_tracer.cu:558 ("gltf")
-    DeviceScene d_scene = scene.copySceneToDevice(*m_ctx);    // :560
-    Camera& camera = scene.m_camera;                          // :562
-    std::vector<unsigned char> fb((size_t)m_width * m_height * 4, 0);
-    // the reference hands this job to VkEngine::run, which calls it once per presented frame until the window closes
-    // (src/vkEngine.cu:294-302); headless: m_frames frames, each an independent nSamplesPerPixel render with a new seed
-    for (int f = 0; f < m_frames; ++f) {
-        doTrace(d_scene, camera, fb.data(), m_spp);
-        std::printf("1 frame: %.3f ms\n", m_lastFrameMs);     // src/vkEngine.cu:300 prints "1 frame"
-        if (!m_progressive) ++m_seed;
-    }
+void PathTracer::writeOutputs(const std::vector<unsigned char>& fb, tpt_accum* acc, uint64_t samples) {
     if (!m_output.empty()) {
         std::vector<uint8_t> rgb((size_t)m_width * m_height * 3);
         for (size_t i = 0; i < (size_t)m_width * m_height; ++i) {   // framebuffer is B,G,R,(A untouched), row 0 = top
@@ -164,13 +153,93 @@ void PathTracer::render(const std::string& meshFile) {
     }
     if (!m_outputFloat.empty()) {
         std::vector<float> sum((size_t)m_width * m_height * 3), img(sum.size());
-        check(tpt_accum_export_f32(m_radiance, sum.data()), "tpt_accum_export_f32");   // radiance SUM, row 0 = bottom
-        const float inv = 1.0f / (float)(m_samplesDone ? m_samplesDone : 1);
+        check(tpt_accum_export_f32(acc, sum.data()), "tpt_accum_export_f32");   // radiance SUM, row 0 = bottom
+        const float inv = 1.0f / (float)(samples ? samples : 1);
         for (int y = 0; y < m_height; ++y)
             for (size_t i = 0; i < (size_t)m_width * 3; ++i)
                 img[(size_t)y * m_width * 3 + i] = sum[(size_t)(m_height - 1 - y) * m_width * 3 + i] * inv;
         writePFM(m_outputFloat, img.data(), m_width, m_height);
     }
+}
+
+void PathTracer::render(const std::string& meshFile) {
+    if (m_devices.size() > 1) {
+        renderMulti(meshFile);
+        return;
+    }
+    Scene scene(meshFile, m_sceneType);                       // src/path_tracer.cu:558 ("gltf")
+    DeviceScene d_scene = scene.copySceneToDevice(*m_ctx);    // :560
+    Camera& camera = scene.m_camera;                          // :562
+    std::vector<unsigned char> fb((size_t)m_width * m_height * 4, 0);
+    // the reference hands this job to VkEngine::run, which calls it once per presented frame until the window closes
+    // (src/vkEngine.cu:294-302); headless: m_frames frames, each an independent nSamplesPerPixel render with a new seed
+    for (int f = 0; f < m_frames; ++f) {
+        doTrace(d_scene, camera, fb.data(), m_spp);
+        std::printf("1 frame: %.3f ms\n", m_lastFrameMs);     // src/vkEngine.cu:300 prints "1 frame"
+        if (!m_progressive) ++m_seed;
+    }
+    writeOutputs(fb, m_radiance, m_samplesDone);
+}
+
+// The same job on several GPUs driven by this one thread: every call below only queues work on its GPU's stream, so the GPUs
+// run concurrently; the exchange is one tpt_accum_allreduce per frame.
+void PathTracer::renderMulti(const std::string& meshFile) {
+    const int n = (int)m_devices.size();
+    if (m_progressive) throw std::runtime_error("PathTracer: progressive mode runs on one GPU");
+    if (m_spp % n) throw std::runtime_error("PathTracer: spp must be a multiple of the number of GPUs");
+    Scene scene(meshFile, m_sceneType);
+    std::vector<std::unique_ptr<Context>> own;   // contexts beyond the constructor's (GPU 0); destroyed after scenes and accumulators
+    std::vector<Context*> ctx(n);
+    for (int g = 0; g < n; ++g) {
+        if (g == 0 && m_devices[0] == 0) {
+            ctx[g] = m_ctx.get();
+        } else {
+            own.emplace_back(new Context(m_devices[g]));
+            ctx[g] = own.back().get();
+            EnvLight env(*ctx[g], m_envFile);
+        }
+    }
+    struct Accums {
+        std::vector<tpt_accum*> a;
+        ~Accums() { for (tpt_accum* p : a) if (p) tpt_accum_destroy(p); }
+    } acc;
+    acc.a.assign(n, nullptr);
+    std::vector<DeviceScene> scenes;
+    for (int g = 0; g < n; ++g) {
+        scenes.push_back(scene.copySceneToDevice(*ctx[g]));
+        check(tpt_accum_create(ctx[g]->handle(), m_width, m_height, &acc.a[g]), "tpt_accum_create");
+    }
+    const tpt_camera cam = scene.m_camera.toABI();
+    std::vector<unsigned char> fb((size_t)m_width * m_height * 4, 0);
+    for (int f = 0; f < m_frames; ++f) {
+        const auto t0 = std::chrono::steady_clock::now();
+        for (int g = 0; g < n; ++g) {
+            tpt_render_config cfg;
+            std::memset(&cfg, 0, sizeof cfg);
+            cfg.width = m_width;
+            cfg.height = m_height;
+            cfg.spp = m_spp / n;
+            cfg.max_depth = m_depth;
+            cfg.seed = m_seed;
+            cfg.sample_offset = g;
+            cfg.sample_stride = n;
+            cfg.flags = (m_envNEE ? TPT_RENDER_ENV_NEE : 0u) | (m_roughMetals ? TPT_RENDER_ROUGH_METALS : 0u);
+            tpt_scene* s = scenes[g].handle.get();
+            if (m_refit && f > 0) check(tpt_bvh_refit(s, nullptr), "tpt_bvh_refit");
+            else check(tpt_bvh_build(s, nullptr), "tpt_bvh_build");
+            check(tpt_accum_clear(acc.a[g]), "tpt_accum_clear");
+            check(tpt_render(s, &cam, &cfg, acc.a[g]), "tpt_render");
+        }
+        check(tpt_accum_allreduce(acc.a.data(), n), "tpt_accum_allreduce");
+        check(tpt_resolve_bgra8(acc.a[0], m_spp, fb.data(), 0), "tpt_resolve_bgra8");
+        m_lastFrameMs = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        std::printf("1 frame: %.3f ms\n", m_lastFrameMs);
+        ++m_seed;
+    }
+    m_samplesDone = (uint64_t)m_spp;
+    for (int g = 1; g < n; ++g) ctx[g]->synchronize();
+    writeOutputs(fb, acc.a[0], m_samplesDone);
+    scenes.clear();   // before the contexts they live in
 }
 
 }   // namespace tpt
