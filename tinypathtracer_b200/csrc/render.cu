@@ -812,10 +812,20 @@ __global__ void __launch_bounds__(128) k_tile_live(BvhView bvh, ShadeParams sp, 
 //     (ray replacement); items come from the global cursor 32-256 at a time and are dealt out warp-locally;
 //   * retiring an extension ray only stages (item, hit) in shared memory; once 32 are staged the whole
 //     warp shades them together (shade_vertex + emit), so the divergent BSDF code also runs on full warps.
+// How many lanes must be idle before the warp stops stepping to retire and refill.  A refill phase costs every lane of the warp
+// (votes, staging, item loads), so it pays to wait until it serves many lanes — as long as the idle lanes are not too many for
+// too long.  Measured (8 / 16 / 20 / 24 idle lanes; ms per frame): ball 31.5 / 30.3 / 29.8 / 29.9, tir 6.26 / 5.77 / 5.68 / 5.53,
+// box 10.34 / 10.18 / 10.27 / 10.71; 10 M-triangle soup, Mrays/s primary | secondary: 2066 | 1312, 2250 | 1299, 2361 | 1263,
+// 2401 | 1225 — coherent rays want a late refill, incoherent ones an early one.  k_wave: 20; k_trace_rays_persistent, which
+// cannot know what it is given: 16.
 #ifndef TPT_REFILL_THRESHOLD
-#define TPT_REFILL_THRESHOLD 8
+#define TPT_REFILL_THRESHOLD 20
+#endif
+#ifndef TPT_TRACE_REFILL_THRESHOLD
+#define TPT_TRACE_REFILL_THRESHOLD 16
 #endif
 constexpr int kRefillThreshold = TPT_REFILL_THRESHOLD;
+constexpr int kTraceRefillThreshold = TPT_TRACE_REFILL_THRESHOLD;
 constexpr uint32_t kGrabMax = 256;
 constexpr int kStage = 64;
 constexpr uint32_t kNoItem = 0xffffffffu;
@@ -1112,7 +1122,7 @@ __global__ void __launch_bounds__(128, 10) k_trace_rays_persistent(BvhView bvh, 
         const unsigned mNode = __ballot_sync(0xffffffffu, ts.cur >= 0);
         const unsigned mLeaf = __ballot_sync(0xffffffffu, ts.cur < 0 && ts.cur != kStackSentinel);
         const unsigned mBusy = mNode | mLeaf;
-        if (mBusy == 0u || (more && 32 - __popc(mBusy) >= kRefillThreshold)) {
+        if (mBusy == 0u || (more && 32 - __popc(mBusy) >= kTraceRefillThreshold)) {
             if (item != ~0ull && !((mBusy >> lane) & 1u)) {   // retire: write the hit
                 reinterpret_cast<float4*>(hits)[item] = make_float4(__int_as_float(ts.best.prim), ts.best.t, ts.best.u, ts.best.v);
                 item = ~0ull;
