@@ -826,6 +826,12 @@ __global__ void __launch_bounds__(128) k_tile_live(BvhView bvh, ShadeParams sp, 
 #endif
 constexpr int kRefillThreshold = TPT_REFILL_THRESHOLD;
 constexpr int kTraceRefillThreshold = TPT_TRACE_REFILL_THRESHOLD;
+#ifndef TPT_KEEP_NUM
+#define TPT_KEEP_NUM 2
+#endif
+// a step kind is repeated without a re-vote while kKeepNum / 4 of its lanes stay in that state (2 / 3 / 4 of 4, ms per frame:
+// box 10.10 / 10.29 / 11.13, ball 29.67 / 30.01 / 30.54; soup within 1 %)
+constexpr int kKeepNum = TPT_KEEP_NUM;
 constexpr uint32_t kGrabMax = 256;
 constexpr int kStage = 64;
 constexpr uint32_t kNoItem = 0xffffffffu;
@@ -1067,7 +1073,7 @@ __global__ void __launch_bounds__(128, TPT_WAVE_MIN_BLOCKS) k_wave(BvhView bvh, 
         if (__popc(mNode) >= __popc(mLeaf)) {
             // box steps for the lanes at internal nodes; keep going without a full re-vote while at least
             // three quarters of them are still descending (coherent rays stay in this loop for many steps)
-            const int keep = max(1, (3 * __popc(mNode)) >> 2);
+            const int keep = max(1, (kKeepNum * __popc(mNode)) >> 2);
             do {
                 if (ts.cur >= 0) {
                     trav_node_step(ts, bvh, stack);
@@ -1075,7 +1081,7 @@ __global__ void __launch_bounds__(128, TPT_WAVE_MIN_BLOCKS) k_wave(BvhView bvh, 
                 }
             } while (__popc(__ballot_sync(0xffffffffu, ts.cur >= 0)) >= keep);
         } else {
-            const int keep = max(1, (3 * __popc(mLeaf)) >> 2);
+            const int keep = max(1, (kKeepNum * __popc(mLeaf)) >> 2);
             do {
                 if (ts.cur < 0 && ts.cur != kStackSentinel) {
                     trav_leaf_step(ts, bvh, kind == 1u, stack);
@@ -1153,7 +1159,7 @@ __global__ void __launch_bounds__(128, 10) k_trace_rays_persistent(BvhView bvh, 
             continue;
         }
         if (__popc(mNode) >= __popc(mLeaf)) {
-            const int keep = max(1, (3 * __popc(mNode)) >> 2);
+            const int keep = max(1, (kKeepNum * __popc(mNode)) >> 2);
             do {
                 if (ts.cur >= 0) {
                     trav_node_step(ts, bvh, stack);
@@ -1161,7 +1167,7 @@ __global__ void __launch_bounds__(128, 10) k_trace_rays_persistent(BvhView bvh, 
                 }
             } while (__popc(__ballot_sync(0xffffffffu, ts.cur >= 0)) >= keep);
         } else {
-            const int keep = max(1, (3 * __popc(mLeaf)) >> 2);
+            const int keep = max(1, (kKeepNum * __popc(mLeaf)) >> 2);
             do {
                 if (ts.cur < 0 && ts.cur != kStackSentinel) {
                     trav_leaf_step(ts, bvh, anyHit != 0, stack);
