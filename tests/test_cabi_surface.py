@@ -48,6 +48,14 @@ def test_no_cpu_fallback_without_a_gpu(tpt):
     with pytest.raises(tpt.TptError) as e:
         tpt.Context(0)
     assert "CUDA" in str(e.value)
+    with pytest.raises(tpt.TptError):
+        tpt.comm_init_all(2)
+    import subprocess
+    exe = ROOT / "tinypathtracer_b200" / "lib" / "tpt_render"
+    gltf = next((d / "box.gltf" for d in (Path("/root/reference/input"), ROOT / "oracle" / "_ref" / "input") if (d / "box.gltf").exists()), None)
+    if gltf is not None:
+        r = subprocess.run([str(exe), "--scene", str(gltf), "--spp", "8"], capture_output=True, text=True, timeout=120)
+        assert r.returncode == 1 and "CUDA" in r.stderr and "1 frame" not in r.stdout
 
 
 def test_product_never_imports_the_oracle():
