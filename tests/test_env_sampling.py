@@ -104,6 +104,57 @@ def test_samples_follow_the_pdf(tpt, ctx):
     assert (env.sample(1024, seed=4) != s[:1024]).any()
 
 
+def test_samples_follow_the_pdf_on_a_4096x2048_map(tpt, ctx):
+    """bench.py's sky has 2^23 texels: bucket choice and the accept / alias coin must come from independent random bits (they
+    used to share one 24-bit uniform, which left the coin one bit: texels with acceptance probability <= 0.5 were kept half the
+    time, the others always).  The sampled histogram over 64 x 32 blocks of texels must follow the block masses, and the
+    alias branch must be taken as often as the tables say."""
+    img = synthetic_sky(4096, 2048)
+    h, w = img.shape[:2]
+    env = tpt.EnvLight(ctx, img)
+    prob, alias, mass = env.sampler_tables()
+    n = 1 << 22
+    s = env.sample(n, seed=11)
+    d = s[:, :3].astype(np.float64)
+    x, y = dir_to_texel(d, w, h)
+    bw, bh = w // 64, h // 32
+    blk = (y // bh) * 64 + (x // bw)
+    hist = np.bincount(blk, minlength=64 * 32).astype(np.float64)
+    exp = mass.astype(np.float64).reshape(32, bh, 64, bw).sum(axis=(1, 3)).ravel() * n
+    big = exp > 50
+    chi2 = (((hist - exp) ** 2 / np.maximum(exp, 1e-30))[big]).sum() / big.sum()
+    assert 0.8 < chi2 < 1.3, chi2
+    # the sun disc (texels of value 255 in all channels) holds a known share of the mass
+    sun = (img[..., :3] == 255).all(axis=-1)
+    share = mass.astype(np.float64)[sun].sum()
+    got = sun[y, x].mean()
+    assert abs(got - share) <= 4.0 * np.sqrt(share * (1 - share) / n) + 1e-4, (got, share)
+    # Monte-Carlo integral of the luminance against the texel sum (a biased texel choice shows here at once)
+    lum = (0.2126 * img[..., 0].astype(np.float64) + 0.7152 * img[..., 1] + 0.0722 * img[..., 2]) / 255.0
+    theta = (1.0 - (np.arange(h) + 0.5) / h) * np.pi
+    exact = (lum * (2 * np.pi / w) * (2.0 * np.sin(np.pi / (2 * h)) * np.sin(theta))[:, None]).sum()
+    mc = (lum[y, x] / s[:, 3].astype(np.float64)).mean()
+    assert abs(mc - exact) <= 3e-3 * exact, (mc, exact)
+
+
+def test_nee_mean_matches_the_default_estimator_under_the_bench_sky(tpt, ctx, built, scenes):
+    """TPT_RENDER_ENV_NEE under the 4096 x 2048 sky bench.py uses: same expectation as the default estimator."""
+    ds, _ = built["ball"]
+    cam = tpt.Camera.from_scene(scenes["ball"])
+    W, H = 64, 36
+    pt = tpt.PathTracer(ctx, W, H, env_rgba8=synthetic_sky(4096, 2048))
+
+    def img(spp, seed, nee):
+        pt.m_radiance.clear()
+        pt.render_into(ds, cam, spp=spp, max_depth=8, seed=seed, env_nee=nee)
+        return pt.m_radiance.to_f32() / spp
+
+    ref = img(1 << 14, 5, False)
+    nee = img(1 << 14, 6, True)
+    assert _relmse(nee, ref) <= 1e-3
+    assert abs(nee.mean() - ref.mean()) <= 5e-3 * ref.mean(), (nee.mean(), ref.mean())
+
+
 def test_env_sample_needs_a_map(tpt, ctx):
     env = tpt.EnvLight(ctx, None)
     with pytest.raises(RuntimeError, match="no environment map"):

@@ -276,6 +276,39 @@ def test_jpeg_decoder_agrees_with_an_independent_one(host, tmp_path):
     assert host.tpt_host_read_image(str(tmp_path / "trunc.jpg").encode(), None, 0, whc.ctypes.data) != 0
 
 
+def test_jpeg_decoder_refuses_malformed_scan_headers(host, tmp_path):
+    """A scan header that names a Huffman table above 3, or a table no DHT / DQT segment defined, or that is shorter than
+    its component list, is refused with a message instead of indexing past the decoder's 4-entry table arrays."""
+    from PIL import Image
+    img = (np.arange(32 * 32 * 3) % 251).astype(np.uint8).reshape(32, 32, 3)
+    Image.fromarray(img).save(tmp_path / "ok.jpg", quality=90, subsampling=0)
+    data = bytearray((tmp_path / "ok.jpg").read_bytes())
+    whc = np.zeros(3, np.int32)
+
+    def refused(blob, needle):
+        (tmp_path / "bad.jpg").write_bytes(bytes(blob))
+        assert host.tpt_host_read_image(str(tmp_path / "bad.jpg").encode(), None, 0, whc.ctypes.data) != 0
+        assert needle in host.tpt_host_last_error(), host.tpt_host_last_error()
+
+    sos = data.index(b"\xff\xda")
+    ns = data[sos + 4]
+    assert ns == 3
+    bad = bytearray(data)
+    bad[sos + 6] = 0x7f                      # component 0: Td = 7, Ta = 15
+    refused(bad, b"Huffman table above 3")
+    bad = bytearray(data)
+    bad[sos + 6] = 0x22                      # tables 2/2: in range but never defined by a DHT segment
+    refused(bad, b"no DHT segment defined")
+    bad = bytearray(data)
+    bad[sos + 2:sos + 4] = (4).to_bytes(2, "big")   # segment length too short for 3 components
+    refused(bad, b"truncated JPEG scan header")
+    # a frame that names quantisation table 3 (never defined)
+    sof = data.index(b"\xff\xc0")
+    bad = bytearray(data)
+    bad[sof + 4 + 8] = 3
+    refused(bad, b"no DQT segment defined")
+
+
 @pytest.mark.gpu
 def test_tpt_render_cli_matches_the_python_binding(tpt, ctx, scenes, tmp_path):
     """src/main.cu's PathTracer(env).render(gltf) through the C++ classes: same seed -> the same framebuffer, byte for byte,

@@ -511,6 +511,8 @@ int tpt_accum_create(tpt_context* ctx, int w, int h, tpt_accum** out) {
 int tpt_accum_wrap(tpt_context* ctx, void* device_i64, int w, int h, tpt_accum** out) {
     TPT_REQUIRE(ctx && out && device_i64, "tpt_accum_wrap: NULL argument");
     TPT_REQUIRE(w > 0 && h > 0, "tpt_accum_wrap: bad size");
+    // the all-reduce kernel reads and writes the buffer with 128-bit accesses (comm.cu), the renderer with 64-bit atomics
+    TPT_REQUIRE(reinterpret_cast<uintptr_t>(device_i64) % 16 == 0, "tpt_accum_wrap: the buffer must be 16-byte aligned");
     tpt_accum* a = new (std::nothrow) tpt_accum();
     if (!a) return TPT_ERR_NOMEM;
     a->ctx = ctx;

@@ -19,8 +19,9 @@ struct PeerPtrs {
 };
 
 // out[i] = sum over the n buffers of p[k][i], i in [begin, end); out is this GPU's own buffer (one of the p[k]): only
-// this GPU reads or writes that slice of it during the launch.  128-bit loads, the peers' data arrives over NVLink.
-__global__ void __launch_bounds__(256) k_reduce_slice(PeerPtrs src, int n, unsigned long long* __restrict__ out, size_t begin, size_t end) {
+// this GPU reads or writes that slice of it during the launch (it aliases src.p[r]: no __restrict__).  128-bit loads — every
+// buffer is 16-byte aligned (cudaMalloc, or checked by tpt_accum_wrap) —, the peers' data arrives over NVLink.
+__global__ void __launch_bounds__(256) k_reduce_slice(PeerPtrs src, int n, unsigned long long* out, size_t begin, size_t end) {
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     const size_t b2 = (begin + 1) & ~(size_t)1, e2 = end & ~(size_t)1;   // 16-byte aligned middle part
     for (size_t i = b2 / 2 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < e2 / 2; i += stride) {

@@ -151,9 +151,14 @@ __host__ __device__ __forceinline__ uint64_t rng_path_key(uint64_t seedKey, uint
     return mix64(seedKey ^ (((uint64_t)pixel << 32) | (uint64_t)sample));
 }
 __host__ __device__ __forceinline__ float rng_u01(uint32_t x) { return (float)((x >> 8) + 1u) * (1.0f / 16777216.0f); }
-__host__ __device__ __forceinline__ void rng_pair(uint64_t key, uint32_t j, float& a, float& b) {
+// the 64 raw bits behind pair j (env.cuh picks an alias-table bucket from all 32 high bits: a 24-bit float cannot address a
+// 4096 x 2048 map's 2^23 texels AND leave bits for anything else)
+__host__ __device__ __forceinline__ uint64_t rng_bits(uint64_t key, uint32_t j) {
     // pair 0 (the pixel jitter, drawn for every camera sample) uses the already-mixed key itself: one mix64 less per sample
-    const uint64_t z = j == 0u ? key : mix64(key + (uint64_t)j * kGolden);
+    return j == 0u ? key : mix64(key + (uint64_t)j * kGolden);
+}
+__host__ __device__ __forceinline__ void rng_pair(uint64_t key, uint32_t j, float& a, float& b) {
+    const uint64_t z = rng_bits(key, j);
     a = rng_u01((uint32_t)(z >> 32));
     b = rng_u01((uint32_t)z);
 }

@@ -36,7 +36,7 @@ __global__ void __launch_bounds__(256) k_env_sample(EnvSampler es, size_t n, uin
         rng_pair(key, 1u, u1, u2);
         rng_pair(key, 2u, u3, u4);
         float pdf;
-        const float3 d = env_sample_dir(es, u1, u2, u3, pdf);
+        const float3 d = env_sample_dir(es, (uint32_t)(rng_bits(key, 1u) >> 32), u4, u2, u3, pdf);
         out[i] = make_float4(d.x, d.y, d.z, pdf);
     }
 }

@@ -22,16 +22,16 @@ struct EnvSampler {
     int w, h;
 };
 
-// Draw one texel and a point inside it: (u1 -> bucket + coin, u2/u3 -> position in the texel).  Returns the unit
-// direction and its density per unit solid angle.
-__device__ __forceinline__ float3 env_sample_dir(const EnvSampler& es, float u1, float u2, float u3, float& pdf) {
+// Draw one texel and a point inside it.  bucketBits (32 uniform bits) picks the alias-table bucket, `coin` in (0, 1] — an
+// INDEPENDENT uniform — decides between the bucket's own texel and its alias, (ux, uy) place the point inside the texel.
+// (Bucket and coin used to come from one 24-bit float: with the 2^23 texels of a 4096 x 2048 map the coin was left with one
+// bit, and the sampled distribution was not `mass`.)  Returns the unit direction and its density per unit solid angle.
+__device__ __forceinline__ float3 env_sample_dir(const EnvSampler& es, uint32_t bucketBits, float coin, float ux, float uy, float& pdf) {
     const uint32_t n = (uint32_t)es.w * (uint32_t)es.h;
-    const float s = fminf(u1, 0.99999994f) * (float)n;
-    uint32_t i = min((uint32_t)s, n - 1u);
-    const float coin = s - (float)i;
-    if (coin >= __ldg(es.prob + i)) i = __ldg(es.alias + i);
+    uint32_t i = min(__umulhi(bucketBits, n), n - 1u);
+    if (coin > __ldg(es.prob + i)) i = __ldg(es.alias + i);   // P(coin <= p) = floor(p * 2^24) / 2^24
     const uint32_t y = i / (uint32_t)es.w, x = i - y * (uint32_t)es.w;
-    const float u = ((float)x + fminf(u2, 0.99999994f)) / (float)es.w, v = ((float)y + fminf(u3, 0.99999994f)) / (float)es.h;
+    const float u = ((float)x + fminf(ux, 0.99999994f)) / (float)es.w, v = ((float)y + fminf(uy, 0.99999994f)) / (float)es.h;
     const float theta = (1.0f - v) * kPi, phi = 2.0f * kPi * u;
     float st, ct, sp, cp;
     sincosf(theta, &st, &ct);

@@ -127,8 +127,10 @@ namespace {
 struct JpegHuff {
     uint8_t bits[17] = {0};
     uint8_t vals[256] = {0};
-    int mincode[17], maxcode[18], valptr[17];
+    int mincode[17] = {0}, maxcode[18] = {0}, valptr[17] = {0};
+    bool defined = false;           // set by a DHT segment; a scan that names an undefined table is refused
     void build() {
+        defined = true;
         int code = 0, k = 0;
         for (int l = 1; l <= 16; ++l) {
             valptr[l] = k;
@@ -221,6 +223,7 @@ static void loadJPEG(const std::string& data, Picture& pic) {
     const uint8_t* p = reinterpret_cast<const uint8_t*>(data.data());
     const size_t n = data.size();
     uint16_t qt[4][64] = {};
+    bool qtDefined[4] = {false, false, false, false};
     JpegHuff dc[4], ac[4];
     std::vector<JpegComp> comps;
     int restartInterval = 0, adobeTransform = -1;
@@ -247,6 +250,7 @@ static void loadJPEG(const std::string& data, Picture& pic) {
                     qt[tq][kZigzag[i]] = pq ? (uint16_t)((seg[o] << 8) | seg[o + 1]) : seg[o];
                     o += pq ? 2 : 1;
                 }
+                qtDefined[tq] = true;
             }
         } else if (m == 0xC4) {   // DHT
             size_t o = 0;
@@ -287,12 +291,20 @@ static void loadJPEG(const std::string& data, Picture& pic) {
             adobeTransform = seg[11];
         } else if (m == 0xDA) {   // SOS: one interleaved scan with every component
             if (!haveFrame) throw std::runtime_error("Picture: JPEG scan before frame header");
+            if (segLen < 1) throw std::runtime_error("Picture: truncated JPEG scan header");
             const int ns = seg[0];
             if (ns != (int)comps.size()) throw std::runtime_error("Picture: non-interleaved JPEG scans are not supported");
+            if (segLen < (size_t)(1 + 2 * ns + 3)) throw std::runtime_error("Picture: truncated JPEG scan header");
             for (int i = 0; i < ns; ++i) {
                 const int cid = seg[1 + 2 * i];
+                const int td = seg[2 + 2 * i] >> 4, ta = seg[2 + 2 * i] & 15;
+                if (td > 3 || ta > 3) throw std::runtime_error("Picture: JPEG scan names a Huffman table above 3");
                 for (JpegComp& c : comps)
-                    if (c.id == cid) { c.td = seg[2 + 2 * i] >> 4; c.ta = seg[2 + 2 * i] & 15; }
+                    if (c.id == cid) { c.td = td; c.ta = ta; }
+            }
+            for (const JpegComp& c : comps) {
+                if (!dc[c.td].defined || !ac[c.ta].defined) throw std::runtime_error("Picture: JPEG scan uses a Huffman table no DHT segment defined");
+                if (!qtDefined[c.tq]) throw std::runtime_error("Picture: JPEG component uses a quantisation table no DQT segment defined");
             }
             int hmax = 1, vmax = 1;
             for (const JpegComp& c : comps) { hmax = std::max(hmax, c.h); vmax = std::max(vmax, c.v); }
@@ -319,6 +331,7 @@ static void loadJPEG(const std::string& data, Picture& pic) {
                             for (int bx = 0; bx < c.h; ++bx) {
                                 std::memset(blk, 0, sizeof blk);
                                 const int t = jpegDecode(br, dc[c.td]);
+                                if (t > 16) throw std::runtime_error("Picture: corrupt JPEG DC size category");
                                 c.pred += jpegExtend(br.receive(t), t);
                                 blk[0] = (float)(c.pred * (int)qt[c.tq][0]);
                                 for (int k = 1; k < 64;) {

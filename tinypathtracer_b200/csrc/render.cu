@@ -452,7 +452,7 @@ __device__ __forceinline__ bool shade_vertex(const BvhView& bvh, const ShadePara
             float u1, u2, u3, u4, pl;
             rng_pair(key, 0x10000u + 2u * (uint32_t)depth, u1, u2);
             rng_pair(key, 0x10001u + 2u * (uint32_t)depth, u3, u4);
-            vx.ldir = env_sample_dir(sp.es, u1, u2, u3, pl);
+            vx.ldir = env_sample_dir(sp.es, (uint32_t)(rng_bits(key, 0x10000u + 2u * (uint32_t)depth) >> 32), u4, u2, u3, pl);
             const float pbl = dot(vx.ldir, nn) * (1.0f / kPi);
             if (pbl > 0.0f && pl > 0.0f) {
                 vx.lw = (vx.Tn * env_lookup(sp.env, sp.envf, sp.envW, sp.envH, vx.ldir)) * (pbl / (pl + pbl));
@@ -496,23 +496,29 @@ __device__ __forceinline__ void emit_vertex(const ShadeParams& sp, const QueueOu
     float4* ext = q.ext + 3 * (size_t)seg * q.extSegCap;
     float4* sec = q.sec + 3 * (size_t)seg * q.secSegCap;
     uint32_t slot = (uint32_t)(base >> 32) + nL * __popc(m & lt) + __popc(bDir & lt) + __popc(bNee & lt);
-    // The pools are sized for the most every path can emit, so a reservation cannot pass the end; should that ever
-    // be wrong, nothing is written out of bounds: the ray is dropped and counted, and the consumer clamps its counts.
+    // The pools are sized for the most every path can emit, so a reservation cannot pass the end; should that ever be wrong,
+    // nothing is written out of bounds and nothing is left unwritten below the cap: every reserved slot that lies inside its pool
+    // is written (the consumer clamps its counts to the cap, so it reads exactly those), the rest is dropped and counted.
     const uint32_t extSlot = (uint32_t)base + __popc(bExt & lt);
     const uint32_t mySec = nL + (vx.direct ? 1u : 0u) + ((NEE && vx.nee) ? 1u : 0u);
-    if (slot + mySec > q.secCap || (vx.next && extSlot >= q.extCap)) {
-        atomicAdd(&ctr->queue_overflow, 1ull);
-        return;
-    }
+    const bool extFits = extSlot < q.extCap;
+    if (slot + mySec > q.secCap || (vx.next && !extFits)) atomicAdd(&ctr->queue_overflow, 1ull);
     // delta lights: one infinite shadow ray per light, contribution T_d * baseColor * Li
-    for (int l = 0; l < (int)nL; ++l) {
+    for (int l = 0; l < (int)nL; ++l, ++slot) {
+        if (slot >= q.secCap) continue;
         float3 ldir, lrad;
         light_incoming(sp.lights[l], vx.P, ldir, lrad);
-        store_path(sec, slot++, vx.P, ldir, vx.Tn * (vx.base * lrad), pixel, sample, kKindShadow);
+        store_path(sec, slot, vx.P, ldir, vx.Tn * (vx.base * lrad), pixel, sample, kKindShadow);
     }
-    if (vx.direct) store_path(sec, slot++, vx.P, vx.ddir, vx.Tn, pixel, sample, kKindDirect);
-    if (NEE && vx.nee) store_path(sec, slot++, vx.P, vx.ldir, vx.lw, pixel, sample, kKindShadow);
-    if (vx.next) store_path(ext, extSlot, vx.P, vx.ndir, vx.Tn, pixel, sample, NEE ? __float_as_uint(vx.pb) : ahead);
+    if (vx.direct) {
+        if (slot < q.secCap) store_path(sec, slot, vx.P, vx.ddir, vx.Tn, pixel, sample, kKindDirect);
+        ++slot;
+    }
+    if (NEE && vx.nee) {
+        if (slot < q.secCap) store_path(sec, slot, vx.P, vx.ldir, vx.lw, pixel, sample, kKindShadow);
+        ++slot;
+    }
+    if (vx.next && extFits) store_path(ext, extSlot, vx.P, vx.ndir, vx.Tn, pixel, sample, NEE ? __float_as_uint(vx.pb) : ahead);
 }
 
 // The delta-light shadow rays of one vertex, traced where the vertex was shaded (k_primary): the lanes of a pixel group sit at
