@@ -228,6 +228,16 @@ int tpt_env_sampler_tables(tpt_context* ctx, float* prob, uint32_t* alias, float
 int tpt_trace_rays(tpt_scene* scene, const tpt_ray* rays, size_t n, tpt_hit* hits, int any_hit, int device_ptrs);
 /* Same, additionally counting node visits and triangle tests into the context counters. */
 int tpt_trace_rays_counted(tpt_scene* scene, const tpt_ray* rays, size_t n, tpt_hit* hits, int any_hit, int device_ptrs);
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same kernel and same results as
+ * tpt_trace_rays, but it allocates nothing, on the device or through any allocating library routine: the scratch the kernel
+ * needs (its work cursor; for host buffers also the ray and hit staging) is a file-scope `static __device__` array of
+ * 256 + TPT_TRACE_STATIC_MAX_RAYS * 40 bytes (about 2.5 MiB) that every GPU which loads the library holds until exit.
+ * n > TPT_TRACE_STATIC_MAX_RAYS is refused with TPT_ERR_INVALID.  rays / hits are host pointers unless device_ptrs != 0
+ * (device buffers are used in place; host buffers make the call synchronous).  All calls on one GPU share the array: calls
+ * that overlap on the GPU (two contexts / streams on the same device) race; calls on one context are ordered by its stream. */
+#define TPT_TRACE_STATIC_MAX_RAYS 65536
+int tpt_trace_rays_static(tpt_scene* scene, const tpt_ray* rays, size_t n, tpt_hit* hits, int any_hit, int device_ptrs);
 /* sampleRays (src/path_tracer.cu:42-59) for every pixel with (u,v) = (0.5,0.5) (jitter == 0) or the
  * sample-0 jitter of `seed`; rays is a device (device_ptrs != 0) or host buffer of width*height tpt_ray,
  * pixel (x,y) at index y*width + x, row 0 = bottom. */

@@ -28,6 +28,7 @@ TPT_RENDER_NO_PIXEL_CANDIDATES = 8
 TPT_RENDER_REFIT = 16
 TPT_RENDER_ROUGH_METALS = 32
 TPT_RENDER_NO_SPECULAR_CONTINUATION = 64
+TPT_TRACE_STATIC_MAX_RAYS = 65536
 
 
 class Ray(C.Structure):
@@ -98,6 +99,7 @@ SIGNATURES = {
     "tpt_env_sampler_tables": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "tpt_trace_rays": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int, C.c_int]),
     "tpt_trace_rays_counted": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int, C.c_int]),
+    "tpt_trace_rays_static": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int, C.c_int]),
     "tpt_generate_primary_rays": (C.c_int, [C.c_void_p, C.POINTER(Camera), C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_void_p, C.c_int]),
     "tpt_accum_create": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]),
     "tpt_accum_wrap": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]),

@@ -26,6 +26,8 @@
 // depend on the order in which kernels, warps or GPUs finish, nor on how terms are grouped.
 #include <algorithm>
 #include <cstring>
+#include <mutex>
+#include <string>
 
 #include "env.cuh"
 #include "traverse.cuh"
@@ -1551,5 +1553,76 @@ int tpt_resolve_impl(tpt_accum* acc, int sppTotal, uint8_t* d_fb) {
         acc->data, acc->width, acc->height, 1.0f / (float)sppTotal, reinterpret_cast<uchar4*>(d_fb));
     TPT_CUDA(cudaGetLastError());
     acc->ctx->kernel_launches += 1;
+    return TPT_OK;
+}
+
+// ---- tpt_trace_rays_static: the batch trace entry for callers that must not allocate ----------------------------------
+// No counterpart in the reference (include/tpt.h).  Same kernel as
+// tpt_trace_rays (k_trace_rays_persistent), but every byte of device scratch it needs — the persistent kernel's work cursor
+// and, for host buffers, the ray / hit staging — lives in ONE file-scope __device__ array of fixed size instead of
+// cudaMalloc'd blocks.  Every GPU that loads the library holds the array (kStaticBytes, about 2.5 MiB) until exit; all calls
+// on one GPU share it, so calls that overlap on the GPU race.  It keeps the last call's contents: the cursor is cleared by
+// every call, the staging areas are overwritten before they are read.
+namespace tpt {
+constexpr size_t kStaticMaxRays = TPT_TRACE_STATIC_MAX_RAYS;
+constexpr size_t kStaticRaysOff = 256;                                                   // [0, 256): the work cursor (8 bytes used)
+constexpr size_t kStaticHitsOff = kStaticRaysOff + kStaticMaxRays * sizeof(tpt_ray);
+constexpr size_t kStaticBytes = kStaticHitsOff + kStaticMaxRays * sizeof(tpt_hit);
+static_assert(kStaticHitsOff % 16 == 0, "hits are written with 128-bit stores");
+static __device__ __align__(256) unsigned char g_trace_static_scratch[kStaticBytes];
+}   // namespace tpt
+
+// In host code `g_trace_static_scratch` is only a handle for the symbol, not a device address: the address is looked up once per
+// device, with that device current, and cached.
+static int trace_static_scratch(int device, unsigned char** out) {
+    constexpr int kMaxDevices = 64;
+    static unsigned char* addr[kMaxDevices] = {};
+    static std::mutex mu;
+    TPT_REQUIRE(device >= 0 && device < kMaxDevices, "tpt_trace_rays_static: device ordinal out of range");
+    std::lock_guard<std::mutex> lock(mu);
+    if (addr[device] == nullptr) {
+        void* p = nullptr;
+        TPT_CUDA(cudaGetSymbolAddress(&p, g_trace_static_scratch));   // the caller has made `device` current
+        TPT_REQUIRE(p != nullptr, "tpt_trace_rays_static: cudaGetSymbolAddress returned NULL");
+        addr[device] = static_cast<unsigned char*>(p);
+    }
+    *out = addr[device];
+    return TPT_OK;
+}
+
+extern "C" int tpt_trace_rays_static(tpt_scene* s, const tpt_ray* rays, size_t n, tpt_hit* hits, int any_hit, int device_ptrs) {
+    TPT_REQUIRE(s && (n == 0 || (rays && hits)), "tpt_trace_rays_static: NULL argument");
+    if (n > kStaticMaxRays) {
+        set_error("tpt_trace_rays_static: " + std::to_string(n) + " rays exceed the static scratch (TPT_TRACE_STATIC_MAX_RAYS = " +
+                  std::to_string(kStaticMaxRays) + "); split the batch or use tpt_trace_rays");
+        return TPT_ERR_INVALID;
+    }
+    if (!s->built) {
+        set_error("tpt_trace_rays_static: call tpt_bvh_build first");
+        return TPT_ERR_STATE;
+    }
+    if (n == 0) return TPT_OK;
+    tpt_context* ctx = s->ctx;
+    TPT_CUDA(cudaSetDevice(ctx->device));
+    unsigned char* scratch = nullptr;
+    TPT_CHECK(trace_static_scratch(ctx->device, &scratch));
+    unsigned long long* cursor = reinterpret_cast<unsigned long long*>(scratch);
+    const tpt_ray* dRays = rays;
+    tpt_hit* dHits = hits;
+    if (!device_ptrs) {
+        dRays = reinterpret_cast<const tpt_ray*>(scratch + kStaticRaysOff);
+        dHits = reinterpret_cast<tpt_hit*>(scratch + kStaticHitsOff);
+        TPT_CUDA(cudaMemcpyAsync(scratch + kStaticRaysOff, rays, n * sizeof(tpt_ray), cudaMemcpyHostToDevice, ctx->stream));
+    }
+    TPT_CUDA(cudaMemsetAsync(cursor, 0, sizeof(unsigned long long), ctx->stream));   // the array keeps the last call's cursor
+    static unsigned grid[64] = {};   // an occupancy query, no allocation
+    if (grid[ctx->device] == 0) grid[ctx->device] = kNumSMs * resident_blocks(k_trace_rays_persistent<false>, 128);
+    k_trace_rays_persistent<false><<<grid[ctx->device], 128, 0, ctx->stream>>>(s->view(), dRays, n, dHits, any_hit, cursor, ctx->d_counters);
+    TPT_CUDA(cudaGetLastError());
+    ctx->kernel_launches += 1;
+    if (!device_ptrs) {
+        TPT_CUDA(cudaMemcpyAsync(hits, dHits, n * sizeof(tpt_hit), cudaMemcpyDeviceToHost, ctx->stream));
+        TPT_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
     return TPT_OK;
 }
