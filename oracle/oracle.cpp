@@ -940,7 +940,81 @@ void orc_primary_rays(const float* cam19, int W, int H, int useJitter, uint64_t 
         }
 }
 
-// mode 0: brute force (authority; lowest ID on exact ties).  mode 1: reference BVH traversal order.
+// Brute force for LARGE triangle counts (the 10 M-triangle soup): the same Möller–Trumbore arithmetic and the same acceptance
+// rule as brute_force() above, evaluated for 8 triangles at a time with the compiler's vector types.  Every vector operation is
+// the element-wise IEEE operation of the scalar code (no contraction: -ffp-contract=off; no reassociation), so each lane
+// computes bit for bit what ray_hit_triangle computes; lanes are then visited in ascending triangle order with the same strict
+// `<`, which keeps the lowest-primitive-id tie rule.  Triangles are processed in cache-sized blocks (outer loop, ascending),
+// all rays per block (parallel), so the cost is arithmetic, not memory.  tests/test_oracle_known_answers.py checks it equals
+// mode 0 exactly.
+typedef float vf8 __attribute__((vector_size(32)));
+typedef int vi8 __attribute__((vector_size(32)));
+constexpr int kBruteBlock = 2048;   // triangles per block: 9 SoA arrays x 2048 x 4 B = 72 KB
+
+__attribute__((target_clones("avx2", "default")))
+void brute_block(const float* soa, int fBase, int count, const float* rays6, long long n, Hit* out) {
+    const int padded = (count + 7) & ~7;
+    const float* V0x = soa, *V0y = soa + kBruteBlock, *V0z = soa + 2 * kBruteBlock;
+    const float* E1x = soa + 3 * kBruteBlock, *E1y = soa + 4 * kBruteBlock, *E1z = soa + 5 * kBruteBlock;
+    const float* E2x = soa + 6 * kBruteBlock, *E2y = soa + 7 * kBruteBlock, *E2z = soa + 8 * kBruteBlock;
+#pragma omp parallel for schedule(dynamic, 64)
+    for (long long i = 0; i < n; ++i) {
+        const float ox = rays6[6 * i], oy = rays6[6 * i + 1], oz = rays6[6 * i + 2];
+        const float dx = rays6[6 * i + 3], dy = rays6[6 * i + 4], dz = rays6[6 * i + 5];
+        Hit h = out[i];
+        for (int j = 0; j < padded; j += 8) {
+            const vf8 v0x = *(const vf8*)(V0x + j), v0y = *(const vf8*)(V0y + j), v0z = *(const vf8*)(V0z + j);
+            const vf8 e1x = *(const vf8*)(E1x + j), e1y = *(const vf8*)(E1y + j), e1z = *(const vf8*)(E1z + j);
+            const vf8 e2x = *(const vf8*)(E2x + j), e2y = *(const vf8*)(E2y + j), e2z = *(const vf8*)(E2z + j);
+            const vf8 tx = ox - v0x, ty = oy - v0y, tz = oz - v0z;                               // t = r.o - v0
+            const vf8 px = dy * e2z - dz * e2y, py = dz * e2x - dx * e2z, pz = dx * e2y - dy * e2x;   // p = cross(r.d, e2)
+            const vf8 qx = ty * e1z - tz * e1y, qy = tz * e1x - tx * e1z, qz = tx * e1y - ty * e1x;   // q = cross(t, e1)
+            const vf8 denom = px * e1x + py * e1y + pz * e1z;
+            const vf8 inv = 1.0f / denom;
+            const vf8 u = (px * tx + py * ty + pz * tz) * inv;
+            const vf8 v = (qx * dx + qy * dy + qz * dz) * inv;
+            const vf8 dist = (qx * e2x + qy * e2y + qz * e2z) * inv;
+            const vi8 reject = (denom == 0.0f) | (u < 0.0f) | (v < 0.0f) | ((u + v) > 1.0f);
+            const vi8 ok = ~reject & (dist < h.dist) & (dist > kDelta);
+            typedef long long vl4 __attribute__((vector_size(32)));
+            const vl4 ok4 = (vl4)ok;
+            if (((ok4[0] | ok4[1]) | (ok4[2] | ok4[3])) == 0) continue;
+            for (int l = 0; l < 8; ++l)   // ascending ids, strict '<' against the running best: brute_force()'s rule
+                if (ok[l] && j + l < count && dist[l] < h.dist) {
+                    h.dist = dist[l];
+                    h.idx = fBase + j + l;
+                    h.u = u[l];
+                    h.v = v[l];
+                }
+        }
+        out[i] = h;
+    }
+}
+
+void brute_force_blocked(const float* wverts, const uint32_t* indices, int F, const float* rays6, long long n, Hit* out) {
+    for (long long i = 0; i < n; ++i) out[i] = no_hit();
+    float* soa = static_cast<float*>(aligned_alloc(64, sizeof(float) * 9 * kBruteBlock));
+    for (int f0 = 0; f0 < F; f0 += kBruteBlock) {
+        const int count = std::min(kBruteBlock, F - f0);
+        for (int k = 0; k < ((count + 7) & ~7); ++k) {
+            V3 v0 = v3(0.f, 0.f, 0.f), e1 = v0, e2 = v0;   // padding lanes: denom == 0 -> rejected
+            if (k < count) {
+                const int f = f0 + k;
+                v0 = ld3(wverts, indices[3 * f]);
+                e1 = ld3(wverts, indices[3 * f + 1]) - v0;   // the subtractions ray_hit_triangle performs per test
+                e2 = ld3(wverts, indices[3 * f + 2]) - v0;
+            }
+            soa[k] = v0.x; soa[kBruteBlock + k] = v0.y; soa[2 * kBruteBlock + k] = v0.z;
+            soa[3 * kBruteBlock + k] = e1.x; soa[4 * kBruteBlock + k] = e1.y; soa[5 * kBruteBlock + k] = e1.z;
+            soa[6 * kBruteBlock + k] = e2.x; soa[7 * kBruteBlock + k] = e2.y; soa[8 * kBruteBlock + k] = e2.z;
+        }
+        brute_block(soa, f0, count, rays6, n, out);
+    }
+    free(soa);
+}
+
+// mode 0: brute force (authority; lowest ID on exact ties).  mode 1: reference BVH traversal order.  mode 2: mode 0's
+// result computed block-wise with vector arithmetic (brute_force_blocked; for millions of triangles).
 // hits: (idx:int32, dist, u, v) 16 bytes each.  counters (optional): [rays, nInt, nLeaf].
 int orc_trace_rays(const float* wverts, const uint32_t* indices, int F, const void* nodes36, const float* rays6, size_t n, int mode,
                    void* hits16, uint64_t* counters) {
@@ -948,6 +1022,11 @@ int orc_trace_rays(const float* wverts, const uint32_t* indices, int F, const vo
     Hit* out = reinterpret_cast<Hit*>(hits16);
     int bad = 0;
     uint64_t nI = 0, nL = 0;
+    if (mode == 2) {
+        brute_force_blocked(wverts, indices, F, rays6, (long long)n, out);
+        if (counters) counters[0] = n, counters[1] = 0, counters[2] = 0;
+        return 0;
+    }
 #pragma omp parallel for schedule(dynamic, 256) reduction(+ : bad, nI, nL)
     for (long long i = 0; i < (long long)n; ++i) {
         Ray r{ld3(rays6, 2 * i), ld3(rays6, 2 * i + 1)};

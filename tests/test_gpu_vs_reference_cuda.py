@@ -26,14 +26,16 @@ def run_reference(scene, W, H, spp, env, out, exe="tpt_ref_headless"):
 
 
 @pytest.mark.parametrize("scene,env,depth,spp", [("box", "black.png", 8, 16384), ("ball", "sky.png", 8, 1024), ("tir", "black.png", 8, 262144),
+                                                 ("tir", "black.png", 32, 262144),    # BASELINE configs[2] at its own depth: DEPTH_TRACE=32 build of the reference
                                                  ("box2", "sky.png", 8, 4096), ("light", "sky.png", 8, 1024), ("square", "black.png", 8, 1024)])
 def test_image_matches_reference_cuda_build(scene, env, depth, spp, tpt, ctx, scenes, tmp_path):
-    if not (REF / "tpt_ref_headless").exists():
-        pytest.skip("oracle/_ref/tpt_ref_headless not built (needs /root/reference at build time)")
+    exe = "tpt_ref_headless_d32" if depth == 32 else "tpt_ref_headless"    # DEPTH_TRACE is a compile-time constant (src/path_tracer.cu:17)
+    if not (REF / exe).exists():
+        pytest.skip(f"oracle/_ref/{exe} not built (needs /root/reference at build time)")
     # spp chosen so that the Monte-Carlo noise floor (ours-vs-ours == ref-vs-ref == ours-vs-ref at every spp, falling as
     # 1/spp: profiles/r01_image_parity_noise_floor.txt) sits below the 1e-3 bar
     W, H = 192, 108
-    ref_fb, info = run_reference(scene, W, H, spp, env, tmp_path / "ref.bgra")
+    ref_fb, info = run_reference(scene, W, H, spp, env, tmp_path / "ref.bgra", exe=exe)
     assert info["depth"] == depth and info["spp"] == spp
     env_img = synthetic_sky(4096, 2048) if env == "sky.png" else None
     ds = tpt.DeviceScene(ctx, scenes[scene])

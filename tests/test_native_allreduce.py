@@ -19,12 +19,17 @@ def _device_count():
 
 
 @pytest.mark.parametrize("n", [2, 3, 8])
-def test_allreduce_of_slices_equals_one_render(n, tpt, scenes):
+def test_allreduce_of_slices_equals_one_render(n, tpt, scenes, capsys):
     ngpu = _device_count()
     if ngpu >= n:
         ctxs = tpt.comm_init_all(n)                       # one context per GPU, peer access enabled
+        form = f"REAL PEERS, one context per GPU 0..{n - 1} (peer loads / cudaMemcpyPeerAsync over NVLink)"
     else:
         ctxs = [tpt.Context(0) for _ in range(n)]          # n contexts on the one GPU there is
+        form = (f"{ngpu} GPU(s) visible -> DEGENERATE form, {n} contexts on GPU 0 (peer accesses are local); the NVLink form runs in "
+                "bench.py --gpus N (native_allreduce_sha256)")
+    with capsys.disabled():     # visible under `pytest -q` too: a pass on a one-GPU box says nothing about the NVLink path
+        print(f"\n[native all-reduce] n={n}: {form}")
     s = scenes["box2"]
     cam = tpt.Camera.from_scene(s)
     W, H, per = 81, 45, 4                                  # 81 * 45 * 3 elements: odd, and not a multiple of n

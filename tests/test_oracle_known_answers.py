@@ -293,3 +293,25 @@ def test_estimator_closed_form_furnace(orc, scenes):
     env = np.full((4, 8, 4), 255, np.uint8)
     img = orc.render(s, 16, 9, 4, max_depth=8, seed=1, env=env) / 4.0
     np.testing.assert_allclose(img, np.broadcast_to(np.array([0.5, 0.25, 1.0], np.float32), img.shape), rtol=2e-6)
+
+
+@pytest.mark.parametrize("name", ["box", "ball", "tir"])
+def test_blocked_vector_brute_force_equals_scalar_brute_force(name, orc, scenes):
+    """Oracle mode 2 (brute_force_blocked: the authority for the 10 M-triangle soup, tests/test_gpu_soup_full.py) must be the
+    scalar brute force (mode 0) bit for bit — ids with the lowest-id tie rule, t, u, v — including rays through shared edges
+    and vertices (pixel-centre primary rays hit the quads' diagonals) and rays that miss."""
+    s = scenes[name]
+    wv, _ = orc.transform(s)
+    rng = np.random.default_rng(9)
+    prim = orc.primary_rays(s, 96, 54)
+    lo, hi = wv.min(0), wv.max(0)
+    o = (lo + (hi - lo) * rng.random((3000, 3))).astype(np.float32)
+    d = rng.normal(size=(3000, 3)).astype(np.float32)
+    # rays aimed exactly at vertices: exact-t ties between the triangles that share them
+    v = wv[rng.integers(0, wv.shape[0], 500)]
+    aimed = np.concatenate([np.broadcast_to(prim[0, :3], (500, 3)), v - prim[0, :3]], axis=1).astype(np.float32)
+    rays = np.concatenate([prim, np.concatenate([o, d], axis=1), aimed])
+    a = orc.trace_rays(wv, s["indices"], rays, mode=0)
+    b = orc.trace_rays(wv, s["indices"], rays, mode=2)
+    assert (a["prim"] >= 0).any() and (a["prim"] < 0).any()
+    assert a.tobytes() == b.tobytes()
