@@ -160,6 +160,8 @@ typedef struct tpt_counters {
                                            * of their pixel's pyramid instead of walking the tree */
     uint64_t queue_overflow;              /* vertices whose rays did not fit their queue and were dropped; 0 by construction (the
                                            * pools hold the worst case), checked by the tests */
+    uint64_t rays_queued;                 /* rays (part of extension + shadow + direct) that passed through a wavefront queue: the
+                                           * HBM traffic of the bundled scenes (48-B record written once, read once) */
 } tpt_counters;
 
 /* Device time per wavefront stage since the last tpt_reset_counters, measured with CUDA events on the
@@ -186,6 +188,12 @@ int tpt_get_stage_times(tpt_context* ctx, tpt_stage_times* out);
 /* Replaces Scene::copySceneToDevice (src/mesh.cu:309-397): host arrays -> device. */
 int tpt_scene_create(tpt_context* ctx, const tpt_scene_desc* desc, tpt_scene** out);
 int tpt_scene_destroy(tpt_scene* scene);
+/* Copy a new set of host arrays into the device arrays of an existing scene: what Scene::copySceneToDevice
+ * (src/mesh.cu:309-397) does per loaded file, without tpt_scene_create's ~24 allocations and tpt_scene_destroy's frees
+ * and synchronisation — for callers that re-upload every frame.  Every count must equal the scene's (TPT_ERR_INVALID
+ * otherwise); the scene must be rebuilt (tpt_bvh_build) before it is traced; tpt_bvh_refit is refused until then.
+ * Asynchronous on the context stream; the host arrays may be reused on return. */
+int tpt_scene_update(tpt_scene* scene, const tpt_scene_desc* desc);
 /* Update per-object transforms (n_objects x 16 each, host pointers); the reference re-reads
  * vertTrans/normalTrans every frame (src/path_tracer.cu:536-537). */
 int tpt_scene_set_transforms(tpt_scene* scene, const float* vert_trans, const float* normal_trans);
@@ -203,6 +211,10 @@ int tpt_bvh_refit(tpt_scene* scene, tpt_bvh_stats* stats);
 /* Structural export in the reference's layout (include/bvh.cuh:34-58, 36-byte BVHNode, internal nodes
  * [0,F-1) then leaves [F-1,2F-1), child indices global, leaf k holds its face id): n_nodes must be 2F-1. */
 int tpt_bvh_export_reference_nodes(tpt_scene* scene, void* out_nodes36, size_t n_nodes);
+/* The leaf order of the last tpt_bvh_build: the sorted Morton keys (m_keys of the reference's BVH, include/bvh.cuh:67, after its
+ * thrust::sort_by_key, src/bvh.cu:326) and the face id of every sorted leaf.  HOST outputs of n_faces entries; either may be
+ * NULL.  The sort is stable: equal keys keep ascending face id. */
+int tpt_bvh_export_order(tpt_scene* scene, uint64_t* keys, uint32_t* faces);
 /* World-space vertices / normals after the transform step (host output, n_vertices x 3 each; either may be NULL). */
 int tpt_scene_export_world(tpt_scene* scene, float* world_vertices, float* world_normals);
 

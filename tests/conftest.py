@@ -13,6 +13,10 @@ if str(ROOT) not in sys.path:
 # the limit so that the continuation is exercised on every fixture — results are bit-identical either way, which is what
 # test_specular_continuation_is_bit_identical_to_queued_paths asserts against the queued form.
 os.environ.setdefault("TPT_SPEC_MAX_FACES", "100000000")
+# 4-wide compressed nodes are built for scenes of 65 536 triangles and more by default (csrc/capi.cu); the tests build them for
+# every scene, so that each traversal test of tpt_trace_rays (brute-force parity on the seven fixtures, the soups) walks the wide
+# tree.  test_wide_and_binary_walks_agree (tests/test_gpu_round2.py) runs the binary walk beside it (TPT_NO_WIDE).
+os.environ.setdefault("TPT_WIDE_MIN_FACES", "2")
 
 SCENES = ["box", "box1", "box2", "tir", "ball", "light", "square"]
 GOLDEN = ROOT / "tests" / "golden"

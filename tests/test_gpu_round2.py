@@ -1,0 +1,160 @@
+"""Round-2 additions to the render path: the cooperative multi-level wave kernel (k_wave_loop), the warp-cooperative tile walk
+in front of the per-pixel candidate lists (tile_collect) and tpt_scene_update.  The first two are pure re-schedulings of the
+same integer-accumulated terms, so the bar is bit-identical accumulation buffers against the per-level / per-pixel forms
+(switched back on with the tuning variables TPT_NO_WAVE_LOOP / TPT_NO_TILE_WALK, which the library reads once per process —
+hence the subprocesses)."""
+import hashlib
+import os
+import subprocess
+import sys
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = Path(__file__).resolve().parents[1]
+
+_SNIPPET = r"""
+import sys, hashlib, json
+sys.path.insert(0, {root!r})
+import numpy as np
+import tinypathtracer_b200 as tpt
+from tinypathtracer_b200.scene_io import load_scene_npz
+from tinypathtracer_b200.sky import synthetic_sky
+out = {{}}
+ctx = tpt.Context(0)
+for name, W, H, spp, depth, env, pif in {cases!r}:
+    scene = load_scene_npz({root!r} + "/tests/golden/scenes/" + name + ".npz")
+    ds = tpt.DeviceScene(ctx, scene)
+    tpt.BVH(ds).construct(stats=False)
+    pt = tpt.PathTracer(ctx, W, H, env_rgba8=synthetic_sky(256, 128) if env else None)
+    pt.render_into(ds, tpt.Camera.from_scene(scene), spp=spp, max_depth=depth, seed=11, paths_in_flight=pif)
+    out[name + str(depth) + str(pif)] = hashlib.sha256(pt.m_radiance.to_i64().tobytes()).hexdigest()
+    c = ctx.counters()
+    assert c["queue_overflow"] == 0
+    ds.close()
+print(json.dumps(out))
+"""
+
+CASES = [("box", 96, 54, 64, 8, False, 0), ("ball", 160, 90, 64, 8, True, 0), ("tir", 96, 54, 64, 32, False, 0), ("light", 96, 54, 32, 8, True, 0),
+         ("square", 64, 36, 32, 8, False, 0), ("box2", 64, 36, 16, 2, True, 0), ("box", 64, 36, 8, 1, False, 0),
+         ("box", 96, 54, 64, 8, False, 20000)]      # several batches (form A and B of k_primary)
+
+
+def _run(extra_env):
+    import json
+    env = dict(os.environ)
+    env.update(extra_env)
+    r = subprocess.run([sys.executable, "-c", _SNIPPET.format(root=str(ROOT), cases=CASES)], capture_output=True, text=True, env=env, timeout=900)
+    assert r.returncode == 0, r.stderr[-3000:]
+    return json.loads(r.stdout.strip().splitlines()[-1])
+
+
+def test_wave_loop_and_tile_walk_keep_every_accumulator_bit():
+    new = _run({})
+    old = _run({"TPT_NO_WAVE_LOOP": "1", "TPT_NO_TILE_WALK": "1"})
+    assert new == old
+    assert _run({"TPT_NO_WAVE_LOOP": "1"}) == new and _run({"TPT_NO_TILE_WALK": "1"}) == new
+
+
+def test_scene_update_equals_a_new_scene(tpt, ctx, scenes, orc):
+    """tpt_scene_update re-uploads into the existing allocations: the rebuilt tree and its hits are those of a scene created
+    from the same arrays; sizes must match; a refit is refused until the scene has been rebuilt."""
+    base = scenes["box"]
+    moved = dict(base)
+    moved["vertices"] = (np.asarray(base["vertices"], np.float32) * np.float32(1.25) + np.float32(0.125)).astype(np.float32)
+    mats = np.array(base["materials"], copy=True)
+    mats["base"][0] = (0.25, 0.5, 0.75)
+    moved["materials"] = mats
+    ds = tpt.DeviceScene(ctx, base)
+    bvh = tpt.BVH(ds)
+    bvh.construct()
+    ds.update(moved)
+    with pytest.raises(tpt.TptError):
+        bvh.refit()                                   # no hierarchy for the new geometry yet
+    rays = orc.primary_rays(moved, 160, 90)
+    with pytest.raises(tpt.TptError):
+        bvh.trace(rays)                               # not built
+    bvh.construct()
+    fresh = tpt.DeviceScene(ctx, moved)
+    fb = tpt.BVH(fresh)
+    fb.construct()
+    a, b = bvh.trace(rays), fb.trace(rays)
+    assert a.tobytes() == b.tobytes() and (a["prim"] >= 0).any()
+    wv, _ = orc.transform(moved)
+    assert np.array_equal(ds.world()[0], wv)
+    ref = orc.trace_rays(wv, moved["indices"], rays, mode=0)
+    assert a.tobytes() == ref.tobytes()
+    # the material table went up too: same image as the fresh scene, bit for bit
+    cam = tpt.Camera.from_scene(moved)
+    imgs = []
+    for d in (ds, fresh):
+        pt = tpt.PathTracer(ctx, 64, 36)
+        pt.render_into(d, cam, spp=8, max_depth=4, seed=3)
+        imgs.append(pt.m_radiance.to_i64())
+    assert (imgs[0] == imgs[1]).all() and imgs[0].any()
+    with pytest.raises(tpt.TptError, match="sizes differ"):
+        ds.update(scenes["ball"])
+    ds.close()
+    fresh.close()
+
+
+_TRACE_SNIPPET = r"""
+import sys, hashlib, json
+sys.path.insert(0, {root!r})
+import numpy as np
+import tinypathtracer_b200 as tpt
+from tinypathtracer_b200.scene_io import load_scene_npz
+from tinypathtracer_b200.soup import make_soup
+out = {{}}
+ctx = tpt.Context(0)
+ball = load_scene_npz({root!r} + "/tests/golden/scenes/ball.npz")
+for name in ["box", "box1", "box2", "tir", "ball", "light", "square", "soup"]:
+    scene = make_soup(ball, 64, 25) if name == "soup" else load_scene_npz({root!r} + "/tests/golden/scenes/" + name + ".npz")
+    ds = tpt.DeviceScene(ctx, scene)
+    bvh = tpt.BVH(ds)
+    bvh.construct(stats=False)
+    wv, _ = ds.world()
+    lo, hi = wv.min(0), wv.max(0)
+    rng = np.random.default_rng(5)
+    n = 200000
+    o = (lo - 0.25 * (hi - lo) + 1.5 * (hi - lo) * rng.random((n, 3))).astype(np.float32)
+    d = rng.normal(size=(n, 3)).astype(np.float32)
+    rays = np.concatenate([o, d], axis=1)
+    prim = ctx.primary_rays(tpt.Camera.from_scene(scene), 320, 180)
+    rays = np.concatenate([rays, np.concatenate([prim["origin"], prim["dir"]], axis=1)])
+    ctx.reset_counters()
+    h = bvh.trace(rays, counted=True)
+    c = ctx.counters()
+    a = bvh.trace(rays, any_hit=True)
+    out[name] = [hashlib.sha256(h.tobytes()).hexdigest(), hashlib.sha256((a["prim"] >= 0).tobytes()).hexdigest(), int((h["prim"] >= 0).sum()),
+                 c["node_visits"], c["tri_tests"]]
+    ds.close()
+print(json.dumps(out))
+"""
+
+
+def test_wide_and_binary_walks_agree(capsys):
+    """tpt_trace_rays over the 4-wide compressed nodes (k_collapse4 + trav_node_step4) and over the binary nodes: the same
+    (prim, t, u, v) bits for 257 600 rays per scene (incoherent + primary) on the seven fixtures and a 78 124-triangle soup, the
+    same any-hit answers, and fewer node visits."""
+    import json
+
+    def run(extra):
+        env = dict(os.environ)
+        env["TPT_WIDE_MIN_FACES"] = "2"
+        env.update(extra)
+        r = subprocess.run([sys.executable, "-c", _TRACE_SNIPPET.format(root=str(ROOT))], capture_output=True, text=True, env=env, timeout=900)
+        assert r.returncode == 0, r.stderr[-3000:]
+        return json.loads(r.stdout.strip().splitlines()[-1])
+
+    wide, binary = run({}), run({"TPT_NO_WIDE": "1"})
+    lines = []
+    for name in wide:
+        assert wide[name][:3] == binary[name][:3], name
+        assert wide[name][2] > 0
+        lines.append(f"{name}: node visits {binary[name][3]} -> {wide[name][3]}, triangle tests {binary[name][4]} -> {wide[name][4]}")
+    assert wide["soup"][3] < 0.7 * binary["soup"][3]
+    with capsys.disabled():
+        print("\n[wide vs binary] " + "; ".join(lines))

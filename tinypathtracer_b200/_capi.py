@@ -65,7 +65,7 @@ class BvhStats(C.Structure):
 
 class Counters(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ("rays_primary", "rays_extension", "rays_shadow", "rays_direct", "node_visits",
-                                          "tri_tests", "samples", "dropped_nonfinite", "kernel_launches", "rays_culled", "rays_candidates", "queue_overflow")]
+                                          "tri_tests", "samples", "dropped_nonfinite", "kernel_launches", "rays_culled", "rays_candidates", "queue_overflow", "rays_queued")]
 
 
 class StageTimes(C.Structure):
@@ -85,10 +85,12 @@ SIGNATURES = {
     "tpt_get_stage_times": (C.c_int, [C.c_void_p, C.POINTER(StageTimes)]),
     "tpt_scene_create": (C.c_int, [C.c_void_p, C.POINTER(SceneDesc), C.POINTER(C.c_void_p)]),
     "tpt_scene_destroy": (C.c_int, [C.c_void_p]),
+    "tpt_scene_update": (C.c_int, [C.c_void_p, C.POINTER(SceneDesc)]),
     "tpt_scene_set_transforms": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "tpt_bvh_build": (C.c_int, [C.c_void_p, C.POINTER(BvhStats)]),
     "tpt_bvh_refit": (C.c_int, [C.c_void_p, C.POINTER(BvhStats)]),
     "tpt_bvh_export_reference_nodes": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
+    "tpt_bvh_export_order": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "tpt_scene_export_world": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "tpt_comm_init_all": (C.c_int, [C.c_int, C.c_void_p]),
     "tpt_accum_allreduce": (C.c_int, [C.c_void_p, C.c_int]),

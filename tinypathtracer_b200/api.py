@@ -131,8 +131,8 @@ class DeviceScene:
     """Device copy of the reference's DeviceScene (include/mesh.cuh:80-96); arrays as produced by
     Scene::copySceneToDevice."""
 
-    def __init__(self, ctx: Context, scene: dict):
-        self.ctx = ctx
+    @staticmethod
+    def _desc(scene: dict):
         keep = dict(
             indices=np.ascontiguousarray(scene["indices"], np.uint32).reshape(-1),
             vertices=np.ascontiguousarray(scene["vertices"], np.float32).reshape(-1, 3),
@@ -150,6 +150,11 @@ class DeviceScene:
         d.objects, d.n_objects = _ptr(keep["objects"]), keep["objects"].shape[0]
         d.vert_trans, d.normal_trans = _ptr(keep["vert_trans"]), _ptr(keep["normal_trans"])
         d.lights, d.n_lights = (_ptr(keep["lights"]) if keep["lights"].size else None), keep["lights"].shape[0]
+        return d, keep
+
+    def __init__(self, ctx: Context, scene: dict):
+        self.ctx = ctx
+        d, keep = self._desc(scene)
         h = C.c_void_p()
         check(lib.tpt_scene_create(ctx._h, C.byref(d), C.byref(h)))
         self._h = h
@@ -157,6 +162,11 @@ class DeviceScene:
         self.n_faces = keep["indices"].size // 3
         self.n_vertices = keep["vertices"].shape[0]
         self.n_objects = keep["objects"].shape[0]
+
+    def update(self, scene: dict):
+        """tpt_scene_update: re-upload host arrays of the same sizes into the existing device arrays (no allocation, no sync)."""
+        d, keep = self._desc(scene)
+        check(lib.tpt_scene_update(self._h, C.byref(d)))
 
     def close(self):
         if self._h:
@@ -210,6 +220,12 @@ class BVH:
         out = np.zeros(n, REF_NODE_DTYPE)
         check(lib.tpt_bvh_export_reference_nodes(self.scene._h, _ptr(out), n))
         return out
+
+    def order(self):
+        """(keys, faces) of the sorted leaves: m_keys after the sort (include/bvh.cuh:67, src/bvh.cu:326) and each leaf's face id."""
+        keys, faces = np.zeros(self.scene.n_faces, np.uint64), np.zeros(self.scene.n_faces, np.uint32)
+        check(lib.tpt_bvh_export_order(self.scene._h, _ptr(keys), _ptr(faces)))
+        return keys, faces
 
     def trace(self, rays: np.ndarray, any_hit: bool = False, counted: bool = False, out: np.ndarray | None = None) -> np.ndarray:
         """Host buffers in, host buffers out (`out`: caller's HIT_DTYPE array, e.g. pinned memory)."""

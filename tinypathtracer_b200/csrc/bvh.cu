@@ -13,34 +13,14 @@
 //                       root with one atomic arrival counter per node; the second arrival owns the
 //                       node.  Grid-wide, replaces the reference's single 1024-thread block
 //                       (computeBBox, src/bvh.cu:220-302).
+#include <algorithm>
 #include <atomic>
 
-#include <cub/device/device_radix_sort.cuh>
-
 #include "scene.cuh"
+#include "sort.cuh"
+#include "traverse.cuh"
 
 namespace tpt {
-
-// ---- ordered-uint encoding of floats for atomicMin/Max ---------------------------------------
-__host__ __device__ __forceinline__ uint32_t f2ord(float f) {
-#ifdef __CUDA_ARCH__
-    uint32_t u = __float_as_uint(f);
-#else
-    uint32_t u;
-    memcpy(&u, &f, 4);
-#endif
-    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
-}
-__host__ __device__ __forceinline__ float ord2f(uint32_t u) {
-    u = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
-#ifdef __CUDA_ARCH__
-    return __uint_as_float(u);
-#else
-    float f;
-    memcpy(&f, &u, 4);
-    return f;
-#endif
-}
 
 __global__ void k_init_bounds(uint32_t* bounds) {
     if (threadIdx.x < 3) bounds[threadIdx.x] = 0xffffffffu;
@@ -97,40 +77,6 @@ __global__ void __launch_bounds__(256) k_transform(const float* __restrict__ obj
     if ((threadIdx.x & 31) == 0 && mn.x <= mx.x) {
         atomicMin(bounds + 0, f2ord(mn.x)); atomicMin(bounds + 1, f2ord(mn.y)); atomicMin(bounds + 2, f2ord(mn.z));
         atomicMax(bounds + 3, f2ord(mx.x)); atomicMax(bounds + 4, f2ord(mx.y)); atomicMax(bounds + 5, f2ord(mx.z));
-    }
-}
-
-__device__ __forceinline__ uint64_t expand21(uint64_t x) {   // spread 21 bits to every third bit
-    x &= 0x1fffffull;
-    x = (x | x << 32) & 0x1f00000000ffffull;
-    x = (x | x << 16) & 0x1f0000ff0000ffull;
-    x = (x | x << 8) & 0x100f00f00f00f00full;
-    x = (x | x << 4) & 0x10c30c30c30c30c3ull;
-    x = (x | x << 2) & 0x1249249249249249ull;
-    return x;
-}
-
-__global__ void __launch_bounds__(256) k_morton(const uint32_t* __restrict__ indices, const float* __restrict__ worldVerts,
-                                                const uint32_t* __restrict__ bounds, uint32_t nFaces, int bitsPerAxis,
-                                                unsigned long long* __restrict__ keys, uint32_t* __restrict__ vals) {
-    const float3 bmin = f3(ord2f(bounds[0]), ord2f(bounds[1]), ord2f(bounds[2]));
-    const float3 bmax = f3(ord2f(bounds[3]), ord2f(bounds[4]), ord2f(bounds[5]));
-    const float3 ext = bmax - bmin;
-    const float k = (float)(1u << bitsPerAxis);   // cells per axis (2^21: the reference's key width; 2^16 for huge scenes)
-    const float qmax = k - 1.0f;
-    const float3 scale = f3(ext.x > 0.f ? k / ext.x : 0.f, ext.y > 0.f ? k / ext.y : 0.f, ext.z > 0.f ? k / ext.z : 0.f);
-    for (uint32_t f = blockIdx.x * blockDim.x + threadIdx.x; f < nFaces; f += gridDim.x * blockDim.x) {
-        const uint32_t i0 = indices[3 * f], i1 = indices[3 * f + 1], i2 = indices[3 * f + 2];
-        const float3 a = f3(worldVerts[3 * i0], worldVerts[3 * i0 + 1], worldVerts[3 * i0 + 2]);
-        const float3 b = f3(worldVerts[3 * i1], worldVerts[3 * i1 + 1], worldVerts[3 * i1 + 2]);
-        const float3 c = f3(worldVerts[3 * i2], worldVerts[3 * i2 + 1], worldVerts[3 * i2 + 2]);
-        const float3 ctr = (fmin3(fmin3(a, b), c) + fmax3(fmax3(a, b), c)) * 0.5f;   // AABB centre, as bvh.cu:139-142
-        const float3 q = (ctr - bmin) * scale;
-        const uint64_t qx = (uint64_t)fminf(fmaxf(q.x, 0.f), qmax);
-        const uint64_t qy = (uint64_t)fminf(fmaxf(q.y, 0.f), qmax);
-        const uint64_t qz = (uint64_t)fminf(fmaxf(q.z, 0.f), qmax);
-        keys[f] = expand21(qx) | (expand21(qy) << 1) | (expand21(qz) << 2);
-        vals[f] = f;
     }
 }
 
@@ -284,6 +230,115 @@ __global__ void __launch_bounds__(256) k_refit_upper(const int* __restrict__ fro
     }
 }
 
+// ---- 4-wide compressed nodes (layout and decode: traverse.cuh "wide compressed nodes") ------------------------------------------
+// One thread per binary node i writes wide node i: it starts from i's two children and twice replaces the internal child with
+// the largest surface area by that child's own two children (greedy surface-area collapse: a node absorbs up to three binary
+// nodes and has 2..4 children).  EVERY binary node gets a wide node at its own index, reachable or not (about half are): no
+// top-down pass, no allocation, no queue — the kernel reads at most three 64-B nodes and writes one.  Child boxes are quantised to
+// 8 bits per coordinate against the node's box (= the union of its children, exactly), lower bounds rounded down and upper
+// bounds up, and each is re-decoded with the traversal's own fma and corrected until the decoded box contains the exact one.
+struct WChild {
+    int id;
+    float3 lo, hi;
+};
+__device__ __forceinline__ void wide_children(const float4* __restrict__ nodes, int i, WChild& l, WChild& r) {
+    const float4* n = nodes + 4 * (size_t)i;
+    const float4 n0 = n[0], n1 = n[1], n2 = n[2];
+    const int2 ch = *reinterpret_cast<const int2*>(n + 3);
+    l.id = ch.x; l.lo = f3(n0.x, n0.z, n2.x); l.hi = f3(n0.y, n0.w, n2.y);
+    r.id = ch.y; r.lo = f3(n1.x, n1.z, n2.z); r.hi = f3(n1.y, n1.w, n2.w);
+}
+__device__ __forceinline__ float wide_area(const WChild& c) {
+    const float3 e = c.hi - c.lo;
+    return e.x * e.y + e.y * e.z + e.z * e.x;
+}
+// smallest biased exponent eb (scale 2^(eb-127)) whose 255 steps from lo reach hi under the decode arithmetic
+__device__ __forceinline__ uint32_t wide_exponent(float lo, float hi) {
+    int e = -126;
+    const float ext = hi - lo;
+    if (ext > 0.0f) {
+        (void)frexpf(ext * (1.0f / 255.0f), &e);   // ext / 255 = m * 2^e, m in [0.5, 1)
+        e = max(-126, min(e, 127));
+    }
+    while (e < 127 && fmaf(255.0f, __uint_as_float((uint32_t)(e + 127) << 23), lo) < hi) ++e;
+    return (uint32_t)(e + 127);
+}
+__device__ __forceinline__ uint32_t wide_qlo(float v, float origin, float scale, float invScale) {
+    int q = (int)fminf(fmaxf(floorf((v - origin) * invScale), 0.0f), 255.0f);
+    while (q > 0 && fmaf((float)q, scale, origin) > v) --q;
+    return (uint32_t)q;
+}
+__device__ __forceinline__ uint32_t wide_qhi(float v, float origin, float scale, float invScale) {
+    int q = (int)fminf(fmaxf(ceilf((v - origin) * invScale), 0.0f), 255.0f);
+    while (q < 255 && fmaf((float)q, scale, origin) < v) ++q;
+    return (uint32_t)q;
+}
+
+__global__ void __launch_bounds__(256) k_collapse4(const float4* __restrict__ nodes, int nInternal, float4* __restrict__ nodes4) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nInternal) return;
+    WChild c[4];
+    int n = 2;
+    wide_children(nodes, i, c[0], c[1]);
+#pragma unroll
+    for (int round = 0; round < 2; ++round) {
+        int best = -1;
+        float bestA = -1.0f;
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            if (k < n && c[k].id >= 0) {
+                const float a = wide_area(c[k]);
+                if (a > bestA) {
+                    bestA = a;
+                    best = k;
+                }
+            }
+        if (best < 0) break;
+        WChild a, b;
+        int id = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            if (k == best) id = c[k].id;
+        wide_children(nodes, id, a, b);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            if (k == best) c[k] = a;
+            if (k == n) c[k] = b;
+        }
+        ++n;
+    }
+    float3 lo = c[0].lo, hi = c[0].hi;
+#pragma unroll
+    for (int k = 1; k < 4; ++k)
+        if (k < n) {
+            lo = fmin3(lo, c[k].lo);
+            hi = fmax3(hi, c[k].hi);
+        }
+    const uint32_t ex = wide_exponent(lo.x, hi.x), ey = wide_exponent(lo.y, hi.y), ez = wide_exponent(lo.z, hi.z);
+    const float sx = __uint_as_float(ex << 23), sy = __uint_as_float(ey << 23), sz = __uint_as_float(ez << 23);
+    const float ix = __uint_as_float((254u - ex) << 23), iy = __uint_as_float((254u - ey) << 23), iz = __uint_as_float((254u - ez) << 23);   // 2^-(e)
+    uint32_t q[6] = {0u, 0u, 0u, 0u, 0u, 0u};   // qlo.x, qlo.y, qlo.z, qhi.x, qhi.y, qhi.z: one byte per child
+    int child[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        child[k] = kWideEmpty;
+        if (k < n) {
+            child[k] = c[k].id;
+            q[0] |= wide_qlo(c[k].lo.x, lo.x, sx, ix) << (8 * k);
+            q[1] |= wide_qlo(c[k].lo.y, lo.y, sy, iy) << (8 * k);
+            q[2] |= wide_qlo(c[k].lo.z, lo.z, sz, iz) << (8 * k);
+            q[3] |= wide_qhi(c[k].hi.x, lo.x, sx, ix) << (8 * k);
+            q[4] |= wide_qhi(c[k].hi.y, lo.y, sy, iy) << (8 * k);
+            q[5] |= wide_qhi(c[k].hi.z, lo.z, sz, iz) << (8 * k);
+        }
+    }
+    float4* out = nodes4 + 4 * (size_t)i;
+    out[0] = make_float4(lo.x, lo.y, lo.z, __uint_as_float(ex | (ey << 8) | (ez << 16) | ((uint32_t)n << 24)));
+    out[1] = make_float4(__int_as_float(child[0]), __int_as_float(child[1]), __int_as_float(child[2]), __int_as_float(child[3]));
+    out[2] = make_float4(__uint_as_float(q[0]), __uint_as_float(q[1]), __uint_as_float(q[2]), __uint_as_float(q[3]));
+    out[3] = make_float4(__uint_as_float(q[4]), __uint_as_float(q[5]), 0.0f, 0.0f);
+}
+
 // ---- export in the reference's 36-byte layout (include/bvh.cuh:34-58) --------------------------
 struct RefNode36 {
     uint32_t parent;
@@ -392,18 +447,36 @@ int tpt_bvh_build_impl(tpt_scene* s) {
     // finer than the triangles, equal keys are ordered by index) so that the radix sort runs 6 passes instead of 8
     const int bitsPerAxis = F >= (1 << 20) ? 16 : 21;
     const int keyBits = 3 * bitsPerAxis;
-    k_morton<<<min(persistent, (int)grid_for(F, 256)), 256, 0, st>>>(s->indices, s->world_verts, s->bounds, (uint32_t)F, bitsPerAxis,
-                                                                      s->keys[0], s->vals[0]);
-    TPT_CUDA(cudaGetLastError());
-    size_t need = 0;
-    TPT_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, need, s->keys[0], s->keys[1], s->vals[0], s->vals[1], F, 0, keyBits, st));
-    if (need > s->sort_tmp_bytes) {
-        TPT_CUDA(cudaStreamSynchronize(st));
-        if (s->sort_tmp) cudaFree(s->sort_tmp);
-        TPT_CUDA(cudaMalloc(&s->sort_tmp, need));
-        s->sort_tmp_bytes = need;
+    // Sorted (key, face) pairs must end in keys[1] / vals[1]; keys[0] / vals[0] are scratch afterwards.
+    const int nPasses = (keyBits + 7) / 8;   // 6 or 8: even, so the ping-pong that starts in buffer 1 ends in buffer 1
+    if (F <= kSortTile) {
+        k_sort_small<<<1, kSortThreads, 0, st>>>(s->indices, s->world_verts, s->bounds, (uint32_t)F, bitsPerAxis, nPasses, s->keys[1], s->vals[1]);
+    } else {
+        const uint32_t nTiles = (uint32_t)((F + kSortTile - 1) / kSortTile);
+        const size_t histBytes = (size_t)kSortMaxPasses * 256 * sizeof(uint32_t), ticketBytes = 64;
+        const size_t need = histBytes + ticketBytes + (size_t)nPasses * nTiles * 256 * sizeof(uint32_t);
+        if (need > s->sort_tmp_bytes) {
+            TPT_CUDA(cudaStreamSynchronize(st));
+            if (s->sort_tmp) cudaFree(s->sort_tmp);
+            s->sort_tmp = nullptr;
+            s->sort_tmp_bytes = 0;
+            TPT_CUDA(cudaMalloc(&s->sort_tmp, need));
+            s->sort_tmp_bytes = need;
+        }
+        uint32_t* hist = static_cast<uint32_t*>(s->sort_tmp);
+        uint32_t* ticket = hist + kSortMaxPasses * 256;
+        uint32_t* status = ticket + ticketBytes / sizeof(uint32_t);
+        TPT_CUDA(cudaMemsetAsync(s->sort_tmp, 0, need, st));
+        k_morton_hist<<<min(persistent, (int)grid_for(F, 256)), 256, 0, st>>>(s->indices, s->world_verts, s->bounds, (uint32_t)F, bitsPerAxis, nPasses,
+                                                                                s->keys[1], s->vals[1], hist);
+        const unsigned grid = (unsigned)std::min<uint32_t>(nTiles, (uint32_t)(kNumSMs * 4));
+        for (int p = 0; p < nPasses; ++p) {
+            const int in = (p & 1) ? 0 : 1, out = in ^ 1;
+            k_onesweep<<<grid, kSortThreads, 0, st>>>(s->keys[in], s->vals[in], s->keys[out], s->vals[out], (uint32_t)F, 8 * p, hist + p * 256,
+                                                      status + (size_t)p * nTiles * 256, ticket + p, nTiles);
+        }
     }
-    TPT_CUDA(cub::DeviceRadixSort::SortPairs(s->sort_tmp, s->sort_tmp_bytes, s->keys[0], s->keys[1], s->vals[0], s->vals[1], F, 0, keyBits, st));
+    TPT_CUDA(cudaGetLastError());
     if (F > 1) {
         TPT_CUDA(cudaMemsetAsync(s->flags, 0, (size_t)(F - 1) * sizeof(uint32_t), st));
         // vals[0] / keys[0] were the sort's input and are free now: range ends and the refit frontier live there
@@ -415,8 +488,12 @@ int tpt_bvh_build_impl(tpt_scene* s) {
                                                                      s->parent_int, s->parent_leaf, reinterpret_cast<const int*>(s->vals[0]),
                                                                      s->flags, s->nodes, s->tri_geom, s->tri_norm, frontier, s->bounds + 6);
     if (F > 1) k_refit_upper<<<grid_for((size_t)F / 2 + 1, 256), 256, 0, st>>>(frontier, s->bounds + 6, s->parent_int, s->flags, s->nodes);
+    if (F > 1 && s->nodes4) {
+        k_collapse4<<<grid_for((size_t)F - 1, 256), 256, 0, st>>>(s->nodes, F - 1, s->nodes4);
+        ctx->kernel_launches += 1;
+    }
     TPT_CUDA(cudaGetLastError());
-    ctx->kernel_launches += 6 + 8;   // + radix sort passes (library, counted nominally)
+    ctx->kernel_launches += 5 + (F <= kSortTile ? 1 : 1 + nPasses);
     s->built = true;
     s->geom_epoch = ++g_geom_epoch;   // unique across scenes: a new scene at a recycled address never matches a cached key
     s->topology = true;
@@ -443,6 +520,10 @@ int tpt_bvh_refit_impl(tpt_scene* s) {
                                                                      s->parent_int, s->parent_leaf, reinterpret_cast<const int*>(s->vals[0]),
                                                                      s->flags, s->nodes, s->tri_geom, s->tri_norm, frontier, s->bounds + 6);
     if (F > 1) k_refit_upper<<<grid_for((size_t)F / 2 + 1, 256), 256, 0, st>>>(frontier, s->bounds + 6, s->parent_int, s->flags, s->nodes);
+    if (F > 1 && s->nodes4) {
+        k_collapse4<<<grid_for((size_t)F - 1, 256), 256, 0, st>>>(s->nodes, F - 1, s->nodes4);
+        ctx->kernel_launches += 1;
+    }
     TPT_CUDA(cudaGetLastError());
     ctx->kernel_launches += 4;
     s->built = true;

@@ -4,6 +4,7 @@
 // kernel sequencing.  There is no CPU implementation of any entry point: when no CUDA device is
 // usable, tpt_context_create fails and nothing else can be called.
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <vector>
@@ -171,6 +172,7 @@ int tpt_get_counters(tpt_context* ctx, tpt_counters* out) {
     out->rays_culled = h.rays_culled;
     out->rays_candidates = h.rays_candidates;
     out->queue_overflow = h.queue_overflow;
+    out->rays_queued = h.rays_queued;
     return TPT_OK;
 }
 
@@ -204,29 +206,61 @@ int tpt_scene_destroy(tpt_scene* s) {
     cudaFree(s->objects); cudaFree(s->vert_trans); cudaFree(s->normal_trans); cudaFree(s->mtl_table); cudaFree(s->lights);
     cudaFree(s->world_verts); cudaFree(s->world_norms); cudaFree(s->keys[0]); cudaFree(s->keys[1]); cudaFree(s->vals[0]);
     cudaFree(s->vals[1]); cudaFree(s->sort_tmp); cudaFree(s->parent_int); cudaFree(s->parent_leaf); cudaFree(s->flags);
-    cudaFree(s->bounds); cudaFree(s->nodes); cudaFree(s->tri_geom); cudaFree(s->tri_norm);
+    cudaFree(s->bounds); cudaFree(s->nodes); cudaFree(s->nodes4); cudaFree(s->tri_geom); cudaFree(s->tri_norm);
     delete s;
     return TPT_OK;
+}
+
+// argument checks shared by tpt_scene_create and tpt_scene_update
+static int check_scene_desc(const tpt_scene_desc* d, const char* who) {
+    const std::string w(who);
+    TPT_REQUIRE(d->n_indices >= 3 && d->n_indices % 3 == 0, w + ": n_indices must be a positive multiple of 3");
+    TPT_REQUIRE(d->n_indices / 3 < (size_t)1 << 30, w + ": too many faces");
+    TPT_REQUIRE(d->n_vertices > 0 && d->indices && d->vertices && d->normals, w + ": geometry arrays missing");
+    TPT_REQUIRE(d->n_objects > 0 && d->objects && d->vert_trans && d->normal_trans, w + ": object table missing");
+    TPT_REQUIRE(d->n_materials > 0 && d->materials, w + ": at least one material is required");
+    TPT_REQUIRE(d->n_lights == 0 || d->lights, w + ": lights pointer is NULL");
+    const size_t F = d->n_indices / 3;
+    for (size_t i = 0; i < d->n_indices; ++i) TPT_REQUIRE(d->indices[i] < d->n_vertices, w + ": vertex index out of range");
+    TPT_REQUIRE(d->objects[0].begin == 0, w + ": first object must begin at face 0");
+    for (size_t o = 0; o < d->n_objects; ++o) {
+        TPT_REQUIRE(d->objects[o].mtl_idx >= 0 && (size_t)d->objects[o].mtl_idx < d->n_materials, w + ": material index out of range");
+        TPT_REQUIRE(o == 0 || d->objects[o].begin >= d->objects[o - 1].begin, w + ": object face ranges must ascend");
+        TPT_REQUIRE((size_t)d->objects[o].begin <= F, w + ": object begin beyond face count");
+    }
+    return TPT_OK;
+}
+
+// host arrays -> the scene's device arrays (+ the per-scene tables derived from them); no allocation, no synchronisation.
+// The sources may be pageable: cudaMemcpyAsync returns once such a buffer has been staged, so they may go away on return.
+static int upload_scene(tpt_scene* s, const tpt_scene_desc* d) {
+    tpt_context* ctx = s->ctx;
+    const size_t F = s->n_faces, V = s->n_vertices, O = s->n_objects;
+    s->any_emissive = s->any_specular = false;
+    for (size_t m = 0; m < d->n_materials; ++m) s->any_emissive = s->any_emissive || d->materials[m].emission > 0.0f;
+    for (size_t m = 0; m < d->n_materials; ++m) s->any_specular = s->any_specular || d->materials[m].eta > 0.0f || d->materials[m].metallic > 0.0f;
+    std::vector<float4> mtl(2 * d->n_materials);
+    for (size_t m = 0; m < d->n_materials; ++m) {
+        const tpt_material& M = d->materials[m];
+        mtl[2 * m] = make_float4(M.base_color[0], M.base_color[1], M.base_color[2], M.emission);
+        mtl[2 * m + 1] = make_float4(M.eta, M.metallic, M.unused[2] /* roughness (include/material.h:113) */, 0.f);
+    }
+    TPT_CHECK(upload(ctx, s->indices, d->indices, 3 * F));
+    TPT_CHECK(upload(ctx, s->obj_verts, d->vertices, 3 * V));
+    TPT_CHECK(upload(ctx, s->obj_norms, d->normals, 3 * V));
+    TPT_CHECK(upload(ctx, s->objects, d->objects, O));
+    TPT_CHECK(upload(ctx, s->vert_trans, d->vert_trans, 16 * O));
+    TPT_CHECK(upload(ctx, s->normal_trans, d->normal_trans, 16 * O));
+    TPT_CHECK(upload(ctx, s->mtl_table, mtl.data(), mtl.size()));
+    TPT_CHECK(upload(ctx, s->lights, d->lights, d->n_lights));
+    return tpt_scene_build_tables(s);
 }
 
 int tpt_scene_create(tpt_context* ctx, const tpt_scene_desc* d, tpt_scene** out) {
     TPT_REQUIRE(ctx && d && out, "tpt_scene_create: NULL argument");
     *out = nullptr;
-    TPT_REQUIRE(d->n_indices >= 3 && d->n_indices % 3 == 0, "tpt_scene_create: n_indices must be a positive multiple of 3");
-    TPT_REQUIRE(d->n_indices / 3 < (size_t)1 << 30, "tpt_scene_create: too many faces");
-    TPT_REQUIRE(d->n_vertices > 0 && d->indices && d->vertices && d->normals, "tpt_scene_create: geometry arrays missing");
-    TPT_REQUIRE(d->n_objects > 0 && d->objects && d->vert_trans && d->normal_trans, "tpt_scene_create: object table missing");
-    TPT_REQUIRE(d->n_materials > 0 && d->materials, "tpt_scene_create: at least one material is required");
-    TPT_REQUIRE(d->n_lights == 0 || d->lights, "tpt_scene_create: lights pointer is NULL");
+    TPT_CHECK(check_scene_desc(d, "tpt_scene_create"));
     const size_t F = d->n_indices / 3;
-    for (size_t i = 0; i < d->n_indices; ++i)
-        TPT_REQUIRE(d->indices[i] < d->n_vertices, "tpt_scene_create: vertex index out of range");
-    TPT_REQUIRE(d->objects[0].begin == 0, "tpt_scene_create: first object must begin at face 0");
-    for (size_t o = 0; o < d->n_objects; ++o) {
-        TPT_REQUIRE(d->objects[o].mtl_idx >= 0 && (size_t)d->objects[o].mtl_idx < d->n_materials, "tpt_scene_create: material index out of range");
-        TPT_REQUIRE(o == 0 || d->objects[o].begin >= d->objects[o - 1].begin, "tpt_scene_create: object face ranges must ascend");
-        TPT_REQUIRE((size_t)d->objects[o].begin <= F, "tpt_scene_create: object begin beyond face count");
-    }
     TPT_CHECK(bind(ctx));
     tpt_scene* s = new (std::nothrow) tpt_scene();
     if (!s) return TPT_ERR_NOMEM;
@@ -236,15 +270,7 @@ int tpt_scene_create(tpt_context* ctx, const tpt_scene_desc* d, tpt_scene** out)
     s->n_objects = d->n_objects;
     s->n_materials = d->n_materials;
     s->n_lights = d->n_lights;
-    for (size_t m = 0; m < d->n_materials; ++m) s->any_emissive = s->any_emissive || d->materials[m].emission > 0.0f;
-    for (size_t m = 0; m < d->n_materials; ++m) s->any_specular = s->any_specular || d->materials[m].eta > 0.0f || d->materials[m].metallic > 0.0f;
     const size_t V = d->n_vertices, O = d->n_objects;
-    std::vector<float4> mtl(2 * d->n_materials);
-    for (size_t m = 0; m < d->n_materials; ++m) {
-        const tpt_material& M = d->materials[m];
-        mtl[2 * m] = make_float4(M.base_color[0], M.base_color[1], M.base_color[2], M.emission);
-        mtl[2 * m + 1] = make_float4(M.eta, M.metallic, M.unused[2] /* roughness (include/material.h:113) */, 0.f);
-    }
     int rc = TPT_OK;
     auto A = [&](int r) { if (rc == TPT_OK) rc = r; };
     A(dev_alloc(&s->indices, 3 * F)); A(dev_alloc(&s->obj_verts, 3 * V)); A(dev_alloc(&s->obj_norms, 3 * V));
@@ -254,17 +280,13 @@ int tpt_scene_create(tpt_context* ctx, const tpt_scene_desc* d, tpt_scene** out)
     A(dev_alloc(&s->keys[0], F)); A(dev_alloc(&s->keys[1], F)); A(dev_alloc(&s->vals[0], F)); A(dev_alloc(&s->vals[1], F));
     A(dev_alloc(&s->parent_int, F)); A(dev_alloc(&s->parent_leaf, F)); A(dev_alloc(&s->flags, F)); A(dev_alloc(&s->bounds, 8));
     A(dev_alloc(&s->nodes, 4 * F)); A(dev_alloc(&s->tri_geom, 3 * F)); A(dev_alloc(&s->tri_norm, 3 * F));
-    A(upload(ctx, s->indices, d->indices, 3 * F));
-    A(upload(ctx, s->obj_verts, d->vertices, 3 * V));
-    A(upload(ctx, s->obj_norms, d->normals, 3 * V));
-    A(upload(ctx, s->objects, d->objects, O));
-    A(upload(ctx, s->vert_trans, d->vert_trans, 16 * O));
-    A(upload(ctx, s->normal_trans, d->normal_trans, 16 * O));
-    A(upload(ctx, s->mtl_table, mtl.data(), mtl.size()));
-    A(upload(ctx, s->lights, d->lights, d->n_lights));
-    if (rc == TPT_OK) rc = tpt_scene_build_tables(s);
+    // 4-wide compressed nodes beside the binary ones (64 B per internal node) for trees too large to be served from L1: the
+    // batch trace entry walks them (traverse.cuh).  TPT_WIDE_MIN_FACES moves the limit (the tests set it to 2).
+    static const size_t wideMinFaces = getenv("TPT_WIDE_MIN_FACES") ? (size_t)atoll(getenv("TPT_WIDE_MIN_FACES")) : (size_t)1 << 16;
+    if (F >= wideMinFaces && F >= 2) A(dev_alloc(&s->nodes4, 4 * F));
+    if (rc == TPT_OK) rc = upload_scene(s, d);
     if (rc == TPT_OK) {
-        cudaError_t e = cudaStreamSynchronize(ctx->stream);   // host staging (mtl vector, caller arrays) may go away
+        cudaError_t e = cudaStreamSynchronize(ctx->stream);
         if (e != cudaSuccess) rc = cuda_fail(e, "scene upload", __FILE__, __LINE__);
     }
     if (rc != TPT_OK) {
@@ -275,6 +297,19 @@ int tpt_scene_create(tpt_context* ctx, const tpt_scene_desc* d, tpt_scene** out)
     }
     *out = s;
     return TPT_OK;
+}
+
+int tpt_scene_update(tpt_scene* s, const tpt_scene_desc* d) {
+    TPT_REQUIRE(s && d, "tpt_scene_update: NULL argument");
+    TPT_CHECK(check_scene_desc(d, "tpt_scene_update"));
+    TPT_REQUIRE(d->n_indices / 3 == s->n_faces && d->n_vertices == s->n_vertices && d->n_objects == s->n_objects &&
+                    d->n_materials == s->n_materials && d->n_lights == s->n_lights,
+                "tpt_scene_update: array sizes differ from the scene's (faces, vertices, objects, materials and lights must match "
+                "tpt_scene_create's; create a new scene otherwise)");
+    TPT_CHECK(bind(s->ctx));
+    s->built = false;
+    s->topology = false;   // new geometry: the hierarchy of the last build says nothing about it
+    return upload_scene(s, d);
 }
 
 int tpt_scene_set_transforms(tpt_scene* s, const float* vert_trans, const float* normal_trans) {
@@ -332,6 +367,19 @@ int tpt_bvh_export_reference_nodes(tpt_scene* s, void* out_nodes36, size_t n_nod
     TPT_REQUIRE(n_nodes == 2 * s->n_faces - 1, "tpt_bvh_export_reference_nodes: n_nodes must be 2F-1");
     TPT_CHECK(bind(s->ctx));
     return tpt_bvh_export_reference_impl(s, out_nodes36, n_nodes);
+}
+
+int tpt_bvh_export_order(tpt_scene* s, uint64_t* keys, uint32_t* faces) {
+    TPT_REQUIRE(s, "tpt_bvh_export_order: scene is NULL");
+    if (!s->built || !s->topology) {
+        set_error("tpt_bvh_export_order: call tpt_bvh_build first");
+        return TPT_ERR_STATE;
+    }
+    TPT_CHECK(bind(s->ctx));
+    if (keys) TPT_CUDA(cudaMemcpyAsync(keys, s->keys[1], s->n_faces * sizeof(uint64_t), cudaMemcpyDeviceToHost, s->ctx->stream));
+    if (faces) TPT_CUDA(cudaMemcpyAsync(faces, s->vals[1], s->n_faces * sizeof(uint32_t), cudaMemcpyDeviceToHost, s->ctx->stream));
+    TPT_CUDA(cudaStreamSynchronize(s->ctx->stream));
+    return TPT_OK;
 }
 
 int tpt_scene_export_world(tpt_scene* s, float* wv, float* wn) {

@@ -29,6 +29,8 @@
 #include <mutex>
 #include <string>
 
+#include <cooperative_groups.h>
+
 #include "env.cuh"
 #include "traverse.cuh"
 
@@ -360,6 +362,7 @@ struct ShadeParams {
     int continueVote;        // ... when at least continueVote / 4 of the lanes that are there together want to
     int roughMetals;         // TPT_RENDER_ROUGH_METALS: metals with roughness^2 >= 1e-3 scatter by GGX instead of mirroring
     int pixelCandidates;     // k_primary: per-pixel candidate triangles instead of one tree traversal per camera sample
+    int noTileWalk;          // tuning switch (TPT_NO_TILE_WALK): every pixel walks the tree itself instead of filtering its tile's leaf list
 };
 
 // ---- one path vertex ------------------------------------------------------------------------------
@@ -642,6 +645,113 @@ __device__ __forceinline__ int pixel_candidates(const BvhView& bvh, const ShadeP
                               : (frustum_may_hit(bvh, pixel_frustum(cam, px, py, o), stack) ? -1 : 0);
 }
 
+// The pyramid of a whole 8x4 pixel tile, grown by 1/32 pixel: it contains the (1/64-pixel grown) pyramid of each of its pixels
+// with 1/64 pixel to spare, so a box that passes a pixel's plane tests passes the tile's whatever the rounding (~1e-7 pixel).
+__device__ __forceinline__ PixelFrustum tile_frustum(const CameraParams& cam, int tx0, int ty0, float3 o) {
+    const float eps = 1.0f / 32.0f;
+    const float x0 = ((float)tx0 - eps) * cam.invW * cam.sensorW - 0.5f * cam.sensorW, x1 = ((float)(tx0 + 8) + eps) * cam.invW * cam.sensorW - 0.5f * cam.sensorW;
+    const float y0 = ((float)ty0 - eps) * cam.invH * cam.sensorH - 0.5f * cam.sensorH, y1 = ((float)(ty0 + 4) + eps) * cam.invH * cam.sensorH - 0.5f * cam.sensorH;
+    float3 c[4] = {mat4_dir(cam.c2w, f3(x0, y0, -1.f)), mat4_dir(cam.c2w, f3(x1, y0, -1.f)), mat4_dir(cam.c2w, f3(x1, y1, -1.f)),
+                   mat4_dir(cam.c2w, f3(x0, y1, -1.f))};
+    const float3 centre = (c[0] + c[1]) + (c[2] + c[3]);
+    PixelFrustum f;
+    f.o = o;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        float3 n = cross(c[k], c[(k + 1) & 3]);
+        if (dot(n, centre) < 0.f) n = -n;
+        f.n[k] = n;
+    }
+    return f;
+}
+
+// Warp-cooperative walk of the tree with the TILE's pyramid, breadth first: the 32 lanes test 32 nodes of the current frontier
+// at a time, surviving internal children form the next frontier, surviving leaves are appended to the tile's leaf list (the
+// parent node and side, where the leaf's box is stored, and the leaf index).  One such walk replaces 32 divergent per-pixel
+// walks: each pixel then only filters the tile's (short) list with its own pyramid.  A triangle some ray of a pixel can hit
+// has its box inside that pixel's pyramid, hence inside the tile's (grown by 1/64 pixel more, five orders of magnitude
+// above the rounding of the plane tests), so per-pixel candidates taken from the tile list are the ones a per-pixel walk
+// collects and hold every triangle a full traversal could return: the hits stay bit-identical.  Returns the number of leaves, or -1 when the frontier or the list
+// overflows (the caller then walks per pixel, as before).  Warp-uniform; all 32 lanes must call it.
+constexpr int kTileFront = 64, kTileLeaves = 64;
+struct TileWalk {
+    int front[2][kTileFront];
+    int leafNode[kTileLeaves];   // (parent node << 1) | side
+    int leafId[kTileLeaves];     // sorted triangle index
+};
+__device__ __forceinline__ int tile_collect(const BvhView& bvh, const PixelFrustum& f, TileWalk& tw, unsigned& nodeVisits) {
+    const uint32_t lane = threadIdx.x & 31, lt = (1u << lane) - 1u;
+    if (bvh.n_faces <= 1) {
+        if (lane == 0) {
+            tw.leafNode[0] = -1;   // no parent: the single triangle is always a candidate
+            tw.leafId[0] = 0;
+        }
+        __syncwarp();
+        return 1;
+    }
+    int cur = 0, nCur = 1, nLeaf = 0;
+    if (lane == 0) tw.front[0][0] = 0;
+    __syncwarp();
+    while (nCur > 0) {
+        int nNext = 0;
+        for (int base = 0; base < nCur; base += 32) {
+            const int idx = base + (int)lane;
+            const bool have = idx < nCur;
+            bool hL = false, hR = false;
+            int2 ch = make_int2(0, 0);
+            int node = 0;
+            if (have) {
+                node = tw.front[cur][idx];
+                const float4* n = bvh.nodes + 4 * (size_t)node;
+                const float4 n0 = __ldg(n), n1 = __ldg(n + 1), n2 = __ldg(n + 2);
+                ch = __ldg(reinterpret_cast<const int2*>(n + 3));
+                hL = frustum_box(f, n0.x, n0.y, n0.z, n0.w, n2.x, n2.y);
+                hR = frustum_box(f, n1.x, n1.y, n1.z, n1.w, n2.z, n2.w);
+                ++nodeVisits;
+            }
+            const bool iL = hL && ch.x >= 0, iR = hR && ch.y >= 0, lL = hL && ch.x < 0, lR = hR && ch.y < 0;
+            const unsigned mIL = __ballot_sync(0xffffffffu, iL), mIR = __ballot_sync(0xffffffffu, iR);
+            const unsigned mLL = __ballot_sync(0xffffffffu, lL), mLR = __ballot_sync(0xffffffffu, lR);
+            const int pIL = nNext + __popc(mIL & lt), pIR = nNext + __popc(mIL) + __popc(mIR & lt);
+            const int pLL = nLeaf + __popc(mLL & lt), pLR = nLeaf + __popc(mLL) + __popc(mLR & lt);
+            nNext += __popc(mIL) + __popc(mIR);
+            nLeaf += __popc(mLL) + __popc(mLR);
+            if (nNext > kTileFront || nLeaf > kTileLeaves) return -1;   // uniform
+            if (iL) tw.front[cur ^ 1][pIL] = ch.x;
+            if (iR) tw.front[cur ^ 1][pIR] = ch.y;
+            if (lL) { tw.leafNode[pLL] = node << 1; tw.leafId[pLL] = ~ch.x; }
+            if (lR) { tw.leafNode[pLR] = (node << 1) | 1; tw.leafId[pLR] = ~ch.y; }
+        }
+        __syncwarp();
+        cur ^= 1;
+        nCur = nNext;
+    }
+    return nLeaf;
+}
+
+// A pixel's candidates out of its tile's leaf list: the same box test, bound and sorted insertion as frustum_collect.
+// Returns like frustum_collect: the number of candidates (at the top of `stack`), -1 when there are more than kMaxCandidates.
+__device__ __forceinline__ int candidates_from_tile(const BvhView& bvh, const PixelFrustum& f, const TileWalk& tw, int nLeaf, int* stack) {
+    int nc = 0;
+    for (int j = 0; j < nLeaf; ++j) {
+        const int code = tw.leafNode[j];
+        float lox, hix, loy, hiy, loz, hiz;
+        if (code < 0) {   // single-triangle scene
+            stack[kStackSize - 1] = 0;
+            stack[kStackSize - 1 - kMaxCandidates] = 0;
+            return 1;
+        }
+        const float4* n = bvh.nodes + 4 * (size_t)(code >> 1);
+        const float4 xy = __ldg(n + (code & 1)), z = __ldg(n + 2);
+        lox = xy.x; hix = xy.y; loy = xy.z; hiy = xy.w;
+        loz = (code & 1) ? z.z : z.x;
+        hiz = (code & 1) ? z.w : z.y;
+        if (frustum_box(f, lox, hix, loy, hiy, loz, hiz))
+            if (!candidate_insert(stack, nc, tw.leafId[j], box_distance_bound(f.o, lox, hix, loy, hiy, loz, hiz))) return -1;
+    }
+    return nc;
+}
+
 // rays k_primary traced in registers (specular continuation) never see a queue, where k_wave counts its rays
 __device__ __forceinline__ void flush_ray_counters(unsigned nExt, unsigned nShadow, DeviceCounters* ctr) {
     const unsigned m = __activemask();
@@ -662,7 +772,7 @@ __device__ __forceinline__ void flush_trav_counters(unsigned nv, unsigned nt, De
 }
 
 // Form A (fewer than 32 samples per pixel in this launch): thread = (pixel of an 8x4 tile, group of `spt`
-// consecutive local samples); the candidates stay in the thread's own stack array.
+// consecutive local samples); the candidates live in a per-thread array of their own.
 template <bool COUNT, bool NEE, int MODE>
 __global__ void __launch_bounds__(128) k_primary(BvhView bvh, ShadeParams sp, CameraParams cam, int W, int H, uint32_t nPadded,
                                                  uint32_t kSamples, uint32_t spt, uint32_t sampleBase, uint32_t sampleStride, QueueOut q,
@@ -693,9 +803,16 @@ __global__ void __launch_bounds__(128) k_primary(BvhView bvh, ShadeParams sp, Ca
         const unsigned n = __reduce_add_sync(m, s1 - s0);
         if ((threadIdx.x & 31) == __ffs(m) - 1) atomicAdd(&ctr->rays_candidates, (unsigned long long)n);
     }
+    // the candidates move out of the stack array: the traversals primary_sample may run (light shadow rays, specular
+    // continuation) use it from the bottom with no depth limit of their own, and an LBVH can be up to 95 levels deep
+    int cand[kMaxCandidates], bound[kMaxCandidates];
+    for (int k = 0; k < nc; ++k) {
+        cand[k] = stack[kStackSize - 1 - k];
+        bound[k] = stack[kStackSize - 1 - kMaxCandidates - k];
+    }
     for (uint32_t sl = s0; sl < s1; ++sl)
-        primary_sample<COUNT, NEE, MODE>(bvh, sp, cam, q, blockIdx.x & (kSegments - 1), px, py, pixel, sampleBase + sl * sampleStride, o, nc, stack + kStackSize - 1,
-                                   stack + kStackSize - 1 - kMaxCandidates, -1, stack, aR, aG, aB, nt, nExt, nShadow, ctr);
+        primary_sample<COUNT, NEE, MODE>(bvh, sp, cam, q, blockIdx.x & (kSegments - 1), px, py, pixel, sampleBase + sl * sampleStride, o, nc, cand, bound, 1,
+                                   stack, aR, aG, aB, nt, nExt, nShadow, ctr);
     if (COUNT) flush_trav_counters(nv, nt, ctr);
     flush_ray_counters(nExt, nShadow, ctr);
     unsigned long long* dst = acc + 3 * (size_t)pixel;
@@ -731,6 +848,7 @@ __global__ void __launch_bounds__(128, TPT_COOP_MIN_BLOCKS) k_primary_coop(BvhVi
                                                       unsigned long long* __restrict__ acc, DeviceCounters* ctr) {
     __shared__ int sCand[4][kCoopCandidates][32];    // [warp][k][lane]: leaf k of the lane's pixel
     __shared__ int sBound[4][kCoopCandidates][32];   //                   its lower bound of t (float bits)
+    __shared__ TileWalk sTile[4];                    // [warp]: frontier and leaf list of the tile walk
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nPadded * ((kSamples + spt - 1) / spt)) return;    // whole warps: nPadded is a multiple of 32
     if (i == 0) atomicAdd(&ctr->rays_primary, (unsigned long long)W * (unsigned long long)H * kSamples);
@@ -744,8 +862,17 @@ __global__ void __launch_bounds__(128, TPT_COOP_MIN_BLOCKS) k_primary_coop(BvhVi
     const float3 o = xmat4_point(cam.c2w, f3(0.f, 0.f, 0.f));
     unsigned nv = 0, nt = 0, nExt = 0, nShadow = 0;
     int nc = 0;
-    if (inside) {
-        nc = pixel_candidates(bvh, sp, cam, px, py, o, stack, nv);
+    // one cooperative walk with the tile's pyramid, then each pixel filters the tile's leaves (tile_collect); per-pixel walks
+    // only when the tile meets too many leaves
+    int nTile = -1;
+    if (sp.pixelCandidates && !sp.noTileWalk) {
+        int tx, ty;
+        tile_decode(p & ~31u, W, H, tx, ty);   // lane 0's pixel = the tile's corner
+        nTile = tile_collect(bvh, tile_frustum(cam, tx, ty, o), sTile[wib], nv);
+    }
+    if (inside && nTile != 0) {
+        nc = nTile > 0 ? candidates_from_tile(bvh, pixel_frustum(cam, px, py, o), sTile[wib], nTile, stack)
+                       : pixel_candidates(bvh, sp, cam, px, py, o, stack, nv);
         if (nc > kCoopCandidates) nc = -1;
         for (int k = 0; k < nc; ++k) {
             sCand[wib][k][lane] = stack[kStackSize - 1 - k];
@@ -802,9 +929,33 @@ __global__ void __launch_bounds__(128) k_tile_live(BvhView bvh, ShadeParams sp, 
     int stack[kStackSize];
     stack[0] = kStackSentinel;
     const float3 o = xmat4_point(cam.c2w, f3(0.f, 0.f, 0.f));
-    // "some leaf box meets the pyramid" is exactly "pixel_candidates(...) != 0" (same walk, same plane-box test), and stops at the
-    // first such leaf instead of collecting and sorting them all
-    const bool hit = inside && frustum_may_hit(bvh, pixel_frustum(cam, px, py, o), stack);
+    // "some leaf box meets the pyramid" is exactly "pixel_candidates(...) != 0" (same plane-box test), and stops at the
+    // first such leaf instead of collecting and sorting them all.  Like k_primary_coop: one cooperative walk per tile first.
+    __shared__ TileWalk sTile[4];
+    TileWalk& tw = sTile[threadIdx.x >> 5];
+    int nTile = -1;
+    if (!sp.noTileWalk) {
+        int tx, ty;
+        unsigned nvUnused = 0;
+        tile_decode(i & ~31u, W, H, tx, ty);
+        nTile = tile_collect(bvh, tile_frustum(cam, tx, ty, o), tw, nvUnused);
+    }
+    bool hit = false;
+    if (inside && nTile < 0) {
+        hit = frustum_may_hit(bvh, pixel_frustum(cam, px, py, o), stack);
+    } else if (inside && nTile > 0) {
+        const PixelFrustum f = pixel_frustum(cam, px, py, o);
+        for (int j = 0; j < nTile && !hit; ++j) {
+            const int code = tw.leafNode[j];
+            if (code < 0) {
+                hit = true;
+                break;
+            }
+            const float4* n = bvh.nodes + 4 * (size_t)(code >> 1);
+            const float4 xy = __ldg(n + (code & 1)), z = __ldg(n + 2);
+            hit = frustum_box(f, xy.x, xy.y, xy.z, xy.w, (code & 1) ? z.z : z.x, (code & 1) ? z.w : z.y);
+        }
+    }
     const unsigned live = __ballot_sync(0xffffffffu, hit);
     if ((threadIdx.x & 31) == 0) tileLive[i >> 5] = (uint8_t)__popc(live);
 }
@@ -847,7 +998,7 @@ constexpr uint32_t kNoItem = 0xffffffffu;
 template <bool NEE>
 __device__ __forceinline__ void shade_staged(const BvhView& bvh, const ShadeParams& sp, const float4* __restrict__ extIn, const QueueOut& q,
                                              unsigned long long* __restrict__ acc, DeviceCounters* ctr, const uint32_t* myIdx,
-                                             const float4* myHit, uint32_t count) {
+                                             const float4* myHit, uint32_t count, int depth) {
     const uint32_t lane = threadIdx.x & 31;
     if (lane < count) {
         const PathRec p = load_path(extIn, myIdx[lane]);
@@ -861,7 +1012,7 @@ __device__ __forceinline__ void shade_staged(const BvhView& bvh, const ShadePara
         float3 term;
         Vertex vx;
         const uint32_t ahead = NEE ? 0u : p.w;
-        if (shade_vertex<NEE>(bvh, sp, sp.depth + (int)ahead, p.o, p.d, p.T, NEE ? p.w : 0u, p.pixel, p.sample, h, term, vx, ctr))
+        if (shade_vertex<NEE>(bvh, sp, depth + (int)ahead, p.o, p.d, p.T, NEE ? p.w : 0u, p.pixel, p.sample, h, term, vx, ctr))
             emit_vertex<NEE, true>(sp, q, 0u, vx, p.pixel, p.sample, ahead, ctr);
         else accum_add(acc, p.pixel, term, ctr);
     }
@@ -874,10 +1025,13 @@ __device__ __forceinline__ void shade_staged(const BvhView& bvh, const ShadePara
 // SEGIN: the input level is the segmented one k_primary wrote (wave 1); k_wave itself appends to segment 0 only — its
 // warps issue one atomic per 32 shaded vertices, far below what one counter sustains — so the levels it produces
 // are plain queues that use the whole pool.
-template <bool COUNT, bool NEE, bool SEGIN>
-__global__ void __launch_bounds__(128, TPT_WAVE_MIN_BLOCKS) k_wave(BvhView bvh, ShadeParams sp, const float4* __restrict__ extIn, const float4* __restrict__ secIn,
-                                              void* __restrict__ levelIn, QueueOut q, unsigned long long* __restrict__ acc,
-                                              DeviceCounters* ctr) {
+// One level (= wave `depth`) of the persistent scheduler; every thread of the block calls it.
+// LOOP: called level after level inside one kernel (k_wave_loop) — the queues it reads were written earlier in the SAME launch,
+// so their loads must not use the non-coherent path (ld.global.nc is only valid for data that is read-only during the launch).
+template <bool COUNT, bool NEE, bool SEGIN, bool LOOP = false>
+__device__ __forceinline__ void wave_level(const BvhView& bvh, const ShadeParams& sp, int depth, const float4* __restrict__ extIn,
+                                           const float4* __restrict__ secIn, void* __restrict__ levelIn, const QueueOut& q,
+                                           unsigned long long* __restrict__ acc, DeviceCounters* ctr) {
     __shared__ uint32_t sIdx[4][kStage];
     __shared__ float4 sHit[4][kStage];
     // The level's items form one virtual queue: the extension rays of segment 0, 1, ... then the secondary rays of
@@ -945,6 +1099,7 @@ __global__ void __launch_bounds__(128, TPT_WAVE_MIN_BLOCKS) k_wave(BvhView bvh, 
         atomicAdd(&ctr->rays_extension, (unsigned long long)nExt);
         atomicAdd(&ctr->rays_direct, (unsigned long long)nDirect);
         atomicAdd(&ctr->rays_shadow, (unsigned long long)(nSec - nDirect));
+        atomicAdd(&ctr->rays_queued, (unsigned long long)total);
     }
     uint32_t* cursor = &seg_level(levelIn, 0)->cursor;
     const uint32_t lane = threadIdx.x & 31, ltMask = (1u << lane) - 1u;
@@ -1004,7 +1159,7 @@ __global__ void __launch_bounds__(128, TPT_WAVE_MIN_BLOCKS) k_wave(BvhView bvh, 
             if (fin) item = kNoItem;
             __syncwarp();
             if (nStaged >= 32u) {
-                shade_staged<NEE>(bvh, sp, extIn, q, acc, ctr, myIdx, myHit, 32u);
+                shade_staged<NEE>(bvh, sp, extIn, q, acc, ctr, myIdx, myHit, 32u, depth);
                 const uint32_t r = nStaged - 32u;
                 uint32_t ti = 0;
                 float4 th = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -1068,8 +1223,9 @@ __global__ void __launch_bounds__(128, TPT_WAVE_MIN_BLOCKS) k_wave(BvhView bvh, 
                     kind = isExt ? 0u : 1u + __float_as_uint(__ldcs(reinterpret_cast<const float*>(src + 2) + 3));
 #else
                     // cached loads: the rest of the item is read again when the ray retires (shade_staged / accumulate)
-                    const float4 a = __ldg(src), b = __ldg(src + 1);
-                    kind = isExt ? 0u : 1u + __float_as_uint(__ldg(reinterpret_cast<const float*>(src + 2) + 3));
+                    const float4 a = LOOP ? __ldcg(src) : __ldg(src), b = LOOP ? __ldcg(src + 1) : __ldg(src + 1);
+                    const float* kp = reinterpret_cast<const float*>(src + 2) + 3;
+                    kind = isExt ? 0u : 1u + __float_as_uint(LOOP ? __ldcg(kp) : __ldg(kp));
 #endif
                     trav_begin(ts, bvh, f3(a.x, a.y, a.z), f3(a.w, b.x, b.y));
                 }
@@ -1098,7 +1254,7 @@ __global__ void __launch_bounds__(128, TPT_WAVE_MIN_BLOCKS) k_wave(BvhView bvh, 
             } while (__popc(__ballot_sync(0xffffffffu, ts.cur < 0 && ts.cur != kStackSentinel)) >= keep);
         }
     }
-    if (nStaged) shade_staged<NEE>(bvh, sp, extIn, q, acc, ctr, myIdx, myHit, nStaged);
+    if (nStaged) shade_staged<NEE>(bvh, sp, extIn, q, acc, ctr, myIdx, myHit, nStaged, depth);
     if (COUNT) {
         const unsigned sv = __reduce_add_sync(0xffffffffu, nv), st = __reduce_add_sync(0xffffffffu, nt);
         if (lane == 0) {
@@ -1108,8 +1264,44 @@ __global__ void __launch_bounds__(128, TPT_WAVE_MIN_BLOCKS) k_wave(BvhView bvh, 
     }
 }
 
+template <bool COUNT, bool NEE, bool SEGIN>
+__global__ void __launch_bounds__(128, TPT_WAVE_MIN_BLOCKS) k_wave(BvhView bvh, ShadeParams sp, const float4* __restrict__ extIn, const float4* __restrict__ secIn,
+                                              void* __restrict__ levelIn, QueueOut q, unsigned long long* __restrict__ acc,
+                                              DeviceCounters* ctr) {
+    wave_level<COUNT, NEE, SEGIN>(bvh, sp, sp.depth, extIn, secIn, levelIn, q, acc, ctr);
+}
+
+// Waves wFirst..wLast in ONE cooperative launch: the same scheduler level after level, separated by a grid-wide barrier
+// instead of a kernel boundary, and the loop ends as soon as a level is empty.  The deep waves of most frames hold a
+// tiny share of the paths (ball.gltf: waves 2-8 together 0.15 % of wave 1) and cost a launch each — seven launches of
+// 0.1-0.2 ms per batch, which is what did not shrink when the samples were spread over 8 GPUs.
+// Same items, same order-independent integer accumulation: the accumulator bits do not change.
+struct WaveLoopParams {
+    float4* ext[2];
+    float4* sec[2];
+    char* levels;               // level w's counter blocks at levels + w * levelBytes
+    uint32_t levelBytes;
+    int wFirst, wLast;
+    uint32_t extSegCap, secSegCap, extCap, secCap;
+};
+template <bool COUNT, bool NEE>
+__global__ void __launch_bounds__(128, 6) k_wave_loop(BvhView bvh, ShadeParams sp, WaveLoopParams lp, unsigned long long* __restrict__ acc,
+                                                                      DeviceCounters* ctr) {
+    cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+    for (int w = lp.wFirst; w <= lp.wLast; ++w) {
+        const int in = w & 1, out = in ^ 1;
+        void* levelIn = lp.levels + (size_t)w * lp.levelBytes;
+        // written by the previous level (or launch) and final since the barrier: the same value in every block
+        const unsigned long long counts = __ldcg(&seg_level(levelIn, 0)->counts);
+        if (counts == 0ull) break;
+        const QueueOut q{lp.ext[out], lp.sec[out], lp.levels + (size_t)(w + 1) * lp.levelBytes, lp.extSegCap, lp.secSegCap, lp.extCap, lp.secCap};
+        wave_level<COUNT, NEE, false, true>(bvh, sp, w, lp.ext[in], lp.sec[in], levelIn, q, acc, ctr);
+        if (w < lp.wLast) grid.sync();
+    }
+}
+
 // ---- tpt_trace_rays, persistent form: the scheduler of k_wave without the shading ------------------------
-template <bool COUNT>
+template <bool COUNT, bool WIDE = false>
 __global__ void __launch_bounds__(128, 10) k_trace_rays_persistent(BvhView bvh, const tpt_ray* __restrict__ rays, unsigned long long n,
                                                                    tpt_hit* __restrict__ hits, int anyHit, unsigned long long* cursor,
                                                                    DeviceCounters* ctr) {
@@ -1118,11 +1310,11 @@ __global__ void __launch_bounds__(128, 10) k_trace_rays_persistent(BvhView bvh, 
     const unsigned long long grab = perWarp >= kGrabMax ? kGrabMax : (perWarp >= 32ull ? (perWarp & ~31ull) : 32ull);
 #if TPT_SMEM_STACK > 0
     __shared__ int sStack[kSmemStack][128];
-    int stackDeep[kStackSize - kSmemStack];
+    int stackDeep[(WIDE ? kWideStackSize : kStackSize) - kSmemStack];   // wide nodes push up to three children per visit
     const HybridStack stack{&sStack[0][threadIdx.x], stackDeep};
     sStack[0][threadIdx.x] = kStackSentinel;
 #else
-    int stackArr[kStackSize];
+    int stackArr[WIDE ? kWideStackSize : kStackSize];
     stackArr[0] = kStackSentinel;
     const LocalStack stack{stackArr};
 #endif
@@ -1170,7 +1362,8 @@ __global__ void __launch_bounds__(128, 10) k_trace_rays_persistent(BvhView bvh, 
             const int keep = max(1, (kKeepNum * __popc(mNode)) >> 2);
             do {
                 if (ts.cur >= 0) {
-                    trav_node_step(ts, bvh, stack);
+                    if (WIDE) trav_node_step4(ts, bvh.nodes4, stack);
+                    else trav_node_step(ts, bvh, stack);
                     if (COUNT) ++nv;
                 }
             } while (__popc(__ballot_sync(0xffffffffu, ts.cur >= 0)) >= keep);
@@ -1277,14 +1470,22 @@ int tpt_trace_rays_impl(tpt_scene* s, const tpt_ray* d_rays, size_t n, tpt_hit* 
     } else {
         if (!ctx->trace_cursor) TPT_CUDA(cudaMalloc(&ctx->trace_cursor, sizeof(unsigned long long)));
         if (ctx->trace_grid == 0) {
-            ctx->trace_grid = kNumSMs * resident_blocks(k_trace_rays_persistent<false>, 128);
-            ctx->trace_grid_counted = kNumSMs * resident_blocks(k_trace_rays_persistent<true>, 128);
+            ctx->trace_grid = kNumSMs * resident_blocks(k_trace_rays_persistent<false, false>, 128);
+            ctx->trace_grid_counted = kNumSMs * resident_blocks(k_trace_rays_persistent<true, false>, 128);
+            ctx->trace_grid_wide = kNumSMs * resident_blocks(k_trace_rays_persistent<false, true>, 128);
+            ctx->trace_grid_wide_counted = kNumSMs * resident_blocks(k_trace_rays_persistent<true, true>, 128);
         }
         TPT_CUDA(cudaMemsetAsync(ctx->trace_cursor, 0, sizeof(unsigned long long), ctx->stream));
-        if (counted)
-            k_trace_rays_persistent<true><<<ctx->trace_grid_counted, 128, 0, ctx->stream>>>(v, d_rays, n, d_hits, anyHit, ctx->trace_cursor, ctx->d_counters);
+        static const bool noWide = getenv("TPT_NO_WIDE") != nullptr;   // tuning / check switch: binary nodes even where wide ones exist
+        const bool wide = v.nodes4 != nullptr && !noWide && s->n_faces > 1;
+        if (wide && counted)
+            k_trace_rays_persistent<true, true><<<ctx->trace_grid_wide_counted, 128, 0, ctx->stream>>>(v, d_rays, n, d_hits, anyHit, ctx->trace_cursor, ctx->d_counters);
+        else if (wide)
+            k_trace_rays_persistent<false, true><<<ctx->trace_grid_wide, 128, 0, ctx->stream>>>(v, d_rays, n, d_hits, anyHit, ctx->trace_cursor, ctx->d_counters);
+        else if (counted)
+            k_trace_rays_persistent<true, false><<<ctx->trace_grid_counted, 128, 0, ctx->stream>>>(v, d_rays, n, d_hits, anyHit, ctx->trace_cursor, ctx->d_counters);
         else
-            k_trace_rays_persistent<false><<<ctx->trace_grid, 128, 0, ctx->stream>>>(v, d_rays, n, d_hits, anyHit, ctx->trace_cursor, ctx->d_counters);
+            k_trace_rays_persistent<false, false><<<ctx->trace_grid, 128, 0, ctx->stream>>>(v, d_rays, n, d_hits, anyHit, ctx->trace_cursor, ctx->d_counters);
     }
     TPT_CUDA(cudaGetLastError());
     ctx->kernel_launches += 1;
@@ -1347,6 +1548,8 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
     sp.depth = 0;
     sp.directRays = s->any_emissive ? 1 : 0;
     sp.pixelCandidates = (cfg->flags & TPT_RENDER_NO_PIXEL_CANDIDATES) ? 0 : 1;
+    static const bool noTileWalk = getenv("TPT_NO_TILE_WALK") != nullptr;
+    sp.noTileWalk = noTileWalk ? 1 : 0;
     sp.roughMetals = (cfg->flags & TPT_RENDER_ROUGH_METALS) ? 1 : 0;
     static const int specChain = getenv("TPT_SPEC_CHAIN") ? atoi(getenv("TPT_SPEC_CHAIN")) : 4;   // tuning switches
     static const int specVote = getenv("TPT_SPEC_VOTE") ? atoi(getenv("TPT_SPEC_VOTE")) : 3;
@@ -1466,6 +1669,17 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
     }
     const int variant = (counted ? 1 : 0) + (nee ? 2 : 0);
     const unsigned gridWave = ctx->wave_grid[variant];
+    static const bool noWaveLoop = getenv("TPT_NO_WAVE_LOOP") != nullptr;   // tuning switch: one launch per wave, as before
+    const void* kWaveLoop = variant == 0 ? (const void*)k_wave_loop<false, false> : variant == 1 ? (const void*)k_wave_loop<true, false>
+                          : variant == 2 ? (const void*)k_wave_loop<false, true> : (const void*)k_wave_loop<true, true>;
+    if (ctx->wave_loop_grid[variant] == 0) {
+        int coop = 0;
+        cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, ctx->device);
+        ctx->wave_loop_grid[variant] = !coop ? 1u   // 1 = not available (a real grid is a multiple of 148)
+            : kNumSMs * (unsigned)(variant == 0 ? resident_blocks(k_wave_loop<false, false>, 128) : variant == 1 ? resident_blocks(k_wave_loop<true, false>, 128)
+                                 : variant == 2 ? resident_blocks(k_wave_loop<false, true>, 128) : resident_blocks(k_wave_loop<true, true>, 128));
+    }
+    const bool waveLoop = !noWaveLoop && ctx->wave_loop_grid[variant] > 1u;
     // SPEC kernels (specular continuation) only where they pay: the scene has a mirror / glass material, no env NEE, and the
     // tree is shallow.  Following a ray in k_primary saves a queue round trip and k_wave's scheduling (a fixed cost per ray) but
     // walks the tree in lock-step with the warp's other rays; measured: light.gltf (80 triangles) 18.1 -> 14.7 ms, tir.gltf
@@ -1507,7 +1721,8 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
         mark();
         // wave w traces extension rays towards vertex w and the secondary rays of vertex w-1; the last wave
         // (w == max_depth) only has secondary rays left.
-        for (int w = 1; w <= cfg->max_depth; ++w) {
+        const int perLevelLast = waveLoop ? 1 : cfg->max_depth;   // wave 1 reads the segmented level k_primary wrote: its own launch
+        for (int w = 1; w <= perLevelLast; ++w) {
             const int in = w & 1, out = in ^ 1;
             sp.depth = w;
             const QueueOut q{ctx->q_ext[out], ctx->q_sec[out], levels + (size_t)(w + 1) * levelBytes, (uint32_t)extSegCap, (uint32_t)secSegCap,
@@ -1515,7 +1730,26 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
             (w == 1 ? kWave1 : kWave)<<<gridWave, 128, 0, st>>>(view, sp, ctx->q_ext[in], ctx->q_sec[in], levels + (size_t)w * levelBytes, q, acc->data, ctx->d_counters);
             mark();
         }
-        ctx->kernel_launches += 1 + (uint64_t)cfg->max_depth;
+        uint64_t nLaunches = 1 + (uint64_t)perLevelLast;
+        if (waveLoop && cfg->max_depth >= 2) {   // waves 2..max_depth: one cooperative launch, a grid barrier between levels
+            WaveLoopParams lp;
+            lp.ext[0] = ctx->q_ext[0]; lp.ext[1] = ctx->q_ext[1];
+            lp.sec[0] = ctx->q_sec[0]; lp.sec[1] = ctx->q_sec[1];
+            lp.levels = levels;
+            lp.levelBytes = (uint32_t)levelBytes;
+            lp.wFirst = 2;
+            lp.wLast = cfg->max_depth;
+            lp.extSegCap = (uint32_t)extSegCap; lp.secSegCap = (uint32_t)secSegCap;
+            lp.extCap = (uint32_t)(extSegCap * kSegments); lp.secCap = (uint32_t)(secSegCap * kSegments);
+            BvhView v = view;
+            unsigned long long* accData = acc->data;
+            DeviceCounters* ctr = ctx->d_counters;
+            void* args[] = {&v, &sp, &lp, &accData, &ctr};
+            TPT_CUDA(cudaLaunchCooperativeKernel(kWaveLoop, dim3(ctx->wave_loop_grid[variant]), dim3(128), args, 0, st));
+            mark();
+            nLaunches += 1;
+        }
+        ctx->kernel_launches += nLaunches;
         TPT_CUDA(cudaGetLastError());
         if (timed) {
             TPT_CUDA(cudaEventSynchronize(ctx->stage_events[ev - 1]));
@@ -1616,8 +1850,8 @@ extern "C" int tpt_trace_rays_static(tpt_scene* s, const tpt_ray* rays, size_t n
     }
     TPT_CUDA(cudaMemsetAsync(cursor, 0, sizeof(unsigned long long), ctx->stream));   // the array keeps the last call's cursor
     static unsigned grid[64] = {};   // an occupancy query, no allocation
-    if (grid[ctx->device] == 0) grid[ctx->device] = kNumSMs * resident_blocks(k_trace_rays_persistent<false>, 128);
-    k_trace_rays_persistent<false><<<grid[ctx->device], 128, 0, ctx->stream>>>(s->view(), dRays, n, dHits, any_hit, cursor, ctx->d_counters);
+    if (grid[ctx->device] == 0) grid[ctx->device] = kNumSMs * resident_blocks(k_trace_rays_persistent<false, false>, 128);
+    k_trace_rays_persistent<false, false><<<grid[ctx->device], 128, 0, ctx->stream>>>(s->view(), dRays, n, dHits, any_hit, cursor, ctx->d_counters);
     TPT_CUDA(cudaGetLastError());
     ctx->kernel_launches += 1;
     if (!device_ptrs) {

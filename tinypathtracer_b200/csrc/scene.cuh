@@ -29,10 +29,12 @@ struct DeviceCounters {
     unsigned long long rays_culled;   // camera samples answered by pixel-frustum culling (counted in rays_primary too)
     unsigned long long rays_candidates;   // camera samples answered by testing their pixel's candidate triangles (in rays_primary too)
     unsigned long long queue_overflow;    // vertices whose rays did not fit their queue (must stay 0: the pools hold the worst case)
+    unsigned long long rays_queued;       // rays that went through a wavefront queue (written once, read once); the rest were traced where they were born
 };
 
 struct BvhView {
     const float4* nodes;
+    const float4* nodes4;     // 4-wide compressed nodes (traverse.cuh), or nullptr when the scene has none
     const float4* tri_geom;
     const float4* tri_norm;
     int n_faces;
@@ -71,8 +73,9 @@ struct tpt_context {
     size_t ext_capacity = 0, sec_capacity = 0;
     void* levels = nullptr;                       // QueueLevel[kMaxLevels] (render.cu)
     unsigned wave_grid[4] = {0, 0, 0, 0};          // persistent grid sizes of k_wave<COUNT, NEE> (148 x resident blocks), index COUNT + 2*NEE
+    unsigned wave_loop_grid[4] = {0, 0, 0, 0};     // cooperative grid of k_wave_loop<COUNT, NEE> (0 = not queried yet, 1 = no cooperative launch)
     unsigned long long* trace_cursor = nullptr;    // item cursor of k_trace_rays_persistent
-    unsigned trace_grid = 0, trace_grid_counted = 0;
+    unsigned trace_grid = 0, trace_grid_counted = 0, trace_grid_wide = 0, trace_grid_wide_counted = 0;
     // scratch for trace_rays with host pointers
     void* io_rays = nullptr;
     void* io_hits = nullptr;
@@ -118,6 +121,7 @@ struct tpt_scene {
     uint32_t* flags = nullptr;    // refit arrival counters
     uint32_t* bounds = nullptr;   // 6 ordered-uint encoded floats (min xyz, max xyz)
     float4* nodes = nullptr;
+    float4* nodes4 = nullptr;     // allocated when the scene is large enough for the wide traversal to pay (tpt_scene_create)
     float4* tri_geom = nullptr;
     float4* tri_norm = nullptr;
     bool built = false;
@@ -125,7 +129,7 @@ struct tpt_scene {
     bool topology = false;        // hierarchy (children, parents, leaf order, range ends) of the last full build is intact: tpt_bvh_refit may reuse it
     bool any_specular = false;    // some material is a mirror or glass (metallic > 0 or eta > 0): k_primary's specular continuation can apply
     bool any_emissive = false;    // some material has emission > 0 (else the reference's extra "direct" rays add nothing and are not traced)
-    tpt::BvhView view() const { return tpt::BvhView{nodes, tri_geom, tri_norm, (int)n_faces}; }
+    tpt::BvhView view() const { return tpt::BvhView{nodes, nodes4, tri_geom, tri_norm, (int)n_faces}; }
 };
 
 struct tpt_accum {

@@ -230,6 +230,67 @@ __device__ __forceinline__ void trav_leaf_step(TravState& s, const BvhView& bvh,
     else s.cur = stack.pop(s.sp);
 }
 
+// ---- wide compressed nodes (BVH4) for trees that do not live in L1 --------------------------------------------------------
+// north_star: "compressed BVH nodes ... read with coalesced 128-bit loads".  For incoherent rays on the 10 M-triangle soup the
+// BVH2 walk is bound by the L1 data pipe (one wavefront per lane and load instruction, 72.9 node visits per secondary ray) and by
+// the chain of dependent node fetches.  A 4-wide node halves both: 64 bytes — two 256-bit loads, like a BVH2 node — hold FOUR child
+// boxes quantised to 8 bits per coordinate against the node's own box, so one visit replaces two levels of the binary tree.
+//   w0 = (origin.x, origin.y, origin.z, ex | ey << 8 | ez << 16)     box minimum of the node; per-axis scale 2^(e - 127)
+//   w1 = child[0..3]            >= 0: internal node (same index as in the binary tree)   < 0: leaf ~child (sorted triangle)
+//   w2 = (qlo.x[4], qlo.y[4], qlo.z[4], qhi.x[4])    one byte per child;  w3 = (qhi.y[4], qhi.z[4], -, -)
+// A child box decodes as lo = fma(qlo, scale, origin), hi = fma(qhi, scale, origin); the builder (bvh.cu: k_collapse4) rounds qlo
+// down and qhi up and CHECKS, with this very fma, that the decoded box contains the exact one, so culling stays conservative
+// and (prim, t, u, v) stay bit-identical to the binary walk and to brute force.  An unused slot holds kWideEmpty.  Leaves and their
+// exactly-rounded triangle test are unchanged.
+constexpr int kWideEmpty = (int)0x80000001;   // neither a node, nor a leaf code (~leaf >= -2^30), nor the stack sentinel
+__device__ __forceinline__ float wide_scale(uint32_t e) { return __uint_as_float((e & 255u) << 23); }
+__device__ __forceinline__ float wide_byte(uint32_t w, int c) { return (float)((w >> (8 * c)) & 255u); }
+
+// Ordered traversal pushes at most three children per visit and the tree is at most 95 levels deep (63 key bits + 32 index bits)
+constexpr int kWideStackSize = 3 * 96;
+
+template <class Stack>
+__device__ __forceinline__ void trav_node_step4(TravState& s, const float4* __restrict__ nodes4, const Stack& stack) {
+    const float4* n = nodes4 + 4 * (size_t)s.cur;
+    const F8 a = ldg256(n), b = ldg256(n + 2);
+    const uint32_t meta = __float_as_uint(a.a.w);
+    const float sx = wide_scale(meta), sy = wide_scale(meta >> 8), sz = wide_scale(meta >> 16);
+    const uint32_t qlx = __float_as_uint(b.a.x), qly = __float_as_uint(b.a.y), qlz = __float_as_uint(b.a.z);
+    const uint32_t qhx = __float_as_uint(b.a.w), qhy = __float_as_uint(b.b.x), qhz = __float_as_uint(b.b.y);
+    const int child[4] = {__float_as_int(a.b.x), __float_as_int(a.b.y), __float_as_int(a.b.z), __float_as_int(a.b.w)};
+    float t[4];
+    int c[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        float lo;
+        const bool hit = slab(fmaf(wide_byte(qlx, k), sx, a.a.x), fmaf(wide_byte(qhx, k), sx, a.a.x), fmaf(wide_byte(qly, k), sy, a.a.y),
+                              fmaf(wide_byte(qhy, k), sy, a.a.y), fmaf(wide_byte(qlz, k), sz, a.a.z), fmaf(wide_byte(qhz, k), sz, a.a.z), s.o, s.inv,
+                              s.best.t, lo);
+        t[k] = (hit && child[k] != kWideEmpty) ? lo : FLT_MAX;
+        c[k] = child[k];
+    }
+    // sort the four (entry distance, child) pairs, nearest first: 5 compare-exchanges; misses (FLT_MAX) sink to the end
+#define TPT_CSWAP(i, j)                    \
+    if (t[j] < t[i]) {                     \
+        const float tt = t[i];             \
+        t[i] = t[j];                       \
+        t[j] = tt;                         \
+        const int cc = c[i];               \
+        c[i] = c[j];                       \
+        c[j] = cc;                         \
+    }
+    TPT_CSWAP(0, 1) TPT_CSWAP(2, 3) TPT_CSWAP(0, 2) TPT_CSWAP(1, 3) TPT_CSWAP(1, 2)
+#undef TPT_CSWAP
+    if (t[0] == FLT_MAX) {
+        s.cur = stack.pop(s.sp);
+        return;
+    }
+    if (t[3] != FLT_MAX) stack.push(s.sp, c[3]);   // farthest first: the nearest of the pushed ones pops first
+    if (t[2] != FLT_MAX) stack.push(s.sp, c[2]);
+    if (t[1] != FLT_MAX) stack.push(s.sp, c[1]);
+    s.cur = c[0];
+}
+
 // ---- pixel-frustum culling (k_primary) -------------------------------------------------------------------------
 // All camera samples of one pixel leave the same origin through the pixel's quadrilateral on the image plane, so
 // they lie inside a four-sided pyramid.  If that pyramid misses every leaf box of the tree, none of the pixel's
