@@ -109,140 +109,263 @@ def my_slices(rank: int, world: int):
     return [s for s in range(N_SLICES) if s % world == rank]
 
 
+def _ncu_capture(fixture: str, kernel: str):
+    """Counters of the committed `ncu --set full` capture of `kernel` on this workload (profiles/, newest round first):
+    {duration_ms, dram_bytes, issue_active_pct, lanes_per_inst, l1_wavefront_pct, file} or None."""
+    unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
+    for rnd in ("r02", "r01"):
+        f = ROOT / "profiles" / f"{rnd}_ncu_full_{kernel}_{fixture}.csv"
+        if not f.exists():
+            continue
+        try:
+            rows = {r[0]: r for r in (ln.split(",") for ln in f.read_text().splitlines()) if len(r) >= 3}
+            col = 2          # launch1
+            val = lambda k: float(rows[k][col])
+            return {"duration_ms": val("gpu__time_duration.sum") * {"ms": 1.0, "us": 1e-3, "ns": 1e-6, "s": 1e3}.get(rows["gpu__time_duration.sum"][1], 1.0),
+                    "dram_bytes": sum(val(k) * unit[rows[k][1]] for k in ("dram__bytes_read.sum", "dram__bytes_write.sum")),
+                    "issue_active_pct": val("smsp__issue_active.avg.pct_of_peak_sustained_active"),
+                    "lanes_per_inst": val("smsp__thread_inst_executed_per_inst_executed.ratio"),
+                    "l1_wavefront_pct": val("l1tex__data_pipe_lsu_wavefronts.sum.pct_of_peak_sustained_elapsed")
+                    if "l1tex__data_pipe_lsu_wavefronts.sum.pct_of_peak_sustained_elapsed" in rows else None,
+                    "file": str(f.relative_to(ROOT))}
+        except Exception:
+            continue
+    return None
+
+
+class FrameBench:
+    """One workload of WORKLOADS on this rank's GPU: device-resident frames (`value`), end-to-end frames through host buffers
+    (`e2e`), and the counters the roofline object is computed from."""
+
+    def __init__(self, args, workload, spp_override=0):
+        import torch
+        import torch.distributed as dist
+        import tinypathtracer_b200 as tpt
+        self.torch, self.dist, self.tpt, self.args = torch, dist, tpt, args
+        self.rank, self.world, self.local = dist_env()
+        self.fixture, self.W, self.H, self.spp, self.depth, self.envkind, self.seed = WORKLOADS[workload]
+        if spp_override:
+            self.spp = spp_override
+        assert self.spp % N_SLICES == 0, "spp must be a multiple of the 8 fixed slices"
+        assert N_SLICES % self.world == 0, "the 8 fixed slices are dealt to 1, 2, 4 or 8 ranks"
+        self.per_slice = self.spp // N_SLICES
+        self.scene = load_scene(self.fixture)
+        self.env = synthetic_sky() if self.envkind == "sky" else None
+        W, H = self.W, self.H
+        self.ctx = tpt.Context(self.local)
+        self.stream = torch.cuda.current_stream()
+        self.ctx.set_stream(self.stream.cuda_stream)          # kernels, torch events and NCCL all on one stream
+        self.pt = tpt.PathTracer(self.ctx, W, H, env_rgba8=self.env)
+        self.acc_t = torch.zeros((H, W, 3), dtype=torch.int64, device="cuda")     # accumulation buffer owned by torch (NCCL operand)
+        self.acc = tpt.Accum(self.ctx, W, H, device_ptr=self.acc_t.data_ptr())
+        self.fb_dev = [torch.zeros((H, W, 4), dtype=torch.uint8, device="cuda") for _ in range(2)]
+        self.fb_host = [torch.zeros((H, W, 4), dtype=torch.uint8).pin_memory() for _ in range(2)]
+        self.cam = tpt.Camera.from_scene(self.scene)
+        self.slices = my_slices(self.rank, self.world)
+        self.dscene = tpt.DeviceScene(self.ctx, self.scene)
+        self.copy_stream = torch.cuda.Stream()
+        self.workload_name = f"{self.fixture}.gltf {W}x{H} {self.spp}spp depth{self.depth} env={self.envkind or 'black'} seed={self.seed}"
+
+    def close(self):
+        self.dscene.close()
+        self.acc.close()
+        self.ctx.close()
+
+    def frame(self, dscene=None, fb=0, counters=False, stage_times=False, flags_nee=False):
+        """One doTrace (reference src/path_tracer.cu:491-554) with device-resident inputs."""
+        import ctypes as C
+        from tinypathtracer_b200._capi import lib, check
+        tpt, dist = self.tpt, self.dist
+        dscene = dscene or self.dscene
+        tpt.BVH(dscene).construct(stats=False)
+        self.acc.clear()
+        # this rank's slices {s : s mod N == rank} are exactly the sample indices i with i mod N == rank (N divides 8):
+        # one call with offset = rank, stride = N renders them all (integer accumulation: grouping cannot change a bit)
+        self.pt.render_into(dscene, self.cam, spp=self.per_slice * len(self.slices), max_depth=self.depth, seed=self.seed, sample_offset=self.rank,
+                            sample_stride=self.world, accum=self.acc, counters=counters, stage_times=stage_times, env_nee=flags_nee,
+                            paths_in_flight=self.args.paths_in_flight)
+        if self.world > 1:
+            dist.all_reduce(self.acc_t, op=dist.ReduceOp.SUM)
+        check(lib.tpt_resolve_bgra8(self.acc._h, self.spp, C.c_void_p(self.fb_dev[fb].data_ptr()), 1))
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def timed(self, fn, steps, finish=None):
+        """K calls of fn bracketed by barrier + synchronize, CUDA events on the launching stream, max over ranks (ms total)."""
+        torch, dist = self.torch, self.dist
+        self.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(self.stream)
+        for i in range(steps):
+            fn(i)
+        if finish:
+            finish()
+        e1.record(self.stream)
+        self.barrier()
+        ms = e0.elapsed_time(e1)
+        if self.world > 1:
+            t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    def run_value(self, steps, warmup, **kw):
+        for _ in range(warmup):
+            self.frame(**kw)
+        self.ctx.reset_counters()
+        ms = self.timed(lambda i: self.frame(**kw), steps) / steps
+        ctr = self.ctx.counters()
+        if ctr["queue_overflow"] or ctr["dropped_nonfinite"] > 1e-6 * max(ctr["samples"], 1):
+            raise SystemExit(f"invalid run: queue_overflow={ctr['queue_overflow']} dropped_nonfinite={ctr['dropped_nonfinite']}")
+        return ms, ctr
+
+    def run_e2e(self, steps):
+        """The same frame end to end through the C ABI: every step uploads the scene's host arrays (tpt_scene_update: H2D into
+        the scene's existing device arrays) and reads the framebuffer back into pinned host memory.  The read-back of frame i
+        runs on a copy stream while frame i+1 is built and traced (two framebuffers); the timed region ends when the last
+        read-back has landed."""
+        torch = self.torch
+        ds = self.tpt.DeviceScene(self.ctx, self.scene)          # allocations made once, outside the timed region
+        done = [torch.cuda.Event() for _ in range(2)]
+        copied = [torch.cuda.Event() for _ in range(2)]
+        state = {"used": [False, False]}
+
+        def step(i):
+            b = i & 1
+            ds.update(self.scene)                                  # H2D of every scene array
+            if state["used"][b]:
+                self.stream.wait_event(copied[b])                  # framebuffer b is free again once its last read-back is done
+            self.frame(ds, fb=b)
+            done[b].record(self.stream)
+            self.copy_stream.wait_event(done[b])
+            with torch.cuda.stream(self.copy_stream):
+                self.fb_host[b].copy_(self.fb_dev[b], non_blocking=True)   # D2H of the step's result
+                copied[b].record(self.copy_stream)
+            state["used"][b] = True
+
+        def finish():
+            for b in range(2):
+                if state["used"][b]:
+                    self.stream.wait_event(copied[b])
+
+        step(0)
+        finish()
+        ms = self.timed(step, steps, finish) / steps
+        ds.close()
+        return ms
+
+    def accum_sha(self):
+        import hashlib
+        self.frame()
+        self.torch.cuda.synchronize()
+        return hashlib.sha256(self.acc_t.cpu().numpy().tobytes()).hexdigest() if self.rank == 0 else None
+
+    def rays_traversed(self, ctr):
+        # camera samples whose pixel pyramid misses every leaf box are answered without a traversal
+        return ctr["rays_primary"] - ctr["rays_culled"] + ctr["rays_extension"] + ctr["rays_shadow"] + ctr["rays_direct"]
+
+
+def native_allreduce_check(fb: "FrameBench"):
+    """tpt_accum_allreduce (csrc/comm.cu: peer loads + cudaMemcpyPeerAsync over NVLink, no library collective) on REAL peers:
+    rank 0 alone drives all `world` GPUs of the box from one process — one context per GPU, each renders its rank's samples —
+    and the all-reduced buffer must carry the SHA-256 of the NCCL frames.  The other ranks wait at a host (gloo) barrier."""
+    import hashlib
+    tpt, torch = fb.tpt, fb.torch
+    n = fb.world
+    ctxs = tpt.comm_init_all(n)
+    pts, dss = [], []
+    for r, c in enumerate(ctxs):
+        ds = tpt.DeviceScene(c, fb.scene)
+        tpt.BVH(ds).construct(stats=False)
+        pt = tpt.PathTracer(c, fb.W, fb.H, env_rgba8=fb.env)
+        pts.append(pt)
+        dss.append(ds)
+    ms = None
+    for it in range(3):
+        for r, (pt, ds) in enumerate(zip(pts, dss)):
+            pt.m_radiance.clear()
+            pt.render_into(ds, fb.cam, spp=fb.per_slice * len(my_slices(r, n)), max_depth=fb.depth, seed=fb.seed, sample_offset=r, sample_stride=n)
+        for c in ctxs:
+            c.synchronize()
+        t0 = time.perf_counter()
+        tpt.accum_allreduce([pt.m_radiance for pt in pts])
+        for c in ctxs:
+            c.synchronize()
+        ms = (time.perf_counter() - t0) * 1e3
+    shas = {hashlib.sha256(pt.m_radiance.to_i64().tobytes()).hexdigest() for pt in pts}
+    for c in ctxs:
+        c.close()
+    assert len(shas) == 1, "tpt_accum_allreduce left different buffers on different GPUs"
+    return shas.pop(), ms
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
-    import tinypathtracer_b200 as tpt
     from tinypathtracer_b200.scene_io import scene_upload_bytes
 
     rank, world, local = dist_env()
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device — the hot path has no CPU fallback")
     torch.cuda.set_device(local)
+    host_group = None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    fixture, W, H, spp, depth, envkind, seed = WORKLOADS[args.workload]
-    if args.spp:
-        spp = args.spp
-    assert spp % N_SLICES == 0, "spp must be a multiple of the 8 fixed slices"
-    assert N_SLICES % world == 0, "the 8 fixed slices are dealt to 1, 2, 4 or 8 ranks"
-    per_slice = spp // N_SLICES
-    scene = load_scene(fixture)
-    env = synthetic_sky() if envkind == "sky" else None
+        host_group = dist.new_group(backend="gloo")
+    fb = FrameBench(args, args.workload, args.spp)
+    W, H, spp, depth = fb.W, fb.H, fb.spp, fb.depth
+    ctx = fb.ctx
 
-    ctx = tpt.Context(local)
-    stream = torch.cuda.current_stream()
-    ctx.set_stream(stream.cuda_stream)          # kernels, torch events and NCCL all on one stream
-    pt = tpt.PathTracer(ctx, W, H, env_rgba8=env)
-    acc_t = torch.zeros((H, W, 3), dtype=torch.int64, device="cuda")     # accumulation buffer owned by torch (NCCL operand)
-    acc = tpt.Accum(ctx, W, H, device_ptr=acc_t.data_ptr())
-    fb_dev = torch.zeros((H, W, 4), dtype=torch.uint8, device="cuda")
-    fb_host = torch.zeros((H, W, 4), dtype=torch.uint8).pin_memory()
-    cam = tpt.Camera.from_scene(scene)
-    slices = my_slices(rank, world)
-    import ctypes as C
-    from tinypathtracer_b200._capi import lib, check
-
-    def frame(dscene, counters=False, stage_times=False):
-        """One doTrace (reference src/path_tracer.cu:491-554) with device-resident inputs."""
-        tpt.BVH(dscene).construct(stats=False)
-        acc.clear()
-        # this rank's slices {s : s mod N == rank} are exactly the sample indices i with i mod N == rank (N divides 8):
-        # one call with offset = rank, stride = N renders them all (integer accumulation: grouping cannot change a bit)
-        pt.render_into(dscene, cam, spp=per_slice * len(slices), max_depth=depth, seed=seed, sample_offset=rank, sample_stride=world,
-                       accum=acc, counters=counters, stage_times=stage_times, paths_in_flight=args.paths_in_flight)
-        if world > 1:
-            dist.all_reduce(acc_t, op=dist.ReduceOp.SUM)
-        check(lib.tpt_resolve_bgra8(acc._h, spp, C.c_void_p(fb_dev.data_ptr()), 1))
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def timed(fn, steps):
-        barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(stream)
-        for _ in range(steps):
-            fn()
-        e1.record(stream)
-        barrier()
-        ms = e0.elapsed_time(e1)
-        if world > 1:
-            t = torch.tensor([ms], device="cuda", dtype=torch.float64)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t.item())
-        return ms
-
-    dscene = tpt.DeviceScene(ctx, scene)
-    for _ in range(args.warmup):
-        frame(dscene)
     # ---- value: device-resident inputs -------------------------------------------------------------------
+    for _ in range(args.warmup):
+        fb.frame()
     ctx.reset_counters()
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()
-    ms_total = timed(lambda: frame(dscene), args.steps)
+    ms_step = fb.timed(lambda i: fb.frame(), args.steps) / args.steps
     clk = clocks.stop() if rank == 0 else {}
     ctr = ctx.counters()
     launches = ctr["kernel_launches"]
     if ctr["queue_overflow"] or ctr["dropped_nonfinite"] > 1e-6 * max(ctr["samples"], 1):
         raise SystemExit(f"invalid run: queue_overflow={ctr['queue_overflow']} dropped_nonfinite={ctr['dropped_nonfinite']}")
-    ms_step = ms_total / args.steps
     samples_step = W * H * spp                       # whole job, all ranks
-    # rays actually traversed: camera samples whose pixel pyramid misses every leaf box are answered without a traversal
-    rays_rank = ctr["rays_primary"] - ctr["rays_culled"] + ctr["rays_extension"] + ctr["rays_shadow"] + ctr["rays_direct"]
-    rays_t = torch.tensor([rays_rank], device="cuda", dtype=torch.int64)
+    sums = torch.tensor([fb.rays_traversed(ctr), ctr["rays_queued"]], device="cuda", dtype=torch.int64)
     if world > 1:
-        dist.all_reduce(rays_t)
-    rays_step = int(rays_t.item()) / args.steps
+        dist.all_reduce(sums)
+    rays_step, queued_step = int(sums[0].item()) / args.steps, int(sums[1].item()) / args.steps
     value = samples_step / (ms_step * 1e-3) / 1e6
 
-    # ---- e2e: host buffers in, host framebuffer out, through the C ABI -------------------------------------
-    def frame_e2e():
-        ds = tpt.DeviceScene(ctx, scene)          # tpt_scene_create: H2D of every scene array
-        frame(ds)
-        fb_host.copy_(fb_dev, non_blocking=True)  # D2H of the step's result
-        torch.cuda.current_stream().synchronize()
-        ds.close()
-
-    frame_e2e()
-    ms_e2e = timed(frame_e2e, args.steps) / args.steps
+    # ---- e2e: host arrays in, host framebuffer out, through the C ABI --------------------------------------
+    ms_e2e = fb.run_e2e(args.steps)
     e2e_value = samples_step / (ms_e2e * 1e-3) / 1e6
 
     # ---- determinism evidence: SHA-256 of the all-reduced int64 accumulation buffer of one more frame (untimed)
-    frame(dscene)
-    torch.cuda.synchronize()
-    import hashlib
-    accum_sha = hashlib.sha256(acc_t.cpu().numpy().tobytes()).hexdigest() if rank == 0 else None
+    accum_sha = fb.accum_sha()
 
     line = None
     if rank == 0:
         # ---- roofline pass (untimed for `value`): per-stage CUDA-event times + node/triangle counters --------
+        tpt = fb.tpt
         ctx.reset_counters()
-        bvh = tpt.BVH(dscene)
-        bstats = bvh.construct(stats=True)
-        acc.clear()
-        # (1) one whole frame of this rank with CUDA events around every launch (same batches as the timed frames)
-        rank_spp = per_slice * len(slices)
-        pt.render_into(dscene, cam, spp=rank_spp, max_depth=depth, seed=seed, sample_offset=rank, sample_stride=world, accum=acc,
-                       stage_times=True, paths_in_flight=args.paths_in_flight)
+        bstats = tpt.BVH(fb.dscene).construct(stats=True)
+        fb.acc.clear()
+        rank_spp = fb.per_slice * len(fb.slices)
+        fb.pt.render_into(fb.dscene, fb.cam, spp=rank_spp, max_depth=depth, seed=fb.seed, sample_offset=rank, sample_stride=world, accum=fb.acc,
+                          stage_times=True, paths_in_flight=args.paths_in_flight)
         st = ctx.stage_times()
         c1 = ctx.counters()
         ctx.reset_counters()
-        # (2) node / triangle visits per traversed ray on the same tree, counted build, a few samples per pixel
         prof_spp = max(1, min(rank_spp, 4))
-        pt.render_into(dscene, cam, spp=prof_spp, max_depth=depth, seed=seed, accum=acc, counters=True,
-                       paths_in_flight=args.paths_in_flight)
+        fb.pt.render_into(fb.dscene, fb.cam, spp=prof_spp, max_depth=depth, seed=fb.seed, accum=fb.acc, counters=True, paths_in_flight=args.paths_in_flight)
         c2 = ctx.counters()
         ctx.synchronize()
-        n_all = c1["rays_primary"] - c1["rays_culled"] + c1["rays_extension"] + c1["rays_shadow"] + c1["rays_direct"]
-        n_cnt = c2["rays_primary"] - c2["rays_culled"] + c2["rays_extension"] + c2["rays_shadow"] + c2["rays_direct"]
-        n_int = c2["node_visits"] / max(n_cnt, 1)
-        n_leaf = c2["tri_tests"] / max(n_cnt, 1)
-        bytes_per_ray = 56.0 * n_int + 40.0 * n_leaf + 88.0          # SURVEY §8(d) algorithmic bytes per ray
-        trav_ms = st["primary"]["ms"] + st["wave"]["ms"]            # every ray is traced inside these two kernels
+        n_all, n_cnt = fb.rays_traversed(c1), fb.rays_traversed(c2)
+        n_int, n_leaf = c2["node_visits"] / max(n_cnt, 1), c2["tri_tests"] / max(n_cnt, 1)
+        trav_ms = st["primary"]["ms"] + st["wave"]["ms"]
         trav_launches = st["primary"]["launches"] + st["wave"]["launches"]
         peaks = {}
         try:
@@ -250,45 +373,111 @@ def run_ours(args):
         except Exception:
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
-        achieved = bytes_per_ray * n_all / (trav_ms * 1e-3) / 1e9 if trav_ms > 0 else 0.0
-        roofline = {"bound": "hbm", "kernel": "k_primary+k_wave (BVH traversal fused with shading)", "achieved": round(achieved, 2), "peak": peak,
-                    "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback (B200_PROFILING.md)", "unit": "GB/s",
-                    "frac": round(achieved / peak, 5), "traffic": None,
-                    "bytes_per_ray": round(bytes_per_ray, 1), "n_int_per_ray": round(n_int, 2), "n_leaf_per_ray": round(n_leaf, 2),
-                    "rays_per_launch": round(n_all / max(trav_launches, 1), 1),
-                    "avg_launch_us": round(1e3 * trav_ms / max(trav_launches, 1), 2),
-                    "share_of_step": round(trav_ms / ms_step, 4),
-                    "stage_ms": {k: round(v["ms"], 3) for k, v in st.items()},
-                    "rays": {k: c1[k] for k in ("rays_primary", "rays_culled", "rays_candidates", "rays_extension", "rays_shadow", "rays_direct")},
-                    "note": "BVH of this workload is L1/L2-resident; node fetches never reach HBM, the HBM fraction is an upper-bound accounting (SURVEY §8d)"}
-        # DRAM traffic of the dominant launch (k_wave, wave 1 of one batch) from the committed ncu --set full capture of this workload
-        prof = ROOT / "profiles" / f"r01_ncu_full_k_wave_{fixture}.csv"
-        if prof.exists() and world == 1:
-            try:
-                unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
-                rows = {r[0]: r for r in (ln.split(",") for ln in prof.read_text().splitlines()) if len(r) >= 3}
-                tr = sum(float(rows[k][2]) * unit[rows[k][1]] for k in ("dram__bytes_read.sum", "dram__bytes_write.sum"))
-                roofline["traffic"] = round(tr)
-                roofline["traffic_of"] = f"one k_wave launch (wave 1 of a batch), ncu --set full, {prof.relative_to(ROOT)}"
-            except Exception:
-                pass
-        cpu = cpu_baseline(args, fixture, W, H, depth, env, seed) if world == 1 and not args.no_cpu_baseline else None
+        # The BVH of a bundled scene (<= 250 KB) lives in L1/L2: node and triangle fetches never reach HBM.  What does is the
+        # wavefront records (88 B per queued ray, written once and read once) and the accumulator (24 B per pixel
+        # and accumulation pass, 16 B per pixel for the resolve): THAT is the HBM figure of this workload.  The limiter is
+        # instruction issue, reported from the committed ncu captures of this build's two kernels.
+        batches = max(1, st["primary"]["launches"])
+        hbm_bytes = 88.0 * queued_step / max(world, 1) + W * H * (24.0 * (1 + batches) + 16.0)
+        hbm_ach = hbm_bytes / (ms_step * 1e-3) / 1e9
+        caps = {k: _ncu_capture(fb.fixture, k) for k in ("k_primary", "k_wave")}
+        issue = None
+        if all(caps.values()):
+            w = {"k_primary": st["primary"]["ms"], "k_wave": st["wave"]["ms"]}
+            tot = sum(w.values()) or 1.0
+            util = sum(w[k] * caps[k]["issue_active_pct"] * caps[k]["lanes_per_inst"] / 32.0 for k in caps) / tot
+            issue = {"thread_issue_utilisation_pct": round(util, 2),
+                     "formula": "sum over kernels of stage_ms x smsp__issue_active% x (thread instructions per warp instruction / 32) / sum stage_ms",
+                     "kernels": {k: {"issue_active_pct": round(caps[k]["issue_active_pct"], 1), "lanes_per_inst": round(caps[k]["lanes_per_inst"], 1),
+                                     "dram_bytes": round(caps[k]["dram_bytes"]), "capture_ms": round(caps[k]["duration_ms"], 3), "file": caps[k]["file"]}
+                                 for k in caps}}
+        traffic = round(sum(caps[k]["dram_bytes"] for k in caps)) if all(caps.values()) else None
+        roofline = {"bound": "issue" if issue else "hbm", "kernel": "k_primary + k_wave (BVH traversal fused with shading)",
+                    "achieved": issue["thread_issue_utilisation_pct"] if issue else round(hbm_ach, 2),
+                    "peak": 100.0 if issue else peak, "unit": "% of peak thread-instruction issue (warp issue slots x 32 lanes)" if issue else "GB/s",
+                    "frac": round(issue["thread_issue_utilisation_pct"] / 100.0, 4) if issue else round(hbm_ach / peak, 5),
+                    "traffic": traffic,
+                    "traffic_of": "dram__bytes_read + write of one k_primary launch + one k_wave (wave 1) launch = one batch, from the captures named under issue.kernels"
+                    if traffic else None,
+                    "issue": issue,
+                    "hbm": {"achieved": round(hbm_ach, 2), "peak": peak, "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback (B200_PROFILING.md)",
+                            "unit": "GB/s", "frac": round(hbm_ach / peak, 5), "algorithmic_bytes_per_step": round(hbm_bytes),
+                            "what": "88 B per queued ray (record written once, read once) + accumulator clear / accumulate / resolve; node and "
+                                    "triangle fetches are served by L1/L2 (the tree is %d KB)" % ((bstats["n_faces"] * 112) // 1024)},
+                    "traversal_accounting": {"bytes_per_ray": round(56.0 * n_int + 40.0 * n_leaf + 88.0, 1), "n_int_per_ray": round(n_int, 2),
+                                             "n_leaf_per_ray": round(n_leaf, 2),
+                                             "cache_level_gbs": round((56.0 * n_int + 40.0 * n_leaf + 88.0) * n_all / (trav_ms * 1e-3) / 1e9, 1) if trav_ms > 0 else None,
+                                             "note": "SURVEY §8(d)'s per-ray formula; these bytes are L1/L2 traffic here, not HBM, and are not a roofline fraction"},
+                    "rays_per_launch": round(n_all / max(trav_launches, 1), 1), "avg_launch_us": round(1e3 * trav_ms / max(trav_launches, 1), 2),
+                    "share_of_step": round(trav_ms / ms_step, 4), "stage_ms": {k: round(v["ms"], 3) for k, v in st.items()},
+                    "stage_launches": {k: v["launches"] for k, v in st.items()},
+                    "rays": {k: c1[k] for k in ("rays_primary", "rays_culled", "rays_candidates", "rays_extension", "rays_shadow", "rays_direct", "rays_queued")}}
+        pool_gb = 2 * 48 * (c1["rays_queued"] and max(c1["rays_extension"], 1) or 1) / 1e9
         line = {
             "metric": "Msamples/s (whole frames: transform + BVH build + render + resolve)", "value": round(value, 3), "unit": "Msamples/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 3), "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"{fixture}.gltf {W}x{H} {spp}spp depth{depth} env={envkind or 'black'} seed={seed}",
-                       "parallelism": f"spp-slices x{world}", "slices": N_SLICES,
-                       "l2": "per-step working set (path pools + accumulators, ~0.5 GB) exceeds the 126 MB L2"},
+            "config": {"workload": fb.workload_name, "parallelism": f"spp-slices x{world}", "slices": N_SLICES,
+                       "l2": "inputs larger than L2: every step writes and reads %.1f GB of wavefront records (%d M queued rays x 96 B) through "
+                             "HBM, far above the 126 MB L2; no flush between steps" % (96.0 * queued_step / max(world, 1) / 1e9, round(queued_step / 1e6))},
             "mrays_per_s": round(rays_step / (ms_step * 1e-3) / 1e6, 2), "rays_per_sample": round(rays_step / samples_step, 4),
+            "rays_note": "rays actually traversed; the reference traverses every camera ray and every 'direct' ray (see reference arm's rays_per_sample)",
             "bvh_build_ms": round(bstats["build_ms"], 4), "bvh_faces": bstats["n_faces"],
             "e2e": {"value": round(e2e_value, 3), "unit": "Msamples/s", "ms_per_step": round(ms_e2e, 3),
-                    "h2d_bytes_per_step": scene_upload_bytes(scene), "d2h_bytes_per_step": W * H * 4},
+                    "h2d_bytes_per_step": scene_upload_bytes(fb.scene), "d2h_bytes_per_step": W * H * 4,
+                    "how": "tpt_scene_update (H2D of all scene arrays) + frame + D2H of the BGRA8 framebuffer into pinned memory, read-back of frame i "
+                           "overlapped with frame i+1"},
             "gpu_launches": int(launches), "clocks": clk, "roofline": roofline,
             "accum_sha256": accum_sha,   # identical for 1, 2, 4 and 8 GPUs (exact integer accumulation + all-reduce)
         }
-        if cpu is not None:
-            line["cpu_baseline"] = cpu
+        del pool_gb
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(args, fb.fixture, W, H, depth, fb.env, fb.seed)
+    # ---- N > 1: the library's own all-reduce over NVLink peers, driven by rank 0 alone ---------------------------
+    if world > 1:
+        torch.cuda.synchronize()
+        dist.barrier(group=host_group)
+        if rank == 0:
+            try:
+                sha, ms = native_allreduce_check(fb)
+                line["native_allreduce_sha256"] = sha
+                line["native_allreduce_ms"] = round(ms, 3)
+                line["native_allreduce_matches_nccl"] = bool(sha == accum_sha)
+            except Exception as e:   # reported, never hidden
+                line["native_allreduce_error"] = str(e)[:300]
+        dist.barrier(group=host_group)
+    # ---- the other BASELINE configs, a few steps each (one GPU only): driver-visible numbers for north_star's box / tir target
+    if world == 1 and not args.no_also and args.workload == "ball" and not args.spp:
+        also = {}
+        fb.close()
+        for name in ("box", "tir", "light"):
+            try:
+                o = FrameBench(args, name)
+                ms, c = o.run_value(max(3, args.steps), args.warmup)
+                ms_e = o.run_e2e(max(3, args.steps))
+                n = o.W * o.H * o.spp
+                also[name] = {"workload": o.workload_name, "ms_per_step": round(ms, 3), "value": round(n / (ms * 1e-3) / 1e6, 3), "unit": "Msamples/s",
+                              "e2e_ms_per_step": round(ms_e, 3), "e2e_value": round(n / (ms_e * 1e-3) / 1e6, 3),
+                              "mrays_per_s": round(o.rays_traversed(c) / max(3, args.steps) / (ms * 1e-3) / 1e6, 2), "accum_sha256": o.accum_sha()}
+                o.close()
+            except Exception as e:
+                also[name] = {"error": str(e)[:300]}
+        # configs[1] with the alias-table environment sampling north_star names (TPT_RENDER_ENV_NEE; off in the headline
+        # because the reference never samples its CDF): same frame, one extra shadow ray per diffuse vertex
+        try:
+            o = FrameBench(args, "ball")
+            ms, c = o.run_value(max(3, args.steps // 2), 2, flags_nee=True)
+            also["ball_env_nee"] = {"workload": o.workload_name + " TPT_RENDER_ENV_NEE", "ms_per_step": round(ms, 3),
+                                    "value": round(o.W * o.H * o.spp / (ms * 1e-3) / 1e6, 3), "unit": "Msamples/s"}
+            o.close()
+        except Exception as e:
+            also["ball_env_nee"] = {"error": str(e)[:300]}
+        if not args.no_also_soup:
+            try:
+                also["soup"] = soup_measure(args, small=False, steps=3, warmup=1, with_e2e=False)
+            except Exception as e:
+                also["soup"] = {"error": str(e)[:300]}
+        line["also"] = also
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -297,17 +486,20 @@ def run_ours(args):
 
 
 def run_soup(args):
+    print(json.dumps(soup_measure(args, small=args.soup_small, steps=args.steps, warmup=args.warmup, with_e2e=True)))
+
+
+def soup_measure(args, small, steps, warmup, with_e2e):
     """BASELINE.json configs[3]: synthetic 10 000 004-triangle instanced soup — BVH build time and primary / secondary
     ray traversal throughput through tpt_trace_rays (device buffers for `value`, host buffers for `e2e`)."""
     import torch
     import tinypathtracer_b200 as tpt
     from tinypathtracer_b200.api import primary_rays_device
-    from tinypathtracer_b200.scene_io import scene_upload_bytes
     from tinypathtracer_b200.soup import make_soup, secondary_rays
 
     rank, world, local = dist_env()
     torch.cuda.set_device(local)
-    nb, nx = (8192, 3211) if not args.soup_small else (64, 25)
+    nb, nx = (8192, 3211) if not small else (64, 25)
     scene = make_soup(load_scene("ball"), nb, nx)
     F = scene["indices"].size // 3
     W, H = 3840, 2160
@@ -321,7 +513,7 @@ def run_soup(args):
     rays_t = torch.empty((n, 6), dtype=torch.float32, device="cuda")
     hits_t = torch.empty((n, 4), dtype=torch.float32, device="cuda")
     # ---- BVH build: median of 5 after warm-up (CUDA events inside tpt_bvh_build)
-    for _ in range(max(1, args.warmup)):
+    for _ in range(max(1, warmup)):
         bvh.construct(stats=True)
     builds = sorted(bvh.construct(stats=True)["build_ms"] for _ in range(5))
     build_ms = builds[2]
@@ -342,47 +534,54 @@ def run_soup(args):
     sec_t = torch.from_numpy(sec_h.view(np.float32).reshape(-1, 6)).cuda()
     sec_hits_t = torch.empty((ns, 4), dtype=torch.float32, device="cuda")
 
-    def timed(fn, steps):
+    def timed(fn, k):
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
-        for _ in range(steps):
+        for _ in range(k):
             fn()
         e1.record(stream)
         torch.cuda.synchronize()
-        return e0.elapsed_time(e1) / steps
+        return e0.elapsed_time(e1) / k
 
     def step():   # one pass of the hot path over the batch: both ray sets
         bvh.trace_device(rays_t.data_ptr(), n, hits_t.data_ptr())
         bvh.trace_device(sec_t.data_ptr(), ns, sec_hits_t.data_ptr())
 
-    for _ in range(args.warmup):
+    for _ in range(warmup):
         step()
     ctx.reset_counters()
     clocks = ClockSampler(local)
     clocks.start()
-    ms_step = timed(step, args.steps)
+    ms_step = timed(step, steps)
     launches = ctx.counters()["kernel_launches"]
-    timed(step, max(args.steps, 40))            # keep the GPU under the same load long enough for nvidia-smi's 100 ms sampler
+    timed(step, max(steps, 40))            # keep the GPU under the same load long enough for nvidia-smi's 100 ms sampler
     clk = clocks.stop()
-    ms_pri = timed(lambda: bvh.trace_device(rays_t.data_ptr(), n, hits_t.data_ptr()), args.steps)
-    ms_sec = timed(lambda: bvh.trace_device(sec_t.data_ptr(), ns, sec_hits_t.data_ptr()), args.steps)
-    # ---- e2e: host ray buffers in, host hits out, through tpt_trace_rays(device_ptrs = 0)
-    def pinned(a):   # host staging in page-locked memory, as a caller who cares about PCIe throughput would hold it
-        t = torch.from_numpy(a.view(np.float32).reshape(a.shape[0], -1).copy()).pin_memory()
-        return t, t.numpy().view(a.dtype).reshape(-1)
-    _k1, rays_p = pinned(rays_h)
-    _k2, sec_p = pinned(sec_h)
-    _k3, hits_p = pinned(np.zeros(n, tpt.HIT_DTYPE))
-    _k4, shits_p = pinned(np.zeros(ns, tpt.HIT_DTYPE))
-    bvh.trace(rays_p, out=hits_p)
-    reps = max(1, args.steps // 2)
-    t0 = time.perf_counter()
-    for _ in range(reps):
+    ms_pri = timed(lambda: bvh.trace_device(rays_t.data_ptr(), n, hits_t.data_ptr()), steps)
+    ms_sec = timed(lambda: bvh.trace_device(sec_t.data_ptr(), ns, sec_hits_t.data_ptr()), steps)
+    import hashlib
+    torch.cuda.synchronize()
+    hits_sha = hashlib.sha256(hits_t.cpu().numpy().tobytes() + sec_hits_t.cpu().numpy().tobytes()).hexdigest()
+    e2e = None
+    if with_e2e:
+        # ---- e2e: host ray buffers in, host hits out, through tpt_trace_rays(device_ptrs = 0)
+        def pinned(a):   # host staging in page-locked memory, as a caller who cares about PCIe throughput would hold it
+            t = torch.from_numpy(a.view(np.float32).reshape(a.shape[0], -1).copy()).pin_memory()
+            return t, t.numpy().view(a.dtype).reshape(-1)
+        _k1, rays_p = pinned(rays_h)
+        _k2, sec_p = pinned(sec_h)
+        _k3, hits_p = pinned(np.zeros(n, tpt.HIT_DTYPE))
+        _k4, shits_p = pinned(np.zeros(ns, tpt.HIT_DTYPE))
         bvh.trace(rays_p, out=hits_p)
-        bvh.trace(sec_p, out=shits_p)
-    e2e_ms = (time.perf_counter() - t0) * 1e3 / reps
-    assert np.array_equal(hits_p["prim"], hits_h["prim"])
+        reps = max(1, steps // 2)
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            bvh.trace(rays_p, out=hits_p)
+            bvh.trace(sec_p, out=shits_p)
+        e2e_ms = (time.perf_counter() - t0) * 1e3 / reps
+        assert np.array_equal(hits_p["prim"], hits_h["prim"])
+        e2e = {"value": round((n + ns) / (e2e_ms * 1e-3) / 1e6, 2), "unit": "Mrays/s", "ms_per_step": round(e2e_ms, 3),
+               "h2d_bytes_per_step": int((n + ns) * 24), "d2h_bytes_per_step": int((n + ns) * 16)}
     # ---- counted pass for the roofline: node / triangle visits per ray on the same tree
     ctx.reset_counters()
     bvh.trace_device(rays_t.data_ptr(), n, hits_t.data_ptr(), counted=True)
@@ -396,43 +595,46 @@ def run_soup(args):
     except Exception:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
-    bpr_sec = 56.0 * c_sec["node_visits"] / ns + 40.0 * c_sec["tri_tests"] / ns + 88.0
-    bpr_pri = 56.0 * c_pri["node_visits"] / n + 40.0 * c_pri["tri_tests"] / n + 88.0
+    # 56 B per internal node whose children were tested (BINARY nodes; a 4-wide visit tests four children and is counted
+    # as two binary visits' worth of boxes: 2 x 48 B + 16 B of child indices = 112 B), 40 B per triangle tested, 88 B of record traffic
+    wide = os.environ.get("TPT_NO_WIDE") is None and F >= int(os.environ.get("TPT_WIDE_MIN_FACES", 1 << 16))
+    node_bytes = 112.0 if wide else 56.0
+    bpr_sec = node_bytes * c_sec["node_visits"] / ns + 40.0 * c_sec["tri_tests"] / ns + 88.0
+    bpr_pri = node_bytes * c_pri["node_visits"] / n + 40.0 * c_pri["tri_tests"] / n + 88.0
     ach = bpr_sec * ns / (ms_sec * 1e-3) / 1e9
     build_gbs = 408.0 * F / (build_ms * 1e-3) / 1e9
-    # DRAM traffic of the secondary-ray launch from the committed ncu --set full capture (launch2 of that file; full-size soup only)
-    traffic, traffic_of = None, None
-    prof = ROOT / "profiles" / "r01_ncu_full_k_trace_rays_soup.csv"
-    if prof.exists() and not args.soup_small:
-        try:
-            unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
-            rows = {r[0]: r for r in (ln.split(",") for ln in prof.read_text().splitlines()) if len(r) >= 5}
-            traffic = round(sum(float(rows[k][4]) * unit[rows[k][1]] for k in ("dram__bytes_read.sum", "dram__bytes_write.sum")))
-            traffic_of = f"the secondary-ray k_trace_rays_persistent launch, ncu --set full, {prof.relative_to(ROOT)} (launch2)"
-        except Exception:
-            pass
+    # DRAM traffic and L1 pressure of the secondary-ray launch from the committed ncu --set full capture (full-size soup only)
+    cap = None if small else _ncu_capture("soup", "k_trace_rays")
     line = {
         "metric": "Mrays/s (tpt_trace_rays, primary + secondary ray sets; BVH build ms beside it)", "value": round((n + ns) / (ms_step * 1e-3) / 1e6, 2),
-        "unit": "Mrays/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 3), "higher_is_better": True,
+        "unit": "Mrays/s", "n_gpus": 1, "steps": steps, "warmup": warmup, "ms_per_step": round(ms_step, 3), "higher_is_better": True,
         "scaling": "replicas only", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"synthetic soup {F} triangles ({nb} spheres x 1216 + {nx} boxes x 12), {W}x{H} pixel-centre primary rays + {ns} cosine secondary rays",
-                   "l2": "BVH (640 MB nodes + 480 MB triangles) and ray buffers exceed the 126 MB L2"},
+                   "l2": "inputs larger than L2: BVH (640 MB binary + 640 MB wide nodes, 480 MB triangles) and ray buffers exceed the 126 MB L2",
+                   "nodes": "4-wide compressed (64 B, 8-bit child boxes)" if wide else "binary (64 B, fp32 child boxes)"},
         "bvh_build_ms": round(build_ms, 4), "bvh_build_ms_all": [round(b, 4) for b in builds], "bvh_faces": int(F), "bvh_max_depth": bstats["max_depth"],
         "bvh_refit_ms": round(refit_ms, 4), "bvh_sah_cost": round(bstats["sah_cost"], 2),
         "primary_mrays_per_s": round(n / (ms_pri * 1e-3) / 1e6, 2), "secondary_mrays_per_s": round(ns / (ms_sec * 1e-3) / 1e6, 2),
-        "primary_hit_fraction": round(float((hits_h["prim"] >= 0).mean()), 4),
-        "e2e": {"value": round((n + ns) / (e2e_ms * 1e-3) / 1e6, 2), "unit": "Mrays/s", "ms_per_step": round(e2e_ms, 3),
-                "h2d_bytes_per_step": int((n + ns) * 24), "d2h_bytes_per_step": int((n + ns) * 16)},
+        "primary_hit_fraction": round(float((hits_h["prim"] >= 0).mean()), 4), "hits_sha256": hits_sha,
         "gpu_launches": int(launches), "clocks": clk,
-        "roofline": {"bound": "hbm", "kernel": "k_trace_rays (secondary ray set, incoherent)", "achieved": round(ach, 2), "peak": peak,
+        "roofline": {"bound": "hbm", "kernel": "k_trace_rays_persistent (secondary ray set, incoherent)", "achieved": round(ach, 2), "peak": peak,
                      "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback (B200_PROFILING.md)", "unit": "GB/s", "frac": round(ach / peak, 5),
-                     "traffic": traffic, "traffic_of": traffic_of, "bytes_per_ray": round(bpr_sec, 1), "n_int_per_ray": round(c_sec["node_visits"] / ns, 2),
+                     "traffic": round(cap["dram_bytes"]) if cap else None,
+                     "traffic_ratio": round(cap["dram_bytes"] / (bpr_sec * ns), 3) if cap else None,
+                     "traffic_of": f"dram bytes of the secondary-ray launch, ncu --set full, {cap['file']}; traffic_ratio = measured DRAM bytes / algorithmic bytes "
+                                   "(below 1: most node fetches are served by L1/L2; the kernel's limiter is the L1 data pipe, l1_wavefront_pct)" if cap else None,
+                     "l1_wavefront_pct": cap["l1_wavefront_pct"] if cap else None,
+                     "bytes_per_ray": round(bpr_sec, 1), "n_int_per_ray": round(c_sec["node_visits"] / ns, 2),
                      "n_leaf_per_ray": round(c_sec["tri_tests"] / ns, 2), "rays_per_launch": ns, "avg_launch_us": round(ms_sec * 1e3, 1),
                      "primary": {"bytes_per_ray": round(bpr_pri, 1), "n_int_per_ray": round(c_pri["node_visits"] / n, 2),
                                  "n_leaf_per_ray": round(c_pri["tri_tests"] / n, 2), "achieved": round(bpr_pri * n / (ms_pri * 1e-3) / 1e9, 2)},
                      "bvh_build": {"algorithmic_bytes_per_triangle": 408, "achieved": round(build_gbs, 2), "frac": round(build_gbs / peak, 5)}},
     }
-    print(json.dumps(line))
+    if e2e:
+        line["e2e"] = e2e
+    dscene.close()
+    ctx.close()
+    return line
 
 
 def cpu_baseline(args, fixture, W, H, depth, env, seed):
@@ -642,6 +844,8 @@ def main():
     ap.add_argument("--paths-in-flight", type=int, default=0)
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-also", action="store_true", help="skip the other BASELINE configs (box, tir, light, NEE, soup) after the headline")
+    ap.add_argument("--no-also-soup", action="store_true", help="skip only the 10M-triangle soup in the `also` section")
     ap.add_argument("--ref-cpu", action="store_true", help="reference arm: force the CPU oracle port")
     ap.add_argument("--ref-timeout", type=float, default=900.0)
     args = ap.parse_args()
