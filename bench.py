@@ -135,9 +135,15 @@ def _ncu_capture(fixture: str, kernel: str):
 
 class FrameBench:
     """One workload of WORKLOADS on this rank's GPU: device-resident frames (`value`), end-to-end frames through host buffers
-    (`e2e`), and the counters the roofline object is computed from."""
+    (`e2e`), and the counters the roofline object is computed from.
 
-    def __init__(self, args, workload, spp_override=0):
+    Frames are independent (the reference's loop renders one after the other from scratch, src/vkEngine.cu:294-302), so
+    `--frames-in-flight` (default 2) of them are kept in flight: frame i runs on lane i mod 2 — a context, stream, device scene,
+    queue pools, accumulator and framebuffer of its own — and the latency-bound end of one frame (its deep waves hold a
+    handful of rays and cost the latency of the slowest, the all-reduce, the resolve, the read-back) overlaps the start of
+    the next.  Every frame still does everything: build, clear, all its samples, all-reduce, resolve."""
+
+    def __init__(self, args, workload, spp_override=0, lanes=None):
         import torch
         import torch.distributed as dist
         import tinypathtracer_b200 as tpt
@@ -152,41 +158,53 @@ class FrameBench:
         self.scene = load_scene(self.fixture)
         self.env = synthetic_sky() if self.envkind == "sky" else None
         W, H = self.W, self.H
-        self.ctx = tpt.Context(self.local)
-        self.stream = torch.cuda.current_stream()
-        self.ctx.set_stream(self.stream.cuda_stream)          # kernels, torch events and NCCL all on one stream
-        self.pt = tpt.PathTracer(self.ctx, W, H, env_rgba8=self.env)
-        self.acc_t = torch.zeros((H, W, 3), dtype=torch.int64, device="cuda")     # accumulation buffer owned by torch (NCCL operand)
-        self.acc = tpt.Accum(self.ctx, W, H, device_ptr=self.acc_t.data_ptr())
-        self.fb_dev = [torch.zeros((H, W, 4), dtype=torch.uint8, device="cuda") for _ in range(2)]
-        self.fb_host = [torch.zeros((H, W, 4), dtype=torch.uint8).pin_memory() for _ in range(2)]
+        self.n_lanes = max(1, lanes if lanes is not None else args.frames_in_flight)
+        self.main = torch.cuda.current_stream()
+        self.streams = [self.main] + [torch.cuda.Stream() for _ in range(self.n_lanes - 1)]
+        self.ctxs, self.pts, self.acc_ts, self.accs, self.dscenes, self.fb_dev, self.fb_host = [], [], [], [], [], [], []
+        for k in range(self.n_lanes):
+            c = tpt.Context(self.local)
+            c.set_stream(self.streams[k].cuda_stream)          # kernels, torch events and NCCL of a lane all on one stream
+            self.ctxs.append(c)
+            self.pts.append(tpt.PathTracer(c, W, H, env_rgba8=self.env))
+            t = torch.zeros((H, W, 3), dtype=torch.int64, device="cuda")     # accumulation buffer owned by torch (NCCL operand)
+            self.acc_ts.append(t)
+            self.accs.append(tpt.Accum(c, W, H, device_ptr=t.data_ptr()))
+            self.dscenes.append(tpt.DeviceScene(c, self.scene))
+            self.fb_dev.append(torch.zeros((H, W, 4), dtype=torch.uint8, device="cuda"))
+            self.fb_host.append(torch.zeros((H, W, 4), dtype=torch.uint8).pin_memory())
+        self.ctx, self.pt, self.acc_t, self.acc, self.dscene, self.stream = (self.ctxs[0], self.pts[0], self.acc_ts[0], self.accs[0],
+                                                                             self.dscenes[0], self.main)
         self.cam = tpt.Camera.from_scene(self.scene)
         self.slices = my_slices(self.rank, self.world)
-        self.dscene = tpt.DeviceScene(self.ctx, self.scene)
         self.copy_stream = torch.cuda.Stream()
         self.workload_name = f"{self.fixture}.gltf {W}x{H} {self.spp}spp depth{self.depth} env={self.envkind or 'black'} seed={self.seed}"
 
     def close(self):
-        self.dscene.close()
-        self.acc.close()
-        self.ctx.close()
+        self.torch.cuda.synchronize()
+        for k in range(self.n_lanes):
+            self.dscenes[k].close()
+            self.accs[k].close()
+            self.ctxs[k].close()
 
-    def frame(self, dscene=None, fb=0, counters=False, stage_times=False, flags_nee=False):
-        """One doTrace (reference src/path_tracer.cu:491-554) with device-resident inputs."""
+    def frame(self, i=0, dscene=None, counters=False, stage_times=False, flags_nee=False):
+        """One doTrace (reference src/path_tracer.cu:491-554) with device-resident inputs, on lane i mod n_lanes."""
         import ctypes as C
         from tinypathtracer_b200._capi import lib, check
-        tpt, dist = self.tpt, self.dist
-        dscene = dscene or self.dscene
-        tpt.BVH(dscene).construct(stats=False)
-        self.acc.clear()
-        # this rank's slices {s : s mod N == rank} are exactly the sample indices i with i mod N == rank (N divides 8):
-        # one call with offset = rank, stride = N renders them all (integer accumulation: grouping cannot change a bit)
-        self.pt.render_into(dscene, self.cam, spp=self.per_slice * len(self.slices), max_depth=self.depth, seed=self.seed, sample_offset=self.rank,
-                            sample_stride=self.world, accum=self.acc, counters=counters, stage_times=stage_times, env_nee=flags_nee,
-                            paths_in_flight=self.args.paths_in_flight)
-        if self.world > 1:
-            dist.all_reduce(self.acc_t, op=dist.ReduceOp.SUM)
-        check(lib.tpt_resolve_bgra8(self.acc._h, self.spp, C.c_void_p(self.fb_dev[fb].data_ptr()), 1))
+        tpt, dist, torch = self.tpt, self.dist, self.torch
+        k = i % self.n_lanes
+        dscene = dscene or self.dscenes[k]
+        with torch.cuda.stream(self.streams[k]):
+            tpt.BVH(dscene).construct(stats=False)
+            self.accs[k].clear()
+            # this rank's slices {s : s mod N == rank} are exactly the sample indices i with i mod N == rank (N divides 8):
+            # one call with offset = rank, stride = N renders them all (integer accumulation: grouping cannot change a bit)
+            self.pts[k].render_into(dscene, self.cam, spp=self.per_slice * len(self.slices), max_depth=self.depth, seed=self.seed,
+                                    sample_offset=self.rank, sample_stride=self.world, accum=self.accs[k], counters=counters, stage_times=stage_times,
+                                    env_nee=flags_nee, paths_in_flight=self.args.paths_in_flight)
+            if self.world > 1:
+                dist.all_reduce(self.acc_ts[k], op=dist.ReduceOp.SUM)
+            check(lib.tpt_resolve_bgra8(self.accs[k]._h, self.spp, C.c_void_p(self.fb_dev[k].data_ptr()), 1))
 
     def barrier(self):
         if self.world > 1:
@@ -194,16 +212,23 @@ class FrameBench:
         self.torch.cuda.synchronize()
 
     def timed(self, fn, steps, finish=None):
-        """K calls of fn bracketed by barrier + synchronize, CUDA events on the launching stream, max over ranks (ms total)."""
+        """K calls of fn bracketed by barrier + synchronize, CUDA events on the launching stream (the lanes' streams start after
+        the first event and the second waits for all of them), max over ranks (ms total)."""
         torch, dist = self.torch, self.dist
         self.barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(self.stream)
+        e0.record(self.main)
+        for s in self.streams[1:]:
+            s.wait_event(e0)
         for i in range(steps):
             fn(i)
         if finish:
             finish()
-        e1.record(self.stream)
+        for s in self.streams[1:]:
+            ev = torch.cuda.Event()
+            ev.record(s)
+            self.main.wait_event(ev)
+        e1.record(self.main)
         self.barrier()
         ms = e0.elapsed_time(e1)
         if self.world > 1:
@@ -212,56 +237,70 @@ class FrameBench:
             ms = float(t.item())
         return ms
 
+    def counters_sum(self):
+        out = None
+        for c in self.ctxs:
+            d = c.counters()
+            out = d if out is None else {k: out[k] + d[k] for k in d}
+        return out
+
+    def reset_counters(self):
+        for c in self.ctxs:
+            c.reset_counters()
+
     def run_value(self, steps, warmup, **kw):
-        for _ in range(warmup):
-            self.frame(**kw)
-        self.ctx.reset_counters()
-        ms = self.timed(lambda i: self.frame(**kw), steps) / steps
-        ctr = self.ctx.counters()
+        for i in range(warmup):
+            self.frame(i, **kw)
+        self.reset_counters()
+        ms = self.timed(lambda i: self.frame(i, **kw), steps) / steps
+        ctr = self.counters_sum()
         if ctr["queue_overflow"] or ctr["dropped_nonfinite"] > 1e-6 * max(ctr["samples"], 1):
             raise SystemExit(f"invalid run: queue_overflow={ctr['queue_overflow']} dropped_nonfinite={ctr['dropped_nonfinite']}")
         return ms, ctr
 
     def run_e2e(self, steps):
         """The same frame end to end through the C ABI: every step uploads the scene's host arrays (tpt_scene_update: H2D into
-        the scene's existing device arrays) and reads the framebuffer back into pinned host memory.  The read-back of frame i
-        runs on a copy stream while frame i+1 is built and traced (two framebuffers); the timed region ends when the last
-        read-back has landed."""
+        the lane's existing device arrays) and reads the framebuffer back into pinned host memory.  The read-back of a frame
+        runs on a copy stream while the next frames are built and traced (a framebuffer per lane); the timed region ends when
+        the last read-back has landed."""
         torch = self.torch
-        ds = self.tpt.DeviceScene(self.ctx, self.scene)          # allocations made once, outside the timed region
-        done = [torch.cuda.Event() for _ in range(2)]
-        copied = [torch.cuda.Event() for _ in range(2)]
-        state = {"used": [False, False]}
+        ds = [self.tpt.DeviceScene(self.ctxs[k], self.scene) for k in range(self.n_lanes)]   # allocations made once, outside the timed region
+        done = [torch.cuda.Event() for _ in range(self.n_lanes)]
+        copied = [torch.cuda.Event() for _ in range(self.n_lanes)]
+        used = [False] * self.n_lanes
 
         def step(i):
-            b = i & 1
-            ds.update(self.scene)                                  # H2D of every scene array
-            if state["used"][b]:
-                self.stream.wait_event(copied[b])                  # framebuffer b is free again once its last read-back is done
-            self.frame(ds, fb=b)
-            done[b].record(self.stream)
-            self.copy_stream.wait_event(done[b])
+            k = i % self.n_lanes
+            with torch.cuda.stream(self.streams[k]):
+                ds[k].update(self.scene)                           # H2D of every scene array
+                if used[k]:
+                    self.streams[k].wait_event(copied[k])          # the lane's framebuffer is free again once its last read-back is done
+            self.frame(i, ds[k])
+            done[k].record(self.streams[k])
+            self.copy_stream.wait_event(done[k])
             with torch.cuda.stream(self.copy_stream):
-                self.fb_host[b].copy_(self.fb_dev[b], non_blocking=True)   # D2H of the step's result
-                copied[b].record(self.copy_stream)
-            state["used"][b] = True
+                self.fb_host[k].copy_(self.fb_dev[k], non_blocking=True)   # D2H of the step's result
+                copied[k].record(self.copy_stream)
+            used[k] = True
 
         def finish():
-            for b in range(2):
-                if state["used"][b]:
-                    self.stream.wait_event(copied[b])
+            for k in range(self.n_lanes):
+                if used[k]:
+                    self.main.wait_event(copied[k])
 
         step(0)
         finish()
         ms = self.timed(step, steps, finish) / steps
-        ds.close()
+        self.torch.cuda.synchronize()
+        for d in ds:
+            d.close()
         return ms
 
     def accum_sha(self):
         import hashlib
-        self.frame()
+        self.frame(0)
         self.torch.cuda.synchronize()
-        return hashlib.sha256(self.acc_t.cpu().numpy().tobytes()).hexdigest() if self.rank == 0 else None
+        return hashlib.sha256(self.acc_ts[0].cpu().numpy().tobytes()).hexdigest() if self.rank == 0 else None
 
     def rays_traversed(self, ctr):
         # camera samples whose pixel pyramid misses every leaf box are answered without a traversal
@@ -320,15 +359,15 @@ def run_ours(args):
     ctx = fb.ctx
 
     # ---- value: device-resident inputs -------------------------------------------------------------------
-    for _ in range(args.warmup):
-        fb.frame()
-    ctx.reset_counters()
+    for i in range(args.warmup):
+        fb.frame(i)
+    fb.reset_counters()
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()
-    ms_step = fb.timed(lambda i: fb.frame(), args.steps) / args.steps
+    ms_step = fb.timed(lambda i: fb.frame(i), args.steps) / args.steps
     clk = clocks.stop() if rank == 0 else {}
-    ctr = ctx.counters()
+    ctr = fb.counters_sum()
     launches = ctr["kernel_launches"]
     if ctr["queue_overflow"] or ctr["dropped_nonfinite"] > 1e-6 * max(ctr["samples"], 1):
         raise SystemExit(f"invalid run: queue_overflow={ctr['queue_overflow']} dropped_nonfinite={ctr['dropped_nonfinite']}")
@@ -338,6 +377,8 @@ def run_ours(args):
         dist.all_reduce(sums)
     rays_step, queued_step = int(sums[0].item()) / args.steps, int(sums[1].item()) / args.steps
     value = samples_step / (ms_step * 1e-3) / 1e6
+    # one frame at a time on lane 0, for the record: what a single frame takes when nothing overlaps it
+    ms_serial = fb.timed(lambda i: fb.frame(0), max(3, args.steps // 2)) / max(3, args.steps // 2)
 
     # ---- e2e: host arrays in, host framebuffer out, through the C ABI --------------------------------------
     ms_e2e = fb.run_e2e(args.steps)
@@ -350,6 +391,7 @@ def run_ours(args):
     if rank == 0:
         # ---- roofline pass (untimed for `value`): per-stage CUDA-event times + node/triangle counters --------
         tpt = fb.tpt
+        torch.cuda.synchronize()
         ctx.reset_counters()
         bstats = tpt.BVH(fb.dscene).construct(stats=True)
         fb.acc.clear()
@@ -417,16 +459,17 @@ def run_ours(args):
             "metric": "Msamples/s (whole frames: transform + BVH build + render + resolve)", "value": round(value, 3), "unit": "Msamples/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 3), "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": fb.workload_name, "parallelism": f"spp-slices x{world}", "slices": N_SLICES,
+            "config": {"workload": fb.workload_name, "parallelism": f"spp-slices x{world}", "slices": N_SLICES, "frames_in_flight": fb.n_lanes,
                        "l2": "inputs larger than L2: every step writes and reads %.1f GB of wavefront records (%d M queued rays x 96 B) through "
                              "HBM, far above the 126 MB L2; no flush between steps" % (96.0 * queued_step / max(world, 1) / 1e9, round(queued_step / 1e6))},
             "mrays_per_s": round(rays_step / (ms_step * 1e-3) / 1e6, 2), "rays_per_sample": round(rays_step / samples_step, 4),
             "rays_note": "rays actually traversed; the reference traverses every camera ray and every 'direct' ray (see reference arm's rays_per_sample)",
             "bvh_build_ms": round(bstats["build_ms"], 4), "bvh_faces": bstats["n_faces"],
+            "frame_latency_ms": round(ms_serial, 3),   # one frame alone on one lane (no overlap); ms_per_step = timed region / steps with frames_in_flight
             "e2e": {"value": round(e2e_value, 3), "unit": "Msamples/s", "ms_per_step": round(ms_e2e, 3),
                     "h2d_bytes_per_step": scene_upload_bytes(fb.scene), "d2h_bytes_per_step": W * H * 4,
-                    "how": "tpt_scene_update (H2D of all scene arrays) + frame + D2H of the BGRA8 framebuffer into pinned memory, read-back of frame i "
-                           "overlapped with frame i+1"},
+                    "how": "tpt_scene_update (H2D of all scene arrays) + frame + D2H of the BGRA8 framebuffer into pinned memory; frames_in_flight "
+                           "frames overlap, read-backs on a copy stream"},
             "gpu_launches": int(launches), "clocks": clk, "roofline": roofline,
             "accum_sha256": accum_sha,   # identical for 1, 2, 4 and 8 GPUs (exact integer accumulation + all-reduce)
         }
@@ -597,7 +640,7 @@ def soup_measure(args, small, steps, warmup, with_e2e):
     peak = float(peaks.get("hbm_gbs", 6650.0))
     # 56 B per internal node whose children were tested (BINARY nodes; a 4-wide visit tests four children and is counted
     # as two binary visits' worth of boxes: 2 x 48 B + 16 B of child indices = 112 B), 40 B per triangle tested, 88 B of record traffic
-    wide = os.environ.get("TPT_NO_WIDE") is None and F >= int(os.environ.get("TPT_WIDE_MIN_FACES", 1 << 16))
+    wide = os.environ.get("TPT_NO_WIDE") is None and "TPT_WIDE_MIN_FACES" in os.environ and F >= int(os.environ["TPT_WIDE_MIN_FACES"])
     node_bytes = 112.0 if wide else 56.0
     bpr_sec = node_bytes * c_sec["node_visits"] / ns + 40.0 * c_sec["tri_tests"] / ns + 88.0
     bpr_pri = node_bytes * c_pri["node_visits"] / n + 40.0 * c_pri["tri_tests"] / n + 88.0
@@ -610,7 +653,7 @@ def soup_measure(args, small, steps, warmup, with_e2e):
         "unit": "Mrays/s", "n_gpus": 1, "steps": steps, "warmup": warmup, "ms_per_step": round(ms_step, 3), "higher_is_better": True,
         "scaling": "replicas only", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"synthetic soup {F} triangles ({nb} spheres x 1216 + {nx} boxes x 12), {W}x{H} pixel-centre primary rays + {ns} cosine secondary rays",
-                   "l2": "inputs larger than L2: BVH (640 MB binary + 640 MB wide nodes, 480 MB triangles) and ray buffers exceed the 126 MB L2",
+                   "l2": "inputs larger than L2: BVH (640 MB nodes, 480 MB triangles) and ray buffers exceed the 126 MB L2",
                    "nodes": "4-wide compressed (64 B, 8-bit child boxes)" if wide else "binary (64 B, fp32 child boxes)"},
         "bvh_build_ms": round(build_ms, 4), "bvh_build_ms_all": [round(b, 4) for b in builds], "bvh_faces": int(F), "bvh_max_depth": bstats["max_depth"],
         "bvh_refit_ms": round(refit_ms, 4), "bvh_sah_cost": round(bstats["sah_cost"], 2),
@@ -668,34 +711,57 @@ def run_reference(args):
     if rank != 0:
         return
     if args.workload == "soup":
-        return run_reference_soup(args)
-    fixture, W, H, spp, depth, envkind, seed = WORKLOADS[args.workload]
-    if args.spp:
-        spp = args.spp
+        print(json.dumps(run_reference_soup(args)))
+        return
+    line = reference_frames(args, args.workload, args.spp, args.steps, args.warmup)
+    # the other BASELINE configs with the same binary, so that the driver's record holds both arms of each
+    if args.workload == "ball" and not args.spp and not args.no_also:
+        also = {}
+        for name in ("box", "tir", "light"):
+            try:
+                o = reference_frames(args, name, 0, max(3, args.steps), args.warmup)
+                also[name] = {k: o[k] for k in ("ms_per_step", "value", "unit", "rays_per_sample", "mrays_per_s", "reference_kind") if k in o}
+                also[name]["workload"] = o["config"]["workload"]
+            except Exception as e:
+                also[name] = {"error": str(e)[:300]}
+        if not args.no_also_soup:
+            try:
+                o = run_reference_soup(args)
+                also["soup"] = {k: o[k] for k in ("unavailable", "value", "unit", "ms_per_step", "bvh_build_ms", "primary_mrays_per_s", "secondary_mrays_per_s",
+                                                  "reference_kind") if k in o}
+            except Exception as e:
+                also["soup"] = {"error": str(e)[:300]}
+        line["also"] = also
+    print(json.dumps(line))
+
+
+def reference_frames(args, workload, spp_override, steps, warmup):
+    fixture, W, H, spp, depth, envkind, seed = WORKLOADS[workload]
+    if spp_override:
+        spp = spp_override
     cfg = {"workload": f"{fixture}.gltf {W}x{H} {spp}spp depth{depth} env={envkind or 'black'} seed={seed}"}
     exe = ROOT / "oracle" / "_ref" / "tpt_ref_headless"
     ref_scene = ROOT / "oracle" / "_ref" / "input" / f"{fixture}.gltf"
     if exe.exists() and ref_scene.exists() and not args.ref_cpu:
         import torch
         if torch.cuda.is_available():
-            out = run_reference_cuda(args, exe, ref_scene, W, H, spp, depth, envkind, cfg)
+            out = run_reference_cuda(args, exe, ref_scene, W, H, spp, depth, envkind, cfg, steps, warmup)
             if out is not None:
-                print(json.dumps(out))
-                return
+                return out
     env = synthetic_sky() if envkind == "sky" else None
     res = []
-    for _ in range(args.warmup + args.steps):
+    for _ in range(warmup + steps):
         res.append(cpu_baseline(args, fixture, W, H, depth, env, seed))
-    res = res[args.warmup:]
+    res = res[warmup:]
     v = float(np.mean([r["value"] for r in res]))
     cb = dict(res[-1])
     cb["value"] = round(v, 4)
-    print(json.dumps({"impl": "reference", "metric": "Msamples/s (whole frames: transform + BVH build + render + resolve)",
-                      "value": round(v, 4), "unit": "Msamples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-                      "ms_per_step": round(1e3 * W * H * spp / (v * 1e6), 1), "higher_is_better": True, "scaling": "strong",
-                      "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg, "cpu_baseline": cb,
-                      "reference_kind": "cpu oracle port (reference CUDA build not present)",
-                      "e2e": {"value": round(v, 4), "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+    return {"impl": "reference", "metric": "Msamples/s (whole frames: transform + BVH build + render + resolve)",
+            "value": round(v, 4), "unit": "Msamples/s", "n_gpus": 1, "steps": steps, "warmup": warmup,
+            "ms_per_step": round(1e3 * W * H * spp / (v * 1e6), 1), "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg, "cpu_baseline": cb,
+            "reference_kind": "cpu oracle port (reference CUDA build not present)",
+            "e2e": {"value": round(v, 4), "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
 
 
 def _world_vertices_numpy(scene):
@@ -734,8 +800,7 @@ def run_reference_soup(args):
     from tinypathtracer_b200.scene_io import load_scene_npz
     exe = ROOT / "oracle" / "_ref" / "tpt_ref_headless"
     if not exe.exists():
-        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/tpt_ref_headless is not built (needs /root/reference at build time)"}))
-        return
+        return {"impl": "reference", "unavailable": "oracle/_ref/tpt_ref_headless is not built (needs /root/reference at build time)"}
     nb, nx = (8192, 3211) if not args.soup_small else (64, 25)
     scene = make_soup(load_scene_npz(ROOT / "tests" / "golden" / "scenes" / "ball.npz"), nb, nx)
     F = scene["indices"].size // 3
@@ -747,8 +812,7 @@ def run_reference_soup(args):
     cells = (_reference_morton_cells(ctr[:, 0]) | (_reference_morton_cells(ctr[:, 1]) << 21) | (_reference_morton_cells(ctr[:, 2]) << 42))
     _, counts = np.unique(cells, return_counts=True)
     if counts.max() >= 3:
-        print(json.dumps({"impl": "reference", "unavailable": f"soup has a run of {int(counts.max())} equal reference Morton keys: its builder would hang"}))
-        return
+        return {"impl": "reference", "unavailable": f"soup has a run of {int(counts.max())} equal reference Morton keys: its builder would hang"}
     rays = orc.primary_rays(scene, W, H).astype(np.float32).reshape(-1, 6)
     tmp = Path(tempfile.mkdtemp(prefix="tpt_soup_"))
 
@@ -775,15 +839,14 @@ def run_reference_soup(args):
         write(tmp / "b.bin", sec)
         d = run(tmp / "b.bin", None, max(1, min(args.steps, 3)), max(1, min(args.steps, 3)))
     except Exception as e:
-        print(json.dumps({"impl": "reference", "unavailable": f"reference soup run failed: {e}"}))
-        return
+        return {"impl": "reference", "unavailable": f"reference soup run failed: {e}"}
     finally:
         import shutil
         shutil.rmtree(tmp, ignore_errors=True)
     n, ns = d["primary_rays"], d["secondary_rays"]
     ms = d["primary_ms"] + d["secondary_ms"]
     v = (n + ns) / (ms * 1e-3) / 1e6
-    print(json.dumps({"impl": "reference", "metric": "Mrays/s (tpt_trace_rays, primary + secondary ray sets; BVH build ms beside it)", "value": round(v, 3),
+    return ({"impl": "reference", "metric": "Mrays/s (tpt_trace_rays, primary + secondary ray sets; BVH build ms beside it)", "value": round(v, 3),
                       "unit": "Mrays/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms, 3), "higher_is_better": True,
                       "scaling": "replicas only", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                       "config": {"workload": f"synthetic soup {F} triangles, {W}x{H} pixel-centre primary rays + {ns} cosine secondary rays"},
@@ -791,34 +854,47 @@ def run_reference_soup(args):
                       "secondary_mrays_per_s": round(ns / d["secondary_ms"] / 1e3, 3), "primary_hit_fraction": round(float((hs["prim"] >= 0).mean()), 4),
                       "reference_kind": f"reference BVH::construct + traverseBVH, headless, {d['build']}, on GPU 0",
                       "cpu_baseline": {"value": round(v, 3), "unit": "Mrays/s", "cores": 0, "kind": "reference", "sample": "whole workload on the GPU (the reference has no CPU path)"},
-                      "e2e": {"value": round(v, 3), "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+                      "e2e": {"value": round(v, 3), "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
 
 
-def run_reference_cuda(args, exe, ref_scene, W, H, spp, depth, envkind, cfg):
+def run_reference_cuda(args, exe, ref_scene, W, H, spp, depth, envkind, cfg, steps, warmup):
     """Runs the headless build of the reference's own CUDA sources; it prints one JSON object with frame times."""
     # the reference cannot run without an env texture (uninitialised handle, SURVEY §3.3): black env = a black PNG
     env_png = ROOT / "oracle" / "_ref" / ("sky.png" if envkind == "sky" else "black.png")
     if depth == 32:
         exe = exe.with_name("tpt_ref_headless_d32")     # DEPTH_TRACE is a compile-time constant of the reference
-    cmd = [str(exe), "--scene", str(ref_scene), "--width", str(W), "--height", str(H), "--spp", str(spp), "--depth", str(depth),
-           "--frames", str(args.steps), "--warmup", str(args.warmup)]
+    base = ["--scene", str(ref_scene), "--width", str(W), "--height", str(H), "--spp", str(spp), "--depth", str(depth)]
     if env_png.exists():
-        cmd += ["--env", str(env_png)]
+        base += ["--env", str(env_png)]
     try:
-        r = subprocess.run(cmd, capture_output=True, text=True, timeout=args.ref_timeout)
+        r = subprocess.run([str(exe), *base, "--frames", str(steps), "--warmup", str(warmup)], capture_output=True, text=True, timeout=args.ref_timeout)
         data = json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1])
     except Exception as e:   # the binary is a build of foreign code: fall back to the port, loudly
         sys.stderr.write(f"reference CUDA build failed to run ({e}); falling back to the CPU oracle port\n")
         return None
     ms = float(data["ms_per_frame"])
     v = W * H * spp / (ms * 1e-3) / 1e6
-    return {"impl": "reference", "metric": "Msamples/s (whole frames: transform + BVH build + render + resolve)", "value": round(v, 3),
-            "unit": "Msamples/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms, 3),
-            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
-            "reference_kind": f"reference CUDA sources, headless, -O3 sm_100 ({data.get('build', '')}) on GPU 0; depth is compile-time {data.get('depth')}",
-            "cpu_baseline": {"value": round(v, 3), "unit": "Msamples/s", "cores": 0, "kind": "reference",
-                             "sample": "whole workload on the GPU (the reference has no CPU path)"},
-            "e2e": {"value": round(v, 3), "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    out = {"impl": "reference", "metric": "Msamples/s (whole frames: transform + BVH build + render + resolve)", "value": round(v, 3),
+           "unit": "Msamples/s", "n_gpus": 1, "steps": steps, "warmup": warmup, "ms_per_step": round(ms, 3),
+           "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
+           "reference_kind": f"reference CUDA sources, headless, -O3 sm_100 ({data.get('build', '')}) on GPU 0; depth is compile-time {data.get('depth')}",
+           "cpu_baseline": {"value": round(v, 3), "unit": "Msamples/s", "cores": 0, "kind": "reference",
+                            "sample": "whole workload on the GPU (the reference has no CPU path)"},
+           "e2e": {"value": round(v, 3), "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    # rays per sample from the COUNTING build of the same sources (one atomicAdd per traverseBVH call; one untimed frame), so that
+    # north_star's Mrays/s wording can be answered: Mrays/s = rays per sample x Msamples/s of the timed (uncounted) build
+    cexe = exe.with_name("tpt_ref_headless_count_d32" if depth == 32 else "tpt_ref_headless_count")
+    if cexe.exists():
+        try:
+            r = subprocess.run([str(cexe), *base, "--frames", "1", "--warmup", "0"], capture_output=True, text=True, timeout=args.ref_timeout)
+            c = json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1])
+            rps = float(c["rays_all_frames"]) / (W * H * spp)
+            out["rays_per_sample"] = round(rps, 4)
+            out["mrays_per_s"] = round(rps * v, 2)
+            out["rays_note"] = "traverseBVH calls per camera sample counted by oracle/_ref/" + cexe.name + " (one frame); mrays_per_s = rays_per_sample x value"
+        except Exception as e:
+            out["rays_note"] = f"counting build failed: {e}"
+    return out
 
 
 def _json_only_stdout():
@@ -842,6 +918,7 @@ def main():
     ap.add_argument("--soup-small", action="store_true", help="soup workload at 1/128 size (smoke test)")
     ap.add_argument("--spp", type=int, default=0, help="override the workload's spp (multiple of 8)")
     ap.add_argument("--paths-in-flight", type=int, default=0)
+    ap.add_argument("--frames-in-flight", type=int, default=2, help="independent frames kept in flight (each on its own stream, scene, pools and accumulator)")
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-also", action="store_true", help="skip the other BASELINE configs (box, tir, light, NEE, soup) after the headline")

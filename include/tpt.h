@@ -202,6 +202,15 @@ int tpt_scene_set_transforms(tpt_scene* scene, const float* vert_trans, const fl
  * (src/bvh.cu:304-331, called :541-542): object->world vertices/normals, Morton keys, radix sort,
  * hierarchy, refit.  Asynchronous when stats == NULL. */
 int tpt_bvh_build(tpt_scene* scene, tpt_bvh_stats* stats);
+/* BVH::construct(thrust::device_vector<Vec3>& vertices, thrust::device_vector<uint32_t>& indices) of the reference
+ * (include/bvh.cuh:60-68, src/bvh.cu:304-331) for callers that own WORLD-SPACE geometry on the device, as its PathTracer does
+ * (m_wVertices, src/path_tracer.cu:515-542): d_world_vertices = n_vertices x 3 floats, d_indices = 3 x n_faces uint32, both
+ * DEVICE pointers.  *scene == NULL: a scene of that size is created first (one object, identity transform, one default
+ * material, no normals: it can be built, traced and exported; rendering it shades with zero normals) and returned; otherwise
+ * the scene must come from an earlier call with the same sizes.  The arrays are copied (device to device) and the tree is
+ * built like tpt_bvh_build.  Asynchronous when stats == NULL. */
+int tpt_bvh_build_from_world(tpt_context* ctx, const float* d_world_vertices, size_t n_vertices, const uint32_t* d_indices, size_t n_faces,
+                             tpt_scene** scene, tpt_bvh_stats* stats);
 /* After tpt_scene_set_transforms on an unchanged mesh: keep the hierarchy of the last tpt_bvh_build (leaf order, children,
  * parents) and redo only what depends on the matrices — object->world transform, triangle/normal records, bottom-up boxes.
  * The reference has no such call (it rebuilds per frame, src/path_tracer.cu:540-542).  Hits are those of a
@@ -288,6 +297,13 @@ int tpt_resolve_bgra8(tpt_accum* acc, int spp_total, uint8_t* fb, int device_ptr
 /* One-call form of PathTracer::doTrace (src/path_tracer.cu:491-554): transform + BVH build + clear +
  * render + resolve into a HOST framebuffer.  Synchronous. */
 int tpt_do_trace(tpt_scene* scene, const tpt_camera* cam, const tpt_render_config* cfg, tpt_accum* acc, uint8_t* host_fb);
+
+/* PathTracer::doTrace as the reference's displayer calls it (include/path_tracer.h:34; src/vkEngine.cu:244 hands it a DEVICE
+ * pointer to W*H*4 bytes): like tpt_do_trace with the framebuffer on the device; asynchronous on the context stream. */
+int tpt_do_trace_device(tpt_scene* scene, const tpt_camera* cam, const tpt_render_config* cfg, tpt_accum* acc, uint8_t* device_fb);
+/* 1 if p is device (or managed) memory, 0 if it is host memory: lets a host layer without CUDA headers accept either kind of
+ * framebuffer behind one signature, as the reference's doTrace does. */
+int tpt_pointer_is_device(const void* p);
 
 #ifdef __cplusplus
 }

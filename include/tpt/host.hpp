@@ -103,6 +103,9 @@ public:
     tpt_context* handle() const { return m_ctx; }
     void synchronize();
     tpt_counters counters();
+    // The reference has no context: device 0 and the default stream are implicit (src/path_tracer.cu:491-554).  Its signatures
+    // without a context argument (Scene::copySceneToDevice(), EnvLight(file), BVH(nFaces)) use this process-wide one on device 0.
+    static Context& defaultContext();
 
 private:
     explicit Context(tpt_context* adopted) : m_ctx(adopted) {}
@@ -136,6 +139,7 @@ public:
     Scene(const std::string& filename, const std::string& type);
     DeviceScene flatten() const;                                   // host part of copySceneToDevice (src/mesh.cu:309-397)
     DeviceScene copySceneToDevice(Context& ctx) const;             // + tpt_scene_create
+    DeviceScene copySceneToDevice() const { return copySceneToDevice(Context::defaultContext()); }   // the reference's signature (include/mesh.cuh:103)
     Camera m_camera;
     const std::vector<Mesh>& meshes() const { return m_meshes; }
     const std::map<std::string, Material>& materials() const { return m_materials; }
@@ -157,6 +161,19 @@ struct BVHNode36 {   // include/bvh.cuh:34-58, the reference's 36-byte node (str
 class BVH {
 public:
     explicit BVH(DeviceScene& scene) : m_scene(scene.handle) {}
+    // The reference's own form (include/bvh.cuh:60-68): BVH bvh(nFaces); bvh.construct(m_wVertices, d_scene.indices) with
+    // WORLD-SPACE vertices and indices in thrust::device_vectors (src/path_tracer.cu:541-542).  Any pair of containers whose
+    // data() yields device pointers works (thrust::raw_pointer_cast is found by argument-dependent lookup; this header needs no
+    // thrust); elements: 12-byte vertices, uint32 indices.
+    explicit BVH(size_t nFaces) : m_nFaces(nFaces) {}
+    template <class DeviceVertices, class DeviceIndices>
+    void construct(DeviceVertices& vertices, DeviceIndices& indices) {
+        static_assert(sizeof(*raw_pointer_cast(vertices.data())) == 12 && sizeof(*raw_pointer_cast(indices.data())) == 4, "Vec3 / uint32_t elements");
+        constructFromWorld(reinterpret_cast<const float*>(raw_pointer_cast(vertices.data())), vertices.size(),
+                           reinterpret_cast<const uint32_t*>(raw_pointer_cast(indices.data())), indices.size() / 3);
+    }
+    void constructFromWorld(const float* deviceWorldVertices, size_t nVertices, const uint32_t* deviceIndices, size_t nFaces,
+                            Context& ctx = Context::defaultContext());   // tpt_bvh_build_from_world
     void construct();                       // `transform` kernel + BVH::construct of the reference
     tpt_bvh_stats constructWithStats();
     void refit();                           // after new object matrices on the same mesh: keeps the hierarchy
@@ -166,6 +183,7 @@ public:
 
 private:
     std::shared_ptr<tpt_scene> m_scene;
+    size_t m_nFaces = 0;
 };
 
 // 8-bit image, top-down rows, 3 or 4 channels (include/picture.h loads through FreeImage; here: PNG, baseline JPEG, binary PPM).
@@ -191,6 +209,7 @@ void writePFM(const std::string& filename, const float* rgbTopDown, int width, i
 class EnvLight {
 public:
     EnvLight(Context& ctx, const std::string& file);   // "" -> black environment (the reference: uninitialised texture)
+    explicit EnvLight(const std::string& file) : EnvLight(Context::defaultContext(), file) {}   // the reference's signature (include/env_light.cuh:12)
 };
 
 class PathTracer {
@@ -198,7 +217,10 @@ public:
     PathTracer();
     explicit PathTracer(const std::string& envLightFile);
     void render(const std::string& meshFile);   // load, upload, m_frames x doTrace, PNG of the last frame if m_output is set
-    void doTrace(DeviceScene& scene, Camera& camera, unsigned char* framebuffer /*host BGRA8*/, int nSamplesPerPixel);
+    // framebuffer: W*H*4 bytes, B,G,R,(A untouched), row 0 = top — a DEVICE pointer as the reference's displayer passes it
+    // (include/path_tracer.h:34, src/vkEngine.cu:244; the call is then asynchronous like the reference's copyToFB launch) or a host
+    // pointer (filled on return); told apart at run time (tpt_pointer_is_device)
+    void doTrace(DeviceScene& scene, Camera& camera, unsigned char* framebuffer, int nSamplesPerPixel);
 
     // run-time forms of the reference's compile-time constants (include/vkEngine.h:24, src/path_tracer.cu:17,559,493)
     int m_width = 1920, m_height = 1080;

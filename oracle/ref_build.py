@@ -50,6 +50,12 @@ def patch_sources():
     src = src.replace(a, "#ifndef TPT_REF_DEPTH\n#define TPT_REF_DEPTH 8\n#endif\n\tconstexpr int DEPTH_TRACE = TPT_REF_DEPTH;")
     src = src.replace(b, "int nSamplesPerPixel = tpt_ref_spp();")
     src = "int tpt_ref_spp();\n" + src
+    # counting build: one atomicAdd per traverseBVH call in the DEVICE compilation of the generated copy, compiled in
+    # only with -DTPT_REF_COUNT_RAYS (tpt_ref_headless_count); the timed builds are untouched
+    c = "\tint call_stack[64];\n\tint stackPtr = 1;"
+    assert src.count(c) == 1, "reference source changed: traverseBVH patch point not found"
+    src = src.replace(c, "#if defined(TPT_REF_COUNT_RAYS) && defined(__CUDA_ARCH__)\n\tatomicAdd(&g_tpt_ref_rays, 1ull);\n#endif\n" + c)
+    src = "#ifdef TPT_REF_COUNT_RAYS\n__device__ unsigned long long g_tpt_ref_rays;\n#endif\n" + src
     (p / "path_tracer.cu").write_text(src)
 
 
@@ -125,7 +131,9 @@ def main():
     only = set(sys.argv[1:])
     targets = [("libref_host.so", None), ("tpt_ref_headless", (["-O3", "-arch=sm_100"], 8, "-O3 -arch=sm_100")),
                ("tpt_ref_headless_d32", (["-O3", "-arch=sm_100"], 32, "-O3 -arch=sm_100 DEPTH_TRACE=32")),
-               ("tpt_ref_headless_G", (["-G", "-arch=sm_100"], 8, "-G -arch=sm_100 (as shipped, CMakeLists.txt:59)"))]
+               ("tpt_ref_headless_G", (["-G", "-arch=sm_100"], 8, "-G -arch=sm_100 (as shipped, CMakeLists.txt:59)")),
+               ("tpt_ref_headless_count", (["-O3", "-arch=sm_100", "-DTPT_REF_COUNT_RAYS"], 8, "-O3 -arch=sm_100 + one atomicAdd per traverseBVH call (ray counting; not timed)")),
+               ("tpt_ref_headless_count_d32", (["-O3", "-arch=sm_100", "-DTPT_REF_COUNT_RAYS"], 32, "-O3 -arch=sm_100 DEPTH_TRACE=32 + ray counting (not timed)"))]
     for name, spec in targets:
         if only and name not in only:
             continue
@@ -139,7 +147,7 @@ def main():
             built[name] = f"FAILED: {e}"
         print(name, built[name])
     (OUT / "BUILD.json").write_text(json.dumps({"built": built, "edits": ["DEPTH_TRACE -> -DTPT_REF_DEPTH", "nSamplesPerPixel -> --spp",
-                                                                           "window extent via VkExtent2D stand-in",
+                                                                           "window extent via VkExtent2D stand-in", "count builds only: one atomicAdd per traverseBVH call (-DTPT_REF_COUNT_RAYS)",
                                                                            "ball.gltf/square.gltf: default material injected"]}, indent=1))
     return 0
 

@@ -164,9 +164,13 @@ int main(int argc, char** argv) {
     if (g_ms.empty()) return 1;
     std::vector<double> s = g_ms;
     std::sort(s.begin(), s.end());
-    printf("{\"ms_per_frame\": %.4f, \"ms_median\": %.4f, \"frames\": %d, \"warmup\": %d, \"width\": %u, \"height\": %u, \"spp\": %d, \"depth\": %d, \"build\": \"%s\"}\n",
+    unsigned long long rays = 0;   // counting build only: traverseBVH calls of ALL frames run (warm-up included)
+#ifdef TPT_REF_COUNT_RAYS
+    cudaMemcpyFromSymbol(&rays, g_tpt_ref_rays, sizeof rays);
+#endif
+    printf("{\"ms_per_frame\": %.4f, \"ms_median\": %.4f, \"frames\": %d, \"warmup\": %d, \"width\": %u, \"height\": %u, \"spp\": %d, \"depth\": %d, \"rays_all_frames\": %llu, \"build\": \"%s\"}\n",
            g_ms_sum / g_ms.size(), s[s.size() / 2], (int)g_ms.size(), g_warmup, g_tpt_ref_width ? g_tpt_ref_width : 1920u,
-           g_tpt_ref_height ? g_tpt_ref_height : 1080u, g_tpt_ref_spp, DEPTH_TRACE, TPT_REF_BUILD);
+           g_tpt_ref_height ? g_tpt_ref_height : 1080u, g_tpt_ref_spp, DEPTH_TRACE, rays, TPT_REF_BUILD);
     return 0;
 }
 #endif

@@ -458,8 +458,8 @@ def test_live_pixel_batches_change_nothing(tpt, ctx, built, scenes):
     pt.render_into(ds, cam, spp=spp, max_depth=32, seed=3, paths_in_flight=W * H * 32)
     four = ctx.counters()["kernel_launches"] - n0
     assert (pt.m_radiance.to_i64() == a).all() and a.any()
-    # k_tile_live + k_primary + k_wave (wave 1) + k_wave_loop (waves 2..32, one cooperative launch) against 4 x 3
-    assert one <= 5 and four >= 4 * 3
+    # k_tile_live + k_primary + 32 waves against 4 x (k_primary + 32 waves)   (TPT_WAVE_LOOP=1: 4 against 12)
+    assert one <= 35 and four >= 3 * one
     # another camera (closer: more live pixels) must not reuse the first camera's table
     sc = scenes["tir"]
     c2w = np.array(sc["c2w"], np.float32).reshape(16).copy()

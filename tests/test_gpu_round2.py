@@ -2,7 +2,8 @@
 in front of the per-pixel candidate lists (tile_collect) and tpt_scene_update.  The first two are pure re-schedulings of the
 same integer-accumulated terms, so the bar is bit-identical accumulation buffers against the per-level / per-pixel forms
 (switched back on with the tuning variables TPT_NO_WAVE_LOOP / TPT_NO_TILE_WALK, which the library reads once per process —
-hence the subprocesses)."""
+hence the subprocesses).  k_wave_loop and path_tail are opt-in (TPT_WAVE_LOOP, TPT_PATH_TAIL_MAX): measured, they do not pay
+(DESIGN.md §7), but they stay correct."""
 import hashlib
 import os
 import subprocess
@@ -52,10 +53,12 @@ def _run(extra_env):
 
 
 def test_wave_loop_and_tile_walk_keep_every_accumulator_bit():
-    new = _run({})
-    old = _run({"TPT_NO_WAVE_LOOP": "1", "TPT_NO_TILE_WALK": "1"})
-    assert new == old
-    assert _run({"TPT_NO_WAVE_LOOP": "1"}) == new and _run({"TPT_NO_TILE_WALK": "1"}) == new
+    base = _run({})                                   # one launch per wave, tile walk on
+    assert _run({"TPT_NO_TILE_WALK": "1"}) == base
+    loop = _run({"TPT_WAVE_LOOP": "1"})               # waves 2.. in one cooperative launch
+    assert loop == base
+    # ... with the path-by-path finish of small levels (path_tail) forced for every level after wave 1
+    assert _run({"TPT_WAVE_LOOP": "1", "TPT_PATH_TAIL_MAX": "4000000000"}) == base
 
 
 def test_scene_update_equals_a_new_scene(tpt, ctx, scenes, orc):
@@ -158,3 +161,57 @@ def test_wide_and_binary_walks_agree(capsys):
     assert wide["soup"][3] < 0.7 * binary["soup"][3]
     with capsys.disabled():
         print("\n[wide vs binary] " + "; ".join(lines))
+
+
+def test_lazy_normal_records_of_large_scenes(tpt, ctx, scenes, orc):
+    """Scenes of 65 536 triangles and more leave the per-leaf shading-normal records out of the build (k_leaf_normals writes them
+    when a render first needs them): the image must be the oracle's, the first and a later render of the same build identical,
+    and a rebuild + render identical again."""
+    from tinypathtracer_b200.soup import make_soup
+    scene = make_soup(scenes["ball"], 64, 25)            # 78 124 triangles
+    c2w = np.eye(4, dtype=np.float32)
+    c2w[2, 3] = 130.0
+    scene["c2w"] = np.ascontiguousarray(c2w.T).reshape(16)
+    ds = tpt.DeviceScene(ctx, scene)
+    bvh = tpt.BVH(ds)
+    bvh.construct()
+    cam = tpt.Camera.from_scene(scene)
+    W, H, spp = 64, 36, 8
+    from conftest import synthetic_sky
+    env = synthetic_sky(256, 128)
+    pt = tpt.PathTracer(ctx, W, H, env_rgba8=env)
+    imgs = []
+    for rebuild in (False, False, True):
+        if rebuild:
+            bvh.construct()
+        pt.m_radiance.clear()
+        pt.render_into(ds, cam, spp=spp, max_depth=4, seed=9)
+        imgs.append(pt.m_radiance.to_i64())
+    assert (imgs[0] == imgs[1]).all() and (imgs[0] == imgs[2]).all() and imgs[0].any()
+    img = pt.m_radiance.to_f32() / spp
+    oimg = orc.render(scene, W, H, spp, max_depth=4, seed=9, env=env) / spp
+    relmse = float(((img - oimg) ** 2).sum() / (oimg ** 2).sum())
+    assert relmse < 1e-3, relmse          # same RNG: per-sample agreement up to rounding-flipped decisions
+    ds.close()
+
+
+def test_eight_contexts_share_one_gpu(tpt, scenes):
+    """The wavefront queue pools are sized from what the device can spare (min(40 GiB, 60 % of free memory) per context, looked up at
+    the context's first render), not from a constant: eight contexts on ONE GPU each render a frame whose worst case wants the full
+    budget (box.gltf at 1920 x 1080: every pixel live) — the later ones get smaller batches, nothing fails, and every context
+    produces the same accumulator bits."""
+    import hashlib
+    scene = scenes["box"]
+    ctxs = [tpt.Context(0) for _ in range(8)]
+    shas, keep = [], []
+    for c in ctxs:
+        ds = tpt.DeviceScene(c, scene)
+        tpt.BVH(ds).construct(stats=False)
+        pt = tpt.PathTracer(c, 1920, 1080)
+        pt.render_into(ds, tpt.Camera.from_scene(scene), spp=96, max_depth=8, seed=21)
+        shas.append(hashlib.sha256(pt.m_radiance.to_i64().tobytes()).hexdigest())
+        assert c.counters()["queue_overflow"] == 0
+        keep.append((ds, pt))          # pools stay allocated while the next context sizes its own
+    assert len(set(shas)) == 1
+    for c in ctxs:
+        c.close()

@@ -89,6 +89,9 @@ SIGNATURES = {
     "tpt_scene_set_transforms": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "tpt_bvh_build": (C.c_int, [C.c_void_p, C.POINTER(BvhStats)]),
     "tpt_bvh_refit": (C.c_int, [C.c_void_p, C.POINTER(BvhStats)]),
+    "tpt_bvh_build_from_world": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p), C.POINTER(BvhStats)]),
+    "tpt_do_trace_device": (C.c_int, [C.c_void_p, C.POINTER(Camera), C.POINTER(RenderConfig), C.c_void_p, C.c_void_p]),
+    "tpt_pointer_is_device": (C.c_int, [C.c_void_p]),
     "tpt_bvh_export_reference_nodes": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
     "tpt_bvh_export_order": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "tpt_scene_export_world": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),

@@ -159,12 +159,14 @@ __global__ void __launch_bounds__(kRefitBlock) k_leaves_refit(const uint32_t* __
     __stcs(triGeom + 3 * (size_t)leaf + 0, make_float4(a.x, a.y, a.z, e1.x));
     __stcs(triGeom + 3 * (size_t)leaf + 1, make_float4(e1.y, e1.z, e2.x, e2.y));
     __stcs(triGeom + 3 * (size_t)leaf + 2, make_float4(e2.z, __int_as_float((int)f), __int_as_float((int)faceMtl[f]), 0.f));
-    const float3 n0 = f3(worldNorms[3 * i0], worldNorms[3 * i0 + 1], worldNorms[3 * i0 + 2]);
-    const float3 n1 = f3(worldNorms[3 * i1], worldNorms[3 * i1 + 1], worldNorms[3 * i1 + 2]);
-    const float3 n2 = f3(worldNorms[3 * i2], worldNorms[3 * i2 + 1], worldNorms[3 * i2 + 2]);
-    __stcs(triNorm + 3 * (size_t)leaf + 0, make_float4(n0.x, n0.y, n0.z, n1.x));
-    __stcs(triNorm + 3 * (size_t)leaf + 1, make_float4(n1.y, n1.z, n2.x, n2.y));
-    __stcs(triNorm + 3 * (size_t)leaf + 2, make_float4(n2.z, 0.f, 0.f, 0.f));
+    if (triNorm != nullptr) {   // small scenes: with the leaf; large ones: k_leaf_normals, when a render first needs them
+        const float3 n0 = f3(worldNorms[3 * i0], worldNorms[3 * i0 + 1], worldNorms[3 * i0 + 2]);
+        const float3 n1 = f3(worldNorms[3 * i1], worldNorms[3 * i1 + 1], worldNorms[3 * i1 + 2]);
+        const float3 n2 = f3(worldNorms[3 * i2], worldNorms[3 * i2 + 1], worldNorms[3 * i2 + 2]);
+        __stcs(triNorm + 3 * (size_t)leaf + 0, make_float4(n0.x, n0.y, n0.z, n1.x));
+        __stcs(triNorm + 3 * (size_t)leaf + 1, make_float4(n1.y, n1.z, n2.x, n2.y));
+        __stcs(triNorm + 3 * (size_t)leaf + 2, make_float4(n2.z, 0.f, 0.f, 0.f));
+    }
     if (nFaces == 1) return;
 
     float3 mn = fmin3(fmin3(a, b), c), mx = fmax3(fmax3(a, b), c);
@@ -196,6 +198,22 @@ __global__ void __launch_bounds__(kRefitBlock) k_leaves_refit(const uint32_t* __
             return;
         }
     }
+}
+
+// The per-leaf shading-normal records (read only by the renderer's shade step, never by traversal), for scenes whose build
+// left them out: a 10 M-triangle build that is only traced (tpt_trace_rays) does not pay 36 B of gathers + 48 B of writes per leaf.
+__global__ void __launch_bounds__(256) k_leaf_normals(const uint32_t* __restrict__ sortedFaces, const uint32_t* __restrict__ indices,
+                                                      const float* __restrict__ worldNorms, int nFaces, float4* __restrict__ triNorm) {
+    const int leaf = blockIdx.x * blockDim.x + threadIdx.x;
+    if (leaf >= nFaces) return;
+    const uint32_t f = sortedFaces[leaf];
+    const uint32_t i0 = indices[3 * f], i1 = indices[3 * f + 1], i2 = indices[3 * f + 2];
+    const float3 n0 = f3(worldNorms[3 * i0], worldNorms[3 * i0 + 1], worldNorms[3 * i0 + 2]);
+    const float3 n1 = f3(worldNorms[3 * i1], worldNorms[3 * i1 + 1], worldNorms[3 * i1 + 2]);
+    const float3 n2 = f3(worldNorms[3 * i2], worldNorms[3 * i2 + 1], worldNorms[3 * i2 + 2]);
+    __stcs(triNorm + 3 * (size_t)leaf + 0, make_float4(n0.x, n0.y, n0.z, n1.x));
+    __stcs(triNorm + 3 * (size_t)leaf + 1, make_float4(n1.y, n1.z, n2.x, n2.y));
+    __stcs(triNorm + 3 * (size_t)leaf + 2, make_float4(n2.z, 0.f, 0.f, 0.f));
 }
 
 __global__ void __launch_bounds__(256) k_refit_upper(const int* __restrict__ frontier, const uint32_t* __restrict__ frontierCount,
@@ -420,6 +438,7 @@ __global__ void k_bvh_stats(const float4* __restrict__ nodes, const int* __restr
 
 using namespace tpt;
 
+constexpr size_t kLazyNormalFaces = (size_t)1 << 16;
 static std::atomic<uint64_t> g_geom_epoch{0};   // one counter for all scenes and contexts
 static inline unsigned grid_for(size_t n, int block) { return (unsigned)((n + block - 1) / block); }
 
@@ -439,16 +458,20 @@ int tpt_bvh_build_impl(tpt_scene* s) {
     const int F = (int)s->n_faces;
     const uint32_t V = (uint32_t)s->n_vertices;
     const int persistent = kNumSMs * 8;
+    const bool lazyNormals = s->n_faces >= kLazyNormalFaces;   // large scenes: normal records on first render (tpt_scene_ensure_normals)
 
     k_init_bounds<<<1, 32, 0, st>>>(s->bounds);
     k_transform<<<min(persistent, (int)grid_for(V, 256)), 256, 0, st>>>(s->obj_verts, s->obj_norms, s->vert_obj, s->vert_trans,
                                                                          s->normal_trans, V, s->world_verts, s->world_norms, s->bounds);
     // 63-bit keys like the reference (21 bits per axis); from 2^20 triangles on, 16 bits per axis (65 536^3 cells is still far
     // finer than the triangles, equal keys are ordered by index) so that the radix sort runs 6 passes instead of 8
-    const int bitsPerAxis = F >= (1 << 20) ? 16 : 21;
+    // 63-bit keys like the reference (21 bits per axis); from 2^20 triangles on, 13 bits per axis (8 192^3 cells: at 10 M triangles still
+    // ~50 000 cells per triangle; equal keys are ordered by index) so that the radix sort runs 5 passes instead of 8
+    const int bitsPerAxis = F >= (1 << 20) ? 13 : 21;
     const int keyBits = 3 * bitsPerAxis;
     // Sorted (key, face) pairs must end in keys[1] / vals[1]; keys[0] / vals[0] are scratch afterwards.
-    const int nPasses = (keyBits + 7) / 8;   // 6 or 8: even, so the ping-pong that starts in buffer 1 ends in buffer 1
+    const int nPasses = (keyBits + 7) / 8;   // 5 or 8
+    const int first = (nPasses & 1) ? 0 : 1; // the ping-pong starts in the buffer that makes it END in buffer 1
     if (F <= kSortTile) {
         k_sort_small<<<1, kSortThreads, 0, st>>>(s->indices, s->world_verts, s->bounds, (uint32_t)F, bitsPerAxis, nPasses, s->keys[1], s->vals[1]);
     } else {
@@ -468,10 +491,10 @@ int tpt_bvh_build_impl(tpt_scene* s) {
         uint32_t* status = ticket + ticketBytes / sizeof(uint32_t);
         TPT_CUDA(cudaMemsetAsync(s->sort_tmp, 0, need, st));
         k_morton_hist<<<min(persistent, (int)grid_for(F, 256)), 256, 0, st>>>(s->indices, s->world_verts, s->bounds, (uint32_t)F, bitsPerAxis, nPasses,
-                                                                                s->keys[1], s->vals[1], hist);
+                                                                                s->keys[first], s->vals[first], hist);
         const unsigned grid = (unsigned)std::min<uint32_t>(nTiles, (uint32_t)(kNumSMs * 4));
         for (int p = 0; p < nPasses; ++p) {
-            const int in = (p & 1) ? 0 : 1, out = in ^ 1;
+            const int in = first ^ (p & 1), out = in ^ 1;
             k_onesweep<<<grid, kSortThreads, 0, st>>>(s->keys[in], s->vals[in], s->keys[out], s->vals[out], (uint32_t)F, 8 * p, hist + p * 256,
                                                       status + (size_t)p * nTiles * 256, ticket + p, nTiles);
         }
@@ -486,7 +509,7 @@ int tpt_bvh_build_impl(tpt_scene* s) {
     int* frontier = reinterpret_cast<int*>(s->keys[0]);
     k_leaves_refit<<<grid_for(F, kRefitBlock), kRefitBlock, 0, st>>>(s->vals[1], s->indices, s->world_verts, s->world_norms, s->face_mtl, F,
                                                                      s->parent_int, s->parent_leaf, reinterpret_cast<const int*>(s->vals[0]),
-                                                                     s->flags, s->nodes, s->tri_geom, s->tri_norm, frontier, s->bounds + 6);
+                                                                     s->flags, s->nodes, s->tri_geom, lazyNormals ? nullptr : s->tri_norm, frontier, s->bounds + 6);
     if (F > 1) k_refit_upper<<<grid_for((size_t)F / 2 + 1, 256), 256, 0, st>>>(frontier, s->bounds + 6, s->parent_int, s->flags, s->nodes);
     if (F > 1 && s->nodes4) {
         k_collapse4<<<grid_for((size_t)F - 1, 256), 256, 0, st>>>(s->nodes, F - 1, s->nodes4);
@@ -496,6 +519,7 @@ int tpt_bvh_build_impl(tpt_scene* s) {
     ctx->kernel_launches += 5 + (F <= kSortTile ? 1 : 1 + nPasses);
     s->built = true;
     s->geom_epoch = ++g_geom_epoch;   // unique across scenes: a new scene at a recycled address never matches a cached key
+    if (!lazyNormals) s->norm_epoch = s->geom_epoch;
     s->topology = true;
     return TPT_OK;
 }
@@ -511,6 +535,7 @@ int tpt_bvh_refit_impl(tpt_scene* s) {
     const int F = (int)s->n_faces;
     const uint32_t V = (uint32_t)s->n_vertices;
     const int persistent = kNumSMs * 8;
+    const bool lazyNormals = s->n_faces >= kLazyNormalFaces;   // large scenes: normal records on first render (tpt_scene_ensure_normals)
     k_init_bounds<<<1, 32, 0, st>>>(s->bounds);
     k_transform<<<min(persistent, (int)grid_for(V, 256)), 256, 0, st>>>(s->obj_verts, s->obj_norms, s->vert_obj, s->vert_trans,
                                                                          s->normal_trans, V, s->world_verts, s->world_norms, s->bounds);
@@ -518,7 +543,7 @@ int tpt_bvh_refit_impl(tpt_scene* s) {
     int* frontier = reinterpret_cast<int*>(s->keys[0]);
     k_leaves_refit<<<grid_for(F, kRefitBlock), kRefitBlock, 0, st>>>(s->vals[1], s->indices, s->world_verts, s->world_norms, s->face_mtl, F,
                                                                      s->parent_int, s->parent_leaf, reinterpret_cast<const int*>(s->vals[0]),
-                                                                     s->flags, s->nodes, s->tri_geom, s->tri_norm, frontier, s->bounds + 6);
+                                                                     s->flags, s->nodes, s->tri_geom, lazyNormals ? nullptr : s->tri_norm, frontier, s->bounds + 6);
     if (F > 1) k_refit_upper<<<grid_for((size_t)F / 2 + 1, 256), 256, 0, st>>>(frontier, s->bounds + 6, s->parent_int, s->flags, s->nodes);
     if (F > 1 && s->nodes4) {
         k_collapse4<<<grid_for((size_t)F - 1, 256), 256, 0, st>>>(s->nodes, F - 1, s->nodes4);
@@ -528,6 +553,17 @@ int tpt_bvh_refit_impl(tpt_scene* s) {
     ctx->kernel_launches += 4;
     s->built = true;
     s->geom_epoch = ++g_geom_epoch;   // unique across scenes: a new scene at a recycled address never matches a cached key
+    if (!lazyNormals) s->norm_epoch = s->geom_epoch;
+    return TPT_OK;
+}
+
+int tpt_scene_ensure_normals(tpt_scene* s) {
+    if (s->norm_epoch == s->geom_epoch) return TPT_OK;
+    const int F = (int)s->n_faces;
+    k_leaf_normals<<<grid_for(F, 256), 256, 0, s->ctx->stream>>>(s->vals[1], s->indices, s->world_norms, F, s->tri_norm);
+    TPT_CUDA(cudaGetLastError());
+    s->ctx->kernel_launches += 1;
+    s->norm_epoch = s->geom_epoch;
     return TPT_OK;
 }
 

@@ -280,9 +280,12 @@ int tpt_scene_create(tpt_context* ctx, const tpt_scene_desc* d, tpt_scene** out)
     A(dev_alloc(&s->keys[0], F)); A(dev_alloc(&s->keys[1], F)); A(dev_alloc(&s->vals[0], F)); A(dev_alloc(&s->vals[1], F));
     A(dev_alloc(&s->parent_int, F)); A(dev_alloc(&s->parent_leaf, F)); A(dev_alloc(&s->flags, F)); A(dev_alloc(&s->bounds, 8));
     A(dev_alloc(&s->nodes, 4 * F)); A(dev_alloc(&s->tri_geom, 3 * F)); A(dev_alloc(&s->tri_norm, 3 * F));
-    // 4-wide compressed nodes beside the binary ones (64 B per internal node) for trees too large to be served from L1: the
-    // batch trace entry walks them (traverse.cuh).  TPT_WIDE_MIN_FACES moves the limit (the tests set it to 2).
-    static const size_t wideMinFaces = getenv("TPT_WIDE_MIN_FACES") ? (size_t)atoll(getenv("TPT_WIDE_MIN_FACES")) : (size_t)1 << 16;
+    // 4-wide compressed nodes beside the binary ones (64 B per internal node; traverse.cuh) — OPT-IN: TPT_WIDE_MIN_FACES=<n> builds and
+    // walks them for scenes of n triangles and more (the tests use 2).  Measured on the 10 M-triangle soup they halve the node visits
+    // (72.9 -> 36.7 per incoherent ray) but not the time (1 274 vs 1 279 Mrays/s; coherent primary rays 1 893 vs 2 270): a wide visit
+    // costs ~3.4x the instructions of a binary one and pushes up to three stack entries, so the walk turns from L1-bound to
+    // issue-bound at the same speed, and the collapse adds 0.35 ms to a 10 M build.  Off by default until that is fixed.
+    static const size_t wideMinFaces = getenv("TPT_WIDE_MIN_FACES") ? (size_t)atoll(getenv("TPT_WIDE_MIN_FACES")) : ~(size_t)0;
     if (F >= wideMinFaces && F >= 2) A(dev_alloc(&s->nodes4, 4 * F));
     if (rc == TPT_OK) rc = upload_scene(s, d);
     if (rc == TPT_OK) {
@@ -336,6 +339,45 @@ int tpt_bvh_build(tpt_scene* s, tpt_bvh_stats* stats) {
         TPT_CUDA(cudaEventElapsedTime(&stats->build_ms, ctx->ev0, ctx->ev1));
     }
     return TPT_OK;
+}
+
+int tpt_bvh_build_from_world(tpt_context* ctx, const float* d_verts, size_t n_vertices, const uint32_t* d_indices, size_t n_faces, tpt_scene** scene,
+                             tpt_bvh_stats* stats) {
+    TPT_REQUIRE(ctx && d_verts && d_indices && scene, "tpt_bvh_build_from_world: NULL argument");
+    TPT_REQUIRE(n_vertices > 0 && n_faces > 0 && n_faces < (size_t)1 << 30, "tpt_bvh_build_from_world: bad sizes");
+    TPT_CHECK(bind(ctx));
+    if (*scene == nullptr) {
+        // a one-object scene of the right size: identity matrices (M * v == v exactly), one default material, zero normals
+        std::vector<uint32_t> idx(3 * n_faces, 0u);
+        std::vector<float> zeros(3 * n_vertices, 0.0f);
+        const float ident[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+        tpt_material mtl;
+        std::memset(&mtl, 0, sizeof mtl);
+        mtl.base_color[0] = mtl.base_color[1] = mtl.base_color[2] = 0.8f;
+        const tpt_mtl_interval obj = {0, 0};
+        tpt_scene_desc d;
+        std::memset(&d, 0, sizeof d);
+        d.indices = idx.data();
+        d.n_indices = idx.size();
+        d.vertices = zeros.data();
+        d.normals = zeros.data();
+        d.n_vertices = n_vertices;
+        d.materials = &mtl;
+        d.n_materials = 1;
+        d.objects = &obj;
+        d.n_objects = 1;
+        d.vert_trans = ident;
+        d.normal_trans = ident;
+        TPT_CHECK(tpt_scene_create(ctx, &d, scene));
+    }
+    tpt_scene* s = *scene;
+    TPT_REQUIRE(s->ctx == ctx && s->n_faces == n_faces && s->n_vertices == n_vertices && s->n_objects == 1,
+                "tpt_bvh_build_from_world: the scene was not made by this call for these sizes");
+    TPT_CUDA(cudaMemcpyAsync(s->indices, d_indices, 3 * n_faces * sizeof(uint32_t), cudaMemcpyDeviceToDevice, ctx->stream));
+    TPT_CUDA(cudaMemcpyAsync(s->obj_verts, d_verts, 3 * n_vertices * sizeof(float), cudaMemcpyDeviceToDevice, ctx->stream));
+    TPT_CHECK(tpt_scene_build_tables(s));   // which vertices the new indices reference
+    s->topology = false;
+    return tpt_bvh_build(s, stats);
 }
 
 int tpt_bvh_refit(tpt_scene* s, tpt_bvh_stats* stats) {
@@ -673,6 +715,24 @@ int tpt_do_trace(tpt_scene* s, const tpt_camera* cam, const tpt_render_config* c
     TPT_CHECK(tpt_accum_clear(acc));
     TPT_CHECK(tpt_render(s, cam, cfg, acc));
     return tpt_resolve_bgra8(acc, cfg->spp, host_fb, 0);
+}
+
+int tpt_do_trace_device(tpt_scene* s, const tpt_camera* cam, const tpt_render_config* cfg, tpt_accum* acc, uint8_t* device_fb) {
+    TPT_REQUIRE(s && cam && cfg && acc && device_fb, "tpt_do_trace_device: NULL argument");
+    if ((cfg->flags & TPT_RENDER_REFIT) && s->topology) TPT_CHECK(tpt_bvh_refit(s, nullptr));
+    else TPT_CHECK(tpt_bvh_build(s, nullptr));
+    TPT_CHECK(tpt_accum_clear(acc));
+    TPT_CHECK(tpt_render(s, cam, cfg, acc));
+    return tpt_resolve_bgra8(acc, cfg->spp, device_fb, 1);
+}
+
+int tpt_pointer_is_device(const void* p) {
+    cudaPointerAttributes a;
+    if (p == nullptr || cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return (a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged) ? 1 : 0;
 }
 
 }   // extern "C"

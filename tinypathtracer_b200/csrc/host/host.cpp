@@ -512,6 +512,17 @@ void DeviceScene::uploadTransforms() {
 
 // ---- BVH -------------------------------------------------------------------------------------------------------
 void BVH::construct() { check(tpt_bvh_build(m_scene.get(), nullptr), "tpt_bvh_build"); }
+void BVH::constructFromWorld(const float* dVerts, size_t nVertices, const uint32_t* dIndices, size_t nFaces, Context& ctx) {
+    if (m_nFaces && nFaces != m_nFaces) throw std::runtime_error("BVH::construct: the index array does not hold the face count the BVH was made for");
+    tpt_scene* s = m_scene.get();
+    const bool fresh = s == nullptr;
+    check(tpt_bvh_build_from_world(ctx.handle(), dVerts, nVertices, dIndices, nFaces, &s, nullptr), "tpt_bvh_build_from_world");
+    if (fresh) m_scene = std::shared_ptr<tpt_scene>(s, [](tpt_scene* p) { tpt_scene_destroy(p); });
+}
+Context& Context::defaultContext() {
+    static Context ctx(0);
+    return ctx;
+}
 tpt_bvh_stats BVH::constructWithStats() {
     tpt_bvh_stats st;
     check(tpt_bvh_build(m_scene.get(), &st), "tpt_bvh_build");

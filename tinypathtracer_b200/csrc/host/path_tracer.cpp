@@ -128,15 +128,17 @@ void PathTracer::doTrace(DeviceScene& scene, Camera& camera, unsigned char* fram
     cfg.flags = (m_envNEE ? TPT_RENDER_ENV_NEE : 0u) | (m_roughMetals ? TPT_RENDER_ROUGH_METALS : 0u) | (m_refit ? TPT_RENDER_REFIT : 0u);
     const tpt_camera cam = camera.toABI();
     const auto t0 = std::chrono::steady_clock::now();
+    const int onDevice = tpt_pointer_is_device(framebuffer);
     if (!m_progressive) {
-        check(tpt_do_trace(scene.handle.get(), &cam, &cfg, m_radiance, framebuffer), "tpt_do_trace");
+        if (onDevice) check(tpt_do_trace_device(scene.handle.get(), &cam, &cfg, m_radiance, framebuffer), "tpt_do_trace_device");
+        else check(tpt_do_trace(scene.handle.get(), &cam, &cfg, m_radiance, framebuffer), "tpt_do_trace");
         m_samplesDone = (uint64_t)nSamplesPerPixel;
     } else {
         cfg.sample_offset = (uint32_t)m_samplesDone;
         check(tpt_bvh_build(scene.handle.get(), nullptr), "tpt_bvh_build");
         check(tpt_render(scene.handle.get(), &cam, &cfg, m_radiance), "tpt_render");
         m_samplesDone += (uint64_t)nSamplesPerPixel;
-        check(tpt_resolve_bgra8(m_radiance, (int)m_samplesDone, framebuffer, 0), "tpt_resolve_bgra8");
+        check(tpt_resolve_bgra8(m_radiance, (int)m_samplesDone, framebuffer, onDevice), "tpt_resolve_bgra8");
     }
     m_lastFrameMs = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
 }

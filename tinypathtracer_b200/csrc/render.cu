@@ -888,6 +888,37 @@ __global__ void __launch_bounds__(128, TPT_COOP_MIN_BLOCKS) k_primary_coop(BvhVi
     // kCoopLanes lanes work on one pixel, 32 / kCoopLanes pixels at a time (the next ones that have work)
     const uint32_t grp = lane / kCoopLanes, sub = lane % kCoopLanes;
     unsigned todo = __ballot_sync(0xffffffffu, inside && (nc != 0 || sp.has_env()));
+    // Pixels no sample of which can hit anything only look the environment up.  Where they are many (a tile of sky: three quarters
+    // of ball.gltf's tiles) each lane keeps ITS pixel and runs the samples one after the other: the same number of warp iterations
+    // as one pixel at a time with 32 lanes, without the per-pixel hand-over (shuffles, the 64-bit group sums, the votes), which
+    // at 32 samples per pixel and launch — one iteration per pixel — was half of what such a pixel cost.
+    const unsigned culledMask = __ballot_sync(0xffffffffu, inside && nc == 0);
+    if (sp.has_env() && 2 * __popc(culledMask) * ((s1 - s0 + 31) / 32) >= (s1 - s0)) {
+        if (inside && nc == 0) {
+            long long aR = 0, aG = 0, aB = 0;
+            const uint32_t pixel = (uint32_t)(px + py * W);
+            for (uint32_t sl = s0; sl < s1; ++sl) {   // primary_sample for a ray that misses: jitter, direction, environment (weight 1)
+                float ju, jv;
+                rng_pair(rng_path_key(sp.seedKey, pixel, sampleBase + sl * sampleStride), 0u, ju, jv);
+                const float3 term = env_lookup(sp.env, sp.envf, sp.envW, sp.envH, primary_dir(cam, px, py, ju, jv));
+                if (term.x != 0.f || term.y != 0.f || term.z != 0.f) {
+                    if (finite3(term)) {
+                        aR += to_fixed(term.x);
+                        aG += to_fixed(term.y);
+                        aB += to_fixed(term.z);
+                    } else {
+                        atomicAdd(&ctr->dropped_nonfinite, 1ull);
+                    }
+                }
+            }
+            unsigned long long* dst = acc + 3 * (size_t)pixel;
+            if (aR) atomicAdd(dst + 0, (unsigned long long)aR);
+            if (aG) atomicAdd(dst + 1, (unsigned long long)aG);
+            if (aB) atomicAdd(dst + 2, (unsigned long long)aB);
+        }
+        __syncwarp();
+        todo &= ~culledMask;
+    }
     while (todo) {
         const unsigned src = __fns(todo, 0, (int)grp + 1);   // lane of my group's pixel; 0xffffffff when fewer pixels are left
         const bool have = src != 0xffffffffu;
@@ -1271,6 +1302,94 @@ __global__ void __launch_bounds__(128, TPT_WAVE_MIN_BLOCKS) k_wave(BvhView bvh, 
     wave_level<COUNT, NEE, SEGIN>(bvh, sp, sp.depth, extIn, secIn, levelIn, q, acc, ctr);
 }
 
+// A small level finished path by path.  When a level holds fewer items than the grid has threads, a level-synchronous wave costs
+// what its SLOWEST ray costs — measured on ball.gltf: ~80 us for each of waves 2..8 whatever the item count (the survivors are
+// the grazing rays, the longest walks there are), 0.54 ms per batch that does not shrink with the samples per GPU.  Here each
+// thread takes one item of the level and follows it to the end of its path in registers: closest hit, shade, the vertex's
+// shadow / "direct" rays traced at once, next bounce.  The time becomes that of the longest single PATH, not the sum over levels
+// of the longest ray.  Every term added is the one the queued form adds (same arithmetic, same RNG dimensions, exact integer
+// accumulation), so the accumulator bits are unchanged.
+template <bool COUNT, bool NEE>
+__device__ __forceinline__ void path_tail(const BvhView& bvh, const ShadeParams& sp, int w, const float4* extIn, const float4* secIn, uint32_t nExt,
+                                          uint32_t nSec, uint32_t nDirect, unsigned long long* __restrict__ acc, DeviceCounters* ctr) {
+    const uint32_t total = nExt + nSec;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        atomicAdd(&ctr->rays_extension, (unsigned long long)nExt);
+        atomicAdd(&ctr->rays_direct, (unsigned long long)nDirect);
+        atomicAdd(&ctr->rays_shadow, (unsigned long long)(nSec - nDirect));
+        atomicAdd(&ctr->rays_queued, (unsigned long long)total);
+    }
+    int stack[kStackSize];
+    stack[0] = kStackSentinel;
+    unsigned nExtra = 0, nShadowExtra = 0, nDirectExtra = 0;   // rays traced here that never saw a queue
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        if (i >= nExt) {   // a secondary ray of vertex w-1
+            const size_t j = (size_t)(i - nExt);
+            const float4 a = __ldcg(secIn + 3 * j), b = __ldcg(secIn + 3 * j + 1), c = __ldcg(secIn + 3 * j + 2);
+            const uint32_t kind = __float_as_uint(c.w);
+            const HitRec h = traverse<COUNT>(bvh, f3(a.x, a.y, a.z), f3(a.w, b.x, b.y), kind == kKindShadow, stack, &ctr->node_visits, &ctr->tri_tests);
+            float e = 1.0f;
+            bool add = h.leaf < 0;
+            if (kind == kKindDirect) {
+                add = false;
+                if (h.leaf >= 0) {
+                    e = __ldg(sp.mtl + 2 * __float_as_int(__ldg(bvh.tri_geom + 3 * (size_t)h.leaf + 2).z)).w;
+                    add = e != 0.0f;
+                }
+            }
+            if (add) accum_add(acc, __float_as_uint(c.y), f3(b.z, b.w, c.x) * e, ctr);
+            continue;
+        }
+        const float4 a = __ldcg(extIn + 3 * (size_t)i), b = __ldcg(extIn + 3 * (size_t)i + 1), c = __ldcg(extIn + 3 * (size_t)i + 2);
+        float3 o = f3(a.x, a.y, a.z), d = f3(a.w, b.x, b.y), T = f3(b.z, b.w, c.x);
+        const uint32_t pixel = __float_as_uint(c.y), sample = __float_as_uint(c.z);
+        uint32_t pbBits = NEE ? __float_as_uint(c.w) : 0u;
+        int depth = w + (NEE ? 0 : (int)__float_as_uint(c.w));
+        while (true) {
+            const HitRec h = traverse<COUNT>(bvh, o, d, false, stack, &ctr->node_visits, &ctr->tri_tests);
+            float3 term;
+            Vertex vx;
+            if (!shade_vertex<NEE>(bvh, sp, depth, o, d, T, pbBits, pixel, sample, h, term, vx, ctr)) {
+                accum_add(acc, pixel, term, ctr);
+                break;
+            }
+            for (int l = 0; l < sp.nLights; ++l) {   // what emit_vertex queues and the next wave adds, in the same arithmetic
+                float3 ldir, lrad;
+                light_incoming(sp.lights[l], vx.P, ldir, lrad);
+                const float3 contrib = vx.Tn * (vx.base * lrad);
+                ++nShadowExtra;
+                if (traverse<COUNT>(bvh, vx.P, ldir, true, stack, &ctr->node_visits, &ctr->tri_tests).leaf < 0) accum_add(acc, pixel, contrib * 1.0f, ctr);
+            }
+            if (vx.direct) {
+                ++nDirectExtra;
+                const HitRec hd = traverse<COUNT>(bvh, vx.P, vx.ddir, false, stack, &ctr->node_visits, &ctr->tri_tests);
+                if (hd.leaf >= 0) {
+                    const float e = __ldg(sp.mtl + 2 * __float_as_int(__ldg(bvh.tri_geom + 3 * (size_t)hd.leaf + 2).z)).w;
+                    if (e != 0.0f) accum_add(acc, pixel, vx.Tn * e, ctr);
+                }
+            }
+            if (NEE && vx.nee) {
+                ++nShadowExtra;
+                if (traverse<COUNT>(bvh, vx.P, vx.ldir, true, stack, &ctr->node_visits, &ctr->tri_tests).leaf < 0) accum_add(acc, pixel, vx.lw * 1.0f, ctr);
+            }
+            if (!vx.next) break;
+            o = vx.P;
+            d = vx.ndir;
+            T = vx.Tn;
+            pbBits = NEE ? __float_as_uint(vx.pb) : 0u;
+            ++depth;
+            ++nExtra;
+        }
+    }
+    const unsigned m = __activemask();
+    const unsigned se = __reduce_add_sync(m, nExtra), ss = __reduce_add_sync(m, nShadowExtra), sd = __reduce_add_sync(m, nDirectExtra);
+    if ((threadIdx.x & 31) == __ffs(m) - 1) {
+        if (se) atomicAdd(&ctr->rays_extension, (unsigned long long)se);
+        if (ss) atomicAdd(&ctr->rays_shadow, (unsigned long long)ss);
+        if (sd) atomicAdd(&ctr->rays_direct, (unsigned long long)sd);
+    }
+}
+
 // Waves wFirst..wLast in ONE cooperative launch: the same scheduler level after level, separated by a grid-wide barrier
 // instead of a kernel boundary, and the loop ends as soon as a level is empty.  The deep waves of most frames hold a
 // tiny share of the paths (ball.gltf: waves 2-8 together 0.15 % of wave 1) and cost a launch each — seven launches of
@@ -1283,6 +1402,7 @@ struct WaveLoopParams {
     uint32_t levelBytes;
     int wFirst, wLast;
     uint32_t extSegCap, secSegCap, extCap, secCap;
+    uint32_t pathTailMax;       // a level with at most this many items is finished path by path (path_tail)
 };
 template <bool COUNT, bool NEE>
 __global__ void __launch_bounds__(128, 6) k_wave_loop(BvhView bvh, ShadeParams sp, WaveLoopParams lp, unsigned long long* __restrict__ acc,
@@ -1294,6 +1414,11 @@ __global__ void __launch_bounds__(128, 6) k_wave_loop(BvhView bvh, ShadeParams s
         // written by the previous level (or launch) and final since the barrier: the same value in every block
         const unsigned long long counts = __ldcg(&seg_level(levelIn, 0)->counts);
         if (counts == 0ull) break;
+        const uint32_t nExt = min((uint32_t)counts, lp.extCap), nSec = min((uint32_t)(counts >> 32), lp.secCap);
+        if (nExt + nSec <= lp.pathTailMax) {   // few items left: finish them path by path, no further level
+            path_tail<COUNT, NEE>(bvh, sp, w, lp.ext[in], lp.sec[in], nExt, nSec, __ldcg(&seg_level(levelIn, 0)->n_direct), acc, ctr);
+            break;
+        }
         const QueueOut q{lp.ext[out], lp.sec[out], lp.levels + (size_t)(w + 1) * lp.levelBytes, lp.extSegCap, lp.secSegCap, lp.extCap, lp.secCap};
         wave_level<COUNT, NEE, false, true>(bvh, sp, w, lp.ext[in], lp.sec[in], levelIn, q, acc, ctr);
         if (w < lp.wLast) grid.sync();
@@ -1497,6 +1622,16 @@ constexpr int kMaxLevels = 72;   // waves 0..max_depth (max_depth <= 64), see tp
 // Queue pools: a batch of P camera samples can emit at most P extension rays and P*(L+1) secondary rays
 // per wave (every live path emits one ray of each sort and one shadow ray per light).  `paths` = kSegments x the
 // segment capacity, which is what the k_primary blocks of one segment can emit (launch_plan below).
+static int pool_alloc_failed(tpt_context* ctx, size_t bytes) {
+    cudaGetLastError();
+    size_t freeB = 0, totalB = 0;
+    cudaMemGetInfo(&freeB, &totalB);
+    ctx->pool_budget = 0;   // look the free memory up again next time
+    set_error("tpt_render: cannot allocate a " + std::to_string(bytes >> 20) + " MiB wavefront queue (" + std::to_string(freeB >> 20) + " MiB free on device " +
+              std::to_string(ctx->device) + "); render with a smaller tpt_render_config.paths_in_flight or free device memory");
+    return TPT_ERR_NOMEM;
+}
+
 static int ensure_pools(tpt_context* ctx, size_t paths, size_t secPerPath) {
     const size_t secNeed = paths * secPerPath;
     if (!ctx->levels) TPT_CUDA(cudaMalloc(&ctx->levels, (size_t)kMaxLevels * kSegments * kLevelStride));
@@ -1507,7 +1642,8 @@ static int ensure_pools(tpt_context* ctx, size_t paths, size_t secPerPath) {
             ctx->q_ext[k] = nullptr;
         }
         ctx->ext_capacity = 0;
-        for (int k = 0; k < 2; ++k) TPT_CUDA(cudaMalloc(&ctx->q_ext[k], paths * 3 * sizeof(float4)));
+        for (int k = 0; k < 2; ++k)
+            if (cudaMalloc(&ctx->q_ext[k], paths * 3 * sizeof(float4)) != cudaSuccess) return pool_alloc_failed(ctx, paths * 3 * sizeof(float4));
         ctx->ext_capacity = paths;
     }
     if (secNeed > ctx->sec_capacity) {
@@ -1517,7 +1653,8 @@ static int ensure_pools(tpt_context* ctx, size_t paths, size_t secPerPath) {
             ctx->q_sec[k] = nullptr;
         }
         ctx->sec_capacity = 0;
-        for (int k = 0; k < 2; ++k) TPT_CUDA(cudaMalloc(&ctx->q_sec[k], secNeed * 3 * sizeof(float4)));
+        for (int k = 0; k < 2; ++k)
+            if (cudaMalloc(&ctx->q_sec[k], secNeed * 3 * sizeof(float4)) != cudaSuccess) return pool_alloc_failed(ctx, secNeed * 3 * sizeof(float4));
         ctx->sec_capacity = secNeed;
     }
     return TPT_OK;
@@ -1525,6 +1662,7 @@ static int ensure_pools(tpt_context* ctx, size_t paths, size_t secPerPath) {
 
 
 int tpt_env_build_sampler(tpt_context* ctx);   // env.cu
+int tpt_scene_ensure_normals(tpt_scene* s);     // bvh.cu
 
 int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config* cfg, tpt_accum* acc) {
     tpt_context* ctx = s->ctx;
@@ -1532,6 +1670,7 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
     // environment next-event estimation needs a map to sample; without one the flag changes nothing
     const bool nee = (cfg->flags & TPT_RENDER_ENV_NEE) != 0 && (ctx->env != nullptr || ctx->envf != nullptr);
     if (nee) TPT_CHECK(tpt_env_build_sampler(ctx));
+    TPT_CHECK(tpt_scene_ensure_normals(s));   // the shade step reads the per-leaf normal records
     const int W = cfg->width, H = cfg->height;
     const uint32_t nPadded = tiles_x(W) * tiles_y(H) * 32u;
     const CameraParams cp = make_camera(cam, W, H);
@@ -1561,7 +1700,16 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
     // batch budget: as many LIVE camera samples as a 40 GiB queue budget allows (2 sides x (2+L) rays x 48 B each), at most
     // 2^27 — sized for 180 GB of HBM: fewer, larger batches mean fewer (mostly empty) deep-wave launches per frame
     const size_t secPerPath = s->n_lights + 1 + (nee ? 1 : 0);
-    size_t target = ((size_t)40 << 30) / (96 * (1 + secPerPath));
+    // ... and as the device can spare: at most 60 % of what is free (plus what this context's pools already hold), looked up when the
+    // context first renders (and again after an allocation has failed) — several contexts on one GPU, or a GPU shared with other
+    // work, get smaller batches instead of a failed cudaMalloc
+    if (ctx->pool_budget == 0) {
+        size_t freeB = 0, totalB = 0;
+        TPT_CUDA(cudaMemGetInfo(&freeB, &totalB));
+        const size_t have = (ctx->ext_capacity + ctx->sec_capacity) * 2 * 3 * sizeof(float4);
+        ctx->pool_budget = std::max<size_t>(std::min<size_t>((size_t)40 << 30, (freeB + have) / 10 * 6), (size_t)64 << 20);
+    }
+    size_t target = ctx->pool_budget / (96 * (1 + secPerPath));
     if (target > ((size_t)1 << 27)) target = (size_t)1 << 27;
     if (cfg->paths_in_flight > 0) target = (size_t)cfg->paths_in_flight;
     // Live pixels per 8x4 tile (k_tile_live): only they can put rays into the queues.  One small kernel, one 1-byte-per-tile
@@ -1669,7 +1817,12 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
     }
     const int variant = (counted ? 1 : 0) + (nee ? 2 : 0);
     const unsigned gridWave = ctx->wave_grid[variant];
-    static const bool noWaveLoop = getenv("TPT_NO_WAVE_LOOP") != nullptr;   // tuning switch: one launch per wave, as before
+    // One launch per wave by default.  The cooperative multi-level kernel (k_wave_loop, TPT_WAVE_LOOP=1) was built to save the deep
+    // waves' launches and measured: no gain (ball.gltf, 32 spp per launch: 4.68 vs 4.64 ms per frame) — a small level costs the
+    // latency of its slowest ray (~80 us), not a launch — and its 888 resident blocks hold the register file while they wait at the
+    // grid barrier, which keeps the NEXT frame's kernels (another stream) off the SMs; the per-wave kernels exit at once when a level
+    // is empty and let them in.
+    static const bool noWaveLoop = getenv("TPT_WAVE_LOOP") == nullptr || getenv("TPT_NO_WAVE_LOOP") != nullptr;
     const void* kWaveLoop = variant == 0 ? (const void*)k_wave_loop<false, false> : variant == 1 ? (const void*)k_wave_loop<true, false>
                           : variant == 2 ? (const void*)k_wave_loop<false, true> : (const void*)k_wave_loop<true, true>;
     if (ctx->wave_loop_grid[variant] == 0) {
@@ -1741,6 +1894,11 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
             lp.wLast = cfg->max_depth;
             lp.extSegCap = (uint32_t)extSegCap; lp.secSegCap = (uint32_t)secSegCap;
             lp.extCap = (uint32_t)(extSegCap * kSegments); lp.secCap = (uint32_t)(secSegCap * kSegments);
+            static const long pathTailEnv = getenv("TPT_PATH_TAIL_MAX") ? atol(getenv("TPT_PATH_TAIL_MAX")) : -1;   // tuning switch (0 = off)
+            // Off by default: measured on ball.gltf at 32 spp per launch the path-by-path finish is SLOWER than the level loop (wave stage
+            // 2.13 vs 1.96 ms): the lanes of a warp wait for each other in every one of the nested walks, so a warp still pays the
+            // slowest ray of each phase.  What a small level costs is the latency of its longest ray (~80 us, grazing rays), either way.
+            lp.pathTailMax = pathTailEnv >= 0 ? (uint32_t)pathTailEnv : 0u;
             BvhView v = view;
             unsigned long long* accData = acc->data;
             DeviceCounters* ctr = ctx->d_counters;

@@ -71,6 +71,7 @@ struct tpt_context {
     float4* q_ext[2] = {nullptr, nullptr};
     float4* q_sec[2] = {nullptr, nullptr};
     size_t ext_capacity = 0, sec_capacity = 0;
+    size_t pool_budget = 0;                       // bytes the queue pools may take (min(40 GiB, 60 % of free memory)); 0 = not looked up yet
     void* levels = nullptr;                       // QueueLevel[kMaxLevels] (render.cu)
     unsigned wave_grid[4] = {0, 0, 0, 0};          // persistent grid sizes of k_wave<COUNT, NEE> (148 x resident blocks), index COUNT + 2*NEE
     unsigned wave_loop_grid[4] = {0, 0, 0, 0};     // cooperative grid of k_wave_loop<COUNT, NEE> (0 = not queried yet, 1 = no cooperative launch)
@@ -126,6 +127,7 @@ struct tpt_scene {
     float4* tri_norm = nullptr;
     bool built = false;
     uint64_t geom_epoch = 0;      // bumped by every build / refit: world-space geometry may have changed
+    uint64_t norm_epoch = ~0ull;  // geom_epoch the per-leaf normal records (tri_norm) were written for (large scenes write them lazily)
     bool topology = false;        // hierarchy (children, parents, leaf order, range ends) of the last full build is intact: tpt_bvh_refit may reuse it
     bool any_specular = false;    // some material is a mirror or glass (metallic > 0 or eta > 0): k_primary's specular continuation can apply
     bool any_emissive = false;    // some material has emission > 0 (else the reference's extra "direct" rays add nothing and are not traced)

@@ -151,6 +151,30 @@ __device__ __forceinline__ MortonParams morton_params(const uint32_t* __restrict
 }
 
 // ---- small inputs: everything in one block --------------------------------------------------------------------------
+// The pairs are dealt evenly: with `items` = ceil(F / 256) pairs per thread, warp w owns pairs [w * 32 * items, (w + 1) * 32 * items)
+// and item k of lane l is pair w * 32 * items + k * 32 + l, so all eight warps rank (ball.gltf: 5 rounds of match instead of 16 in
+// three warps).  Rounds k >= items hold no pair and are skipped by the whole block.
+__device__ __forceinline__ void warp_rank_n(const unsigned long long (&key)[kSortItems], const bool (&valid)[kSortItems], int items, int shift,
+                                            uint32_t* wh, uint32_t (&rank)[kSortItems]) {
+    const uint32_t lane = threadIdx.x & 31, lt = (1u << lane) - 1u;
+#pragma unroll
+    for (int k = 0; k < kSortItems; ++k) {
+        if (k < items) {   // uniform
+            const uint32_t d = valid[k] ? (uint32_t)(key[k] >> shift) & 255u : 256u;
+            const unsigned m = __match_any_sync(0xffffffffu, d);
+            const int leader = __ffs(m) - 1;
+            uint32_t base = 0;
+            if ((int)lane == leader && d < 256u) {
+                base = wh[d];
+                wh[d] = base + (uint32_t)__popc(m);
+            }
+            base = __shfl_sync(0xffffffffu, base, leader);
+            rank[k] = base + (uint32_t)__popc(m & lt);
+            __syncwarp();
+        }
+    }
+}
+
 __global__ void __launch_bounds__(kSortThreads) k_sort_small(const uint32_t* __restrict__ indices, const float* __restrict__ worldVerts,
                                                              const uint32_t* __restrict__ bounds, uint32_t nFaces, int bitsPerAxis, int nPasses,
                                                              unsigned long long* __restrict__ keysOut, uint32_t* __restrict__ valsOut) {
@@ -158,20 +182,23 @@ __global__ void __launch_bounds__(kSortThreads) k_sort_small(const uint32_t* __r
     uint32_t* sv = reinterpret_cast<uint32_t*>(sm.keys);   // the values take the same route through the same buffer, after the keys
     const MortonParams mp = morton_params(bounds, bitsPerAxis);
     const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int items = (int)((nFaces + kSortThreads - 1) / kSortThreads);
+    const uint32_t warpBase = w * 32u * (uint32_t)items;
     unsigned long long key[kSortItems];
     uint32_t val[kSortItems], rank[kSortItems];
     bool valid[kSortItems];
 #pragma unroll
     for (int k = 0; k < kSortItems; ++k) {
-        const uint32_t f = w * kSortWarpItems + k * 32 + lane;
-        valid[k] = f < nFaces;
+        const uint32_t f = warpBase + k * 32 + lane;
+        valid[k] = k < items && f < nFaces;
         val[k] = f;
         key[k] = valid[k] ? face_key(indices, worldVerts, mp, f) : ~0ull;
+        rank[k] = 0;
     }
     for (int p = 0; p < nPasses; ++p) {
         for (int i = threadIdx.x; i < kSortWarps * 256; i += kSortThreads) (&sm.warpHist[0][0])[i] = 0u;
         __syncthreads();
-        warp_rank(key, valid, 8 * p, sm.warpHist[w], rank);
+        warp_rank_n(key, valid, items, 8 * p, sm.warpHist[w], rank);
         __syncthreads();
         const uint32_t count = warp_offsets(sm);
         __syncthreads();
@@ -184,32 +211,26 @@ __global__ void __launch_bounds__(kSortThreads) k_sort_small(const uint32_t* __r
                 sm.keys[rank[k]] = key[k];
             }
         __syncthreads();
-        // back to the thread arrangement: item (w, k, lane) = pair w * 512 + k * 32 + lane of the reordered tile
+        // back to the thread arrangement (valid[] is the same before and after: it only depends on the pair's index)
 #pragma unroll
-        for (int k = 0; k < kSortItems; ++k) {
-            const uint32_t j = w * kSortWarpItems + k * 32 + lane;
-            if (j < nFaces) key[k] = sm.keys[j];
-        }
+        for (int k = 0; k < kSortItems; ++k)
+            if (valid[k]) key[k] = sm.keys[warpBase + k * 32 + lane];
         __syncthreads();
 #pragma unroll
         for (int k = 0; k < kSortItems; ++k)
             if (valid[k]) sv[rank[k]] = val[k];
         __syncthreads();
 #pragma unroll
-        for (int k = 0; k < kSortItems; ++k) {
-            const uint32_t j = w * kSortWarpItems + k * 32 + lane;
-            if (j < nFaces) val[k] = sv[j];
-        }
+        for (int k = 0; k < kSortItems; ++k)
+            if (valid[k]) val[k] = sv[warpBase + k * 32 + lane];
         __syncthreads();
     }
 #pragma unroll
-    for (int k = 0; k < kSortItems; ++k) {
-        const uint32_t j = w * kSortWarpItems + k * 32 + lane;
-        if (j < nFaces) {
-            keysOut[j] = key[k];
-            valsOut[j] = val[k];
+    for (int k = 0; k < kSortItems; ++k)
+        if (valid[k]) {
+            keysOut[warpBase + k * 32 + lane] = key[k];
+            valsOut[warpBase + k * 32 + lane] = val[k];
         }
-    }
 }
 
 // ---- large inputs ------------------------------------------------------------------------------------------------------
