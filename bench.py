@@ -40,6 +40,11 @@ WORKLOADS = {
     "box2_4k": ("box2", 3840, 2160, 4096, 8, "sky", 5),  # configs[4]
 }
 N_SLICES = 8
+# traverseBVH calls per camera sample of the REFERENCE on each workload, counted by its counting build (oracle/_ref/tpt_ref_headless_count,
+# `bench.py --impl reference` prints them as rays_per_sample; profiles/r02_reference_ball.json).  The product traverses fewer rays for the
+# same samples (pixel-pyramid culling, no "direct" rays in emitter-free scenes), so its own Mrays/s is over a smaller ray population;
+# mrays_per_s_at_reference_ray_count = these x the product's Msamples/s is the like-for-like figure for north_star's Mrays/s wording.
+REFERENCE_RAYS_PER_SAMPLE = {"ball": 1.5419, "box": 4.4084, "tir": 1.1797, "light": 1.3210}
 
 
 def synthetic_sky(width=4096, height=2048):
@@ -220,8 +225,10 @@ class FrameBench:
         e0.record(self.main)
         for s in self.streams[1:]:
             s.wait_event(e0)
+        t0 = time.perf_counter()
         for i in range(steps):
             fn(i)
+        self.host_ms = (time.perf_counter() - t0) * 1e3 / max(steps, 1)   # what the host spends enqueueing one step (Python + driver)
         if finish:
             finish()
         for s in self.streams[1:]:
@@ -269,10 +276,12 @@ class FrameBench:
         copied = [torch.cuda.Event() for _ in range(self.n_lanes)]
         used = [False] * self.n_lanes
 
+        desc = self.tpt.DeviceScene.prepare(self.scene)       # the caller's arrays as the C ABI takes them (no per-frame numpy work)
+
         def step(i):
             k = i % self.n_lanes
             with torch.cuda.stream(self.streams[k]):
-                ds[k].update(self.scene)                           # H2D of every scene array
+                ds[k].update_prepared(desc)                        # tpt_scene_update: H2D of every scene array
                 if used[k]:
                     self.streams[k].wait_event(copied[k])          # the lane's framebuffer is free again once its last read-back is done
             self.frame(i, ds[k])
@@ -366,6 +375,7 @@ def run_ours(args):
     if rank == 0:
         clocks.start()
     ms_step = fb.timed(lambda i: fb.frame(i), args.steps) / args.steps
+    host_ms_value = fb.host_ms
     clk = clocks.stop() if rank == 0 else {}
     ctr = fb.counters_sum()
     launches = ctr["kernel_launches"]
@@ -382,6 +392,7 @@ def run_ours(args):
 
     # ---- e2e: host arrays in, host framebuffer out, through the C ABI --------------------------------------
     ms_e2e = fb.run_e2e(args.steps)
+    host_ms_e2e = fb.host_ms
     e2e_value = samples_step / (ms_e2e * 1e-3) / 1e6
 
     # ---- determinism evidence: SHA-256 of the all-reduced int64 accumulation buffer of one more frame (untimed)
@@ -464,7 +475,9 @@ def run_ours(args):
                              "HBM, far above the 126 MB L2; no flush between steps" % (96.0 * queued_step / max(world, 1) / 1e9, round(queued_step / 1e6))},
             "mrays_per_s": round(rays_step / (ms_step * 1e-3) / 1e6, 2), "rays_per_sample": round(rays_step / samples_step, 4),
             "rays_note": "rays actually traversed; the reference traverses every camera ray and every 'direct' ray (see reference arm's rays_per_sample)",
+            "mrays_per_s_at_reference_ray_count": round(REFERENCE_RAYS_PER_SAMPLE[fb.fixture] * value, 2) if fb.fixture in REFERENCE_RAYS_PER_SAMPLE else None,
             "bvh_build_ms": round(bstats["build_ms"], 4), "bvh_faces": bstats["n_faces"],
+            "host_enqueue_ms_per_step": {"value": round(host_ms_value, 3), "e2e": round(host_ms_e2e, 3)},   # rank 0's host time to enqueue one step
             "frame_latency_ms": round(ms_serial, 3),   # one frame alone on one lane (no overlap); ms_per_step = timed region / steps with frames_in_flight
             "e2e": {"value": round(e2e_value, 3), "unit": "Msamples/s", "ms_per_step": round(ms_e2e, 3),
                     "h2d_bytes_per_step": scene_upload_bytes(fb.scene), "d2h_bytes_per_step": W * H * 4,
@@ -501,7 +514,9 @@ def run_ours(args):
                 n = o.W * o.H * o.spp
                 also[name] = {"workload": o.workload_name, "ms_per_step": round(ms, 3), "value": round(n / (ms * 1e-3) / 1e6, 3), "unit": "Msamples/s",
                               "e2e_ms_per_step": round(ms_e, 3), "e2e_value": round(n / (ms_e * 1e-3) / 1e6, 3),
-                              "mrays_per_s": round(o.rays_traversed(c) / max(3, args.steps) / (ms * 1e-3) / 1e6, 2), "accum_sha256": o.accum_sha()}
+                              "mrays_per_s": round(o.rays_traversed(c) / max(3, args.steps) / (ms * 1e-3) / 1e6, 2),
+                              "mrays_per_s_at_reference_ray_count": round(REFERENCE_RAYS_PER_SAMPLE.get(name, 0.0) * n / (ms * 1e-3) / 1e6, 2),
+                              "accum_sha256": o.accum_sha()}
                 o.close()
             except Exception as e:
                 also[name] = {"error": str(e)[:300]}

@@ -215,3 +215,50 @@ def test_eight_contexts_share_one_gpu(tpt, scenes):
     assert len(set(shas)) == 1
     for c in ctxs:
         c.close()
+
+
+def test_reference_style_entry_points(tpt, ctx, scenes, orc):
+    """The boundary forms the reference itself uses: BVH::construct on WORLD-SPACE device arrays (include/bvh.cuh:60-68 as called
+    at src/path_tracer.cu:541-542) -> tpt_bvh_build_from_world, and doTrace with a DEVICE framebuffer (include/path_tracer.h:34,
+    src/vkEngine.cu:244) -> tpt_do_trace_device.  Same hits / same bytes as the host-array forms."""
+    import ctypes as C
+    import torch
+    from tinypathtracer_b200._capi import check, lib, RenderConfig
+    scene = scenes["box"]
+    ds = tpt.DeviceScene(ctx, scene)
+    bvh = tpt.BVH(ds)
+    bvh.construct()
+    wv, _ = ds.world()
+    idx = np.ascontiguousarray(scene["indices"], np.uint32)
+    used = np.zeros(wv.shape[0], bool)
+    used[idx] = True
+    wv = np.where(used[:, None], wv, 0.0).astype(np.float32)     # vertices no face references are never transformed
+    d_wv, d_idx = torch.from_numpy(wv).cuda(), torch.from_numpy(idx.astype(np.int32)).cuda()
+    h = C.c_void_p()
+    for _ in range(2):                                           # second call: the scene is reused
+        check(lib.tpt_bvh_build_from_world(ctx._h, C.c_void_p(d_wv.data_ptr()), wv.shape[0], C.c_void_p(d_idx.data_ptr()), idx.size // 3, C.byref(h), None))
+    rays = orc.primary_rays(scene, 160, 90)
+    want = bvh.trace(rays)
+    got = np.zeros(rays.shape[0], tpt.HIT_DTYPE)
+    r32 = np.ascontiguousarray(rays, np.float32)
+    check(lib.tpt_trace_rays(h, r32.ctypes.data_as(C.c_void_p), rays.shape[0], got.ctypes.data_as(C.c_void_p), 0, 0))
+    assert got.tobytes() == want.tobytes() and (got["prim"] >= 0).any()
+    with pytest.raises(tpt.TptError):
+        check(lib.tpt_bvh_build_from_world(ctx._h, C.c_void_p(d_wv.data_ptr()), wv.shape[0] - 1, C.c_void_p(d_idx.data_ptr()), idx.size // 3, C.byref(h), None))
+    lib.tpt_scene_destroy(h)
+    # device framebuffer
+    W, H, spp = 96, 54, 8
+    pt = tpt.PathTracer(ctx, W, H)
+    cam = tpt.Camera.from_scene(scene)
+    fb_host = np.full((H, W, 4), 7, np.uint8)
+    pt.doTrace(ds, cam, fb_host, spp, max_depth=8, seed=4)
+    fb_dev = torch.full((H, W, 4), 7, dtype=torch.uint8, device="cuda")
+    torch.cuda.synchronize()
+    from tinypathtracer_b200.api import render_config
+    cfg = render_config(W, H, spp, 8, 4)
+    check(lib.tpt_do_trace_device(ds._h, C.byref(cam.c), C.byref(cfg), pt.m_radiance._h, C.c_void_p(fb_dev.data_ptr())))
+    ctx.synchronize()
+    assert np.array_equal(fb_dev.cpu().numpy(), fb_host) and (fb_host[..., 3] == 7).all() and fb_host[..., :3].any()
+    assert lib.tpt_pointer_is_device(C.c_void_p(fb_dev.data_ptr())) == 1
+    assert lib.tpt_pointer_is_device(fb_host.ctypes.data_as(C.c_void_p)) == 0
+    ds.close()

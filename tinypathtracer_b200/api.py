@@ -163,6 +163,15 @@ class DeviceScene:
         self.n_vertices = keep["vertices"].shape[0]
         self.n_objects = keep["objects"].shape[0]
 
+    @staticmethod
+    def prepare(scene: dict):
+        """The scene's arrays laid out as the C ABI takes them (tpt_scene_desc + the arrays it points into): for callers that
+        upload the same host arrays every frame (update_prepared)."""
+        return DeviceScene._desc(scene)
+
+    def update_prepared(self, prepared):
+        check(lib.tpt_scene_update(self._h, C.byref(prepared[0])))
+
     def update(self, scene: dict):
         """tpt_scene_update: re-upload host arrays of the same sizes into the existing device arrays (no allocation, no sync)."""
         d, keep = self._desc(scene)

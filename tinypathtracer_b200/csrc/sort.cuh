@@ -40,6 +40,9 @@ __host__ __device__ __forceinline__ float ord2f(uint32_t u) {
 #endif
 }
 
+#ifndef TPT_SORT_MIN_BLOCKS
+#define TPT_SORT_MIN_BLOCKS 3
+#endif
 constexpr int kSortThreads = 256;
 constexpr int kSortItems = 16;                            // pairs per thread
 constexpr int kSortTile = kSortThreads * kSortItems;      // 4096 pairs: 32 KB of keys in shared memory
@@ -257,7 +260,7 @@ __global__ void __launch_bounds__(256) k_morton_hist(const uint32_t* __restrict_
 
 // One pass.  hist = this pass's 256 global digit counts; status = nTiles x 256 words (zeroed), tile t digit d at [t * 256 + d]:
 // count | kFlagAgg once the tile's own count is known, inclusive prefix | kFlagPrefix once everything before it is too.
-__global__ void __launch_bounds__(kSortThreads, 3) k_onesweep(const unsigned long long* __restrict__ keysIn, const uint32_t* __restrict__ valsIn,
+__global__ void __launch_bounds__(kSortThreads, TPT_SORT_MIN_BLOCKS) k_onesweep(const unsigned long long* __restrict__ keysIn, const uint32_t* __restrict__ valsIn,
                                                            unsigned long long* __restrict__ keysOut, uint32_t* __restrict__ valsOut, uint32_t n, int shift,
                                                            const uint32_t* __restrict__ hist, volatile uint32_t* status, uint32_t* ticket, uint32_t nTiles) {
     __shared__ SortSmem sm;
