@@ -1147,6 +1147,9 @@ __device__ __forceinline__ void wave_level(const BvhView& bvh, const ShadeParams
     TravState ts;
     ts.cur = kStackSentinel;
     ts.sp = 1;
+#if TPT_STACK_TOP_SM
+    ts.top = kNoTop;
+#endif
     uint32_t item = kNoItem, kind = 0;   // kind: 0 extension, 1 shadow (any hit), 2 direct
     uint32_t lo = 0, hi = 0;             // warp-local range of items not yet dealt out
     uint32_t gBase = 0, gEnd = 0;        // SEGIN: virtual index -> pool slot for the run of one segment the current grab starts in
@@ -1446,6 +1449,9 @@ __global__ void __launch_bounds__(128, 10) k_trace_rays_persistent(BvhView bvh, 
     TravState ts;
     ts.cur = kStackSentinel;
     ts.sp = 1;
+#if TPT_STACK_TOP_SM
+    ts.top = kNoTop;
+#endif
     unsigned long long item = ~0ull, lo = 0, hi = 0;
     bool more = true;
     unsigned nv = 0, nt = 0;

@@ -91,6 +91,19 @@ __device__ __forceinline__ bool leaf_test(const BvhView& bvh, int leaf, float3 o
 }
 
 constexpr int kStackSentinel = (int)0x80000000;   // negative, and never a valid leaf code (~leaf >= -2^30)
+// The newest stack entry can live in a REGISTER (`top`); memory then only sees an entry when a second one is pushed on top of it.  In a
+// depth-first walk most pushes are popped again before the next push (visit: push far child, descend near child, miss, pop), so
+// about half of the stack's loads and stores — each a wavefront of the L1 data pipe per lane — never happen.  Measured (ms per frame
+// stage / Mrays/s, with | without): the while-while walk of k_primary gains (ball 16.59 | 16.92, tir 2.42 | 2.59), the per-lane state
+// machine of k_wave and k_trace_rays_persistent LOSES (box 9.60 | 9.08, ball 11.94 | 11.85, soup 1 240 | 1 277 Mrays/s: at 64 / 48
+// registers the extra live value spills).  So: on in traverse(), off in the state machine.  kNoTop: the register is empty.
+#ifndef TPT_STACK_TOP
+#define TPT_STACK_TOP 1      // traverse() (while-while)
+#endif
+#ifndef TPT_STACK_TOP_SM
+#define TPT_STACK_TOP_SM 0   // TravState (persistent kernels)
+#endif
+constexpr int kNoTop = 0x7fffffff;
 
 // "while-while" traversal (Aila & Laine 2009): the inner loop descends internal nodes until the lane holds
 // a leaf, so that the lanes of a warp run their (expensive, exactly-rounded) triangle tests together
@@ -110,6 +123,26 @@ __device__ __forceinline__ HitRec traverse(const BvhView& bvh, float3 o, float3 
     int sp = 1;
     int cur = bvh.n_faces > 1 ? 0 : ~0;   // single-triangle scene: the root is leaf 0
     unsigned nv = 0, nt = 0;
+#if TPT_STACK_TOP
+    int top = kNoTop;
+#define TPT_PUSH(v)                        \
+    do {                                   \
+        if (top != kNoTop) stack[sp++] = top; \
+        top = (v);                         \
+    } while (0)
+#define TPT_POP(dst)                       \
+    do {                                   \
+        if (top != kNoTop) {               \
+            dst = top;                     \
+            top = kNoTop;                  \
+        } else {                           \
+            dst = stack[--sp];             \
+        }                                  \
+    } while (0)
+#else
+#define TPT_PUSH(v) stack[sp++] = (v)
+#define TPT_POP(dst) dst = stack[--sp]
+#endif
 
     while (cur != kStackSentinel) {
         while (cur >= 0) {
@@ -123,20 +156,22 @@ __device__ __forceinline__ HitRec traverse(const BvhView& bvh, float3 o, float3 
             if (hL && hR) {
                 const bool rightFirst = loR < loL;
                 cur = rightFirst ? n3.y : n3.x;
-                stack[sp++] = rightFirst ? n3.x : n3.y;
+                TPT_PUSH(rightFirst ? n3.x : n3.y);
             } else if (hL) {
                 cur = n3.x;
             } else if (hR) {
                 cur = n3.y;
             } else {
-                cur = stack[--sp];
+                TPT_POP(cur);
             }
         }
         if (cur == kStackSentinel) break;
         if (COUNT) ++nt;
         if (leaf_test(bvh, ~cur, o, d, best) && anyHit) break;
-        cur = stack[--sp];
+        TPT_POP(cur);
     }
+#undef TPT_PUSH
+#undef TPT_POP
     if (COUNT) {   // one atomic per converged group of lanes, not per ray
         const unsigned m = __activemask();
         const unsigned sv = __reduce_add_sync(m, nv), st = __reduce_add_sync(m, nt);
@@ -156,6 +191,9 @@ struct TravState {
     float3 o, d, inv;
     HitRec best;
     int cur, sp;
+#if TPT_STACK_TOP_SM
+    int top;   // newest stack entry, or kNoTop
+#endif
 };
 // stack[0] must hold kStackSentinel (written once by the kernel)
 __device__ __forceinline__ void trav_begin(TravState& s, const BvhView& bvh, float3 o, float3 d) {
@@ -167,6 +205,9 @@ __device__ __forceinline__ void trav_begin(TravState& s, const BvhView& bvh, flo
     s.best.leaf = -1;
     s.best.prim = -1;
     s.sp = 1;
+#if TPT_STACK_TOP_SM
+    s.top = kNoTop;
+#endif
     s.cur = bvh.n_faces > 1 ? 0 : ~0;
 }
 // Traversal stack of the persistent kernels.  A per-thread array in LOCAL memory is interleaved by lane, so a push or pop costs
@@ -182,21 +223,41 @@ constexpr int kSmemStack = TPT_SMEM_STACK;
 struct HybridStack {
     int* sh;      // this thread's column of the block's shared array (stride 128 ints); entry 0 holds the sentinel
     int* local;   // entries kSmemStack.. (kStackSize - kSmemStack ints)
-    __device__ __forceinline__ void push(int& sp, int v) const {
+    __device__ __forceinline__ void mem_push(int& sp, int v) const {
         if (sp < kSmemStack) sh[sp * 128] = v;
         else local[sp - kSmemStack] = v;
         ++sp;
     }
-    __device__ __forceinline__ int pop(int& sp) const {
+    __device__ __forceinline__ int mem_pop(int& sp) const {
         --sp;
         return sp < kSmemStack ? sh[sp * 128] : local[sp - kSmemStack];
     }
 };
 struct LocalStack {
     int* p;
-    __device__ __forceinline__ void push(int& sp, int v) const { p[sp++] = v; }
-    __device__ __forceinline__ int pop(int& sp) const { return p[--sp]; }
+    __device__ __forceinline__ void mem_push(int& sp, int v) const { p[sp++] = v; }
+    __device__ __forceinline__ int mem_pop(int& sp) const { return p[--sp]; }
 };
+template <class Stack>
+__device__ __forceinline__ void stack_push(const Stack& st, TravState& s, int v) {
+#if TPT_STACK_TOP_SM
+    if (s.top != kNoTop) st.mem_push(s.sp, s.top);
+    s.top = v;
+#else
+    st.mem_push(s.sp, v);
+#endif
+}
+template <class Stack>
+__device__ __forceinline__ int stack_pop(const Stack& st, TravState& s) {
+#if TPT_STACK_TOP_SM
+    if (s.top != kNoTop) {
+        const int r = s.top;
+        s.top = kNoTop;
+        return r;
+    }
+#endif
+    return st.mem_pop(s.sp);
+}
 
 template <class Stack>
 __device__ __forceinline__ void trav_node_step(TravState& s, const BvhView& bvh, const Stack& stack) {
@@ -215,19 +276,19 @@ __device__ __forceinline__ void trav_node_step(TravState& s, const BvhView& bvh,
     if (hL && hR) {
         const bool rightFirst = loR < loL;
         s.cur = rightFirst ? n3.y : n3.x;
-        stack.push(s.sp, rightFirst ? n3.x : n3.y);
+        stack_push(stack, s, rightFirst ? n3.x : n3.y);
     } else if (hL) {
         s.cur = n3.x;
     } else if (hR) {
         s.cur = n3.y;
     } else {
-        s.cur = stack.pop(s.sp);
+        s.cur = stack_pop(stack, s);
     }
 }
 template <class Stack>
 __device__ __forceinline__ void trav_leaf_step(TravState& s, const BvhView& bvh, bool anyHit, const Stack& stack) {
     if (leaf_test(bvh, ~s.cur, s.o, s.d, s.best) && anyHit) s.cur = kStackSentinel;
-    else s.cur = stack.pop(s.sp);
+    else s.cur = stack_pop(stack, s);
 }
 
 // ---- wide compressed nodes (BVH4) for trees that do not live in L1 --------------------------------------------------------
@@ -285,12 +346,12 @@ __device__ __forceinline__ void trav_node_step4(TravState& s, const float4* __re
     TPT_CSWAP(0, 1) TPT_CSWAP(2, 3) TPT_CSWAP(0, 2) TPT_CSWAP(1, 3) TPT_CSWAP(1, 2)
 #undef TPT_CSWAP
     if (t[0] == FLT_MAX) {
-        s.cur = stack.pop(s.sp);
+        s.cur = stack_pop(stack, s);
         return;
     }
-    if (t[3] != FLT_MAX) stack.push(s.sp, c[3]);   // farthest first: the nearest of the pushed ones pops first
-    if (t[2] != FLT_MAX) stack.push(s.sp, c[2]);
-    if (t[1] != FLT_MAX) stack.push(s.sp, c[1]);
+    if (t[3] != FLT_MAX) stack_push(stack, s, c[3]);   // farthest first: the nearest of the pushed ones pops first
+    if (t[2] != FLT_MAX) stack_push(stack, s, c[2]);
+    if (t[1] != FLT_MAX) stack_push(stack, s, c[1]);
     s.cur = c[0];
 }
 
