@@ -276,7 +276,7 @@ class FrameBench:
         copied = [torch.cuda.Event() for _ in range(self.n_lanes)]
         used = [False] * self.n_lanes
 
-        desc = self.tpt.DeviceScene.prepare(self.scene)       # the caller's arrays as the C ABI takes them (no per-frame numpy work)
+        desc = self.tpt.DeviceScene.prepare(self.scene, pinned=True)   # the caller's arrays in page-locked memory, as the C ABI takes them
 
         def step(i):
             k = i % self.n_lanes

@@ -192,7 +192,8 @@ int tpt_scene_destroy(tpt_scene* scene);
  * (src/mesh.cu:309-397) does per loaded file, without tpt_scene_create's ~24 allocations and tpt_scene_destroy's frees
  * and synchronisation — for callers that re-upload every frame.  Every count must equal the scene's (TPT_ERR_INVALID
  * otherwise); the scene must be rebuilt (tpt_bvh_build) before it is traced; tpt_bvh_refit is refused until then.
- * Asynchronous on the context stream; the host arrays may be reused on return. */
+ * Asynchronous on the context stream.  Pageable host arrays may be reused on return (the runtime stages them, and may wait for the
+ * stream first); page-locked arrays make the call fully asynchronous and must stay unchanged until the stream has passed the copies. */
 int tpt_scene_update(tpt_scene* scene, const tpt_scene_desc* desc);
 /* Update per-object transforms (n_objects x 16 each, host pointers); the reference re-reads
  * vertTrans/normalTrans every frame (src/path_tracer.cu:536-537). */

@@ -44,7 +44,6 @@ for cubin in tmp.glob("*.cubin"):
 fn = [f for f in lines if kern in f]
 if not fn:
     sys.exit(f"no kernel matching {kern!r} in {lib}")
-tab = lines[fn[0]]
 
 # ---- per-instruction counts from the report
 raw = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
@@ -61,6 +60,19 @@ b = blocks[launch]
 hdr, data = b["rows"][0], b["rows"][1:]
 iA, iS, iE, iT = hdr.index("Address"), hdr.index("Source"), hdr.index("Instructions Executed"), hdr.index("Thread Instructions Executed")
 base = int(data[0][iA], 16)
+
+
+def mismatches(tab):
+    bad = 0
+    for r in data:
+        sass = tab.get(int(r[iA], 16) - base, (None, ""))[1]
+        if sass.split()[:1] != r[iS].strip().replace("@", " ").split()[-0:1] and sass[:6] != r[iS].strip()[:6]:
+            bad += 1
+    return bad
+
+
+# several template instantiations share the name: take the one whose SASS is the profiled one
+tab = min((lines[f] for f in fn), key=mismatches)
 per_line = collections.defaultdict(lambda: [0, 0])
 tot = totT = 0
 mismatch = 0

@@ -164,10 +164,24 @@ class DeviceScene:
         self.n_objects = keep["objects"].shape[0]
 
     @staticmethod
-    def prepare(scene: dict):
+    def prepare(scene: dict, pinned: bool = False):
         """The scene's arrays laid out as the C ABI takes them (tpt_scene_desc + the arrays it points into): for callers that
-        upload the same host arrays every frame (update_prepared)."""
-        return DeviceScene._desc(scene)
+        upload the same host arrays every frame (update_prepared).  pinned: the arrays live in page-locked memory (torch), so
+        the uploads are truly asynchronous."""
+        if not pinned:
+            return DeviceScene._desc(scene)
+        import torch
+        keep_t, staged = [], dict(scene)
+        for k in ("indices", "vertices", "normals", "materials", "objects", "vert_trans", "normal_trans", "lights"):
+            a = np.ascontiguousarray(scene[k])
+            if a.size == 0:
+                continue
+            t = torch.from_numpy(a.view(np.uint8).reshape(-1).copy()).pin_memory()
+            keep_t.append(t)
+            staged[k] = t.numpy().view(a.dtype).reshape(a.shape)
+        d, keep = DeviceScene._desc(staged)
+        keep["_pinned"] = keep_t
+        return d, keep
 
     def update_prepared(self, prepared):
         check(lib.tpt_scene_update(self._h, C.byref(prepared[0])))

@@ -207,6 +207,10 @@ int tpt_scene_destroy(tpt_scene* s) {
     cudaFree(s->world_verts); cudaFree(s->world_norms); cudaFree(s->keys[0]); cudaFree(s->keys[1]); cudaFree(s->vals[0]);
     cudaFree(s->vals[1]); cudaFree(s->sort_tmp); cudaFree(s->parent_int); cudaFree(s->parent_leaf); cudaFree(s->flags);
     cudaFree(s->bounds); cudaFree(s->nodes); cudaFree(s->nodes4); cudaFree(s->tri_geom); cudaFree(s->tri_norm);
+    for (int k = 0; k < 4; ++k) {
+        if (s->h_mtl[k]) cudaFreeHost(s->h_mtl[k]);
+        if (s->h_mtl_free[k]) cudaEventDestroy(s->h_mtl_free[k]);
+    }
     delete s;
     return TPT_OK;
 }
@@ -231,15 +235,23 @@ static int check_scene_desc(const tpt_scene_desc* d, const char* who) {
     return TPT_OK;
 }
 
-// host arrays -> the scene's device arrays (+ the per-scene tables derived from them); no allocation, no synchronisation.
-// The sources may be pageable: cudaMemcpyAsync returns once such a buffer has been staged, so they may go away on return.
+// host arrays -> the scene's device arrays (+ the per-scene tables derived from them); no device allocation.  The sources may be
+// pageable (cudaMemcpyAsync then returns once the buffer has been staged, and may first wait for the stream) or page-locked (the
+// copies are asynchronous: the caller keeps the arrays alive until the stream has passed them — bench.py's e2e does this).
 static int upload_scene(tpt_scene* s, const tpt_scene_desc* d) {
     tpt_context* ctx = s->ctx;
     const size_t F = s->n_faces, V = s->n_vertices, O = s->n_objects;
     s->any_emissive = s->any_specular = false;
     for (size_t m = 0; m < d->n_materials; ++m) s->any_emissive = s->any_emissive || d->materials[m].emission > 0.0f;
     for (size_t m = 0; m < d->n_materials; ++m) s->any_specular = s->any_specular || d->materials[m].eta > 0.0f || d->materials[m].metallic > 0.0f;
-    std::vector<float4> mtl(2 * d->n_materials);
+    const unsigned slot = s->h_mtl_next++ & 3u;
+    if (!s->h_mtl[slot]) {
+        TPT_CUDA(cudaMallocHost(reinterpret_cast<void**>(&s->h_mtl[slot]), 2 * s->n_materials * sizeof(float4)));
+        TPT_CUDA(cudaEventCreateWithFlags(&s->h_mtl_free[slot], cudaEventDisableTiming));
+    } else {
+        TPT_CUDA(cudaEventSynchronize(s->h_mtl_free[slot]));   // the upload four updates ago has read this buffer
+    }
+    float4* mtl = s->h_mtl[slot];
     for (size_t m = 0; m < d->n_materials; ++m) {
         const tpt_material& M = d->materials[m];
         mtl[2 * m] = make_float4(M.base_color[0], M.base_color[1], M.base_color[2], M.emission);
@@ -251,7 +263,8 @@ static int upload_scene(tpt_scene* s, const tpt_scene_desc* d) {
     TPT_CHECK(upload(ctx, s->objects, d->objects, O));
     TPT_CHECK(upload(ctx, s->vert_trans, d->vert_trans, 16 * O));
     TPT_CHECK(upload(ctx, s->normal_trans, d->normal_trans, 16 * O));
-    TPT_CHECK(upload(ctx, s->mtl_table, mtl.data(), mtl.size()));
+    TPT_CHECK(upload(ctx, s->mtl_table, mtl, 2 * d->n_materials));
+    TPT_CUDA(cudaEventRecord(s->h_mtl_free[slot], ctx->stream));
     TPT_CHECK(upload(ctx, s->lights, d->lights, d->n_lights));
     return tpt_scene_build_tables(s);
 }

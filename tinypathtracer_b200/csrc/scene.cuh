@@ -109,6 +109,11 @@ struct tpt_scene {
     float* vert_trans = nullptr;
     float* normal_trans = nullptr;
     float4* mtl_table = nullptr;
+    // page-locked staging of the material table (a pageable source would make cudaMemcpyAsync wait for the stream): a ring of four
+    // buffers, each with the event of the last copy out of it, so that a host running a few frames ahead never waits for one
+    float4* h_mtl[4] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t h_mtl_free[4] = {nullptr, nullptr, nullptr, nullptr};
+    unsigned h_mtl_next = 0;
     tpt_delta_light* lights = nullptr;
     // per-build
     float* world_verts = nullptr;
