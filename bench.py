@@ -138,6 +138,16 @@ def _ncu_capture(fixture: str, kernel: str):
     return None
 
 
+HOST_GROUP = None   # gloo group of the ranks (host-side barriers, exchange handles); set by run_ours when world > 1
+
+
+class _DevicePtr:
+    """A device buffer the library owns, as something torch.as_tensor can view (CUDA array interface)."""
+
+    def __init__(self, ptr, shape):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "|u1", "data": (int(ptr), False), "version": 2}
+
+
 class FrameBench:
     """One workload of WORKLOADS on this rank's GPU: device-resident frames (`value`), end-to-end frames through host buffers
     (`e2e`), and the counters the roofline object is computed from.
@@ -146,7 +156,12 @@ class FrameBench:
     `--frames-in-flight` (default 2) of them are kept in flight: frame i runs on lane i mod 2 — a context, stream, device scene,
     queue pools, accumulator and framebuffer of its own — and the latency-bound end of one frame (its deep waves hold a
     handful of rays and cost the latency of the slowest, the all-reduce, the resolve, the read-back) overlaps the start of
-    the next.  Every frame still does everything: build, clear, all its samples, all-reduce, resolve."""
+    the next.  Every frame still does everything: build, clear, all its samples, the exchange between the ranks, resolve.
+
+    The exchange at world > 1 (--exchange): "peer" (default) = tpt_exchange_resolve, the library's own fused kernel — every rank
+    sums its 1/N of the pixels out of all ranks' accumulators over NVLink peer mappings, resolves them and stores the BGRA8
+    pixels into rank 0's framebuffer; "nccl" = torch.distributed all-reduce of the int64 buffers, then every rank resolves the
+    whole frame (round 1's path; still what `accum_sha256` is computed from, and the byte-for-byte check of the peer path)."""
 
     def __init__(self, args, workload, spp_override=0, lanes=None):
         import torch
@@ -180,6 +195,34 @@ class FrameBench:
             self.fb_host.append(torch.zeros((H, W, 4), dtype=torch.uint8).pin_memory())
         self.ctx, self.pt, self.acc_t, self.acc, self.dscene, self.stream = (self.ctxs[0], self.pts[0], self.acc_ts[0], self.accs[0],
                                                                              self.dscenes[0], self.main)
+        self.exchange = "none" if self.world == 1 else args.exchange
+        self.exchange_note = None
+        self.xaccs, self.xchg, self.fb_view = [], [], []
+        if self.exchange == "peer":
+            try:
+                for k in range(self.n_lanes):
+                    a = tpt.Accum(self.ctxs[k], W, H)                # the library's own allocation: peers map it through CUDA IPC
+                    x = tpt.FrameExchange(self.ctxs[k], a, self.rank, self.world, alpha=0)
+                    self.xaccs.append(a)
+                    self.xchg.append(x)
+                ok = 1
+            except tpt.TptError as e:
+                ok, self.exchange_note = 0, str(e)
+            flags = [None] * self.world
+            dist.all_gather_object(flags, ok, group=HOST_GROUP)
+            if all(flags):
+                try:
+                    for x in self.xchg:
+                        x.connect_over(dist, group=HOST_GROUP)
+                except tpt.TptError as e:
+                    ok, self.exchange_note = 0, str(e)
+                dist.all_gather_object(flags, ok, group=HOST_GROUP)
+            if not all(flags):                                       # e.g. no IPC in this container: say so and use the library collective
+                if self.rank == 0:
+                    print(f"bench.py: peer exchange unavailable ({self.exchange_note or 'another rank failed'}); using NCCL", file=sys.stderr)
+                self.exchange, self.exchange_note = "nccl", self.exchange_note or "another rank could not set up the peer exchange"
+            else:
+                self.fb_view = [torch.as_tensor(_DevicePtr(x.framebuffer_ptr(), (H, W, 4)), device="cuda") for x in self.xchg]
         self.cam = tpt.Camera.from_scene(self.scene)
         self.slices = my_slices(self.rank, self.world)
         self.copy_stream = torch.cuda.Stream()
@@ -187,18 +230,35 @@ class FrameBench:
 
     def close(self):
         self.torch.cuda.synchronize()
+        for x in self.xchg:
+            x.status()                                               # raises if a handshake ever timed out
+            x.close()
+        if self.xchg:
+            self.dist.barrier(group=HOST_GROUP)                      # every rank has closed its mappings before any accumulator is freed
+        for a in self.xaccs:
+            a.close()
         for k in range(self.n_lanes):
             self.dscenes[k].close()
             self.accs[k].close()
             self.ctxs[k].close()
 
-    def frame(self, i=0, dscene=None, counters=False, stage_times=False, flags_nee=False):
+    def frame(self, i=0, dscene=None, counters=False, stage_times=False, flags_nee=False, exchange=None):
         """One doTrace (reference src/path_tracer.cu:491-554) with device-resident inputs, on lane i mod n_lanes."""
         import ctypes as C
         from tinypathtracer_b200._capi import lib, check
         tpt, dist, torch = self.tpt, self.dist, self.torch
         k = i % self.n_lanes
         dscene = dscene or self.dscenes[k]
+        exchange = exchange or self.exchange
+        if exchange == "peer":
+            with torch.cuda.stream(self.streams[k]):
+                tpt.BVH(dscene).construct(stats=False)
+                self.xaccs[k].clear()
+                self.pts[k].render_into(dscene, self.cam, spp=self.per_slice * len(self.slices), max_depth=self.depth, seed=self.seed,
+                                        sample_offset=self.rank, sample_stride=self.world, accum=self.xaccs[k], counters=counters,
+                                        stage_times=stage_times, env_nee=flags_nee, paths_in_flight=self.args.paths_in_flight)
+                self.xchg[k].resolve(self.spp, 0)                    # handshake + reduce-scatter + resolve + pixels to rank 0, one pass
+            return
         with torch.cuda.stream(self.streams[k]):
             tpt.BVH(dscene).construct(stats=False)
             self.accs[k].clear()
@@ -288,7 +348,10 @@ class FrameBench:
             done[k].record(self.streams[k])
             self.copy_stream.wait_event(done[k])
             with torch.cuda.stream(self.copy_stream):
-                self.fb_host[k].copy_(self.fb_dev[k], non_blocking=True)   # D2H of the step's result
+                if self.exchange != "peer":
+                    self.fb_host[k].copy_(self.fb_dev[k], non_blocking=True)   # D2H of the step's result
+                elif self.rank == 0:
+                    self.fb_host[k].copy_(self.fb_view[k], non_blocking=True)  # the frame lives in rank 0's framebuffer
                 copied[k].record(self.copy_stream)
             used[k] = True
 
@@ -307,9 +370,19 @@ class FrameBench:
 
     def accum_sha(self):
         import hashlib
-        self.frame(0)
+        self.frame(0, exchange="nccl" if self.world > 1 else None)
         self.torch.cuda.synchronize()
         return hashlib.sha256(self.acc_ts[0].cpu().numpy().tobytes()).hexdigest() if self.rank == 0 else None
+
+    def exchange_check(self):
+        """The peer exchange's framebuffer on rank 0 against all-reduce + tpt_resolve_bgra8 of the same frame: must be the same bytes."""
+        if self.exchange != "peer":
+            return None
+        self.frame(0)
+        self.frame(0, exchange="nccl")
+        self.torch.cuda.synchronize()
+        self.barrier()
+        return bool((self.fb_view[0] == self.fb_dev[0]).all().item()) if self.rank == 0 else None
 
     def rays_traversed(self, ctr):
         # camera samples whose pixel pyramid misses every leaf box are answered without a traversal
@@ -363,6 +436,8 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
         host_group = dist.new_group(backend="gloo")
+        global HOST_GROUP
+        HOST_GROUP = host_group
     fb = FrameBench(args, args.workload, args.spp)
     W, H, spp, depth = fb.W, fb.H, fb.spp, fb.depth
     ctx = fb.ctx
@@ -397,6 +472,7 @@ def run_ours(args):
 
     # ---- determinism evidence: SHA-256 of the all-reduced int64 accumulation buffer of one more frame (untimed)
     accum_sha = fb.accum_sha()
+    exchange_ok = fb.exchange_check()
 
     line = None
     if rank == 0:
@@ -471,6 +547,8 @@ def run_ours(args):
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 3), "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": fb.workload_name, "parallelism": f"spp-slices x{world}", "slices": N_SLICES, "frames_in_flight": fb.n_lanes,
+                       "exchange": {"none": "single GPU: tpt_resolve_bgra8", "nccl": "NCCL all-reduce of the int64 accumulators, then tpt_resolve_bgra8 on every rank",
+                                    "peer": "tpt_exchange_resolve: fused reduce-scatter + resolve over NVLink peer mappings (CUDA IPC), pixels to rank 0"}[fb.exchange],
                        "l2": "inputs larger than L2: every step writes and reads %.1f GB of wavefront records (%d M queued rays x 96 B) through "
                              "HBM, far above the 126 MB L2; no flush between steps" % (96.0 * queued_step / max(world, 1) / 1e9, round(queued_step / 1e6))},
             "mrays_per_s": round(rays_step / (ms_step * 1e-3) / 1e6, 2), "rays_per_sample": round(rays_step / samples_step, 4),
@@ -478,6 +556,8 @@ def run_ours(args):
             "mrays_per_s_at_reference_ray_count": round(REFERENCE_RAYS_PER_SAMPLE[fb.fixture] * value, 2) if fb.fixture in REFERENCE_RAYS_PER_SAMPLE else None,
             "bvh_build_ms": round(bstats["build_ms"], 4), "bvh_faces": bstats["n_faces"],
             "host_enqueue_ms_per_step": {"value": round(host_ms_value, 3), "e2e": round(host_ms_e2e, 3)},   # rank 0's host time to enqueue one step
+            "exchange_matches_allreduce": exchange_ok,   # peer exchange's framebuffer == all-reduce + resolve of the same frame, byte for byte (None: not used)
+            "exchange_note": fb.exchange_note,
             "frame_latency_ms": round(ms_serial, 3),   # one frame alone on one lane (no overlap); ms_per_step = timed region / steps with frames_in_flight
             "e2e": {"value": round(e2e_value, 3), "unit": "Msamples/s", "ms_per_step": round(ms_e2e, 3),
                     "h2d_bytes_per_step": scene_upload_bytes(fb.scene), "d2h_bytes_per_step": W * H * 4,
@@ -537,6 +617,7 @@ def run_ours(args):
                 also["soup"] = {"error": str(e)[:300]}
         line["also"] = also
     if world > 1:
+        fb.close()                                                   # raises if the peer exchange ever timed out
         dist.barrier()
         dist.destroy_process_group()
     if rank == 0:
@@ -934,6 +1015,8 @@ def main():
     ap.add_argument("--spp", type=int, default=0, help="override the workload's spp (multiple of 8)")
     ap.add_argument("--paths-in-flight", type=int, default=0)
     ap.add_argument("--frames-in-flight", type=int, default=2, help="independent frames kept in flight (each on its own stream, scene, pools and accumulator)")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                    help="how the ranks' accumulators meet at world > 1: the library's fused peer-memory kernel, or torch.distributed all-reduce")
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-also", action="store_true", help="skip the other BASELINE configs (box, tir, light, NEE, soup) after the headline")

@@ -281,6 +281,29 @@ int tpt_accum_clear(tpt_accum* acc);                      /* thrust::fill at src
  * buffer instead (tpt_accum_wrap / tpt_accum_device_ptr) and use the framework's all-reduce: int64 sums are exact either way. */
 int tpt_comm_init_all(int ngpu, tpt_context** out_contexts);
 int tpt_accum_allreduce(tpt_accum** per_gpu, int n);
+/* Multi-GPU with one process PER GPU (torchrun): the frame exchange.  Rank r of `world` creates an exchange for its
+ * accumulator (one made by tpt_accum_create) and publishes TPT_EXCHANGE_HANDLE_BYTES; the host gathers every rank's bytes in rank
+ * order (any transport: torch.distributed, MPI, a file) and hands the world*TPT_EXCHANGE_HANDLE_BYTES to tpt_exchange_connect,
+ * which maps the peers' accumulators and framebuffers (CUDA IPC; NVLink peer access).  tpt_exchange_resolve then replaces
+ * "all-reduce the accumulators, then copyToFB" (src/path_tracer.cu:451-471 on the summed buffer) by ONE fused pass: after a
+ * flag handshake in peer memory every rank sums ITS 1/world of the pixels straight out of all accumulators, converts them
+ * exactly as tpt_resolve_bgra8 does (alpha byte = the `alpha` given at creation) and stores them into the framebuffer of
+ * rank `root` (every rank's if root == -1) — 24 bytes per pixel cross NVLink once and 4 come back.  Asynchronous on the
+ * context's stream, to be called by every rank once per frame after its tpt_render calls; when the call's work has completed
+ * on a rank, that rank's accumulator may be cleared again and (root) its framebuffer, tpt_exchange_framebuffer — device
+ * memory, width*height*4, row 0 = top — holds the frame.  The accumulators themselves are left unsummed.  A rank that waits
+ * longer than 20 s (TPT_EXCHANGE_TIMEOUT_MS) for another gives up instead of hanging the GPU: tpt_exchange_status (synchronous)
+ * then returns an error.  Destroy the exchange on every rank before any rank destroys its accumulator.  The reference has one
+ * GPU and no counterpart of this. */
+#define TPT_EXCHANGE_HANDLE_BYTES 168
+typedef struct tpt_exchange tpt_exchange;
+int tpt_exchange_create(tpt_context* ctx, tpt_accum* acc, int rank, int world, unsigned char alpha, tpt_exchange** out, void* handle_out);
+int tpt_exchange_connect(tpt_exchange* x, const void* all_handles);
+int tpt_exchange_resolve(tpt_exchange* x, int spp_total, int root);
+void* tpt_exchange_framebuffer(tpt_exchange* x);
+int tpt_exchange_read_framebuffer(tpt_exchange* x, uint8_t* host_fb);   /* synchronous copy of this rank's framebuffer to the host */
+int tpt_exchange_status(tpt_exchange* x);
+int tpt_exchange_destroy(tpt_exchange* x);
 int tpt_accum_add(tpt_accum* dst, const tpt_accum* src);   /* dst += src (same context) */
 void* tpt_accum_device_ptr(tpt_accum* acc);               /* int64[height][width][3], row 0 = bottom */
 int tpt_accum_export_f32(tpt_accum* acc, float* host_rgb); /* radiance SUM, float[height][width][3] */

@@ -5,8 +5,8 @@ tinypathtracer_b200/lib/libtpt_b200.so (hand-written CUDA, built by build.py).  
 without the built library raises ImportError: there is no fallback path.
 """
 from .api import (Accum, BVH, Camera, Context, DeviceScene, EnvLight, PathTracer, HIT_DTYPE, RAY_DTYPE, REF_NODE_DTYPE,
-                  MATERIAL_DTYPE, MTL_INTERVAL_DTYPE, LIGHT_DTYPE, ACCUM_FRAC_BITS, render_config, comm_init_all, accum_allreduce)
+                  MATERIAL_DTYPE, MTL_INTERVAL_DTYPE, LIGHT_DTYPE, ACCUM_FRAC_BITS, render_config, comm_init_all, accum_allreduce, FrameExchange)
 from ._capi import TptError, LIB_PATH
 
 __all__ = ["Accum", "BVH", "Camera", "Context", "DeviceScene", "EnvLight", "PathTracer", "TptError", "LIB_PATH", "HIT_DTYPE",
-           "RAY_DTYPE", "REF_NODE_DTYPE", "MATERIAL_DTYPE", "MTL_INTERVAL_DTYPE", "LIGHT_DTYPE", "ACCUM_FRAC_BITS", "render_config", "comm_init_all", "accum_allreduce"]
+           "RAY_DTYPE", "REF_NODE_DTYPE", "MATERIAL_DTYPE", "MTL_INTERVAL_DTYPE", "LIGHT_DTYPE", "ACCUM_FRAC_BITS", "render_config", "comm_init_all", "accum_allreduce", "FrameExchange"]

@@ -73,6 +73,8 @@ class StageTimes(C.Structure):
 
 
 # every symbol include/tpt.h declares, with its signature
+TPT_EXCHANGE_HANDLE_BYTES = 168
+
 SIGNATURES = {
     "tpt_last_error": (C.c_char_p, []),
     "tpt_abi_version": (C.c_int, []),
@@ -97,6 +99,13 @@ SIGNATURES = {
     "tpt_scene_export_world": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "tpt_comm_init_all": (C.c_int, [C.c_int, C.c_void_p]),
     "tpt_accum_allreduce": (C.c_int, [C.c_void_p, C.c_int]),
+    "tpt_exchange_create": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_ubyte, C.POINTER(C.c_void_p), C.c_void_p]),
+    "tpt_exchange_connect": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "tpt_exchange_resolve": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
+    "tpt_exchange_framebuffer": (C.c_void_p, [C.c_void_p]),
+    "tpt_exchange_read_framebuffer": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "tpt_exchange_status": (C.c_int, [C.c_void_p]),
+    "tpt_exchange_destroy": (C.c_int, [C.c_void_p]),
     "tpt_env_set_rgba8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
     "tpt_env_set_rgb32f": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
     "tpt_env_clear": (C.c_int, [C.c_void_p]),

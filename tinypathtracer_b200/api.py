@@ -47,7 +47,8 @@ class Context:
 
     def close(self):
         if self._h:
-            for child in list(self._children):
+            kids = list(self._children)
+            for child in sorted(kids, key=lambda c: not isinstance(c, FrameExchange)):   # exchanges first: they use accumulators
                 child.close()
             lib.tpt_context_destroy(self._h)
             self._h = None
@@ -125,6 +126,61 @@ def accum_allreduce(accums: list):
     """tpt_accum_allreduce: every accumulator (one per context) ends up holding the exact sum of all of them."""
     arr = (C.c_void_p * len(accums))(*[a._h for a in accums])
     check(lib.tpt_accum_allreduce(arr, len(accums)))
+
+
+class FrameExchange:
+    """tpt_exchange_*: the end of a frame with one process PER GPU.  Every rank sums its 1/world of the pixels straight out of
+    all ranks' accumulators (peer memory, CUDA IPC), resolves them like tpt_resolve_bgra8 and stores them into the root's
+    framebuffer — one fused pass instead of all-reduce + resolve.  `handle` is what the ranks exchange (any transport);
+    `connect` takes all of them, in rank order."""
+
+    def __init__(self, ctx: Context, accum: "Accum", rank: int, world: int, alpha: int = 0):
+        h = C.c_void_p()
+        buf = (C.c_ubyte * capi.TPT_EXCHANGE_HANDLE_BYTES)()
+        check(lib.tpt_exchange_create(ctx._h, accum._h, rank, world, alpha, C.byref(h), buf))
+        self._h, self.ctx, self.accum, self.rank, self.world = h, ctx, accum, rank, world
+        self.handle = bytes(buf)
+        ctx._children.add(self)
+
+    def connect(self, handles):
+        """handles: the `handle` of rank 0, 1, ... world-1 (a list of bytes, or their concatenation)."""
+        raw = handles if isinstance(handles, (bytes, bytearray)) else b"".join(handles)
+        if len(raw) != self.world * capi.TPT_EXCHANGE_HANDLE_BYTES:
+            raise capi.TptError(f"FrameExchange.connect: {len(raw)} bytes for {self.world} ranks")
+        check(lib.tpt_exchange_connect(self._h, C.c_char_p(bytes(raw))))
+
+    def connect_over(self, dist, group=None):
+        """Gather the handles with torch.distributed (all_gather_object on `group`: a gloo group keeps it off the GPU) and connect."""
+        out = [None] * self.world
+        dist.all_gather_object(out, self.handle, group=group)
+        self.connect(out)
+
+    def resolve(self, spp_total: int, root: int = 0):
+        check(lib.tpt_exchange_resolve(self._h, spp_total, root))
+
+    def framebuffer_ptr(self) -> int:
+        return int(lib.tpt_exchange_framebuffer(self._h) or 0)
+
+    def framebuffer(self) -> np.ndarray:
+        """Synchronous copy of this rank's framebuffer: uint8 [height][width][4] (B, G, R, alpha), row 0 = top."""
+        fb = np.zeros((self.accum.height, self.accum.width, 4), np.uint8)
+        check(lib.tpt_exchange_read_framebuffer(self._h, _ptr(fb)))
+        return fb
+
+    def status(self):
+        """Synchronises; raises if a wait for another rank timed out."""
+        check(lib.tpt_exchange_status(self._h))
+
+    def close(self):
+        if self._h:
+            lib.tpt_exchange_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 class DeviceScene:

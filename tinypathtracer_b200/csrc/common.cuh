@@ -151,6 +151,17 @@ __host__ __device__ __forceinline__ uint64_t rng_path_key(uint64_t seedKey, uint
     return mix64(seedKey ^ (((uint64_t)pixel << 32) | (uint64_t)sample));
 }
 __host__ __device__ __forceinline__ float rng_u01(uint32_t x) { return (float)((x >> 8) + 1u) * (1.0f / 16777216.0f); }
+
+// Spectrum::toUChar, include/material.h:74-81: (unsigned char) clamp(255 * L / spp, 0, 255) by truncation; one fixed-point
+// accumulator word (2^-36 units) -> mean radiance.  Shared by k_resolve (render.cu) and k_xchg_resolve (comm.cu): same bytes.
+__device__ __forceinline__ unsigned char to_uchar(float v) {
+    const float x = v * 255.0f;
+    const float c = fmaxf((x < 255.0f) ? x : 255.0f, 0.0f);   // min(x,255) with the reference's NaN -> 255
+    return (unsigned char)c;
+}
+__device__ __forceinline__ float accum_to_radiance(unsigned long long a, float invSpp) {
+    return (float)((double)(long long)a * (1.0 / 68719476736.0)) * invSpp;
+}
 // the 64 raw bits behind pair j (env.cuh picks an alias-table bucket from all 32 high bits: a 24-bit float cannot address a
 // 4096 x 2048 map's 2^23 texels AND leave bits for anything else)
 __host__ __device__ __forceinline__ uint64_t rng_bits(uint64_t key, uint32_t j) {

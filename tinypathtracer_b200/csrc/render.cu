@@ -1526,21 +1526,13 @@ __global__ void k_accum_to_f32(const unsigned long long* __restrict__ acc, float
         out[i] = (float)((double)(long long)acc[i] * (1.0 / 68719476736.0));
 }
 
-// copyToFB, src/path_tracer.cu:451-471 + Spectrum::toUChar, include/material.h:74-81:
-// (unsigned char) clamp(255 * L / spp, 0, 255) by truncation, B,G,R order, alpha untouched, row H-1-y.
-__device__ __forceinline__ unsigned char to_uchar(float v) {
-    const float x = v * 255.0f;
-    const float c = fmaxf((x < 255.0f) ? x : 255.0f, 0.0f);   // min(x,255) with the reference's NaN -> 255
-    return (unsigned char)c;
-}
+// copyToFB, src/path_tracer.cu:451-471 (to_uchar / accum_to_radiance: common.cuh): B,G,R order, alpha untouched, row H-1-y.
 __global__ void __launch_bounds__(256) k_resolve(const unsigned long long* __restrict__ acc, int W, int H, float invSpp, uchar4* __restrict__ fb) {
     const uint32_t n = (uint32_t)W * (uint32_t)H;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const int x = (int)(i % (uint32_t)W), y = (int)(i / (uint32_t)W);
         const unsigned long long* p = acc + 3 * (size_t)i;
-        const float r = (float)((double)(long long)p[0] * (1.0 / 68719476736.0)) * invSpp;
-        const float g = (float)((double)(long long)p[1] * (1.0 / 68719476736.0)) * invSpp;
-        const float b = (float)((double)(long long)p[2] * (1.0 / 68719476736.0)) * invSpp;
+        const float r = accum_to_radiance(p[0], invSpp), g = accum_to_radiance(p[1], invSpp), b = accum_to_radiance(p[2], invSpp);
         uchar4* dst = fb + (size_t)(H - y - 1) * W + x;
         uchar4 px = *dst;
         px.x = to_uchar(b);
@@ -1923,6 +1915,8 @@ int tpt_render_impl(tpt_scene* s, const tpt_camera* cam, const tpt_render_config
                 const int stage = j == 1 ? 0 : 1;
                 ctx->stage_ms[stage] += ms;
                 ctx->stage_launches[stage] += 1;
+                static const bool detail = getenv("TPT_STAGE_DETAIL") != nullptr;   // diagnostic: every launch's time on stderr
+                if (detail) fprintf(stderr, "[tpt stage] batch@%u %s %.1f us\n", done, j == 1 ? "primary" : "wave", ms * 1e3f);
             }
         }
     }
