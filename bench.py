@@ -153,7 +153,7 @@ class FrameBench:
     (`e2e`), and the counters the roofline object is computed from.
 
     Frames are independent (the reference's loop renders one after the other from scratch, src/vkEngine.cu:294-302), so
-    `--frames-in-flight` (default 2) of them are kept in flight: frame i runs on lane i mod 2 — a context, stream, device scene,
+    `--frames-in-flight` (default: auto = 4) of them are kept in flight: frame i runs on lane i mod 4 — a context, stream, device scene,
     queue pools, accumulator and framebuffer of its own — and the latency-bound end of one frame (its deep waves hold a
     handful of rays and cost the latency of the slowest, the all-reduce, the resolve, the read-back) overlaps the start of
     the next.  Every frame still does everything: build, clear, all its samples, the exchange between the ranks, resolve.
@@ -178,7 +178,14 @@ class FrameBench:
         self.scene = load_scene(self.fixture)
         self.env = synthetic_sky() if self.envkind == "sky" else None
         W, H = self.W, self.H
-        self.n_lanes = max(1, lanes if lanes is not None else args.frames_in_flight)
+        want = lanes if lanes is not None else args.frames_in_flight
+        if not want:
+            # auto: what a frame cannot shrink with its sample count (deep waves of a few rays, the exchange, kernel tails) is hidden
+            # by the other frames in flight, and the shorter the frame the more of them it takes.  Measured, ball.gltf, ms per step with
+            # 2 | 4 frames in flight: 256 spp 25.53 | 25.50, 128 spp 13.03 | 12.97, 64 spp 6.70 | 6.62, 32 spp 3.65 | 3.51 (6: no better).
+            # Four everywhere the queue pools of four frames fit comfortably; two for the very large jobs (4K, 4096 spp).
+            want = 4 if W * H * (self.spp // self.world) <= (1 << 30) else 2
+        self.n_lanes = max(1, want)
         self.main = torch.cuda.current_stream()
         self.streams = [self.main] + [torch.cuda.Stream() for _ in range(self.n_lanes - 1)]
         self.ctxs, self.pts, self.acc_ts, self.accs, self.dscenes, self.fb_dev, self.fb_host = [], [], [], [], [], [], []
@@ -1014,7 +1021,8 @@ def main():
     ap.add_argument("--soup-small", action="store_true", help="soup workload at 1/128 size (smoke test)")
     ap.add_argument("--spp", type=int, default=0, help="override the workload's spp (multiple of 8)")
     ap.add_argument("--paths-in-flight", type=int, default=0)
-    ap.add_argument("--frames-in-flight", type=int, default=2, help="independent frames kept in flight (each on its own stream, scene, pools and accumulator)")
+    ap.add_argument("--frames-in-flight", type=int, default=0,
+                    help="independent frames kept in flight (each on its own stream, scene, pools and accumulator); 0 = auto: 4, or 2 for jobs over 2^30 samples per rank and frame")
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
                     help="how the ranks' accumulators meet at world > 1: the library's fused peer-memory kernel, or torch.distributed all-reduce")
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
