@@ -64,12 +64,18 @@ class ClockSampler:
         self.index = index
         self.rows = []
         self.proc = None
+        self.i0 = 0
+
+    def mark(self):
+        """The timed region starts now: rows from here on (and the one just before, taken under the warm-up's load) are the ones reported.
+        The sampler itself is started earlier — nvidia-smi needs ~0.1 s before its first row, longer than a short timed region."""
+        self.i0 = max(len(self.rows) - 1, 0)
 
     def start(self):
         q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(self.index)],
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "25", "-i", str(self.index)],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -83,13 +89,16 @@ class ClockSampler:
     def stop(self) -> dict:
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        t0 = time.perf_counter()
+        while len(self.rows) <= self.i0 + 1 and time.perf_counter() - t0 < 0.3:   # a very short region: wait for the row that was being taken
+            time.sleep(0.01)
         self.proc.terminate()
         try:
             self.proc.wait(timeout=2)
         except Exception:
             self.proc.kill()
         sm, smax, reasons = [], [], set()
-        for r in self.rows:
+        for r in self.rows[self.i0:]:
             try:
                 sm.append(float(r[0]))
                 smax.append(float(r[1]))
@@ -179,13 +188,19 @@ class FrameBench:
         self.env = synthetic_sky() if self.envkind == "sky" else None
         W, H = self.W, self.H
         want = lanes if lanes is not None else args.frames_in_flight
+        self.tune = not want      # auto: lanes are built for the larger choice, prime() measures both and keeps the faster
         if not want:
-            # auto: what a frame cannot shrink with its sample count (deep waves of a few rays, the exchange, kernel tails) is hidden
-            # by the other frames in flight, and the shorter the frame the more of them it takes.  Measured, ball.gltf, ms per step with
-            # 2 | 4 frames in flight: 256 spp 25.53 | 25.50, 128 spp 13.03 | 12.97, 64 spp 6.70 | 6.62, 32 spp 3.65 | 3.51 (6: no better).
-            # Four everywhere the queue pools of four frames fit comfortably; two for the very large jobs (4K, 4096 spp).
+            # What a frame cannot shrink with its sample count (deep waves of a few rays, the exchange, kernel tails) is hidden by the other
+            # frames in flight, and the shorter the frame the more of them it takes — ball.gltf, ms per step with 2 | 4 frames in flight:
+            # 256 spp 25.61 | 25.54, 128 spp 13.03 | 12.97, 64 spp 6.70 | 6.62, 32 spp (one of 8 ranks) 3.65 | 3.51 (6: no better).  A frame
+            # whose waves are all large has nothing to hide and only pays for the extra queues (box.gltf: 9.16 | 9.37).  So the choice is
+            # MEASURED: prime() times a few untimed frames with 2 and with 4 and keeps the faster (rank 0 decides for all ranks).  Very
+            # large jobs (4K, 4096 spp) keep 2: four sets of queue pools would not fit.
             want = 4 if W * H * (self.spp // self.world) <= (1 << 30) else 2
+            self.tune = want == 4
+        self.tuning = None
         self.n_lanes = max(1, want)
+        self.n_built = self.n_lanes
         self.main = torch.cuda.current_stream()
         self.streams = [self.main] + [torch.cuda.Stream() for _ in range(self.n_lanes - 1)]
         self.ctxs, self.pts, self.acc_ts, self.accs, self.dscenes, self.fb_dev, self.fb_host = [], [], [], [], [], [], []
@@ -244,7 +259,7 @@ class FrameBench:
             self.dist.barrier(group=HOST_GROUP)                      # every rank has closed its mappings before any accumulator is freed
         for a in self.xaccs:
             a.close()
-        for k in range(self.n_lanes):
+        for k in range(self.n_built):
             self.dscenes[k].close()
             self.accs[k].close()
             self.ctxs[k].close()
@@ -328,6 +343,18 @@ class FrameBench:
         for k in range(self.n_lanes):
             self.frame(k, **kw)
         self.torch.cuda.synchronize()
+        if self.tune and self.n_lanes == 4:
+            built, res = self.n_lanes, {}
+            for n in (2, 4):
+                self.n_lanes = n
+                for i in range(n):
+                    self.frame(i, **kw)
+                res[n] = self.timed(lambda i: self.frame(i, **kw), 8) / 8
+            pick = [min(res, key=res.get)]
+            if self.world > 1:
+                self.dist.broadcast_object_list(pick, src=0, group=HOST_GROUP)
+            self.n_lanes, self.tune = int(pick[0]), False
+            self.tuning = {"ms_per_step_with_2": round(res[2], 3), "ms_per_step_with_4": round(res[4], 3), "lanes_built": built}
 
     def run_value(self, steps, warmup, **kw):
         self.prime(**kw)
@@ -459,13 +486,14 @@ def run_ours(args):
     ctx = fb.ctx
 
     # ---- value: device-resident inputs -------------------------------------------------------------------
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
     fb.prime()
     for i in range(args.warmup):
         fb.frame(i)
     fb.reset_counters()
-    clocks = ClockSampler(local)
-    if rank == 0:
-        clocks.start()
+    clocks.mark()
     ms_step = fb.timed(lambda i: fb.frame(i), args.steps) / args.steps
     host_ms_value = fb.host_ms
     clk = clocks.stop() if rank == 0 else {}
@@ -563,7 +591,7 @@ def run_ours(args):
             "metric": "Msamples/s (whole frames: transform + BVH build + render + resolve)", "value": round(value, 3), "unit": "Msamples/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 3), "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": fb.workload_name, "parallelism": f"spp-slices x{world}", "slices": N_SLICES, "frames_in_flight": fb.n_lanes,
+            "config": {"workload": fb.workload_name, "parallelism": f"spp-slices x{world}", "slices": N_SLICES, "frames_in_flight": fb.n_lanes, "frames_in_flight_tuning": fb.tuning,
                        "exchange": {"none": "single GPU: tpt_resolve_bgra8", "nccl": "NCCL all-reduce of the int64 accumulators, then tpt_resolve_bgra8 on every rank",
                                     "peer": "tpt_exchange_resolve: fused reduce-scatter + resolve over NVLink peer mappings (CUDA IPC), pixels to rank 0"}[fb.exchange],
                        "l2": "inputs larger than L2: every step writes and reads %.1f GB of wavefront records (%d M queued rays x 96 B) through "
@@ -1032,7 +1060,7 @@ def main():
     ap.add_argument("--spp", type=int, default=0, help="override the workload's spp (multiple of 8)")
     ap.add_argument("--paths-in-flight", type=int, default=0)
     ap.add_argument("--frames-in-flight", type=int, default=0,
-                    help="independent frames kept in flight (each on its own stream, scene, pools and accumulator); 0 = auto: 4, or 2 for jobs over 2^30 samples per rank and frame")
+                    help="independent frames kept in flight (each on its own stream, scene, pools and accumulator); 0 = auto: 2 or 4, whichever a few untimed frames show to be faster")
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
                     help="how the ranks' accumulators meet at world > 1: the library's fused peer-memory kernel, or torch.distributed all-reduce")
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
