@@ -96,6 +96,52 @@ def test_exchange_equals_one_render_resolved(world, tpt, ctx, scenes, tmp_path, 
         whole.close()
 
 
+def _worker_missing_rank(rank, world, port, out_dir):
+    import torch
+    import torch.distributed as dist
+    sys.path.insert(0, str(ROOT))
+    os.environ["TPT_EXCHANGE_TIMEOUT_MS"] = "400"              # read when the exchange is created
+    import tinypathtracer_b200 as tpt
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    dev = rank % torch.cuda.device_count()
+    torch.cuda.set_device(dev)
+    ctx = tpt.Context(dev)
+    acc = tpt.Accum(ctx, 32, 18)
+    x = tpt.FrameExchange(ctx, acc, rank, world)
+    x.connect_over(dist)
+    acc.clear()
+    x.resolve(1, 0)                                            # frame 1: everybody takes part
+    x.status()
+    dist.barrier()
+    outcome = "skipped"
+    if rank == 0:                                              # frame 2: rank 1 never calls resolve
+        x.resolve(1, 0)
+        try:
+            x.status()
+            outcome = "no error"
+        except tpt.TptError as e:
+            outcome = "timeout reported: " + str(e)
+    (Path(out_dir) / f"outcome_{rank}.txt").write_text(outcome)
+    dist.barrier()
+    x.close()
+    dist.barrier()
+    acc.close()
+    ctx.close()
+    dist.destroy_process_group()
+
+
+def test_a_rank_that_never_arrives_is_an_error_not_a_hang(tmp_path):
+    """The handshake polls peer memory from kernels; a peer that never signals must cost a time-out and an error from
+    tpt_exchange_status, never a GPU that spins for ever."""
+    import time
+    import torch.multiprocessing as mp
+    t0 = time.time()
+    mp.spawn(_worker_missing_rank, args=(2, _free_port(), str(tmp_path)), nprocs=2, join=True)
+    assert (tmp_path / "outcome_0.txt").read_text().startswith("timeout reported"), (tmp_path / "outcome_0.txt").read_text()
+    assert time.time() - t0 < 120
+
+
 def test_exchange_world_one_is_a_plain_resolve(tpt, ctx, scenes):
     s = scenes["box2"]
     cam = tpt.Camera.from_scene(s)
