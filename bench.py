@@ -222,6 +222,8 @@ class FrameBench:
         self.xaccs, self.xchg, self.fb_view = [], [], []
         if self.exchange == "peer":
             try:
+                if os.environ.get("TPT_BENCH_FAIL_EXCHANGE_ON_RANK") == str(self.rank):   # test hook for the fallback below
+                    raise tpt.TptError("forced by TPT_BENCH_FAIL_EXCHANGE_ON_RANK")
                 for k in range(self.n_lanes):
                     a = tpt.Accum(self.ctxs[k], W, H)                # the library's own allocation: peers map it through CUDA IPC
                     x = tpt.FrameExchange(self.ctxs[k], a, self.rank, self.world, alpha=0)
@@ -230,19 +232,29 @@ class FrameBench:
                 ok = 1
             except tpt.TptError as e:
                 ok, self.exchange_note = 0, str(e)
-            flags = [None] * self.world
-            dist.all_gather_object(flags, ok, group=HOST_GROUP)
-            if all(flags):
+            # every collective first, then the local part that can fail: no rank is ever left alone in an all_gather
+            mine = [x.handle for x in self.xchg] if ok else None
+            everyone = [None] * self.world
+            dist.all_gather_object(everyone, mine, group=HOST_GROUP)
+            if all(h is not None for h in everyone):
                 try:
-                    for x in self.xchg:
-                        x.connect_over(dist, group=HOST_GROUP)
+                    for k, x in enumerate(self.xchg):
+                        x.connect([everyone[r][k] for r in range(self.world)])
                 except tpt.TptError as e:
                     ok, self.exchange_note = 0, str(e)
-                dist.all_gather_object(flags, ok, group=HOST_GROUP)
+            else:
+                ok = 0
+            flags = [None] * self.world
+            dist.all_gather_object(flags, ok, group=HOST_GROUP)
             if not all(flags):                                       # e.g. no IPC in this container: say so and use the library collective
                 if self.rank == 0:
                     print(f"bench.py: peer exchange unavailable ({self.exchange_note or 'another rank failed'}); using NCCL", file=sys.stderr)
                 self.exchange, self.exchange_note = "nccl", self.exchange_note or "another rank could not set up the peer exchange"
+                for x in self.xchg:
+                    x.close()
+                for a in self.xaccs:
+                    a.close()
+                self.xchg, self.xaccs = [], []
             else:
                 self.fb_view = [torch.as_tensor(_DevicePtr(x.framebuffer_ptr(), (H, W, 4)), device="cuda") for x in self.xchg]
         self.cam = tpt.Camera.from_scene(self.scene)
