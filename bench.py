@@ -429,6 +429,38 @@ class FrameBench:
         self.torch.cuda.synchronize()
         return hashlib.sha256(self.acc_ts[0].cpu().numpy().tobytes()).hexdigest() if self.rank == 0 else None
 
+    def exchange_alone(self, reps=5):
+        """The exchange by itself on otherwise idle GPUs: CUDA events around tpt_exchange_resolve (handshake + fused reduce + resolve
+        + completion wait) after a barrier, max over ranks, best of `reps`; and the NCCL all-reduce + full resolve it replaces."""
+        if self.world == 1:
+            return None
+        import ctypes as C
+        from tinypathtracer_b200._capi import lib, check
+        torch, dist = self.torch, self.dist
+        out = {}
+        for mode in (["peer"] if self.exchange == "peer" else []) + ["nccl"]:
+            best = None
+            for _ in range(reps + 1):
+                self.barrier()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(self.main)
+                if mode == "peer":
+                    self.xchg[0].resolve(self.spp, 0)
+                else:
+                    dist.all_reduce(self.acc_ts[0], op=dist.ReduceOp.SUM)
+                    check(lib.tpt_resolve_bgra8(self.accs[0]._h, self.spp, C.c_void_p(self.fb_dev[0].data_ptr()), 1))
+                e1.record(self.main)
+                torch.cuda.synchronize()
+                t = torch.tensor([e0.elapsed_time(e1)], device="cuda", dtype=torch.float64)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                best = float(t.item()) if best is None else min(best, float(t.item()))   # the first repetition is a warm-up
+            out[mode + "_ms"] = round(best, 4)
+        n, px = self.world, self.W * self.H
+        if "peer_ms" in out:
+            out["peer_bytes_in_per_rank"] = (n - 1) * (px // n) * 24
+            out["peer_gbs_in_per_rank"] = round(out["peer_bytes_in_per_rank"] / (out["peer_ms"] * 1e-3) / 1e9, 1)
+        return out
+
     def exchange_check(self):
         """The peer exchange's framebuffer on rank 0 against all-reduce + tpt_resolve_bgra8 of the same frame: must be the same bytes."""
         if self.exchange != "peer":
@@ -530,6 +562,7 @@ def run_ours(args):
     # ---- determinism evidence: SHA-256 of the all-reduced int64 accumulation buffer of one more frame (untimed)
     accum_sha = fb.accum_sha()
     exchange_ok = fb.exchange_check()
+    exchange_alone = fb.exchange_alone()
 
     line = None
     if rank == 0:
@@ -615,6 +648,7 @@ def run_ours(args):
             "host_enqueue_ms_per_step": {"value": round(host_ms_value, 3), "e2e": round(host_ms_e2e, 3)},   # rank 0's host time to enqueue one step
             "exchange_matches_allreduce": exchange_ok,   # peer exchange's framebuffer == all-reduce + resolve of the same frame, byte for byte (None: not used)
             "exchange_note": fb.exchange_note,
+            "exchange_alone": exchange_alone,   # the exchange of one frame on idle GPUs (max over ranks, best of 5): peer kernel vs NCCL all-reduce + resolve
             "frame_latency_ms": round(ms_serial, 3),   # one frame alone on one lane (no overlap); ms_per_step = timed region / steps with frames_in_flight
             "e2e": {"value": round(e2e_value, 3), "unit": "Msamples/s", "ms_per_step": round(ms_e2e, 3),
                     "h2d_bytes_per_step": scene_upload_bytes(fb.scene), "d2h_bytes_per_step": W * H * 4,
