@@ -463,14 +463,16 @@ int tpt_bvh_build_impl(tpt_scene* s) {
     k_init_bounds<<<1, 32, 0, st>>>(s->bounds);
     k_transform<<<min(persistent, (int)grid_for(V, 256)), 256, 0, st>>>(s->obj_verts, s->obj_norms, s->vert_obj, s->vert_trans,
                                                                          s->normal_trans, V, s->world_verts, s->world_norms, s->bounds);
-    // 63-bit keys like the reference (21 bits per axis); from 2^20 triangles on, 16 bits per axis (65 536^3 cells is still far
-    // finer than the triangles, equal keys are ordered by index) so that the radix sort runs 6 passes instead of 8
-    // 63-bit keys like the reference (21 bits per axis); from 2^20 triangles on, 13 bits per axis (8 192^3 cells: at 10 M triangles still
-    // ~50 000 cells per triangle; equal keys are ordered by index) so that the radix sort runs 5 passes instead of 8
-    const int bitsPerAxis = F >= (1 << 20) ? 13 : 21;
-    const int keyBits = 3 * bitsPerAxis;
+    // 63-bit keys like the reference (21 bits per axis) below 2^20 triangles.  From there on the radix passes are what the keys cost, and the
+    // tree does not need the resolution: 11 bits per axis, the 33-bit interleaved key cut to 32 bits (x keeps 10) = 4 passes instead of 8;
+    // 2^32 cells are >= 256 per triangle up to 2^24 triangles, equal keys are ordered by index.  Measured on the 10 M-triangle soup
+    // (bits per axis: build ms | primary, secondary Mrays/s | SAH cost): 13: 1.905 | 2 269, 1 275 | 149.1; 11: 1.725 | 2 257, 1 277 | 149.2;
+    // 10: 1.697 | 2 258, 1 280 | 149.4; 9: 1.650 | 2 226, 1 238 | 152.5; 8 (3 passes): 1.477 | 2 162, 1 204 | 159.9.  Above 2^24 triangles: 13 bits, 5 passes.
+    static const int bitsEnv = getenv("TPT_MORTON_BITS_LARGE") ? atoi(getenv("TPT_MORTON_BITS_LARGE")) : 0;   // tuning switch (8..21)
+    const int bitsPerAxis = F < (1 << 20) ? 21 : bitsEnv > 0 ? bitsEnv : F <= (1 << 24) ? 11 : 13;
+    const int keyBits = 3 * bitsPerAxis - morton_key_shift(bitsPerAxis);
     // Sorted (key, face) pairs must end in keys[1] / vals[1]; keys[0] / vals[0] are scratch afterwards.
-    const int nPasses = (keyBits + 7) / 8;   // 5 or 8
+    const int nPasses = (keyBits + 7) / 8;   // 4, 5 or 8
     const int first = (nPasses & 1) ? 0 : 1; // the ping-pong starts in the buffer that makes it END in buffer 1
     if (F <= kSortTile) {
         k_sort_small<<<1, kSortThreads, 0, st>>>(s->indices, s->world_verts, s->bounds, (uint32_t)F, bitsPerAxis, nPasses, s->keys[1], s->vals[1]);

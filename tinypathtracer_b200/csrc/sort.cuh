@@ -118,7 +118,10 @@ __device__ __forceinline__ void digit_scan(SortSmem& sm, uint32_t count) {
 struct MortonParams {
     float3 bmin, scale;
     float qmax;
+    int shift;   // low bits of the interleaved key that are dropped (x's, then y's last bit) so that the key fills whole 8-bit digits
 };
+// 3 * bits that is 1 or 2 above a multiple of 8 (11 bits per axis: 33) is cut down to the multiple: one radix pass fewer for the last bit of one axis
+__host__ __device__ __forceinline__ int morton_key_shift(int bitsPerAxis) { return ((3 * bitsPerAxis) & 7) <= 2 ? ((3 * bitsPerAxis) & 7) : 0; }
 __device__ __forceinline__ uint64_t sort_expand21(uint64_t x) {
     x &= 0x1fffffull;
     x = (x | x << 32) & 0x1f00000000ffffull;
@@ -139,7 +142,7 @@ __device__ __forceinline__ unsigned long long face_key(const uint32_t* __restric
     const uint64_t qx = (uint64_t)fminf(fmaxf(q.x, 0.f), mp.qmax);
     const uint64_t qy = (uint64_t)fminf(fmaxf(q.y, 0.f), mp.qmax);
     const uint64_t qz = (uint64_t)fminf(fmaxf(q.z, 0.f), mp.qmax);
-    return sort_expand21(qx) | (sort_expand21(qy) << 1) | (sort_expand21(qz) << 2);
+    return (sort_expand21(qx) | (sort_expand21(qy) << 1) | (sort_expand21(qz) << 2)) >> mp.shift;
 }
 __device__ __forceinline__ MortonParams morton_params(const uint32_t* __restrict__ bounds, int bitsPerAxis) {
     const float3 bmin = f3(ord2f(bounds[0]), ord2f(bounds[1]), ord2f(bounds[2]));
@@ -150,6 +153,7 @@ __device__ __forceinline__ MortonParams morton_params(const uint32_t* __restrict
     mp.bmin = bmin;
     mp.scale = f3(ext.x > 0.f ? k / ext.x : 0.f, ext.y > 0.f ? k / ext.y : 0.f, ext.z > 0.f ? k / ext.z : 0.f);
     mp.qmax = k - 1.0f;
+    mp.shift = morton_key_shift(bitsPerAxis);
     return mp;
 }
 
