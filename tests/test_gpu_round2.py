@@ -163,6 +163,53 @@ def test_wide_and_binary_walks_agree(capsys):
         print("\n[wide vs binary] " + "; ".join(lines))
 
 
+_BUILD_SNIPPET = r"""
+import sys, hashlib, json
+sys.path.insert(0, {root!r})
+import numpy as np
+import tinypathtracer_b200 as tpt
+from tinypathtracer_b200.scene_io import load_scene_npz
+from tinypathtracer_b200.soup import make_soup
+out = {{}}
+ctx = tpt.Context(0)
+ball = load_scene_npz({root!r} + "/tests/golden/scenes/ball.npz")
+for name in ["box", "box1", "box2", "tir", "ball", "light", "square", "soup_small", "soup"]:
+    scene = make_soup(ball, 64, 25) if name == "soup" else make_soup(ball, 3, 40) if name == "soup_small" else \
+        load_scene_npz({root!r} + "/tests/golden/scenes/" + name + ".npz")
+    ds = tpt.DeviceScene(ctx, scene)
+    bvh = tpt.BVH(ds)
+    st = bvh.construct(stats=True)
+    nodes = bvh.m_nodes                        # the reference's node layout: boxes, children, parents, leaf face ids
+    keys, faces = bvh.order()
+    # a refit on the same topology reads the parents / range ends the build left behind
+    bvh.refit()
+    again = bvh.m_nodes
+    out[name] = [hashlib.sha256(nodes.tobytes()).hexdigest(), hashlib.sha256(faces.tobytes()).hexdigest(), hashlib.sha256(again.tobytes()).hexdigest(),
+                 int(st["n_faces"]), int(st["max_depth"])]
+    ds.close()
+print(json.dumps(out))
+"""
+
+
+def test_bottom_up_hierarchy_is_the_search_based_tree():
+    """A full build emits the hierarchy in the bottom-up walk (k_leaves_build / k_build_upper); TPT_BUILD_KARRAS=1 runs the
+    search-based k_hierarchy + refit walk instead.  Same nodes (boxes, children, parents, leaf order) byte for byte on every
+    fixture, a 3 672-triangle and a 78 124-triangle soup (many blocks, many equal keys), and a refit over either gives the same."""
+    import json
+
+    def run(extra):
+        env = dict(os.environ)
+        env.update(extra)
+        r = subprocess.run([sys.executable, "-c", _BUILD_SNIPPET.format(root=str(ROOT))], capture_output=True, text=True, env=env, timeout=900)
+        assert r.returncode == 0, r.stderr[-3000:]
+        return json.loads(r.stdout.strip().splitlines()[-1])
+
+    walk, search = run({}), run({"TPT_BUILD_KARRAS": "1"})
+    assert walk == search
+    for name, v in walk.items():
+        assert v[0] == v[2], name      # refit of unchanged geometry reproduces the build's nodes
+
+
 def test_lazy_normal_records_of_large_scenes(tpt, ctx, scenes, orc):
     """Scenes of 65 536 triangles and more leave the per-leaf shading-normal records out of the build (k_leaf_normals writes them
     when a render first needs them): the image must be the oracle's, the first and a later render of the same build identical,

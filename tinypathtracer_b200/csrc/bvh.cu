@@ -200,6 +200,214 @@ __global__ void __launch_bounds__(kRefitBlock) k_leaves_refit(const uint32_t* __
     }
 }
 
+// ---- hierarchy emitted BY the bottom-up walk (full builds) ---------------------------------------------------------------------
+// k_hierarchy finds every node's range and split with binary searches over the keys — as many steps as the longest range in the
+// warp, 14 of 32 lanes busy, 0.29 ms at 10 M triangles — and only then can the refit walk start.  The walk can find the tree
+// itself (Apetrei 2014): a finished node [l, r] joins the neighbour it shares the longer key prefix with — to the right if
+// delta(r, r+1) > delta(l-1, l) (it is the LEFT child of the node split between r and r+1), else to the left — and meets its
+// sibling at that split.  Two key reads per level instead of a search, no separate pass.  The numbering stays Karras': a left
+// child is node `r` (its range's right end), a right child node `l`, the root node 0 — so the nodes, parents and range ends
+// written here are THE arrays k_hierarchy + k_leaves_refit + k_refit_upper produce, bit for bit (tests/test_gpu_parity.py
+// compares them with the reference's tree; TPT_BUILD_KARRAS=1 runs the old kernels).  What changes is where siblings meet: a node's
+// own index is only known once BOTH children are there (its direction depends on its whole range), so the first arrival cannot
+// write into the node; it leaves (box, id, far end of its range) in a slot of the SPLIT position instead, and the second arrival
+// writes the finished 64-byte node in one piece.
+//   k_leaves_build  one thread per sorted leaf: triangle record, then up while the parent's whole range lies inside the block's
+//                   256 leaves (slots and keys in shared memory).  Whether it does is one more prefix comparison: the parent of
+//                   a left child ends before the block does iff delta(split+1, first key after the block) < delta(split, split+1).
+//                   At the first parent that spans blocks: global slot + arrival counter; the second arrival queues the split.
+//   k_build_upper   one thread per queued split finishes the walk to the root with the global protocol (as k_refit_upper).
+struct MergeHalf {   // 32 bytes: what a child leaves at its parent's split
+    float mnx, mny, mnz, mxx, mxy, mxz;
+    int id;    // ~leaf, or the child's node index
+    int end;   // the far end of the child's range: its first leaf for a left child, its last for a right child
+};
+__device__ __forceinline__ void merge_store_global(float4* slot, const MergeHalf& h) {
+    __stcg(slot, make_float4(h.mnx, h.mny, h.mnz, h.mxx));
+    __stcg(slot + 1, make_float4(h.mxy, h.mxz, __int_as_float(h.id), __int_as_float(h.end)));
+}
+__device__ __forceinline__ MergeHalf merge_load_global(const float4* slot) {
+    const float4 a = __ldcg(slot), b = __ldcg(slot + 1);
+    return MergeHalf{a.x, a.y, a.z, a.w, b.x, b.y, __float_as_int(b.z), __float_as_int(b.w)};
+}
+// the finished node `k` with children L (range [first, split]) and R ([split+1, last]): record, parents, range end
+__device__ __forceinline__ void write_node(float4* __restrict__ nodes, int* __restrict__ parentInt, int* __restrict__ parentLeaf, int* __restrict__ rangeOther,
+                                           int k, const MergeHalf& L, const MergeHalf& R) {
+    float4* node = nodes + 4 * (size_t)k;
+    __stcg(node + 0, make_float4(L.mnx, L.mxx, L.mny, L.mxy));
+    __stcg(node + 1, make_float4(R.mnx, R.mxx, R.mny, R.mxy));
+    __stcg(node + 2, make_float4(L.mnz, L.mxz, R.mnz, R.mxz));
+    __stcg(reinterpret_cast<int4*>(node + 3), make_int4(L.id, R.id, 0, 0));
+    if (L.id < 0) parentLeaf[~L.id] = k; else parentInt[L.id] = k;
+    if (R.id < 0) parentLeaf[~R.id] = k; else parentInt[R.id] = k;
+    rangeOther[k] = (k == R.end) ? L.end : R.end;   // node k is one end of its range [L.end, R.end]; the root (k = 0 = L.end) gets R.end
+}
+__device__ __forceinline__ MergeHalf merge_union(const MergeHalf& L, const MergeHalf& R) {
+    return MergeHalf{fminf(L.mnx, R.mnx), fminf(L.mny, R.mny), fminf(L.mnz, R.mnz), fmaxf(L.mxx, R.mxx), fmaxf(L.mxy, R.mxy), fmaxf(L.mxz, R.mxz), 0, 0};
+}
+
+// The walk inside a block needs delta() only between NEIGHBOURS and between a position and the block's edges, and for sorted
+// (key, index) pairs delta(x, y) is the minimum of the neighbour deltas in between.  So the block computes adj[j] = delta(j, j+1)
+// for j = b0-1 .. bEnd once (one coalesced key read per thread) and its running minima from either edge; a step of the walk is
+// then three shared-memory integer loads instead of six 64-bit key comparisons.
+constexpr int kDeltaInf = 1 << 20;
+__global__ void __launch_bounds__(kRefitBlock) k_leaves_build(const unsigned long long* __restrict__ keys, const uint32_t* __restrict__ sortedFaces,
+                                                      const uint32_t* __restrict__ indices, const float* __restrict__ worldVerts,
+                                                      const float* __restrict__ worldNorms, const uint32_t* __restrict__ faceMtl, int nFaces,
+                                                      int* __restrict__ parentInt, int* __restrict__ parentLeaf, int* __restrict__ rangeOther,
+                                                      uint32_t* __restrict__ flags, float4* __restrict__ slots, float4* __restrict__ nodes,
+                                                      float4* __restrict__ triGeom, float4* __restrict__ triNorm, int* __restrict__ frontier,
+                                                      uint32_t* __restrict__ frontierCount) {
+    __shared__ unsigned sFlag[kRefitBlock];
+    __shared__ MergeHalf sHalf[kRefitBlock][2];
+    __shared__ int sAdj[kRefitBlock + 1];    // sAdj[i] = delta(w0 + i, w0 + i + 1), w0 = b0 - 1: the pairs (b0-1, b0) ... (bEnd, bEnd+1); -1 beyond the array
+    __shared__ int sPre[kRefitBlock + 1];    // sPre[i + 1] = min(sAdj[0 .. i]) = delta(b0 - 1, w0 + i + 1); sPre[0] = inf (empty)
+    __shared__ int sSuf[kRefitBlock + 2];    // sSuf[i] = min(sAdj[i .. 256]) = delta(w0 + i, bEnd + 1), i >= 1; sSuf[257] = inf (empty)
+    __shared__ int sWarp[2][kRefitBlock / 32];
+    const int b0 = blockIdx.x * kRefitBlock, w0 = b0 - 1;   // the block's leaves are b0 .. bEnd = b0 + 255
+    const int t = threadIdx.x, lane = t & 31, wrp = t >> 5;
+    sFlag[t] = 0u;
+    {
+        const int a0 = delta(keys, nFaces, min(max(w0 + t, 0), nFaces - 1), (w0 + t < 0 || w0 + t >= nFaces) ? -1 : w0 + t + 1);         // pair (w0+t, w0+t+1)
+        const int a1 = delta(keys, nFaces, min(w0 + t + 1, nFaces - 1), (w0 + t + 1 >= nFaces) ? -1 : w0 + t + 2);                       // pair (w0+t+1, w0+t+2)
+        sAdj[t] = a0;
+        if (t == kRefitBlock - 1) sAdj[kRefitBlock] = a1;
+        // running minima: prefix over sAdj[0..255] (thread t owns element t), suffix over sAdj[1..256] (thread t owns element t + 1 = a1)
+        int pre = a0, suf = a1;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int x = __shfl_up_sync(0xffffffffu, pre, o), y = __shfl_down_sync(0xffffffffu, suf, o);
+            if (lane >= o) pre = min(pre, x);
+            if (lane + o < 32) suf = min(suf, y);
+        }
+        if (lane == 31) sWarp[0][wrp] = pre;
+        if (lane == 0) sWarp[1][wrp] = suf;
+        __syncthreads();
+        for (int w = 0; w < wrp; ++w) pre = min(pre, sWarp[0][w]);
+        for (int w = wrp + 1; w < kRefitBlock / 32; ++w) suf = min(suf, sWarp[1][w]);
+        sPre[t + 1] = pre;
+        sSuf[t + 1] = suf;
+        if (t == 0) {
+            sPre[0] = kDeltaInf;
+            sSuf[kRefitBlock + 1] = kDeltaInf;
+            sSuf[0] = kDeltaInf;   // never read
+        }
+    }
+    __syncthreads();
+    const int leaf = b0 + t;
+    if (leaf >= nFaces) return;
+    const uint32_t f = sortedFaces[leaf];
+    const uint32_t i0 = indices[3 * f], i1 = indices[3 * f + 1], i2 = indices[3 * f + 2];
+    const float3 a = f3(worldVerts[3 * i0], worldVerts[3 * i0 + 1], worldVerts[3 * i0 + 2]);
+    const float3 b = f3(worldVerts[3 * i1], worldVerts[3 * i1 + 1], worldVerts[3 * i1 + 2]);
+    const float3 c = f3(worldVerts[3 * i2], worldVerts[3 * i2 + 1], worldVerts[3 * i2 + 2]);
+    const float3 e1 = xsub3(b, a), e2 = xsub3(c, a);   // exactly the edges Möller–Trumbore forms per test in the reference
+    __stcs(triGeom + 3 * (size_t)leaf + 0, make_float4(a.x, a.y, a.z, e1.x));
+    __stcs(triGeom + 3 * (size_t)leaf + 1, make_float4(e1.y, e1.z, e2.x, e2.y));
+    __stcs(triGeom + 3 * (size_t)leaf + 2, make_float4(e2.z, __int_as_float((int)f), __int_as_float((int)faceMtl[f]), 0.f));
+    if (triNorm != nullptr) {   // small scenes: with the leaf; large ones: k_leaf_normals, when a render first needs them
+        const float3 n0 = f3(worldNorms[3 * i0], worldNorms[3 * i0 + 1], worldNorms[3 * i0 + 2]);
+        const float3 n1 = f3(worldNorms[3 * i1], worldNorms[3 * i1 + 1], worldNorms[3 * i1 + 2]);
+        const float3 n2 = f3(worldNorms[3 * i2], worldNorms[3 * i2 + 1], worldNorms[3 * i2 + 2]);
+        __stcs(triNorm + 3 * (size_t)leaf + 0, make_float4(n0.x, n0.y, n0.z, n1.x));
+        __stcs(triNorm + 3 * (size_t)leaf + 1, make_float4(n1.y, n1.z, n2.x, n2.y));
+        __stcs(triNorm + 3 * (size_t)leaf + 2, make_float4(n2.z, 0.f, 0.f, 0.f));
+    }
+    if (nFaces == 1) return;
+
+    const float3 mn = fmin3(fmin3(a, b), c), mx = fmax3(fmax3(a, b), c);
+    MergeHalf me{mn.x, mn.y, mn.z, mx.x, mx.y, mx.z, ~leaf, leaf};
+    int l = leaf, r = leaf;
+    // which way the current node goes: the LEFT child of the node split at r (delta(r, r+1) is the longer prefix), or the RIGHT
+    // child of the node split at l - 1.  adj(j) = sAdj[j - w0]; the ends of the array have adj = -1, so they decide themselves.
+    bool goRight = sAdj[r - w0] > sAdj[l - 1 - w0];
+    while (true) {
+        const int split = goRight ? r : l - 1, side = goRight ? 0 : 1;
+        me.end = goRight ? l : r;
+        const int q = sAdj[split - w0];
+        // does the parent's whole range lie in this block?  left child: iff delta(split + 1, bEnd + 1) < q; right child: iff
+        // delta(b0 - 1, split) < q (empty ranges — the sibling starts outside the block — are inf: no)
+        const bool inBlock = goRight ? sSuf[split + 1 - w0] < q : sPre[split - w0] < q;
+        MergeHalf sib;
+        if (inBlock) {
+            const int k = split - b0;
+            sHalf[k][side] = me;
+            __threadfence_block();
+            if (atomicAdd(&sFlag[k], 1u) == 0u) return;   // first arrival: the sibling will finish this node
+            __threadfence_block();
+            const volatile float* sf = reinterpret_cast<const volatile float*>(&sHalf[k][side ^ 1]);
+            const volatile int* si = reinterpret_cast<const volatile int*>(&sHalf[k][side ^ 1]);
+            sib = MergeHalf{sf[0], sf[1], sf[2], sf[3], sf[4], sf[5], si[6], si[7]};
+        } else {
+            merge_store_global(slots + 4 * (size_t)split + 2 * side, me);
+            __threadfence();
+            if (atomicAdd(flags + split, 1u) == 1u) frontier[atomicAdd(frontierCount, 1u)] = split;   // complete: k_build_upper goes on
+            return;
+        }
+        const MergeHalf& L = side == 0 ? me : sib;
+        const MergeHalf& R = side == 0 ? sib : me;
+        l = L.end;
+        r = R.end;
+        int k = 0;
+        const bool root = l == 0 && r == nFaces - 1;
+        if (!root) {
+            goRight = sAdj[r - w0] > sAdj[l - 1 - w0];
+            k = goRight ? r : l;
+        }
+        write_node(nodes, parentInt, parentLeaf, rangeOther, k, L, R);
+        if (root) {
+            parentInt[0] = -1;
+            return;
+        }
+        const MergeHalf u = merge_union(L, R);
+        me = u;
+        me.id = k;
+    }
+}
+
+__global__ void __launch_bounds__(256) k_build_upper(const unsigned long long* __restrict__ keys, int nFaces, const int* __restrict__ frontier,
+                                                     const uint32_t* __restrict__ frontierCount, int* __restrict__ parentInt,
+                                                     int* __restrict__ parentLeaf, int* __restrict__ rangeOther, uint32_t* __restrict__ flags,
+                                                     float4* __restrict__ slots, float4* __restrict__ nodes) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= *frontierCount) return;
+    int split = frontier[t];
+    MergeHalf L = merge_load_global(slots + 4 * (size_t)split), R = merge_load_global(slots + 4 * (size_t)split + 2);
+    while (true) {
+        const int l = L.end, r = R.end;
+        const bool root = l == 0 && r == nFaces - 1;
+        bool goRight = false;
+        int k = 0;
+        if (!root) {
+            goRight = l == 0 ? true : r == nFaces - 1 ? false : delta(keys, nFaces, r, r + 1) > delta(keys, nFaces, l - 1, l);
+            k = goRight ? r : l;
+        }
+        write_node(nodes, parentInt, parentLeaf, rangeOther, k, L, R);
+        if (root) {
+            parentInt[0] = -1;
+            return;
+        }
+        MergeHalf me = merge_union(L, R);
+        me.id = k;
+        me.end = goRight ? l : r;
+        split = goRight ? r : l - 1;
+        const int side = goRight ? 0 : 1;
+        float4* slot = slots + 4 * (size_t)split;
+        merge_store_global(slot + 2 * side, me);
+        __threadfence();
+        if (atomicAdd(flags + split, 1u) == 0u) return;   // first arrival: the sibling will finish this node
+        __threadfence();
+        const MergeHalf sib = merge_load_global(slot + 2 * (side ^ 1));   // written by another SM: L2 loads
+        if (side == 0) {
+            L = me;
+            R = sib;
+        } else {
+            L = sib;
+            R = me;
+        }
+    }
+}
+
 // The per-leaf shading-normal records (read only by the renderer's shade step, never by traversal), for scenes whose build
 // left them out: a 10 M-triangle build that is only traced (tpt_trace_rays) does not pay 36 B of gathers + 48 B of writes per leaf.
 __global__ void __launch_bounds__(256) k_leaf_normals(const uint32_t* __restrict__ sortedFaces, const uint32_t* __restrict__ indices,
@@ -502,23 +710,30 @@ int tpt_bvh_build_impl(tpt_scene* s) {
         }
     }
     TPT_CUDA(cudaGetLastError());
-    if (F > 1) {
-        TPT_CUDA(cudaMemsetAsync(s->flags, 0, (size_t)(F - 1) * sizeof(uint32_t), st));
-        // vals[0] / keys[0] were the sort's input and are free now: range ends and the refit frontier live there
-        k_hierarchy<<<grid_for(F - 1, 256), 256, 0, st>>>(s->keys[1], F, s->nodes, s->parent_int, s->parent_leaf,
-                                                          reinterpret_cast<int*>(s->vals[0]));
-    }
+    // vals[0] / keys[0] were the sort's input and are free now: range ends and the walk's frontier live there
     int* frontier = reinterpret_cast<int*>(s->keys[0]);
-    k_leaves_refit<<<grid_for(F, kRefitBlock), kRefitBlock, 0, st>>>(s->vals[1], s->indices, s->world_verts, s->world_norms, s->face_mtl, F,
-                                                                     s->parent_int, s->parent_leaf, reinterpret_cast<const int*>(s->vals[0]),
-                                                                     s->flags, s->nodes, s->tri_geom, lazyNormals ? nullptr : s->tri_norm, frontier, s->bounds + 6);
-    if (F > 1) k_refit_upper<<<grid_for((size_t)F / 2 + 1, 256), 256, 0, st>>>(frontier, s->bounds + 6, s->parent_int, s->flags, s->nodes);
+    int* rangeOther = reinterpret_cast<int*>(s->vals[0]);
+    if (F > 1) TPT_CUDA(cudaMemsetAsync(s->flags, 0, (size_t)(F - 1) * sizeof(uint32_t), st));
+    static const bool karras = getenv("TPT_BUILD_KARRAS") != nullptr;   // test / tuning switch: the search-based hierarchy + refit walk
+    if (karras) {
+        if (F > 1) k_hierarchy<<<grid_for(F - 1, 256), 256, 0, st>>>(s->keys[1], F, s->nodes, s->parent_int, s->parent_leaf, rangeOther);
+        k_leaves_refit<<<grid_for(F, kRefitBlock), kRefitBlock, 0, st>>>(s->vals[1], s->indices, s->world_verts, s->world_norms, s->face_mtl, F,
+                                                                         s->parent_int, s->parent_leaf, rangeOther,
+                                                                         s->flags, s->nodes, s->tri_geom, lazyNormals ? nullptr : s->tri_norm, frontier, s->bounds + 6);
+        if (F > 1) k_refit_upper<<<grid_for((size_t)F / 2 + 1, 256), 256, 0, st>>>(frontier, s->bounds + 6, s->parent_int, s->flags, s->nodes);
+    } else {
+        k_leaves_build<<<grid_for(F, kRefitBlock), kRefitBlock, 0, st>>>(s->keys[1], s->vals[1], s->indices, s->world_verts, s->world_norms, s->face_mtl, F,
+                                                                         s->parent_int, s->parent_leaf, rangeOther, s->flags, s->merge_slots, s->nodes,
+                                                                         s->tri_geom, lazyNormals ? nullptr : s->tri_norm, frontier, s->bounds + 6);
+        if (F > 1) k_build_upper<<<grid_for((size_t)F / 2 + 1, 256), 256, 0, st>>>(s->keys[1], F, frontier, s->bounds + 6, s->parent_int, s->parent_leaf,
+                                                                                  rangeOther, s->flags, s->merge_slots, s->nodes);
+    }
     if (F > 1 && s->nodes4) {
         k_collapse4<<<grid_for((size_t)F - 1, 256), 256, 0, st>>>(s->nodes, F - 1, s->nodes4);
         ctx->kernel_launches += 1;
     }
     TPT_CUDA(cudaGetLastError());
-    ctx->kernel_launches += 5 + (F <= kSortTile ? 1 : 1 + nPasses);
+    ctx->kernel_launches += (karras ? 5 : 4) + (F <= kSortTile ? 1 : 1 + nPasses);
     s->built = true;
     s->geom_epoch = ++g_geom_epoch;   // unique across scenes: a new scene at a recycled address never matches a cached key
     if (!lazyNormals) s->norm_epoch = s->geom_epoch;

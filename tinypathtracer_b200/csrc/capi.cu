@@ -205,7 +205,7 @@ int tpt_scene_destroy(tpt_scene* s) {
     cudaFree(s->indices); cudaFree(s->obj_verts); cudaFree(s->obj_norms); cudaFree(s->vert_obj); cudaFree(s->face_mtl);
     cudaFree(s->objects); cudaFree(s->vert_trans); cudaFree(s->normal_trans); cudaFree(s->mtl_table); cudaFree(s->lights);
     cudaFree(s->world_verts); cudaFree(s->world_norms); cudaFree(s->keys[0]); cudaFree(s->keys[1]); cudaFree(s->vals[0]);
-    cudaFree(s->vals[1]); cudaFree(s->sort_tmp); cudaFree(s->parent_int); cudaFree(s->parent_leaf); cudaFree(s->flags);
+    cudaFree(s->vals[1]); cudaFree(s->sort_tmp); cudaFree(s->parent_int); cudaFree(s->parent_leaf); cudaFree(s->flags); cudaFree(s->merge_slots);
     cudaFree(s->bounds); cudaFree(s->nodes); cudaFree(s->nodes4); cudaFree(s->tri_geom); cudaFree(s->tri_norm);
     for (int k = 0; k < 4; ++k) {
         if (s->h_mtl[k]) cudaFreeHost(s->h_mtl[k]);
@@ -293,6 +293,7 @@ int tpt_scene_create(tpt_context* ctx, const tpt_scene_desc* d, tpt_scene** out)
     A(dev_alloc(&s->keys[0], F)); A(dev_alloc(&s->keys[1], F)); A(dev_alloc(&s->vals[0], F)); A(dev_alloc(&s->vals[1], F));
     A(dev_alloc(&s->parent_int, F)); A(dev_alloc(&s->parent_leaf, F)); A(dev_alloc(&s->flags, F)); A(dev_alloc(&s->bounds, 8));
     A(dev_alloc(&s->nodes, 4 * F)); A(dev_alloc(&s->tri_geom, 3 * F)); A(dev_alloc(&s->tri_norm, 3 * F));
+    A(dev_alloc(&s->merge_slots, 4 * F));
     // 4-wide compressed nodes beside the binary ones (64 B per internal node; traverse.cuh) — OPT-IN: TPT_WIDE_MIN_FACES=<n> builds and
     // walks them for scenes of n triangles and more (the tests use 2).  Measured on the 10 M-triangle soup they halve the node visits
     // (72.9 -> 36.7 per incoherent ray) but not the time (1 274 vs 1 279 Mrays/s; coherent primary rays 1 893 vs 2 270): a wide visit

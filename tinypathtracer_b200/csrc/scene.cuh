@@ -125,6 +125,7 @@ struct tpt_scene {
     int* parent_int = nullptr;    // parent of internal node i
     int* parent_leaf = nullptr;   // parent of leaf i
     uint32_t* flags = nullptr;    // refit arrival counters
+    float4* merge_slots = nullptr;   // build: 2 x 32 B per split position, what the first child to arrive leaves for its sibling (bvh.cu, k_leaves_build)
     uint32_t* bounds = nullptr;   // 6 ordered-uint encoded floats (min xyz, max xyz)
     float4* nodes = nullptr;
     float4* nodes4 = nullptr;     // allocated when the scene is large enough for the wide traversal to pay (tpt_scene_create)
