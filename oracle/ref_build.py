@@ -18,6 +18,7 @@ Edits, all in GENERATED copies under oracle/_ref/patched/ (recorded in BUILD.jso
 from __future__ import annotations
 
 import json
+import os
 import re
 import shutil
 import subprocess
@@ -85,16 +86,34 @@ def copy_inputs():
     Image.fromarray(np.zeros((32, 64, 3), np.uint8)).save(OUT / "black.png")
 
 
+def compile_units(jobs):
+    """The translation units of one target, compiled side by side (each nvcc is single-threaded; a target has five)."""
+    from concurrent.futures import ThreadPoolExecutor
+    with ThreadPoolExecutor(max_workers=min(len(jobs), max(1, (os.cpu_count() or 2)))) as pool:
+        list(pool.map(run, jobs))   # re-raises the first failure
+
+
+def up_to_date(target: Path) -> bool:
+    """The target exists and is newer than everything it is made from: the reference's sources, the generated copy's inputs here, this script."""
+    if not target.exists():
+        return False
+    t = target.stat().st_mtime
+    deps = list(HERE.glob("ref_*")) + list((REF / "src").glob("*")) + list((REF / "include").rglob("*"))
+    return all(d.stat().st_mtime <= t for d in deps if d.is_file())
+
+
 def build_exe(name: str, opt: list, depth: int, tag: str):
     objs = []
     work = OUT / f"obj_{name}"
     work.mkdir(exist_ok=True)
     units = [(HERE / "ref_headless.cu", "headless"), (HERE / "ref_hooks_bvh.cu", "bvh"), (REF / "src" / "mesh.cu", "mesh"),
              (REF / "src" / "env_light.cu", "env_light"), (REF / "src" / "texture.cu", "texture")]
+    jobs = []
     for src, stem in units:
         o = work / f"{stem}.o"
-        run([NVCC, *COMMON, *opt, f"-DTPT_REF_DEPTH={depth}", f'-DTPT_REF_BUILD="{tag}"', "-c", str(src), "-o", str(o)])
+        jobs.append([NVCC, *COMMON, *opt, f"-DTPT_REF_DEPTH={depth}", f'-DTPT_REF_BUILD="{tag}"', "-c", str(src), "-o", str(o)])
         objs.append(str(o))
+    compile_units(jobs)
     fo = work / "freeimage_shim.o"
     run(["/usr/bin/g++", "-O2", "-c", f"-I{REF / 'include'}", str(HERE / "ref_freeimage_shim.cpp"), "-o", str(fo)])
     run([NVCC, *opt, "-rdc=true", "-ccbin", "/usr/bin/g++", *objs, str(fo), "-o", str(OUT / name)])
@@ -104,12 +123,13 @@ def build_host_lib():
     work = OUT / "obj_host"
     work.mkdir(exist_ok=True)
     opt = ["-O2", "-arch=sm_100", "-Xcompiler", "-fPIC", "-DTPT_REF_NO_MAIN", '-DTPT_REF_BUILD="host"']
-    objs = []
+    objs, jobs = [], []
     for src, stem in [(HERE / "ref_headless.cu", "headless"), (HERE / "ref_hooks_bvh.cu", "bvh"), (HERE / "ref_hooks_mesh.cu", "mesh"),
                       (REF / "src" / "env_light.cu", "env_light"), (REF / "src" / "texture.cu", "texture")]:
         o = work / f"{stem}.o"
-        run([NVCC, *COMMON, *opt, "-c", str(src), "-o", str(o)])
+        jobs.append([NVCC, *COMMON, *opt, "-c", str(src), "-o", str(o)])
         objs.append(str(o))
+    compile_units(jobs)
     fo = work / "freeimage_shim.o"
     run(["/usr/bin/g++", "-O2", "-fPIC", "-c", f"-I{REF / 'include'}", str(HERE / "ref_freeimage_shim.cpp"), "-o", str(fo)])
     run([NVCC, "-arch=sm_100", "-rdc=true", "-shared", "-Xcompiler", "-fPIC", "-ccbin", "/usr/bin/g++", *objs, str(fo), "-o",
@@ -128,7 +148,7 @@ def main():
         built = json.loads((OUT / "BUILD.json").read_text()).get("built", {})
     except Exception:
         pass
-    only = set(sys.argv[1:])
+    only = {a for a in sys.argv[1:] if not a.startswith("--")}
     targets = [("libref_host.so", None), ("tpt_ref_headless", (["-O3", "-arch=sm_100"], 8, "-O3 -arch=sm_100")),
                ("tpt_ref_headless_d32", (["-O3", "-arch=sm_100"], 32, "-O3 -arch=sm_100 DEPTH_TRACE=32")),
                ("tpt_ref_headless_G", (["-G", "-arch=sm_100"], 8, "-G -arch=sm_100 (as shipped, CMakeLists.txt:59)")),
@@ -138,6 +158,9 @@ def main():
         if only and name not in only:
             continue
         try:
+            if "--force" not in sys.argv and built.get(name) == "ok" and up_to_date(OUT / name):
+                print(name, "up to date")
+                continue
             if spec is None:
                 build_host_lib()
             else:
