@@ -20,6 +20,6 @@ python scripts/sass_lines.py /tmp/r02_k_wave_ball.ncu-rep k_wave tinypathtracer_
 # 3. the 10 M-triangle soup: the trace launches after the warm-up (primary, secondary) and one whole build
 ncu --set full --clock-control none -k regex:k_trace_rays_persistent --launch-skip 2 -c 2 -f -o /tmp/r02_k_trace_rays_soup python bench.py --workload soup --steps 1 --warmup 1 > /dev/null 2>&1
 python scripts/ncu_summary.py /tmp/r02_k_trace_rays_soup.ncu-rep $O/r02_ncu_full_k_trace_rays_soup.csv
-ncu --set full --clock-control none -k 'regex:k_transform|k_morton_hist|k_onesweep|k_hierarchy|k_leaves_refit|k_refit_upper' --launch-skip 10 -c 10 -f -o /tmp/r02_bvh_build_soup python bench.py --workload soup --steps 1 --warmup 1 > /dev/null 2>&1
+ncu --set full --clock-control none -k 'regex:k_transform|k_morton_hist|k_onesweep|k_leaves_build|k_build_upper' --launch-skip 8 -c 8 -f -o /tmp/r02_bvh_build_soup python bench.py --workload soup --steps 1 --warmup 1 > /dev/null 2>&1
 python scripts/ncu_summary.py /tmp/r02_bvh_build_soup.ncu-rep $O/r02_ncu_full_bvh_build_soup.csv
 ls -la $O/r02_*
