@@ -47,6 +47,9 @@ __global__ void k_face_tables(const uint32_t* __restrict__ indices, const tpt_mt
     vertObj[indices[3 * f + 2]] = (uint32_t)lo;
 }
 
+// NORMALS = false (scenes whose normal records are made on first render, tpt_scene_ensure_normals): positions and bounds only —
+// a build that is only traced never reads a normal; k_transform_normals catches up when a render needs them.
+template <bool NORMALS>
 __global__ void __launch_bounds__(256) k_transform(const float* __restrict__ objVerts, const float* __restrict__ objNorms,
                                                    const uint32_t* __restrict__ vertObj, const float* __restrict__ vertTrans,
                                                    const float* __restrict__ normalTrans, uint32_t nVerts,
@@ -57,11 +60,13 @@ __global__ void __launch_bounds__(256) k_transform(const float* __restrict__ obj
         const uint32_t o = vertObj[v];
         if (o == 0xffffffffu) continue;   // not referenced by any face: the reference never writes it either
         const float3 p = f3(objVerts[3 * v], objVerts[3 * v + 1], objVerts[3 * v + 2]);
-        const float3 n = f3(objNorms[3 * v], objNorms[3 * v + 1], objNorms[3 * v + 2]);
         const float3 wp = xmat4_point(vertTrans + 16 * (size_t)o, p);
-        const float3 wn = xnormalize(xmat4_dir(normalTrans + 16 * (size_t)o, n));
         worldVerts[3 * v] = wp.x; worldVerts[3 * v + 1] = wp.y; worldVerts[3 * v + 2] = wp.z;
-        worldNorms[3 * v] = wn.x; worldNorms[3 * v + 1] = wn.y; worldNorms[3 * v + 2] = wn.z;
+        if (NORMALS) {
+            const float3 n = f3(objNorms[3 * v], objNorms[3 * v + 1], objNorms[3 * v + 2]);
+            const float3 wn = xnormalize(xmat4_dir(normalTrans + 16 * (size_t)o, n));
+            worldNorms[3 * v] = wn.x; worldNorms[3 * v + 1] = wn.y; worldNorms[3 * v + 2] = wn.z;
+        }
         mn = fmin3(mn, wp);
         mx = fmax3(mx, wp);
     }
@@ -77,6 +82,17 @@ __global__ void __launch_bounds__(256) k_transform(const float* __restrict__ obj
     if ((threadIdx.x & 31) == 0 && mn.x <= mx.x) {
         atomicMin(bounds + 0, f2ord(mn.x)); atomicMin(bounds + 1, f2ord(mn.y)); atomicMin(bounds + 2, f2ord(mn.z));
         atomicMax(bounds + 3, f2ord(mx.x)); atomicMax(bounds + 4, f2ord(mx.y)); atomicMax(bounds + 5, f2ord(mx.z));
+    }
+}
+
+__global__ void __launch_bounds__(256) k_transform_normals(const float* __restrict__ objNorms, const uint32_t* __restrict__ vertObj,
+                                                           const float* __restrict__ normalTrans, uint32_t nVerts, float* __restrict__ worldNorms) {
+    for (uint32_t v = blockIdx.x * blockDim.x + threadIdx.x; v < nVerts; v += gridDim.x * blockDim.x) {
+        const uint32_t o = vertObj[v];
+        if (o == 0xffffffffu) continue;
+        const float3 n = f3(objNorms[3 * v], objNorms[3 * v + 1], objNorms[3 * v + 2]);
+        const float3 wn = xnormalize(xmat4_dir(normalTrans + 16 * (size_t)o, n));   // the same arithmetic as k_transform<true>
+        worldNorms[3 * v] = wn.x; worldNorms[3 * v + 1] = wn.y; worldNorms[3 * v + 2] = wn.z;
     }
 }
 
@@ -259,7 +275,7 @@ __global__ void __launch_bounds__(kRefitBlock) k_leaves_build(const unsigned lon
                                                       float4* __restrict__ triGeom, float4* __restrict__ triNorm, int* __restrict__ frontier,
                                                       uint32_t* __restrict__ frontierCount) {
     __shared__ unsigned sFlag[kRefitBlock];
-    __shared__ MergeHalf sHalf[kRefitBlock][2];
+    __shared__ float4 sHalf[kRefitBlock][2][2];   // [split - b0][side]: a MergeHalf as two 128-bit words
     __shared__ int sAdj[kRefitBlock + 1];    // sAdj[i] = delta(w0 + i, w0 + i + 1), w0 = b0 - 1: the pairs (b0-1, b0) ... (bEnd, bEnd+1); -1 beyond the array
     __shared__ int sPre[kRefitBlock + 1];    // sPre[i + 1] = min(sAdj[0 .. i]) = delta(b0 - 1, w0 + i + 1); sPre[0] = inf (empty)
     __shared__ int sSuf[kRefitBlock + 2];    // sSuf[i] = min(sAdj[i .. 256]) = delta(w0 + i, bEnd + 1), i >= 1; sSuf[257] = inf (empty)
@@ -315,53 +331,69 @@ __global__ void __launch_bounds__(kRefitBlock) k_leaves_build(const unsigned lon
     }
     if (nFaces == 1) return;
 
-    const float3 mn = fmin3(fmin3(a, b), c), mx = fmax3(fmax3(a, b), c);
-    MergeHalf me{mn.x, mn.y, mn.z, mx.x, mx.y, mx.z, ~leaf, leaf};
-    int l = leaf, r = leaf;
+    float3 mn = fmin3(fmin3(a, b), c), mx = fmax3(fmax3(a, b), c);
+    int id = ~leaf, l = leaf, r = leaf;
     // which way the current node goes: the LEFT child of the node split at r (delta(r, r+1) is the longer prefix), or the RIGHT
     // child of the node split at l - 1.  adj(j) = sAdj[j - w0]; the ends of the array have adj = -1, so they decide themselves.
     bool goRight = sAdj[r - w0] > sAdj[l - 1 - w0];
     while (true) {
         const int split = goRight ? r : l - 1, side = goRight ? 0 : 1;
-        me.end = goRight ? l : r;
+        const int end = goRight ? l : r;   // the far end of this node's range
         const int q = sAdj[split - w0];
         // does the parent's whole range lie in this block?  left child: iff delta(split + 1, bEnd + 1) < q; right child: iff
         // delta(b0 - 1, split) < q (empty ranges — the sibling starts outside the block — are inf: no)
         const bool inBlock = goRight ? sSuf[split + 1 - w0] < q : sPre[split - w0] < q;
-        MergeHalf sib;
-        if (inBlock) {
-            const int k = split - b0;
-            sHalf[k][side] = me;
-            __threadfence_block();
-            if (atomicAdd(&sFlag[k], 1u) == 0u) return;   // first arrival: the sibling will finish this node
-            __threadfence_block();
-            const volatile float* sf = reinterpret_cast<const volatile float*>(&sHalf[k][side ^ 1]);
-            const volatile int* si = reinterpret_cast<const volatile int*>(&sHalf[k][side ^ 1]);
-            sib = MergeHalf{sf[0], sf[1], sf[2], sf[3], sf[4], sf[5], si[6], si[7]};
-        } else {
-            merge_store_global(slots + 4 * (size_t)split + 2 * side, me);
+        const float4 h0 = make_float4(mn.x, mn.y, mn.z, mx.x), h1 = make_float4(mx.y, mx.z, __int_as_float(id), __int_as_float(end));
+        if (!inBlock) {
+            float4* slot = slots + 4 * (size_t)split + 2 * side;
+            __stcg(slot, h0);
+            __stcg(slot + 1, h1);
             __threadfence();
             if (atomicAdd(flags + split, 1u) == 1u) frontier[atomicAdd(frontierCount, 1u)] = split;   // complete: k_build_upper goes on
             return;
         }
-        const MergeHalf& L = side == 0 ? me : sib;
-        const MergeHalf& R = side == 0 ? sib : me;
-        l = L.end;
-        r = R.end;
+        const int ks = split - b0;
+        sHalf[ks][side][0] = h0;
+        sHalf[ks][side][1] = h1;
+        __threadfence_block();
+        if (atomicAdd(&sFlag[ks], 1u) == 0u) return;   // first arrival: the sibling will finish this node
+        __threadfence_block();
+        float4 s0, s1;
+        {   // the sibling's half, written by another thread of the block: volatile 128-bit shared loads
+            const unsigned addr = (unsigned)__cvta_generic_to_shared(&sHalf[ks][side ^ 1][0]);
+            asm volatile("ld.volatile.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(s0.x), "=f"(s0.y), "=f"(s0.z), "=f"(s0.w) : "r"(addr));
+            asm volatile("ld.volatile.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(s1.x), "=f"(s1.y), "=f"(s1.z), "=f"(s1.w) : "r"(addr + 16u));
+        }
+        const float3 smn = f3(s0.x, s0.y, s0.z), smx = f3(s0.w, s1.x, s1.y);
+        const int sid = __float_as_int(s1.z), send = __float_as_int(s1.w);
+        l = goRight ? end : send;   // parent's range: the left child's first leaf ... the right child's last
+        r = goRight ? send : end;
         int k = 0;
         const bool root = l == 0 && r == nFaces - 1;
+        bool up = false;
         if (!root) {
-            goRight = sAdj[r - w0] > sAdj[l - 1 - w0];
-            k = goRight ? r : l;
+            up = sAdj[r - w0] > sAdj[l - 1 - w0];
+            k = up ? r : l;
         }
-        write_node(nodes, parentInt, parentLeaf, rangeOther, k, L, R);
+        // the finished node k: each child's box and id go to its side of the record (layout: scene.cuh), no data is selected
+        float4* node = nodes + 4 * (size_t)k;
+        store_child_box(node, side == 0, mn, mx);
+        store_child_box(node, side != 0, smn, smx);
+        int* ids = reinterpret_cast<int*>(node + 3);
+        __stcg(ids + side, id);
+        __stcg(ids + (side ^ 1), sid);
+        __stcg(reinterpret_cast<int2*>(ids + 2), make_int2(0, 0));
+        if (id < 0) parentLeaf[~id] = k; else parentInt[id] = k;
+        if (sid < 0) parentLeaf[~sid] = k; else parentInt[sid] = k;
+        rangeOther[k] = (k == r) ? l : r;   // node k is one end of its range; the root (k = 0 = l) gets r
         if (root) {
             parentInt[0] = -1;
             return;
         }
-        const MergeHalf u = merge_union(L, R);
-        me = u;
-        me.id = k;
+        mn = fmin3(mn, smn);
+        mx = fmax3(mx, smx);
+        id = k;
+        goRight = up;
     }
 }
 
@@ -669,8 +701,8 @@ int tpt_bvh_build_impl(tpt_scene* s) {
     const bool lazyNormals = s->n_faces >= kLazyNormalFaces;   // large scenes: normal records on first render (tpt_scene_ensure_normals)
 
     k_init_bounds<<<1, 32, 0, st>>>(s->bounds);
-    k_transform<<<min(persistent, (int)grid_for(V, 256)), 256, 0, st>>>(s->obj_verts, s->obj_norms, s->vert_obj, s->vert_trans,
-                                                                         s->normal_trans, V, s->world_verts, s->world_norms, s->bounds);
+    (lazyNormals ? k_transform<false> : k_transform<true>)<<<min(persistent, (int)grid_for(V, 256)), 256, 0, st>>>(
+        s->obj_verts, s->obj_norms, s->vert_obj, s->vert_trans, s->normal_trans, V, s->world_verts, s->world_norms, s->bounds);
     // 63-bit keys like the reference (21 bits per axis) below 2^20 triangles.  From there on the radix passes are what the keys cost, and the
     // tree does not need the resolution: 11 bits per axis, the 33-bit interleaved key cut to 32 bits (x keeps 10) = 4 passes instead of 8;
     // 2^32 cells are >= 256 per triangle up to 2^24 triangles, equal keys are ordered by index.  Measured on the 10 M-triangle soup
@@ -754,8 +786,8 @@ int tpt_bvh_refit_impl(tpt_scene* s) {
     const int persistent = kNumSMs * 8;
     const bool lazyNormals = s->n_faces >= kLazyNormalFaces;   // large scenes: normal records on first render (tpt_scene_ensure_normals)
     k_init_bounds<<<1, 32, 0, st>>>(s->bounds);
-    k_transform<<<min(persistent, (int)grid_for(V, 256)), 256, 0, st>>>(s->obj_verts, s->obj_norms, s->vert_obj, s->vert_trans,
-                                                                         s->normal_trans, V, s->world_verts, s->world_norms, s->bounds);
+    (lazyNormals ? k_transform<false> : k_transform<true>)<<<min(persistent, (int)grid_for(V, 256)), 256, 0, st>>>(
+        s->obj_verts, s->obj_norms, s->vert_obj, s->vert_trans, s->normal_trans, V, s->world_verts, s->world_norms, s->bounds);
     if (F > 1) TPT_CUDA(cudaMemsetAsync(s->flags, 0, (size_t)(F - 1) * sizeof(uint32_t), st));
     int* frontier = reinterpret_cast<int*>(s->keys[0]);
     k_leaves_refit<<<grid_for(F, kRefitBlock), kRefitBlock, 0, st>>>(s->vals[1], s->indices, s->world_verts, s->world_norms, s->face_mtl, F,
@@ -777,9 +809,11 @@ int tpt_bvh_refit_impl(tpt_scene* s) {
 int tpt_scene_ensure_normals(tpt_scene* s) {
     if (s->norm_epoch == s->geom_epoch) return TPT_OK;
     const int F = (int)s->n_faces;
+    const uint32_t V = (uint32_t)s->n_vertices;
+    k_transform_normals<<<min(kNumSMs * 8, (int)grid_for(V, 256)), 256, 0, s->ctx->stream>>>(s->obj_norms, s->vert_obj, s->normal_trans, V, s->world_norms);
     k_leaf_normals<<<grid_for(F, 256), 256, 0, s->ctx->stream>>>(s->vals[1], s->indices, s->world_norms, F, s->tri_norm);
     TPT_CUDA(cudaGetLastError());
-    s->ctx->kernel_launches += 1;
+    s->ctx->kernel_launches += 2;
     s->norm_epoch = s->geom_epoch;
     return TPT_OK;
 }

@@ -32,6 +32,7 @@ int tpt_scene_build_tables(tpt_scene* s);
 int tpt_bvh_build_impl(tpt_scene* s);
 int tpt_bvh_refit_impl(tpt_scene* s);
 int tpt_bvh_stats_impl(tpt_scene* s, tpt_bvh_stats* stats);
+int tpt_scene_ensure_normals(tpt_scene* s);   // bvh.cu
 int tpt_bvh_export_reference_impl(tpt_scene* s, void* out, size_t nNodes);
 int tpt_primary_rays_impl(tpt_context* ctx, const tpt_camera* cam, int W, int H, int jitter, uint64_t seed, tpt_ray* d_rays);
 int tpt_trace_rays_impl(tpt_scene* s, const tpt_ray* d_rays, size_t n, tpt_hit* d_hits, int anyHit, int counted);
@@ -445,6 +446,7 @@ int tpt_scene_export_world(tpt_scene* s, float* wv, float* wn) {
         return TPT_ERR_STATE;
     }
     TPT_CHECK(bind(s->ctx));
+    if (wn) TPT_CHECK(tpt_scene_ensure_normals(s));   // large scenes transform their normals on first use
     if (wv) TPT_CUDA(cudaMemcpyAsync(wv, s->world_verts, 3 * s->n_vertices * sizeof(float), cudaMemcpyDeviceToHost, s->ctx->stream));
     if (wn) TPT_CUDA(cudaMemcpyAsync(wn, s->world_norms, 3 * s->n_vertices * sizeof(float), cudaMemcpyDeviceToHost, s->ctx->stream));
     TPT_CUDA(cudaStreamSynchronize(s->ctx->stream));
