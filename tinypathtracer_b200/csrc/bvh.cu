@@ -401,8 +401,10 @@ __global__ void __launch_bounds__(256) k_build_upper(const unsigned long long* _
                                                      const uint32_t* __restrict__ frontierCount, int* __restrict__ parentInt,
                                                      int* __restrict__ parentLeaf, int* __restrict__ rangeOther, uint32_t* __restrict__ flags,
                                                      float4* __restrict__ slots, float4* __restrict__ nodes) {
-    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= *frontierCount) return;
+    // grid-stride over the queued splits: there are ~F/100 of them (F/2 only for a degenerate chain of a tree), so the launch is
+    // sized for the usual case and loops in the other
+    const uint32_t count = *frontierCount;
+    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < count; t += gridDim.x * blockDim.x) {
     int split = frontier[t];
     MergeHalf L = merge_load_global(slots + 4 * (size_t)split), R = merge_load_global(slots + 4 * (size_t)split + 2);
     while (true) {
@@ -417,7 +419,7 @@ __global__ void __launch_bounds__(256) k_build_upper(const unsigned long long* _
         write_node(nodes, parentInt, parentLeaf, rangeOther, k, L, R);
         if (root) {
             parentInt[0] = -1;
-            return;
+            break;
         }
         MergeHalf me = merge_union(L, R);
         me.id = k;
@@ -427,7 +429,7 @@ __global__ void __launch_bounds__(256) k_build_upper(const unsigned long long* _
         float4* slot = slots + 4 * (size_t)split;
         merge_store_global(slot + 2 * side, me);
         __threadfence();
-        if (atomicAdd(flags + split, 1u) == 0u) return;   // first arrival: the sibling will finish this node
+        if (atomicAdd(flags + split, 1u) == 0u) break;   // first arrival: the sibling will finish this node
         __threadfence();
         const MergeHalf sib = merge_load_global(slot + 2 * (side ^ 1));   // written by another SM: L2 loads
         if (side == 0) {
@@ -437,6 +439,7 @@ __global__ void __launch_bounds__(256) k_build_upper(const unsigned long long* _
             L = sib;
             R = me;
         }
+    }
     }
 }
 
@@ -704,12 +707,13 @@ int tpt_bvh_build_impl(tpt_scene* s) {
     (lazyNormals ? k_transform<false> : k_transform<true>)<<<min(persistent, (int)grid_for(V, 256)), 256, 0, st>>>(
         s->obj_verts, s->obj_norms, s->vert_obj, s->vert_trans, s->normal_trans, V, s->world_verts, s->world_norms, s->bounds);
     // 63-bit keys like the reference (21 bits per axis) below 2^20 triangles.  From there on the radix passes are what the keys cost, and the
-    // tree does not need the resolution: 11 bits per axis, the 33-bit interleaved key cut to 32 bits (x keeps 10) = 4 passes instead of 8;
-    // 2^32 cells are >= 256 per triangle up to 2^24 triangles, equal keys are ordered by index.  Measured on the 10 M-triangle soup
-    // (bits per axis: build ms | primary, secondary Mrays/s | SAH cost): 13: 1.905 | 2 269, 1 275 | 149.1; 11: 1.725 | 2 257, 1 277 | 149.2;
-    // 10: 1.697 | 2 258, 1 280 | 149.4; 9: 1.650 | 2 226, 1 238 | 152.5; 8 (3 passes): 1.477 | 2 162, 1 204 | 159.9.  Above 2^24 triangles: 13 bits, 5 passes.
+    // tree does not need the resolution: 10 bits per axis = 30-bit keys = 4 passes instead of 8; 2^30 cells are >= 64 per triangle up to
+    // 2^24 triangles, equal keys are ordered by index.  Measured on the 10 M-triangle soup with the search-based hierarchy (bits per axis:
+    // build ms | primary, secondary Mrays/s | SAH cost): 13: 1.905 | 2 269, 1 275 | 149.1; 11 (33 bits cut to 32): 1.725 | 2 257, 1 277 | 149.2;
+    // 10: 1.697 | 2 258, 1 280 | 149.4; 9: 1.650 | 2 226, 1 238 | 152.5; 8 (3 passes): 1.477 | 2 162, 1 204 | 159.9 — 10 is the narrowest key
+    // that costs the rays nothing.  Above 2^24 triangles: 13 bits, 5 passes.
     static const int bitsEnv = getenv("TPT_MORTON_BITS_LARGE") ? atoi(getenv("TPT_MORTON_BITS_LARGE")) : 0;   // tuning switch (8..21)
-    const int bitsPerAxis = F < (1 << 20) ? 21 : bitsEnv > 0 ? bitsEnv : F <= (1 << 24) ? 11 : 13;
+    const int bitsPerAxis = F < (1 << 20) ? 21 : bitsEnv > 0 ? bitsEnv : F <= (1 << 24) ? 10 : 13;
     const int keyBits = 3 * bitsPerAxis - morton_key_shift(bitsPerAxis);
     // Sorted (key, face) pairs must end in keys[1] / vals[1]; keys[0] / vals[0] are scratch afterwards.
     const int nPasses = (keyBits + 7) / 8;   // 4, 5 or 8
@@ -757,7 +761,7 @@ int tpt_bvh_build_impl(tpt_scene* s) {
         k_leaves_build<<<grid_for(F, kRefitBlock), kRefitBlock, 0, st>>>(s->keys[1], s->vals[1], s->indices, s->world_verts, s->world_norms, s->face_mtl, F,
                                                                          s->parent_int, s->parent_leaf, rangeOther, s->flags, s->merge_slots, s->nodes,
                                                                          s->tri_geom, lazyNormals ? nullptr : s->tri_norm, frontier, s->bounds + 6);
-        if (F > 1) k_build_upper<<<grid_for((size_t)F / 2 + 1, 256), 256, 0, st>>>(s->keys[1], F, frontier, s->bounds + 6, s->parent_int, s->parent_leaf,
+        if (F > 1) k_build_upper<<<(unsigned)std::min<size_t>(grid_for((size_t)F / 16 + 1, 256), (size_t)kNumSMs * 8), 256, 0, st>>>(s->keys[1], F, frontier, s->bounds + 6, s->parent_int, s->parent_leaf,
                                                                                   rangeOther, s->flags, s->merge_slots, s->nodes);
     }
     if (F > 1 && s->nodes4) {
