@@ -1,7 +1,7 @@
 """The rule behind k_leaves_build / k_build_upper (csrc/bvh.cu), as an executable statement on the CPU: emitting the LBVH bottom-up
 — a finished node [l, r] joins the neighbour it shares the longer (key, index) prefix with, and is numbered by its range's right end
 if it is a left child, by the left end if it is a right child, 0 if it is the root — produces exactly the arrays of the search-based
-construction the reference uses (Karras 2012; `src/bvh.cu:150-218`): children, parents, range ends.  Also the test the kernel uses to
+construction the reference uses (Karras 2012; `getTheOtherEnd` / `findSplitPosition` / `computeNodeRange`, `src/bvh.cu:64-126,150-218`): children, parents, range ends.  Also the test the kernel uses to
 decide whether a parent lies inside a block of 256 leaves: one comparison of prefix lengths.  The GPU counterpart is
 tests/test_gpu_round2.py::test_bottom_up_hierarchy_is_the_search_based_tree."""
 import random
